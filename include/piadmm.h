@@ -1,0 +1,165 @@
+/* piadmm.h -- C ABI of the B200-native PI-ADMM consensus solver (libpiadmm.so).
+ *
+ * Drop-in boundary for the hot path of KaigeTan/Distributed-Local-Planner-PI-ADMM.
+ * The reference has no FFI of its own (pure Python -> CasADi -> OSQP); every entry
+ * point below cites the reference statement block it replaces (paths relative to the
+ * reference repository root):
+ *
+ *   piadmm_x_update      casadi/main.py:81-106   (vehicle QPs: cost_function_primal +
+ *                        nonlcon_function -> ca.qpsol("osqp") -> np.around -> dynamic_update_local)
+ *   piadmm_detect_edges  casadi/main.py:110-118  (edge_mat, flag / early exit)
+ *   piadmm_z_update      casadi/main.py:121-162  (edge problem, non-linear roll-out of z-hat,
+ *                        dual update; PI forms: casadi_old_PI_ADMM/main.py:127-151 and
+ *                        matlab_old_files/ADMM_CVX_two_veh_intesection_PI_antiwindup.m:152-188)
+ *   piadmm_residuals     casadi/main.py:165-180  (error_rk / error_sk, stop test, alias quirk)
+ *   piadmm_step          casadi/main.py:78-181   (the whole outer loop, one persistent kernel)
+ *   piadmm_plant_step    casadi/main.py:185-192  (dynamic_update_edge numeric, xt <- column 1)
+ *
+ * Conventions
+ *   - plain C, no torch types; all array arguments are raw pointers; fp64 = double, i32 = int32_t.
+ *   - return value: 0 = ok, negative = error (PIADMM_E_*); nothing throws across the boundary.
+ *   - device entry points are asynchronous on `stream` (a cudaStream_t passed as void*, NULL =
+ *     legacy default stream).  The library BORROWS the device buffers bound with piadmm_bind();
+ *     the caller (PyTorch on the Python side) owns and frees them.
+ *   - a handle is not thread-safe; one handle per (process, device).
+ *   - there is NO CPU fallback: every compute entry point fails with PIADMM_E_CUDA when no
+ *     CUDA device is usable.
+ *
+ * Array layouts (row-major, contiguous).  S scenarios, V vehicles per scenario, N = num_ho,
+ * D = neighbour slots per vehicle, I = iter_num, E = max edges per scenario = V*D/2 (>=1).
+ */
+#ifndef PIADMM_H
+#define PIADMM_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PIADMM_ABI_VERSION 1
+
+enum {
+  PIADMM_OK = 0,
+  PIADMM_E_ARG = -1,      /* bad argument / shape */
+  PIADMM_E_CUDA = -2,     /* CUDA runtime error (see piadmm_last_error) */
+  PIADMM_E_UNBOUND = -3,  /* piadmm_bind() not called / NULL buffer */
+  PIADMM_E_UNSUPPORTED = -4
+};
+
+/* dual_mode */
+enum { PIADMM_DUAL_PLAIN = 0, PIADMM_DUAL_PI = 1, PIADMM_DUAL_PI_OLD = 2 };
+
+/* bits of status[s] */
+enum {
+  PIADMM_ST_VEH_MAXITER = 1,   /* a vehicle QP hit in_max_iter (reference: CasADi raises) */
+  PIADMM_ST_EDGE_MAXITER = 2,  /* an edge problem hit in_max_iter (reference: error_on_fail=False) */
+  PIADMM_ST_SLOT_OVERFLOW = 4  /* a vehicle needed more than D neighbour slots */
+};
+
+typedef struct piadmm_params {
+  /* --- problem constants: casadi/PI_ADMM_class.py:15-28 --- */
+  double dt, L, dis_thres, beta, Pnorm, Pcost, rho, eps_pri, eps_dual;
+  /* --- PI law --- */
+  double theta1, theta2;   /* MATLAB :22-23 sigmoid gain kP = theta1 - theta2/(1+exp(-min d)) */
+  double kI;               /* MATLAB :21 ; < 0 means "use rho" */
+  double windup_sat;       /* MATLAB :43 (30) ; old main.py:24 (20) */
+  double backcalc;         /* weight of the back-calculation term: 1 (MATLAB :163) or 2 (old main.py:142) */
+  double K_I, KP_num, KP_max, rho_num, rho_min, rho_max; /* old main.py:135-137 */
+  /* --- inner OSQP-style ADMM (OSQP defaults: 0.1, 1e-6, 1.6, 1e-3, 1e-3, 5) --- */
+  double in_rho0, in_sigma, in_alpha, in_eps_abs, in_eps_rel, in_adapt_tol;
+  int32_t num_ho;          /* horizon N (2..32) */
+  int32_t iter_num;        /* outer iteration cap */
+  int32_t dual_mode;       /* PIADMM_DUAL_* */
+  int32_t thr_squared;     /* 0: d^2 < dis_thres (casadi/main.py:113) ; 1: d^2 < dis_thres^2 (MATLAB :109) */
+  int32_t dual_res_alias;  /* casadi/main.py:180 aliasing: dual residual == 0 from outer iteration 2 */
+  int32_t stop_dist_test;  /* MATLAB :202 extra stop condition dis_vec(2) > dis_thres */
+  int32_t pos_nonlinear;   /* MATLAB :312-330: numeric pos_old roll-out is the non-linear one */
+  int32_t curr_iter_latest;/* MATLAB :209 */
+  int32_t round_u;         /* decimals for np.around of the vehicle solution (casadi/main.py:103); <0 = none */
+  int32_t round_edge;      /* decimals for the edge solution (casadi/main.py:153); <0 = none */
+  int32_t al_all;          /* 1: AL term over every j != i (PI_ADMM_class.py:126-129; needs D >= V-1) */
+  int32_t always_edge;     /* old main.py: edge step every iteration, no collision test */
+  int32_t residual_global; /* old main.py:154-155 */
+  int32_t PI, windup, trad;/* MATLAB :24-25 ; old main.py:18 */
+  int32_t in_max_iter, in_check, in_adaptive;
+} piadmm_params;
+
+/* Device buffers owned by the caller.  Shapes in comments. */
+typedef struct piadmm_buffers {
+  /* inputs of one MPC step */
+  const double* xt;      /* [S,V,3]  (x, y, theta) */
+  const double* spd;     /* [S,V] */
+  const double* refwin;  /* [S,V,2,N+1] reference window ref_traj[2i:2i+2, step:step+N+1] */
+  /* primal state */
+  double* u;             /* [S,V,N]     primal_u */
+  double* pos;           /* [S,V,2,N+1] pos_old */
+  /* per directed neighbour slot */
+  int32_t* nbr;          /* [S,V,D] neighbour vehicle id, -1 = empty */
+  double* hat;           /* [S,V,D,2,N+1] hat_pos_old[i,j] */
+  double* dual;          /* [S,V,D,2,N+1] dual_var_old[i,j] */
+  double* integ;         /* [S,V,D,2,N+1] PI integrator (sum_err) */
+  double* diff;          /* [S,V,D,2,N+1] back-calculation term (diff_val) */
+  double* last_hat;      /* [S,V,D,2,N+1] last_iter_hat_pos */
+  /* per scenario */
+  double* rho_s;         /* [S] current penalty (mutated only by dual_mode PI_OLD) */
+  int32_t* flag;         /* [S] "a collision was seen" latch (casadi/main.py:71,115-118) */
+  int32_t* done;         /* [S] 1 once the scenario left the outer loop */
+  int32_t* aliased;      /* [S] alias latch of casadi/main.py:180 */
+  int32_t* curr_iter;    /* [S] iter_his entry */
+  int32_t* n_outer;      /* [S] outer iterations executed */
+  int32_t* status;       /* [S] PIADMM_ST_* bits */
+  double* err_rk;        /* [S,I] primal residual history */
+  double* err_sk;        /* [S,I] dual residual history */
+  int64_t* veh_inner;    /* [S] inner ADMM iterations summed over vehicle QPs */
+  int64_t* edge_inner;   /* [S] inner ADMM iterations summed over edge problems */
+  int32_t* n_veh_solves; /* [S] */
+  int32_t* n_edge_solves;/* [S] */
+  /* edge list of the current outer iteration */
+  int32_t* edge_n;       /* [S] */
+  int32_t* edge_ij;      /* [S,E,2] (veh1 < veh2), sorted */
+  int32_t* edge_slot;    /* [S,E,2] slot of veh2 in veh1's table, slot of veh1 in veh2's table */
+  /* plant */
+  double* xt_next;       /* [S,V,3] */
+} piadmm_buffers;
+
+typedef struct piadmm_handle piadmm_handle;
+
+/* version / introspection (no GPU needed) */
+int piadmm_abi_version(void);
+void piadmm_default_params(piadmm_params* p);          /* casadi/PI_ADMM_class.py:15-28 + casadi/main.py semantics */
+int piadmm_max_edges(int V, int D);
+
+/* lifecycle */
+int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadmm_handle** out);
+int piadmm_set_params(piadmm_handle* h, const piadmm_params* p);   /* num_ho / iter_num must not change */
+int piadmm_bind(piadmm_handle* h, const piadmm_buffers* b);
+void piadmm_destroy(piadmm_handle* h);
+const char* piadmm_last_error(const piadmm_handle* h);             /* h may be NULL: last create error */
+
+/* one MPC step */
+int piadmm_begin_step(piadmm_handle* h, void* stream);   /* casadi/main.py:52-72 re-initialisation */
+int piadmm_x_update(piadmm_handle* h, void* stream);
+int piadmm_detect_edges(piadmm_handle* h, void* stream);
+int piadmm_z_update(piadmm_handle* h, void* stream);     /* edge problems + dual / PI update */
+int piadmm_residuals(piadmm_handle* h, void* stream);    /* histories, stop flags, alias latch */
+int piadmm_num_active(piadmm_handle* h, void* stream, int32_t* host_out); /* scenarios with done==0 (syncs) */
+int piadmm_step(piadmm_handle* h, void* stream);         /* begin_step + all outer iterations, persistent kernel */
+int piadmm_plant_step(piadmm_handle* h, void* stream);
+
+/* host-buffer convenience path (what a ctypes caller without torch uses; copies inside):
+ * runs begin_step + the whole outer loop + plant step for host inputs and returns host outputs. */
+int piadmm_step_host(piadmm_handle* h, const double* xt, const double* spd, const double* refwin,
+                     double* u_out, double* pos_out, double* xt_next_out, int32_t* curr_iter_out,
+                     int32_t* n_outer_out, void* stream);
+
+/* statistics for the roofline: kernels launched by this handle since creation */
+int64_t piadmm_launch_count(const piadmm_handle* h);
+
+/* FP64 FMA micro-benchmark (independent DFMA chains on every SM); returns TFLOP/s in *tflops */
+int piadmm_fp64_peak(int device, int iters, double* tflops, double* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIADMM_H */
