@@ -1,0 +1,703 @@
+// piadmm.cu -- kernels + C ABI (include/piadmm.h) of the B200-native PI-ADMM solver.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include "piadmm_phases.cuh"
+
+#define CTA_THREADS 64
+
+// ------------------------------------------------------------------ thread -> (pair, half, k)
+template <int LPQ>
+struct Who {
+  int warp, lane, k, half, pair_in_cta, group_in_cta;
+  __device__ __forceinline__ Who() {
+    warp = threadIdx.x >> 5;
+    lane = threadIdx.x & 31;
+    k = lane & (LPQ - 1);
+    if (LPQ == 16) { half = lane >> 4; pair_in_cta = warp; group_in_cta = warp * 2 + half; }
+    else { half = warp; pair_in_cta = 0; group_in_cta = warp; }
+  }
+};
+template <int LPQ> __host__ __device__ constexpr int pairs_per_cta() { return LPQ == 16 ? 2 : 1; }
+template <int LPQ> __host__ __device__ constexpr int groups_per_cta() { return CTA_THREADS / LPQ; }
+
+template <int LPQ>
+__device__ __forceinline__ void pair_sync() {
+  if (LPQ == 16) __syncwarp(); else __syncthreads();
+}
+
+template <int LPQ>
+__device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) {
+  for (int t = threadIdx.x; t < LPQ * LPQ; t += blockDim.x) Wsm[t] = c.W[t];
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------ phase kernels (generic V)
+__global__ void k_begin_step(const __grid_constant__ DevCtx c) {
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+  const int N = c.N;
+  const size_t n_slot = (size_t)c.S * c.V * c.D * 2 * (N + 1);
+  for (size_t t = tid; t < n_slot; t += nth) {
+    c.b.hat[t] = 0.0; c.b.dual[t] = 0.0; c.b.integ[t] = 0.0; c.b.diff[t] = 0.0; c.b.last_hat[t] = 0.0;
+  }
+  const size_t n_pos = (size_t)c.S * c.V * 2 * (N + 1);
+  for (size_t t = tid; t < n_pos; t += nth) c.b.pos[t] = 0.0;
+  const size_t n_u = (size_t)c.S * c.V * N;
+  for (size_t t = tid; t < n_u; t += nth) c.b.u[t] = 0.0;
+  const size_t n_nbr = (size_t)c.S * c.V * c.D;
+  for (size_t t = tid; t < n_nbr; t += nth) {
+    const int d = (int)(t % c.D), i = (int)((t / c.D) % c.V);
+    int j = -1;
+    if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;
+    c.b.nbr[t] = j;
+  }
+  const size_t n_h = (size_t)c.S * c.I;
+  for (size_t t = tid; t < n_h; t += nth) { c.b.err_rk[t] = 0.0; c.b.err_sk[t] = 0.0; }
+  for (size_t t = tid; t < (size_t)c.S; t += nth) {
+    c.b.flag[t] = 0; c.b.done[t] = 0; c.b.aliased[t] = 0; c.b.curr_iter[t] = 1; c.b.n_outer[t] = 0;
+    c.b.status[t] = 0; c.b.veh_inner[t] = 0; c.b.edge_inner[t] = 0; c.b.n_veh_solves[t] = 0;
+    c.b.n_edge_solves[t] = 0; c.b.edge_n[t] = 0;
+    c.rho_new[t] = c.b.rho_s[t];
+  }
+}
+
+template <int LPQ>
+__global__ void __launch_bounds__(CTA_THREADS) k_x_update(const __grid_constant__ DevCtx c) {
+  __shared__ __align__(16) double Wsm[LPQ * LPQ];
+  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
+  __shared__ __align__(16) double xch[64];
+  load_W<LPQ>(c, Wsm);
+  Who<LPQ> w;
+  const long a = (long)blockIdx.x * groups_per_cta<LPQ>() + w.group_in_cta;
+  const int s = (int)(a / c.V), i = (int)(a % c.V);
+  const bool valid = a < (long)c.S * c.V && !c.b.done[s];
+  if (!__any_sync(PIADMM_FULL, valid)) return;
+  if (valid && i == 0 && w.k == 0) c.b.n_outer[s] += 1;
+  dev_x_update<LPQ>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch);
+}
+
+// hits[s,i,jb] bit jj = 1 iff j = 32*jb+jj > i collides with i (casadi/main.py:110-113)
+__global__ void k_hits(const __grid_constant__ DevCtx c) {
+  const int N = c.N, words = (c.V + 31) / 32;
+  const long wid = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const long total = (long)c.S * c.V * words;
+  if (wid >= total) return;
+  const int jb = (int)(wid % words), i = (int)((wid / words) % c.V), s = (int)(wid / ((long)words * c.V));
+  if (c.b.done[s]) return;
+  const int j = jb * 32 + lane;
+  bool hit = false;
+  if (j > i && j < c.V) {
+    hit = c.p.always_edge != 0;
+    const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
+    const double* pi = c.b.pos + (((size_t)s * c.V + i) * 2) * (N + 1);
+    const double* pj = c.b.pos + (((size_t)s * c.V + j) * 2) * (N + 1);
+    for (int k = 0; k <= N && !hit; k++) {
+      const double dx = pi[k] - pj[k], dy = pi[N + 1 + k] - pj[N + 1 + k];
+      hit = dx * dx + dy * dy < thr;
+    }
+  }
+  const unsigned m = __ballot_sync(PIADMM_FULL, hit);
+  if (lane == 0) c.hits[wid] = m;
+}
+
+// per vehicle: allocate neighbour slots for newly colliding vehicles, ascending j (this equals the
+// reference's sequential processing of np.where(edge_mat == 1), row-major)
+__global__ void k_slots(const __grid_constant__ DevCtx c) {
+  const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= (long)c.S * c.V) return;
+  const int s = (int)(a / c.V), i = (int)(a % c.V), words = (c.V + 31) / 32;
+  if (c.b.done[s]) return;
+  int32_t* nb = c.b.nbr + a * c.D;
+  const uint32_t* H = c.hits + (size_t)s * c.V * words;
+  int up = 0;
+  bool overflow = false;
+  for (int j = 0; j < c.V; j++) {
+    if (j == i) continue;
+    const int lo = j < i ? j : i, hi = j < i ? i : j;
+    if (!((H[(size_t)lo * words + (hi >> 5)] >> (hi & 31)) & 1u)) continue;
+    int slot = -1;
+    for (int d = 0; d < c.D; d++) if (nb[d] == j) { slot = d; break; }
+    if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = j; slot = d; break; }
+    if (slot < 0) { overflow = true; continue; }
+    if (j > i) up++;
+  }
+  c.up_cnt[a] = up;
+  if (overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
+}
+
+// per scenario: emit the sorted edge list; flag / early-exit logic of casadi/main.py:115-118
+__global__ void k_edges(const __grid_constant__ DevCtx c) {
+  const int s = blockIdx.x, words = (c.V + 31) / 32;
+  if (c.b.done[s]) return;
+  __shared__ int base;
+  __shared__ int scan[256];
+  if (threadIdx.x == 0) base = 0;
+  __syncthreads();
+  const uint32_t* H = c.hits + (size_t)s * c.V * words;
+  for (int i0 = 0; i0 < c.V; i0 += blockDim.x) {
+    const int i = i0 + threadIdx.x;
+    const int cnt = i < c.V ? c.up_cnt[(size_t)s * c.V + i] : 0;
+    scan[threadIdx.x] = cnt;
+    __syncthreads();
+    for (int o = 1; o < (int)blockDim.x; o <<= 1) {
+      int t = threadIdx.x >= o ? scan[threadIdx.x - o] : 0;
+      __syncthreads();
+      scan[threadIdx.x] += t;
+      __syncthreads();
+    }
+    int n = base + scan[threadIdx.x] - cnt;
+    if (i < c.V && cnt > 0) {
+      const int32_t* nbi = c.b.nbr + ((size_t)s * c.V + i) * c.D;
+      for (int j = i + 1; j < c.V; j++) {
+        if (!((H[(size_t)i * words + (j >> 5)] >> (j & 31)) & 1u)) continue;
+        const int32_t* nbj = c.b.nbr + ((size_t)s * c.V + j) * c.D;
+        int di = -1, dj = -1;
+        for (int d = 0; d < c.D; d++) { if (nbi[d] == j) di = d; if (nbj[d] == i) dj = d; }
+        if (n >= c.E) continue;
+        int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + n) * 2;
+        int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + n) * 2;
+        if (di < 0 || dj < 0) {        // slot overflow on the far side (status already set): dead entry
+          eij[0] = -1; eij[1] = -1; esl[0] = 0; esl[1] = 0;
+          double* er = c.edge_res + ((size_t)s * c.E + n) * 4;
+          er[0] = er[1] = er[2] = er[3] = 0.0;
+        } else {
+          eij[0] = i; eij[1] = j; esl[0] = di; esl[1] = dj;
+        }
+        n++;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) base += scan[threadIdx.x];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    c.b.edge_n[s] = base;
+    if (base == 0 && c.b.flag[s] == 0) c.b.done[s] = 1;   // "no collision if no edge links": break
+    else c.b.flag[s] = 1;
+  }
+}
+
+template <int LPQ>
+__global__ void __launch_bounds__(CTA_THREADS) k_z_update(const __grid_constant__ DevCtx c) {
+  __shared__ __align__(16) double Wsm[LPQ * LPQ];
+  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
+  __shared__ __align__(16) double xch[64];
+  load_W<LPQ>(c, Wsm);
+  Who<LPQ> w;
+  const long pidx = (long)blockIdx.x * pairs_per_cta<LPQ>() + w.pair_in_cta;
+  const int s = (int)(pidx / c.E), e = (int)(pidx % c.E);
+  if (s >= c.S || c.b.done[s] || e >= c.b.edge_n[s]) return;   // uniform per pair
+  const int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + e) * 2;
+  const int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + e) * 2;
+  if (eij[0] < 0) return;
+  dev_z_update<LPQ>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
+                    Wsm, gbuf[w.group_in_cta], xch);
+}
+
+// residuals, stop test, alias latch, last_hat copy: casadi/main.py:165-181.  One CTA per scenario.
+__global__ void k_residuals(const __grid_constant__ DevCtx c) {
+  const int s = blockIdx.x, N = c.N;
+  if (c.b.done[s]) return;
+  const piadmm_params& p = c.p;
+  __shared__ double red[3][128];
+  __shared__ int decision;
+  const int n = c.b.edge_n[s];
+  const double rho = (p.dual_mode == PIADMM_DUAL_PI_OLD && n > 0) ? c.rho_new[s] : c.b.rho_s[s];
+  double sk = 0.0, rk = 0.0, bad = 0.0;
+  for (int e = threadIdx.x; e < n; e += blockDim.x) {
+    const double* er = c.edge_res + ((size_t)s * c.E + e) * 4;
+    if (p.residual_global) { sk += sqrt(rho * rho * (er[0] + er[1])); rk += sqrt(er[2] + er[3]); }
+    else { sk += 2.0 * sqrt(rho * rho * er[0]); rk += 2.0 * sqrt(er[2]); }
+  }
+  if (p.stop_dist_test) {
+    for (int t = threadIdx.x; t < c.V * c.D; t += blockDim.x) {
+      const int i = t / c.D, j = c.b.nbr[(size_t)s * c.V * c.D + t];
+      if (j <= i) continue;
+      const double* xi = c.b.xt + ((size_t)s * c.V + i) * 3;
+      const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
+      const double vi = c.b.spd[(size_t)s * c.V + i], vj = c.b.spd[(size_t)s * c.V + j];
+      const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
+      const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
+      if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) bad = 1.0;
+    }
+  }
+  red[0][threadIdx.x] = sk; red[1][threadIdx.x] = rk; red[2][threadIdx.x] = bad;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o >= 1; o >>= 1) {
+    if ((int)threadIdx.x < o) {
+      red[0][threadIdx.x] += red[0][threadIdx.x + o];
+      red[1][threadIdx.x] += red[1][threadIdx.x + o];
+      red[2][threadIdx.x] += red[2][threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    sk = red[0][0]; rk = red[1][0];
+    c.b.err_rk[(size_t)s * c.I + c.i_iter] = rk;
+    c.b.err_sk[(size_t)s * c.I + c.i_iter] = sk;
+    c.b.rho_s[s] = rho;
+    const bool conv = rk <= p.eps_pri && sk <= p.eps_dual && red[2][0] == 0.0;
+    if (conv) { c.b.curr_iter[s] = c.i_iter + 1; c.b.done[s] = 1; }
+    else {
+      if (p.dual_res_alias) c.b.aliased[s] = 1;
+      if (p.curr_iter_latest) c.b.curr_iter[s] = c.i_iter + 1;
+      if (c.i_iter + 1 >= c.I) c.b.done[s] = 1;      // iteration cap reached
+    }
+    decision = conv ? 1 : 0;
+  }
+  __syncthreads();
+  if (!decision) {
+    const size_t o = (size_t)s * c.V * c.D * 2 * (N + 1), cnt = (size_t)c.V * c.D * 2 * (N + 1);
+    for (size_t t = threadIdx.x; t < cnt; t += blockDim.x) c.b.last_hat[o + t] = c.b.hat[o + t];
+  }
+}
+
+__global__ void k_count_active(const __grid_constant__ DevCtx c, int* out) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool act = t < c.S && !c.b.done[t];
+  const unsigned m = __ballot_sync(PIADMM_FULL, act);
+  if ((threadIdx.x & 31) == 0 && m) atomicAdd(out, __popc(m));
+}
+
+__global__ void k_plant(const __grid_constant__ DevCtx c) {
+  const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= (long)c.S * c.V) return;
+  const double* xt = c.b.xt + a * 3;
+  const double v = c.b.spd[a];
+  double* o = c.b.xt_next + a * 3;
+  o[0] = xt[0] + v * cos(xt[2]) * c.p.dt;
+  o[1] = xt[1] + v * sin(xt[2]) * c.p.dt;
+  o[2] = xt[2] + v / c.p.L * c.b.u[a * c.N] * c.p.dt;
+}
+
+// ------------------------------------------------------------------ fused V=2 persistent kernel
+// One pair per scenario runs casadi/main.py:52-181 start to finish: no host round trips, state
+// stays in L1/L2 between phases (each scenario touches ~10 KB).
+template <int LPQ>
+__global__ void __launch_bounds__(CTA_THREADS) k_fused_v2(const __grid_constant__ DevCtx c) {
+  __shared__ __align__(16) double Wsm[LPQ * LPQ];
+  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
+  __shared__ __align__(16) double xch[64];
+  load_W<LPQ>(c, Wsm);
+  Who<LPQ> w;
+  const piadmm_params& p = c.p;
+  const int N = c.N, k = w.k, half = w.half;
+  const int s = blockIdx.x * pairs_per_cta<LPQ>() + w.pair_in_cta;
+  if (s >= c.S) return;                       // warp-uniform (only possible when LPQ == 16)
+  const int i = half, j = half ^ 1;
+  const bool lead = half == 0 && k == 0;
+  const size_t so = SLOT_OFF(s, i, 0);
+  // ---- casadi/main.py:52-72: re-initialise local / edge / dual variables
+  if (k <= N) {
+    for (int cc = 0; cc < 2; cc++) {
+      const size_t o2 = so + (size_t)cc * NP1 + k;
+      c.b.hat[o2] = 0.0; c.b.dual[o2] = 0.0; c.b.integ[o2] = 0.0; c.b.diff[o2] = 0.0; c.b.last_hat[o2] = 0.0;
+      c.b.pos[POS_OFF(s, i) + (size_t)cc * NP1 + k] = 0.0;
+    }
+  }
+  if (k < N) c.b.u[((size_t)s * 2 + i) * N + k] = 0.0;
+  if (k == 0) c.b.nbr[(size_t)s * 2 + i] = p.al_all ? j : -1;
+  for (int t = k + half * LPQ; t < c.I; t += 2 * LPQ) {
+    c.b.err_rk[(size_t)s * c.I + t] = 0.0;
+    c.b.err_sk[(size_t)s * c.I + t] = 0.0;
+  }
+  if (lead) {
+    c.b.aliased[s] = 0; c.b.status[s] = 0; c.b.veh_inner[s] = 0; c.b.edge_inner[s] = 0;
+    c.b.n_veh_solves[s] = 0; c.b.n_edge_solves[s] = 0; c.b.done[s] = 0;
+    c.rho_new[s] = c.b.rho_s[s];
+  }
+  pair_sync<LPQ>();
+  int flag = 0, curr_iter = 1, n_outer = 0, edge_n = 0;
+  const double thr = p.thr_squared ? p.dis_thres * p.dis_thres : p.dis_thres;
+  bool dist_ok = true;
+  if (p.stop_dist_test) {
+    const double* xi = c.b.xt + ((size_t)s * 2) * 3;
+    const double* xj = xi + 3;
+    const double vi = c.b.spd[(size_t)s * 2], vj = c.b.spd[(size_t)s * 2 + 1];
+    const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
+    const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
+    dist_ok = sqrt(dx * dx + dy * dy) > p.dis_thres;
+  }
+  for (int i_iter = 0; i_iter < c.I; i_iter++) {
+    n_outer++;
+    dev_x_update<LPQ>(c, s, i, true, k, w.lane, half, Wsm, gbuf[w.group_in_cta], xch);
+    pair_sync<LPQ>();
+    // ---- collision test, casadi/main.py:110-118
+    bool near = false;
+    if (k <= N) {
+      const double* pi = c.b.pos + POS_OFF(s, i);
+      const double* pj = c.b.pos + POS_OFF(s, j);
+      const double dx = pi[k] - pj[k], dy = pi[NP1 + k] - pj[NP1 + k];
+      near = dx * dx + dy * dy < thr;
+    }
+    const bool hit = p.always_edge || group_any<LPQ>(near, w.lane);
+    edge_n = hit ? 1 : 0;
+    if (!hit && !flag) break;
+    flag = 1;
+    double sk = 0.0, rk = 0.0;
+    if (hit) {
+      if (k == 0) c.b.nbr[(size_t)s * 2 + i] = j;
+      dev_z_update<LPQ>(c, s, 0, 0, 1, 0, 0, true, true, k, w.lane, half, Wsm, gbuf[w.group_in_cta], xch);
+      pair_sync<LPQ>();
+      const double* er = c.edge_res + (size_t)s * c.E * 4;
+      const double rho = p.dual_mode == PIADMM_DUAL_PI_OLD ? c.rho_new[s] : c.b.rho_s[s];
+      if (p.residual_global) { sk = sqrt(rho * rho * (er[0] + er[1])); rk = sqrt(er[2] + er[3]); }
+      else { sk = 2.0 * sqrt(rho * rho * er[0]); rk = 2.0 * sqrt(er[2]); }
+      pair_sync<LPQ>();                       // everyone has read rho_s / edge_res
+      if (lead) c.b.rho_s[s] = rho;
+    }
+    if (lead) { c.b.err_rk[(size_t)s * c.I + i_iter] = rk; c.b.err_sk[(size_t)s * c.I + i_iter] = sk; }
+    if (rk <= p.eps_pri && sk <= p.eps_dual && dist_ok) { curr_iter = i_iter + 1; break; }
+    if (p.dual_res_alias && lead) c.b.aliased[s] = 1;
+    if (k <= N) {
+      c.b.last_hat[so + k] = c.b.hat[so + k];
+      c.b.last_hat[so + NP1 + k] = c.b.hat[so + NP1 + k];
+    }
+    if (p.curr_iter_latest) curr_iter = i_iter + 1;
+    pair_sync<LPQ>();
+  }
+  if (lead) {
+    c.b.flag[s] = flag; c.b.done[s] = 1; c.b.curr_iter[s] = curr_iter; c.b.n_outer[s] = n_outer;
+    c.b.edge_n[s] = edge_n;
+    if (edge_n) {
+      c.b.edge_ij[(size_t)s * c.E * 2] = 0; c.b.edge_ij[(size_t)s * c.E * 2 + 1] = 1;
+      c.b.edge_slot[(size_t)s * c.E * 2] = 0; c.b.edge_slot[(size_t)s * c.E * 2 + 1] = 0;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ FP64 FMA peak micro-benchmark
+__global__ void k_fp64_peak(double* out, int iters) {
+  double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6,
+         a7 = a0 + 7;
+  const double b = 1.0000001, cc = 1e-9;
+  for (int i = 0; i < iters; i++) {
+    a0 = fma(a0, b, cc); a1 = fma(a1, b, cc); a2 = fma(a2, b, cc); a3 = fma(a3, b, cc);
+    a4 = fma(a4, b, cc); a5 = fma(a5, b, cc); a6 = fma(a6, b, cc); a7 = fma(a7, b, cc);
+  }
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+}
+
+// ------------------------------------------------------------------ host side / C ABI
+struct piadmm_handle {
+  DevCtx c;
+  int device;
+  bool bound;
+  int lpq;
+  double* d_W;
+  int* d_count;
+  int64_t launches;
+  std::string err;
+};
+
+static thread_local std::string g_create_err;
+
+#define CK(call)                                                                        \
+  do {                                                                                  \
+    cudaError_t e_ = (call);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                      \
+      return PIADMM_E_CUDA;                                                             \
+    }                                                                                   \
+  } while (0)
+
+static double pow10i(int d) {
+  if (d < 0) return 0.0;
+  double s = 1.0;
+  for (int i = 0; i < d; i++) s *= 10.0;
+  return s;
+}
+
+static int check_params(const piadmm_params* p, int V, int D, std::string& err) {
+  if (!p) { err = "params is NULL"; return PIADMM_E_ARG; }
+  if (p->num_ho < 3 || p->num_ho > 31) { err = "num_ho must be in [3,31]"; return PIADMM_E_ARG; }
+  if (p->iter_num < 1) { err = "iter_num must be >= 1"; return PIADMM_E_ARG; }
+  if (p->in_check < 1 || p->in_max_iter < 1) { err = "in_check / in_max_iter must be >= 1"; return PIADMM_E_ARG; }
+  if (!(p->in_rho0 > 0) || !(p->in_sigma > 0) || !(p->in_alpha > 0) || !(p->dt > 0) || !(p->L > 0)) {
+    err = "in_rho0, in_sigma, in_alpha, dt, L must be > 0"; return PIADMM_E_ARG;
+  }
+  if (p->dual_mode < 0 || p->dual_mode > 2) { err = "bad dual_mode"; return PIADMM_E_ARG; }
+  if (p->al_all && D < V - 1) { err = "al_all needs D >= V-1"; return PIADMM_E_ARG; }
+  return PIADMM_OK;
+}
+
+extern "C" {
+
+int piadmm_abi_version(void) { return PIADMM_ABI_VERSION; }
+
+int piadmm_max_edges(int V, int D) { int e = V * D / 2; return e < 1 ? 1 : e; }
+
+void piadmm_default_params(piadmm_params* p) {
+  memset(p, 0, sizeof *p);
+  p->dt = 0.1; p->L = 1.0; p->dis_thres = 2.0; p->beta = 10.0; p->Pnorm = 1.0; p->Pcost = 1.0;
+  p->rho = 2.0; p->eps_pri = 20.0; p->eps_dual = 1.0;
+  p->theta1 = 5.0; p->theta2 = 3.0; p->kI = -1.0; p->windup_sat = 30.0; p->backcalc = 1.0;
+  p->K_I = 3.0; p->KP_num = 5.0; p->KP_max = 2.5; p->rho_num = 4.0; p->rho_min = 1.0; p->rho_max = 5.0;
+  p->in_rho0 = 0.1; p->in_sigma = 1e-6; p->in_alpha = 1.6; p->in_eps_abs = 1e-3; p->in_eps_rel = 1e-3;
+  p->in_adapt_tol = 5.0;
+  p->num_ho = 15; p->iter_num = 100; p->dual_mode = PIADMM_DUAL_PLAIN;
+  p->thr_squared = 0; p->dual_res_alias = 1; p->stop_dist_test = 0; p->pos_nonlinear = 0;
+  p->curr_iter_latest = 0; p->round_u = 4; p->round_edge = 4; p->al_all = 1; p->always_edge = 0;
+  p->residual_global = 0; p->PI = 1; p->windup = 1; p->trad = 0;
+  p->in_max_iter = 4000; p->in_check = 25; p->in_adaptive = 1;
+}
+
+const char* piadmm_last_error(const piadmm_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+
+int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadmm_handle** out) {
+  if (!out) return PIADMM_E_ARG;
+  *out = nullptr;
+  if (S < 1 || V < 1 || D < 1) { g_create_err = "S, V, D must be >= 1"; return PIADMM_E_ARG; }
+  int rc = check_params(p, V, D, g_create_err);
+  if (rc) return rc;
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev < 1 || device < 0 || device >= ndev) {
+    g_create_err = std::string("no usable CUDA device (there is no CPU fallback): ") +
+                   (ce != cudaSuccess ? cudaGetErrorString(ce) : "bad device index");
+    return PIADMM_E_CUDA;
+  }
+  piadmm_handle* h = new piadmm_handle();
+  memset(&h->c, 0, sizeof h->c);
+  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr;
+  h->c.p = *p; h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
+  h->c.N = p->num_ho; h->c.I = p->iter_num;
+  h->c.round_u_scale = pow10i(p->round_u); h->c.round_edge_scale = pow10i(p->round_edge);
+  h->lpq = p->num_ho <= 15 ? 16 : 32;
+  auto fail = [&](cudaError_t e, const char* what) {
+    g_create_err = std::string(what) + ": " + cudaGetErrorString(e);
+    piadmm_destroy(h);
+    return PIADMM_E_CUDA;
+  };
+  if ((ce = cudaSetDevice(device)) != cudaSuccess) return fail(ce, "cudaSetDevice");
+  // W = M'M, zero padded to LPQ x LPQ
+  const int L = h->lpq, N = p->num_ho;
+  double* W = (double*)calloc((size_t)L * L, sizeof(double));
+  for (int i = 0; i < N; i++)
+    for (int j = 0; j < N; j++) {
+      double s = 0;
+      for (int k = 0; k <= N; k++) {
+        int mi = k - 1 - i, mj = k - 1 - j;
+        if (mi > 0 && mj > 0) s += (double)mi * (double)mj;
+      }
+      W[i * L + j] = s;
+    }
+  ce = cudaMalloc(&h->d_W, sizeof(double) * L * L);
+  if (ce == cudaSuccess) ce = cudaMemcpy(h->d_W, W, sizeof(double) * L * L, cudaMemcpyHostToDevice);
+  free(W);
+  if (ce != cudaSuccess) return fail(ce, "W upload");
+  h->c.W = h->d_W;
+  const int words = (V + 31) / 32;
+  if ((ce = cudaMalloc(&h->c.edge_res, sizeof(double) * (size_t)S * h->c.E * 4)) != cudaSuccess) return fail(ce, "edge_res");
+  if ((ce = cudaMemset(h->c.edge_res, 0, sizeof(double) * (size_t)S * h->c.E * 4)) != cudaSuccess) return fail(ce, "edge_res");
+  if ((ce = cudaMalloc(&h->c.rho_new, sizeof(double) * S)) != cudaSuccess) return fail(ce, "rho_new");
+  if ((ce = cudaMalloc(&h->c.hits, sizeof(uint32_t) * (size_t)S * V * words)) != cudaSuccess) return fail(ce, "hits");
+  if ((ce = cudaMalloc(&h->c.up_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "up_cnt");
+  if ((ce = cudaMalloc(&h->d_count, sizeof(int))) != cudaSuccess) return fail(ce, "count");
+  *out = h;
+  return PIADMM_OK;
+}
+
+void piadmm_destroy(piadmm_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt);
+  cudaFree(h->d_count);
+  delete h;
+}
+
+int piadmm_set_params(piadmm_handle* h, const piadmm_params* p) {
+  if (!h) return PIADMM_E_ARG;
+  int rc = check_params(p, h->c.V, h->c.D, h->err);
+  if (rc) return rc;
+  if (p->num_ho != h->c.N || p->iter_num != h->c.I) { h->err = "num_ho / iter_num are fixed at create time"; return PIADMM_E_ARG; }
+  h->c.p = *p;
+  h->c.round_u_scale = pow10i(p->round_u); h->c.round_edge_scale = pow10i(p->round_edge);
+  return PIADMM_OK;
+}
+
+int piadmm_bind(piadmm_handle* h, const piadmm_buffers* b) {
+  if (!h || !b) return PIADMM_E_ARG;
+  const void* const* ptrs = reinterpret_cast<const void* const*>(b);
+  for (size_t i = 0; i < sizeof(piadmm_buffers) / sizeof(void*); i++)
+    if (!ptrs[i]) { h->err = "piadmm_bind: NULL buffer at field index " + std::to_string(i); return PIADMM_E_UNBOUND; }
+  h->c.b = *b;
+  h->bound = true;
+  return PIADMM_OK;
+}
+
+int64_t piadmm_launch_count(const piadmm_handle* h) { return h ? h->launches : 0; }
+
+#define REQUIRE_BOUND()                                                       \
+  do {                                                                        \
+    if (!h) return PIADMM_E_ARG;                                              \
+    if (!h->bound) { h->err = "buffers not bound"; return PIADMM_E_UNBOUND; } \
+    CK(cudaSetDevice(h->device));                                             \
+  } while (0)
+
+#define LAUNCHED()              \
+  do {                          \
+    h->launches++;              \
+    CK(cudaGetLastError());     \
+  } while (0)
+
+int piadmm_begin_step(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  cudaStream_t st = (cudaStream_t)stream;
+  h->c.i_iter = 0;
+  k_begin_step<<<148 * 4, 256, 0, st>>>(h->c);
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
+int piadmm_x_update(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  cudaStream_t st = (cudaStream_t)stream;
+  const long agents = (long)h->c.S * h->c.V;
+  if (h->lpq == 16) {
+    const int g = groups_per_cta<16>();
+    k_x_update<16><<<(unsigned)((agents + g - 1) / g), CTA_THREADS, 0, st>>>(h->c);
+  } else {
+    const int g = groups_per_cta<32>();
+    k_x_update<32><<<(unsigned)((agents + g - 1) / g), CTA_THREADS, 0, st>>>(h->c);
+  }
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
+int piadmm_detect_edges(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  cudaStream_t st = (cudaStream_t)stream;
+  const int words = (h->c.V + 31) / 32;
+  const long warps = (long)h->c.S * h->c.V * words;
+  k_hits<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(h->c);
+  LAUNCHED();
+  const long agents = (long)h->c.S * h->c.V;
+  k_slots<<<(unsigned)((agents + 127) / 128), 128, 0, st>>>(h->c);
+  LAUNCHED();
+  k_edges<<<h->c.S, 128, 0, st>>>(h->c);
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
+int piadmm_z_update(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  cudaStream_t st = (cudaStream_t)stream;
+  const long pairs = (long)h->c.S * h->c.E;
+  if (h->lpq == 16) {
+    const int g = pairs_per_cta<16>();
+    k_z_update<16><<<(unsigned)((pairs + g - 1) / g), CTA_THREADS, 0, st>>>(h->c);
+  } else {
+    k_z_update<32><<<(unsigned)pairs, CTA_THREADS, 0, st>>>(h->c);
+  }
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
+int piadmm_residuals(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  cudaStream_t st = (cudaStream_t)stream;
+  k_residuals<<<h->c.S, 128, 0, st>>>(h->c);
+  LAUNCHED();
+  h->c.i_iter++;
+  return PIADMM_OK;
+}
+
+int piadmm_num_active(piadmm_handle* h, void* stream, int32_t* host_out) {
+  REQUIRE_BOUND();
+  if (!host_out) return PIADMM_E_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaMemsetAsync(h->d_count, 0, sizeof(int), st));
+  k_count_active<<<(h->c.S + 255) / 256, 256, 0, st>>>(h->c, h->d_count);
+  LAUNCHED();
+  CK(cudaMemcpyAsync(host_out, h->d_count, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return PIADMM_OK;
+}
+
+int piadmm_plant_step(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  cudaStream_t st = (cudaStream_t)stream;
+  const long agents = (long)h->c.S * h->c.V;
+  k_plant<<<(unsigned)((agents + 127) / 128), 128, 0, st>>>(h->c);
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
+int piadmm_step(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h->c.V == 2 && h->c.D == 1) {
+    // one persistent kernel for the whole outer loop
+    if (h->lpq == 16) k_fused_v2<16><<<(h->c.S + 1) / 2, CTA_THREADS, 0, st>>>(h->c);
+    else k_fused_v2<32><<<h->c.S, CTA_THREADS, 0, st>>>(h->c);
+    LAUNCHED();
+    return PIADMM_OK;
+  }
+  // generic V: phase kernels, one readback of the active-scenario count per outer iteration
+  int rc = piadmm_begin_step(h, stream);
+  for (int it = 0; it < h->c.I && rc == PIADMM_OK; it++) {
+    if ((rc = piadmm_x_update(h, stream))) break;
+    if ((rc = piadmm_detect_edges(h, stream))) break;
+    if ((rc = piadmm_z_update(h, stream))) break;
+    if ((rc = piadmm_residuals(h, stream))) break;
+    int32_t act = 0;
+    if ((rc = piadmm_num_active(h, stream, &act))) break;
+    if (act == 0) break;
+  }
+  return rc;
+}
+
+int piadmm_step_host(piadmm_handle* h, const double* xt, const double* spd, const double* refwin,
+                     double* u_out, double* pos_out, double* xt_next_out, int32_t* curr_iter_out,
+                     int32_t* n_outer_out, void* stream) {
+  REQUIRE_BOUND();
+  if (!xt || !spd || !refwin) return PIADMM_E_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t SV = (size_t)h->c.S * h->c.V, N = h->c.N;
+  CK(cudaMemcpyAsync((void*)h->c.b.xt, xt, sizeof(double) * SV * 3, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync((void*)h->c.b.spd, spd, sizeof(double) * SV, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync((void*)h->c.b.refwin, refwin, sizeof(double) * SV * 2 * (N + 1), cudaMemcpyHostToDevice, st));
+  int rc = piadmm_step(h, stream);
+  if (rc) return rc;
+  rc = piadmm_plant_step(h, stream);
+  if (rc) return rc;
+  if (u_out) CK(cudaMemcpyAsync(u_out, h->c.b.u, sizeof(double) * SV * N, cudaMemcpyDeviceToHost, st));
+  if (pos_out) CK(cudaMemcpyAsync(pos_out, h->c.b.pos, sizeof(double) * SV * 2 * (N + 1), cudaMemcpyDeviceToHost, st));
+  if (xt_next_out) CK(cudaMemcpyAsync(xt_next_out, h->c.b.xt_next, sizeof(double) * SV * 3, cudaMemcpyDeviceToHost, st));
+  if (curr_iter_out) CK(cudaMemcpyAsync(curr_iter_out, h->c.b.curr_iter, sizeof(int32_t) * h->c.S, cudaMemcpyDeviceToHost, st));
+  if (n_outer_out) CK(cudaMemcpyAsync(n_outer_out, h->c.b.n_outer, sizeof(int32_t) * h->c.S, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return PIADMM_OK;
+}
+
+int piadmm_fp64_peak(int device, int iters, double* tflops, double* ms) {
+  if (!tflops || iters < 1) return PIADMM_E_ARG;
+  cudaDeviceProp prop;
+  if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) return PIADMM_E_CUDA;
+  const int blocks = prop.multiProcessorCount * 8, threads = 256;
+  double* d = nullptr;
+  if (cudaMalloc(&d, sizeof(double) * (size_t)blocks * threads) != cudaSuccess) return PIADMM_E_CUDA;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int rep = 0; rep < 6; rep++) {       // first 3 are warm-up
+    cudaEventRecord(e0);
+    k_fp64_peak<<<blocks, threads>>>(d, iters);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(d); return PIADMM_E_CUDA; }
+    float t; cudaEventElapsedTime(&t, e0, e1);
+    if (rep >= 3 && t < best) best = t;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  const double flops = 2.0 * 8.0 * (double)iters * (double)blocks * threads;
+  *tflops = flops / (best * 1e-3) / 1e12;
+  if (ms) *ms = best;
+  return PIADMM_OK;
+}
+
+}  // extern "C"

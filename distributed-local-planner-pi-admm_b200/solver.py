@@ -1,0 +1,160 @@
+"""Batched PI-ADMM solver: PyTorch owns the fp64 device buffers, libpiadmm.so (hand-written
+sm_100a CUDA behind the C ABI of include/piadmm.h) does all the arithmetic.
+
+This is the batched form of the loop body of the reference's casadi/main.py:46-192:
+``setup`` = the per-step inputs (xt, reference window), ``iterate`` = the outer ADMM iterations
+(x-update QPs, collision test, edge problems, dual/PI update, residuals), ``residuals`` and
+``trajectories`` = the outputs the script keeps (err_rk_vec, iter_his, primal_u, pos_old).
+
+There is no CPU path: constructing a solver without a CUDA device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _abi
+
+_TORCH_DT = {C.c_double: torch.float64, C.c_int32: torch.int32, C.c_int64: torch.int64}
+
+
+class PIADMMSolver:
+    def __init__(self, params: _abi.Params | None = None, S: int = 1, V: int = 2, D: int | None = None,
+                 device: int | torch.device | None = None):
+        self.lib = _abi.load_library()
+        if not torch.cuda.is_available():
+            raise _abi.PIADMMError("PIADMMSolver needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.params = (params or _abi.default_params()).copy()
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        self.S, self.V = int(S), int(V)
+        self.D = int(D) if D is not None else max(1, (self.V - 1) if self.params.al_all else 1)
+        self.N, self.I = int(self.params.num_ho), int(self.params.iter_num)
+        self.E = _abi.max_edges(self.V, self.D)
+        self._h = C.c_void_p()
+        rc = self.lib.piadmm_create(C.byref(self.params), self.device.index or 0, self.S, self.V, self.D,
+                                    C.byref(self._h))
+        if rc != 0:
+            raise _abi.PIADMMError(f"piadmm_create failed ({rc}): {self.lib.piadmm_last_error(None).decode()}")
+        self.buf = {}
+        b = _abi.Buffers()
+        for name, (ct, shape) in _abi.buffer_shapes(self.S, self.V, self.D, self.N, self.I).items():
+            t = torch.zeros(shape, dtype=_TORCH_DT[ct], device=self.device)
+            self.buf[name] = t
+            setattr(b, name, t.data_ptr())
+        self.buf["rho_s"].fill_(self.params.rho)
+        self._buffers = b
+        self._check(self.lib.piadmm_bind(self._h, C.byref(b)), "piadmm_bind")
+
+    # ------------------------------------------------------------------ plumbing
+    def _check(self, rc, what):
+        if rc != 0:
+            raise _abi.PIADMMError(f"{what} failed ({rc}): {self.lib.piadmm_last_error(self._h).decode()}")
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.piadmm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_params(self, **kw):
+        self.params.update(**kw)
+        self._check(self.lib.piadmm_set_params(self._h, C.byref(self.params)), "piadmm_set_params")
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.piadmm_launch_count(self._h))
+
+    # ------------------------------------------------------------------ per-step API
+    def setup(self, xt, spd, refwin, rho=None):
+        """Inputs of one MPC step.  xt (S,V,3), spd (S,V) or (V,), refwin (S,V,2,N+1); torch or numpy."""
+        def put(name, val):
+            t = torch.as_tensor(val, dtype=torch.float64)
+            self.buf[name].copy_(t.to(self.device, non_blocking=True).expand_as(self.buf[name]))
+        put("xt", xt)
+        put("spd", spd)
+        put("refwin", refwin)
+        if rho is not None:
+            put("rho_s", rho)
+
+    def begin_step(self):
+        self._check(self.lib.piadmm_begin_step(self._h, self._stream()), "piadmm_begin_step")
+
+    def x_update(self):
+        self._check(self.lib.piadmm_x_update(self._h, self._stream()), "piadmm_x_update")
+
+    def detect_edges(self):
+        self._check(self.lib.piadmm_detect_edges(self._h, self._stream()), "piadmm_detect_edges")
+
+    def z_update(self):
+        self._check(self.lib.piadmm_z_update(self._h, self._stream()), "piadmm_z_update")
+
+    def update_residuals(self):
+        self._check(self.lib.piadmm_residuals(self._h, self._stream()), "piadmm_residuals")
+
+    def num_active(self) -> int:
+        out = C.c_int32(0)
+        self._check(self.lib.piadmm_num_active(self._h, self._stream(), C.byref(out)), "piadmm_num_active")
+        return int(out.value)
+
+    def iterate(self, fused: bool | None = None):
+        """Run the whole outer loop of one MPC step (begin_step included).
+
+        fused=None picks the persistent single-kernel path when the scenario shape allows it
+        (V == 2, D == 1) and the phase kernels otherwise; fused=False forces the phase kernels."""
+        if fused is None or fused:
+            if fused and not (self.V == 2 and self.D == 1):
+                raise _abi.PIADMMError("the fused persistent kernel needs V == 2 and D == 1")
+            self._check(self.lib.piadmm_step(self._h, self._stream()), "piadmm_step")
+            return
+        self.begin_step()
+        for _ in range(self.I):
+            self.x_update()
+            self.detect_edges()
+            self.z_update()
+            self.update_residuals()
+            if self.num_active() == 0:
+                break
+
+    def plant_step(self):
+        self._check(self.lib.piadmm_plant_step(self._h, self._stream()), "piadmm_plant_step")
+
+    def step_host(self, xt, spd, refwin):
+        """Host-buffer entry point (numpy in, numpy out; copies happen inside the C call)."""
+        xt = np.ascontiguousarray(xt, dtype=np.float64).reshape(self.S, self.V, 3)
+        spd = np.ascontiguousarray(np.broadcast_to(spd, (self.S, self.V)), dtype=np.float64)
+        refwin = np.ascontiguousarray(refwin, dtype=np.float64).reshape(self.S, self.V, 2, self.N + 1)
+        out = dict(u=np.empty((self.S, self.V, self.N)), pos=np.empty((self.S, self.V, 2, self.N + 1)),
+                   xt_next=np.empty((self.S, self.V, 3)), curr_iter=np.empty(self.S, dtype=np.int32),
+                   n_outer=np.empty(self.S, dtype=np.int32))
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        self._check(self.lib.piadmm_step_host(self._h, p(xt), p(spd), p(refwin), p(out["u"]), p(out["pos"]),
+                                              p(out["xt_next"]), p(out["curr_iter"]), p(out["n_outer"]),
+                                              self._stream()), "piadmm_step_host")
+        return out
+
+    # ------------------------------------------------------------------ outputs
+    def residuals(self):
+        """(err_rk, err_sk) histories (S, iter_num) and the per-scenario iteration counters."""
+        return dict(err_rk=self.buf["err_rk"], err_sk=self.buf["err_sk"], curr_iter=self.buf["curr_iter"],
+                    n_outer=self.buf["n_outer"], status=self.buf["status"])
+
+    def trajectories(self):
+        """primal_u (S,V,N), pos_old (S,V,2,N+1), hat/dual per neighbour slot, next plant state."""
+        return dict(u=self.buf["u"], pos=self.buf["pos"], hat=self.buf["hat"], dual=self.buf["dual"],
+                    nbr=self.buf["nbr"], xt_next=self.buf["xt_next"])
+
+    def to_numpy(self):
+        torch.cuda.synchronize(self.device)
+        return {k: v.detach().cpu().numpy() for k, v in self.buf.items()}
