@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""bench.py -- agent-QP solves/s of one PI-ADMM MPC step over a batch of synthetic scenarios.
+
+  python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c4|c4n30]
+
+Workload (config 4 of BASELINE.json): S = 4096 independent two-vehicle intersection
+scenarios PER GPU (weak scaling, no data-path collective), each one MPC step run to PI-ADMM
+convergence by ONE launch of the fused persistent kernel.  One "step" = that MPC step over the
+whole batch; `value` = agent-QP (vehicle x-update) solves per second, all GPUs together, inputs
+resident in HBM; `e2e` = the same through the host-buffer C-ABI entry point piadmm_step_host
+(pinned host inputs -> H2D -> step -> D2H of u/pos/xt_next/iteration counts inside the timed region).
+
+--impl reference: the reference's CasADi+OSQP stack is not installable here (no wheel, no network),
+so this arm times the oracle's C twin (oracle/piadmm_ref.c, kind "port") on all host cores.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (S per GPU, horizon N)
+    "c4": (4096, 15),
+    "c4n30": (4096, 30),
+}
+
+
+def bench_params(N):
+    """C1 problem constants (casadi/PI_ADMM_class.py:15-28) with the PI + anti-windup dual law and
+    the stop test of the MATLAB CVX script (dual="pi"), OSQP-default inner tolerances."""
+    import pi_admm_b200 as pa
+    p = pa.preset("matlab_pi")
+    p.update(num_ho=N, eps_pri=0.1, eps_dual=0.1, round_u=4, round_edge=4)
+    return p
+
+
+def flops_per_inner_iter(N, edge):
+    """F_iter = 2n^2 + 12m + 6n per inner ADMM iteration (n = N, m = 4N-2);
+    the edge problem here is two halves of n = N unknowns with m = 5N-2 rows each."""
+    if not edge:
+        return 2 * N * N + 12 * (4 * N - 2) + 6 * N
+    return 2 * (2 * N * N + 12 * (5 * N - 2) + 6 * N)
+
+
+def algorithmic_bytes(N, n_veh_solves, n_edge_solves, S):
+    """fp64 bytes one launch has to move: per agent-QP 8*[3 + N + 4(N+1)(1+deg)] with deg = 1
+    (SURVEY.md 8(d)); per edge problem both sides' pos/dual in, hat/dual out."""
+    per_qp = 8 * (3 + N + 4 * (N + 1) * 2)
+    per_edge = 8 * (2 * 4 * (N + 1) + 2 * 4 * (N + 1))
+    return n_veh_solves * per_qp + n_edge_solves * per_edge
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-i", str(self.index), "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.f.read().splitlines():
+            t = [x.strip() for x in line.split(",")]
+            if len(t) < 9:
+                continue
+            try:
+                sm.append(float(t[1])); mx.append(float(t[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, t[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def run_reference(args, rank, world):
+    """CPU arm: oracle C twin on all host cores; rank 0 only."""
+    if rank != 0:
+        return
+    import __graft_entry__ as ge
+    ge.build()
+    from oracle import ctwin
+    from pi_admm_b200.scenarios import c4_scenarios
+    S, N = WORKLOADS[args.workload]
+    p = bench_params(N)
+    xt, spd, refwin = c4_scenarios(S=S, N=N)
+    arrs = ctwin.alloc(S, 2, 1, N, p.iter_num)
+    cores = ctwin.max_threads()
+    for _ in range(args.warmup):
+        ctwin.step(p, xt, spd, refwin, arrs=arrs)
+    t0 = time.perf_counter()
+    solves = 0
+    for _ in range(args.steps):
+        r = ctwin.step(p, xt, spd, refwin, arrs=arrs)
+        solves += int(r["n_veh_solves"].sum())
+    dt = time.perf_counter() - t0
+    val = solves / dt
+    line = {
+        "impl": "reference", "metric": "agent-QP solves/s", "value": val, "unit": "solves/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.workload, S, N, 1),
+        "cpu_baseline": {"value": val, "unit": "solves/s", "cores": cores, "kind": "port",
+                         "sample": f"the full {S}-scenario MPC step x {args.steps} steps on {cores} OpenMP threads "
+                                   "(oracle/piadmm_ref.c; CasADi+OSQP not installable)"},
+        "e2e": {"value": val, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def workload_config(name, S, N, world):
+    return {"workload": f"{name}: {S} independent two-vehicle intersection scenarios per GPU (BASELINE config 4), "
+                        f"horizon N={N}, one MPC step to PI-ADMM convergence",
+            "scenarios_per_gpu": S, "vehicles_per_scenario": 2, "horizon": N,
+            "semantics": "C1 constants (casadi/PI_ADMM_class.py:15-28), dual=pi (MATLAB PI+anti-windup), "
+                         "edge=convex, eps_pri=eps_dual=0.1, inner=osqp_default (eps 1e-3, adaptive rho)",
+            "parallelism": f"scenario-sharded x{world}, no collective",
+            "l2": "L2 flushed (256 MiB write) before every timed step"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from pi_admm_b200.scenarios import c4_scenarios
+    from pi_admm_b200.solver import PIADMMSolver
+    from pi_admm_b200 import _abi
+    import ctypes as C
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    S, N = WORKLOADS[args.workload]
+    p = bench_params(N)
+    # every rank gets its own S scenarios (different seed per rank: weak scaling, no exchange)
+    xt, spd, refwin = c4_scenarios(S=S, N=N, seed=4096 + rank)
+    sol = PIADMMSolver(p, S=S, V=2, device=local_rank)
+    sol.setup(xt, spd, refwin)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=sol.device)
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing -----------------------------------------------------------
+    for _ in range(args.warmup):
+        sol.iterate()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    l0 = sol.launch_count
+    barrier()
+    for a, b in evs:
+        flush.fill_(1)                 # L2 flush, outside the event pair
+        a.record(stream)
+        sol.iterate()                  # ONE fused persistent kernel: all outer iterations of the step
+        b.record(stream)
+    barrier()
+    launches = sol.launch_count - l0
+    step_ms = [a.elapsed_time(b) for a, b in evs]
+    total_ms = sum(step_ms)
+    out = sol.to_numpy()
+    n_veh = int(out["n_veh_solves"].sum()); n_edge = int(out["n_edge_solves"].sum())
+    veh_inner = int(out["veh_inner"].sum()); edge_inner = int(out["edge_inner"].sum())
+    n_outer = out["n_outer"]
+
+    # ---- end to end through the host-buffer C-ABI entry point ------------------------------
+    io = sol.alloc_host_io()
+    io["xt"].copy_(torch.from_numpy(xt)); io["spd"].copy_(torch.from_numpy(spd)); io["refwin"].copy_(torch.from_numpy(refwin))
+    h2d, d2h = sol.host_io_bytes(io)
+    for _ in range(args.warmup):
+        sol.step_host_tensors(io)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sol.step_host_tensors(io)      # synchronous: returns after the D2H copies completed
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- max over ranks, sums of work ------------------------------------------------------
+    stats = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device=sol.device)
+    work = torch.tensor([n_veh, n_edge, veh_inner, edge_inner], dtype=torch.float64, device=sol.device)
+    if world > 1:
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        dist.all_reduce(work, op=dist.ReduceOp.SUM)
+    total_ms, e2e_ms = [float(x) for x in stats.tolist()]
+    g_veh, g_edge, g_vi, g_ei = [float(x) for x in work.tolist()]
+
+    if rank == 0:
+        ms_per_step = total_ms / args.steps
+        value = g_veh / (ms_per_step * 1e-3)
+        e2e_value = g_veh / (e2e_ms / args.steps * 1e-3)
+        # roofline of the dominant (only) kernel k_fused_v2, per launch on this rank
+        flops = veh_inner * flops_per_inner_iter(N, False) + edge_inner * flops_per_inner_iter(N, True)
+        kern_s = (sum(step_ms) / args.steps) * 1e-3
+        tf = C.c_double(0); pm = C.c_double(0)
+        rc = sol.lib.piadmm_fp64_peak(local_rank, 200000, C.byref(tf), C.byref(pm))
+        fp64_peak = float(tf.value) if rc == 0 else None
+        achieved = flops / kern_s / 1e12
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        abytes = algorithmic_bytes(N, n_veh, n_edge, S)
+        roofline = {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
+                    "frac": (achieved / fp64_peak) if fp64_peak else None, "traffic": None,
+                    "kernel": "k_fused_v2", "peak_source": "DFMA micro-benchmark of this repo (piadmm_fp64_peak), "
+                    "MEASURED_PEAKS.json has no fp64 figure",
+                    "flops_per_launch": flops, "inner_iters_per_launch": veh_inner + edge_inner,
+                    "hbm": {"achieved": abytes / kern_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                            "frac": abytes / kern_s / 1e9 / hbm_peak, "algorithmic_bytes": abytes,
+                            "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
+        line = {
+            "metric": "agent-QP solves/s", "value": value, "unit": "solves/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args.workload, S, N, world),
+            "e2e": {"value": e2e_value, "unit": "solves/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms / args.steps,
+                    "api": "piadmm_step_host (C ABI, pinned host buffers, copies inside)"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roofline,
+            "work_per_step": {"agent_qp_solves": g_veh, "edge_solves": g_edge, "veh_inner_iters": g_vi,
+                              "edge_inner_iters": g_ei, "outer_iters_mean": float(n_outer.mean()),
+                              "outer_iters_max": int(n_outer.max()),
+                              "ms_per_mpc_step": ms_per_step},
+        }
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(p, xt, spd, refwin, S, N)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def cpu_baseline(p, xt, spd, refwin, S, N):
+    """Oracle C twin on the box's host cores, ~10 s of CPU work on the same workload."""
+    import __graft_entry__ as ge  # noqa: F401
+    from oracle import ctwin
+    arrs = ctwin.alloc(S, 2, 1, N, p.iter_num)
+    cores = ctwin.max_threads()
+    ctwin.step(p, xt, spd, refwin, arrs=arrs)
+    t0 = time.perf_counter(); reps = 0; solves = 0
+    while time.perf_counter() - t0 < 10.0 and reps < 200:
+        r = ctwin.step(p, xt, spd, refwin, arrs=arrs)
+        solves += int(r["n_veh_solves"].sum()); reps += 1
+    dt = time.perf_counter() - t0
+    return {"value": solves / dt, "unit": "solves/s", "cores": cores, "kind": "port",
+            "sample": f"{reps} repetitions of the same {S}-scenario MPC step (~{dt:.1f} s) with {cores} OpenMP threads, "
+                      "oracle/piadmm_ref.c"}
+
+
+if __name__ == "__main__":
+    main()

@@ -31,7 +31,7 @@ __device__ __forceinline__ void pair_sync() {
 
 template <int LPQ>
 __device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) {
-  for (int t = threadIdx.x; t < LPQ * LPQ; t += blockDim.x) Wsm[t] = c.W[t];
+  for (int t = threadIdx.x; t < 2 * LPQ * LPQ; t += blockDim.x) Wsm[t] = c.W[t];
   __syncthreads();
 }
 
@@ -65,8 +65,8 @@ __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS) k_x_update(const __grid_constant__ DevCtx c) {
-  __shared__ __align__(16) double Wsm[LPQ * LPQ];
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(const __grid_constant__ DevCtx c) {
+  __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
   load_W<LPQ>(c, Wsm);
@@ -182,8 +182,8 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS) k_z_update(const __grid_constant__ DevCtx c) {
-  __shared__ __align__(16) double Wsm[LPQ * LPQ];
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(const __grid_constant__ DevCtx c) {
+  __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
   load_W<LPQ>(c, Wsm);
@@ -278,8 +278,8 @@ __global__ void k_plant(const __grid_constant__ DevCtx c) {
 // One pair per scenario runs casadi/main.py:52-181 start to finish: no host round trips, state
 // stays in L1/L2 between phases (each scenario touches ~10 KB).
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS) k_fused_v2(const __grid_constant__ DevCtx c) {
-  __shared__ __align__(16) double Wsm[LPQ * LPQ];
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
+  __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
   load_W<LPQ>(c, Wsm);
@@ -322,6 +322,7 @@ __global__ void __launch_bounds__(CTA_THREADS) k_fused_v2(const __grid_constant_
     const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
     dist_ok = sqrt(dx * dx + dy * dy) > p.dis_thres;
   }
+#pragma unroll 1
   for (int i_iter = 0; i_iter < c.I; i_iter++) {
     n_outer++;
     dev_x_update<LPQ>(c, s, i, true, k, w.lane, half, Wsm, gbuf[w.group_in_cta], xch);
@@ -476,7 +477,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaSetDevice(device)) != cudaSuccess) return fail(ce, "cudaSetDevice");
   // W = M'M, zero padded to LPQ x LPQ
   const int L = h->lpq, N = p->num_ho;
-  double* W = (double*)calloc((size_t)L * L, sizeof(double));
+  double* W = (double*)calloc((size_t)2 * L * L, sizeof(double));
   for (int i = 0; i < N; i++)
     for (int j = 0; j < N; j++) {
       double s = 0;
@@ -486,8 +487,13 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
       }
       W[i * L + j] = s;
     }
-  ce = cudaMalloc(&h->d_W, sizeof(double) * L * L);
-  if (ce == cudaSuccess) ce = cudaMemcpy(h->d_W, W, sizeof(double) * L * L, cudaMemcpyHostToDevice);
+  for (int r = 0; r + 2 < N; r++) {          // D2'D2, D2 row r = e_r - 2 e_{r+1} + e_{r+2}
+    const double w[3] = {1.0, -2.0, 1.0};
+    for (int a = 0; a < 3; a++)
+      for (int b = 0; b < 3; b++) W[(size_t)L * L + (r + a) * L + (r + b)] += w[a] * w[b];
+  }
+  ce = cudaMalloc(&h->d_W, sizeof(double) * 2 * L * L);
+  if (ce == cudaSuccess) ce = cudaMemcpy(h->d_W, W, sizeof(double) * 2 * L * L, cudaMemcpyHostToDevice);
   free(W);
   if (ce != cudaSuccess) return fail(ce, "W upload");
   h->c.W = h->d_W;

@@ -23,7 +23,7 @@ struct DevCtx {
   piadmm_buffers b;
   int S, V, D, E, N, I;
   double round_u_scale, round_edge_scale;  // 10^decimals, 0 = no rounding
-  const double* W;                         // [LPQ*LPQ] M'M, zero padded, row stride LPQ
+  const double* W;                         // [2][LPQ*LPQ]: M'M and D2'D2, zero padded, row stride LPQ
   double* edge_res;                        // [S,E,4] ss0, ss1, rr0, rr1 of the current outer iteration
   double* rho_new;                         // [S] penalty chosen by the last edge (dual_mode PI_OLD)
   uint32_t* hits;                          // [S,V,ceil(V/32)] collision bit matrix
@@ -32,12 +32,16 @@ struct DevCtx {
 };
 
 // ------------------------------------------------------------------ group primitives
+// v += t on the lanes where k >= o (one predicated DADD instead of a DADD + two FSEL)
+__device__ __forceinline__ void add_if_ge(double& v, double t, int k, int o) {
+  asm("{\n\t.reg .pred p;\n\tsetp.ge.s32 p, %2, %3;\n\t@p add.f64 %0, %0, %1;\n\t}" : "+d"(v) : "d"(t), "r"(k), "r"(o));
+}
 template <int LPQ>
 __device__ __forceinline__ double incl_prefix(double v, int k) {
 #pragma unroll
   for (int o = 1; o < LPQ; o <<= 1) {
     double t = __shfl_up_sync(PIADMM_FULL, v, o, LPQ);
-    if (k >= o) v += t;
+    add_if_ge(v, t, k, o);
   }
   return v;
 }
@@ -46,7 +50,7 @@ __device__ __forceinline__ double incl_suffix(double v, int k) {
 #pragma unroll
   for (int o = 1; o < LPQ; o <<= 1) {
     double t = __shfl_down_sync(PIADMM_FULL, v, o, LPQ);
-    if (k + o < LPQ) v += t;
+    add_if_ge(v, t, LPQ - 1 - k, o);
   }
   return v;
 }
@@ -68,13 +72,13 @@ __device__ __forceinline__ double excl_suffix(double v, int k) { return shift_do
 template <int LPQ>
 __device__ __forceinline__ double group_max(double v) {
 #pragma unroll
-  for (int o = LPQ / 2; o >= 1; o >>= 1) v = fmax(v, __shfl_xor_sync(PIADMM_FULL, v, o));
+  for (int o = LPQ / 2; o >= 1; o >>= 1) { double t = __shfl_xor_sync(PIADMM_FULL, v, o); v = v > t ? v : t; }
   return v;
 }
 template <int LPQ>
 __device__ __forceinline__ double group_min(double v) {
 #pragma unroll
-  for (int o = LPQ / 2; o >= 1; o >>= 1) v = fmin(v, __shfl_xor_sync(PIADMM_FULL, v, o));
+  for (int o = LPQ / 2; o >= 1; o >>= 1) { double t = __shfl_xor_sync(PIADMM_FULL, v, o); v = v < t ? v : t; }
   return v;
 }
 template <int LPQ>
@@ -125,72 +129,63 @@ __device__ __forceinline__ double partner(double mine, double* xch, int k, int h
   }
 }
 
+// max/min without the NaN plumbing of fmax/fmin (inputs are finite): DSETP + 2 SEL
+__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
+__device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
+
 __device__ __forceinline__ double round_scale(double x, double scale) {
   return scale > 0.0 ? rint(x * scale) / scale : x;   // np.around: rint(x*10^d)/10^d
 }
 
 // ------------------------------------------------------------------ K^-1 in registers
-// entries of D2'D2 (second-difference Gram matrix) and T = A'A = 2I + 2 D1'D1
-__device__ __forceinline__ double band_d2(int k, int j, int N) {
-  int lo = max(max(k, j) - 2, 0), hi = min(min(k, j), N - 3);
-  double s = 0.0;
-  for (int r = lo; r <= hi; r++) {
-    int a = k - r, b = j - r;
-    double wa = a == 1 ? -2.0 : 1.0, wb = b == 1 ? -2.0 : 1.0;
-    s += wa * wb;
-  }
-  return s;
-}
-__device__ __forceinline__ double band_t(int k, int j, int N) {
-  if (k == j) return (k == 0 || k == N - 1) ? 4.0 : 6.0;
-  return -2.0;   // |k-j| == 1
-}
-
 // Build K = cI*I + c2*D2'D2 + cW*W + cT*T (row k in a[0..LPQ)) and invert it in place by
 // Gauss-Jordan without pivoting (K is SPD).  rowbuf: LPQ doubles of shared memory per group.
+//
+// The elimination loop is ROLLED (small code, no instruction-cache thrash) and still uses only
+// compile-time register indices: every step rotates the row by one position, so the pivot column
+// is always a[0]; after LPQ steps the rotation has come full circle.  Padded rows/columns (>= N)
+// are identity, for them a step is an exact no-op.
+template <int LPQ>
+__device__ __forceinline__ void gj_step(double (&a)[LPQ], int k, int p, double* rowbuf) {
+  if (k == p) {
+    const double piv = 1.0 / a[0];
+    rowbuf[0] = piv;
+#pragma unroll
+    for (int j = 1; j < LPQ; j++) rowbuf[j] = a[j] * piv;
+  }
+  __syncwarp();
+  const bool me = k == p;                        // lane p: new row = the scaled row itself
+  const double f = a[0];
+#pragma unroll
+  for (int j = 0; j < LPQ; j += 2) {             // in place: a[j-1] <- a[j] - f*row[j], a[LPQ-1] <- -f*row[0]
+    const double2 r = *reinterpret_cast<const double2*>(rowbuf + j);
+    if (j > 0) a[j - 1] = me ? r.x : fma(-f, r.x, a[j]);
+    a[j] = me ? r.y : fma(-f, r.y, a[j + 1]);
+  }
+  {
+    const double r0 = rowbuf[0];
+    a[LPQ - 1] = me ? r0 : -f * r0;
+  }
+  __syncwarp();
+}
+
 template <int LPQ>
 __device__ __forceinline__ void build_Kinv(double (&a)[LPQ], int N, int k, double cI, double c2, double cW,
                                            double cT, const double* __restrict__ Wsm, double* rowbuf) {
+  // Wsm: two symmetric zero-padded LPQ x LPQ tables, W = M'M and D2'D2 (read column-wise: conflict
+  // free).  T = A'A = 2I + 2 D1'D1 is tridiagonal: diag 4 (ends) / 6, off-diagonal -2.
+  const double* D2sm = Wsm + LPQ * LPQ;
+  const double tdiag = (k == 0 || k == N - 1) ? 4.0 : 6.0;
 #pragma unroll
   for (int j = 0; j < LPQ; j++) {
-    double v;
-    if (k < N && j < N) {
-      v = cW * Wsm[j * LPQ + k];         // W symmetric: read column-wise, conflict free
-      int dj = j - k;
-      if (dj >= -2 && dj <= 2) {
-        v += c2 * band_d2(k, j, N);
-        if (dj >= -1 && dj <= 1) v += cT * band_t(k, j, N);
-        if (dj == 0) v += cI;
-      }
-    } else {
-      v = (j == k) ? 1.0 : 0.0;
-    }
+    double v = fma(cW, Wsm[j * LPQ + k], c2 * D2sm[j * LPQ + k]);
+    if (j == k) v += fma(cT, tdiag, cI);
+    if ((j == k + 1 || j == k - 1) && j < N) v = fma(cT, -2.0, v);
+    if (k >= N) v = (j == k) ? 1.0 : 0.0;
     a[j] = v;
   }
-#pragma unroll
-  for (int p = 0; p < LPQ; p++) {
-    if (p < N) {   // uniform
-      if (k == p) {
-        double piv = 1.0 / a[p];
-#pragma unroll
-        for (int j = 0; j < LPQ; j++) a[j] = (j == p) ? piv : a[j] * piv;
-#pragma unroll
-        for (int j = 0; j < LPQ; j++) rowbuf[j] = a[j];
-      }
-      __syncwarp();
-      if (k != p) {
-        double f = a[p];
-        a[p] = 0.0;
-#pragma unroll
-        for (int j = 0; j < LPQ; j += 2) {
-          double2 r = *reinterpret_cast<const double2*>(rowbuf + j);
-          a[j] = fma(-f, r.x, a[j]);
-          a[j + 1] = fma(-f, r.y, a[j + 1]);
-        }
-      }
-      __syncwarp();
-    }
-  }
+#pragma unroll 1
+  for (int p = 0; p < LPQ; p++) gj_step<LPQ>(a, k, p, rowbuf);
 }
 
 // ------------------------------------------------------------------ inner OSQP-style ADMM
@@ -200,42 +195,46 @@ struct InnerOut {
   int status;
 };
 
-// One (EDGE=false) or two coupled (EDGE=true) half problems per group; see oracle/solver.py.
+// One (edge=false) or two coupled (edge=true) half problems per group; see oracle/solver.py.
 //   P = pI*I + p2*D2'D2 + pW*W ; box rows A = [I;-I;-D1;D1] >= -[pi/6,pi/6,pi/9,pi/9]
-//   EDGE: extra rows s = (M x)_{1..N} (lane L <-> row L+1) coupled with the partner by the prox of
-//         beta*max(0, c - a0*s0 - a1*s1).
-// rhsbuf/rowbuf: LPQ doubles of shared memory per group (may alias), xch: 64 doubles per pair.
-template <int LPQ, bool EDGE>
-__device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, int k, int lane, int half,
-                                                double pI, double p2, double pW, double q, double a0,
-                                                double a1, double cvec, const double* __restrict__ Wsm,
-                                                double* rhsbuf, double* xch) {
-  const double al = ip.in_alpha, sg = ip.in_sigma;
+//   edge: extra rows s = (M x)_{1..N} (lane L <-> row L+1) coupled with the partner by the prox of
+//         beta*max(0, c - a0*s0 - a1*s1).  `edge` must be uniform over the pair.
+// rhsbuf: LPQ doubles of shared memory per group, xch: 64 doubles per pair.
+template <int LPQ>
+__device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, int k, int half, bool edge,
+                                             double pI, double p2, double pW, double q, double a0, double a1,
+                                             double cvec, const double* __restrict__ Wsm, double* rhsbuf,
+                                             double* xch) {
+  const double al = ip.in_alpha, sg = ip.in_sigma, oma = 1.0 - al;
   const double l_u = -0.52359877559829887308, l_d = -0.34906585039886591538;  // -pi/6, -pi/9
   double Kinv[LPQ];
   double rho = ip.in_rho0, irho = 1.0 / rho;
   double x = 0.0, z0 = 0.0, z1 = 0.0, z2 = 0.0, z3 = 0.0, y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0;
   double zs = 0.0, ys = 0.0;
-  const double na = EDGE ? fma(a1, a1, a0 * a0) : 0.0;
+  const double na = edge ? fma(a1, a1, a0 * a0) : 1.0;
+  const double a_me = half == 0 ? a0 : a1;
   const bool inner_row = k < N - 1;
-  build_Kinv<LPQ>(Kinv, N, k, pI + sg, p2, EDGE ? pW + rho : pW, rho, Wsm, rhsbuf);
+  const double pWe = edge ? 1.0 : 0.0;       // K = P + sigma I + rho (T + [edge] W)
+  build_Kinv<LPQ>(Kinv, N, k, pI + sg, p2, pW + pWe * rho, rho, Wsm, rhsbuf);
   InnerOut out;
   out.x = 0.0; out.iters = ip.in_max_iter; out.status = 1;
   bool done = false;
+  int chk = ip.in_check;
+#pragma unroll 1
   for (int it = 1; it <= ip.in_max_iter; it++) {
     // ---- rhs = sigma x - q + A'(rho z - y)
-    double e = (rho * z3 - y3) - (rho * z2 - y2);
-    double em = shift_up1<LPQ>(e, k);
+    const double e = (rho * z3 - y3) - (rho * z2 - y2);
+    const double em = shift_up1<LPQ>(e, k);
     double rhs = sg * x - q + ((rho * z0 - y0) - (rho * z1 - y1)) + em - e;
-    if (EDGE) rhs += apply_Mt_s<LPQ>(rho * zs - ys, k);
+    if (edge) rhs += apply_Mt_s<LPQ>(rho * zs - ys, k);
     rhsbuf[k] = rhs;
     __syncwarp();
     // ---- x~ = K^-1 rhs  (row k in registers, rhs broadcast from shared memory)
     double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
 #pragma unroll
     for (int j = 0; j < LPQ; j += 4) {
-      double2 r0 = *reinterpret_cast<const double2*>(rhsbuf + j);
-      double2 r1 = *reinterpret_cast<const double2*>(rhsbuf + j + 2);
+      const double2 r0 = *reinterpret_cast<const double2*>(rhsbuf + j);
+      const double2 r1 = *reinterpret_cast<const double2*>(rhsbuf + j + 2);
       acc0 = fma(Kinv[j], r0.x, acc0);
       acc1 = fma(Kinv[j + 1], r0.y, acc1);
       acc2 = fma(Kinv[j + 2], r1.x, acc2);
@@ -246,69 +245,67 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
     // ---- z~ = A x~, relaxation, projection, dual update
     double d = shift_down1<LPQ>(xt, k) - xt;
     if (!inner_row) d = 0.0;
-    const double zr0 = al * xt + (1.0 - al) * z0;
-    const double zr1 = -al * xt + (1.0 - al) * z1;
-    const double zr2 = -al * d + (1.0 - al) * z2;
-    const double zr3 = al * d + (1.0 - al) * z3;
-    double zrs = 0.0, vs = 0.0;
-    if (EDGE) {
+    const double zr0 = fma(al, xt, oma * z0);
+    const double zr1 = fma(-al, xt, oma * z1);
+    const double zr2 = fma(-al, d, oma * z2);
+    const double zr3 = fma(al, d, oma * z3);
+    x = fma(al, xt, oma * x);
+    double zn;
+    zn = dmax(fma(y0, irho, zr0), l_u); y0 = fma(rho, zr0 - zn, y0); z0 = zn;
+    zn = dmax(fma(y1, irho, zr1), l_u); y1 = fma(rho, zr1 - zn, y1); z1 = zn;
+    zn = dmax(fma(y2, irho, zr2), l_d); y2 = fma(rho, zr2 - zn, y2); z2 = zn;
+    zn = dmax(fma(y3, irho, zr3), l_d); y3 = fma(rho, zr3 - zn, y3); z3 = zn;
+    if (edge) {
       double nxt;
       apply_M<LPQ>(xt, k, &nxt);
       if (k >= N) nxt = 0.0;          // position rows exist for trajectory indices 1..N only
-      zrs = al * nxt + (1.0 - al) * zs;
-      vs = zrs + ys * irho;
-    }
-    x = al * xt + (1.0 - al) * x;
-    double zn;
-    zn = fmax(zr0 + y0 * irho, l_u); y0 += rho * (zr0 - zn); z0 = zn;
-    zn = fmax(zr1 + y1 * irho, l_u); y1 += rho * (zr1 - zn); z1 = zn;
-    zn = fmax(zr2 + y2 * irho, l_d); y2 += rho * (zr2 - zn); z2 = zn;
-    zn = fmax(zr3 + y3 * irho, l_d); y3 += rho * (zr3 - zn); z3 = zn;
-    if (EDGE) {
+      const double zrs = fma(al, nxt, oma * zs);
+      const double vs = fma(ys, irho, zrs);
       const double vo = partner<LPQ>(vs, xch, k, half);
       const double s0 = half == 0 ? vs : vo, s1 = half == 0 ? vo : vs;
       const double tau = fma(a1, s1, a0 * s0);
       const double t = ip.beta * irho;
       double step;
-      if (!(na > 0.0) || tau >= cvec) step = 0.0;
+      if (tau >= cvec) step = 0.0;
       else if (fma(t, na, tau) <= cvec) step = t;
-      else step = (cvec - tau) / (EDGE ? na : 1.0);
-      zn = fma(step, half == 0 ? a0 : a1, vs);
-      ys += rho * (zrs - zn);
+      else step = (cvec - tau) / na;
+      zn = fma(step, a_me, vs);
+      ys = fma(rho, zrs - zn, ys);
       zs = zn;
     }
     // ---- termination / adaptive rho every in_check iterations
-    if (it % ip.in_check == 0) {
+    if (--chk == 0) {
+      chk = ip.in_check;
       double dd = shift_down1<LPQ>(x, k) - x;
       if (!inner_row) dd = 0.0;
-      double rp = fmax(fmax(fabs(x - z0), fabs(-x - z1)), fmax(fabs(-dd - z2), fabs(dd - z3)));
-      double np = fmax(fmax(fabs(x), fabs(dd)), fmax(fmax(fabs(z0), fabs(z1)), fmax(fabs(z2), fabs(z3))));
+      double rp = dmax(dmax(fabs(x - z0), fabs(-x - z1)), dmax(fabs(-dd - z2), fabs(dd - z3)));
+      double np = dmax(dmax(fabs(x), fabs(dd)), dmax(dmax(fabs(z0), fabs(z1)), dmax(fabs(z2), fabs(z3))));
       double nxt;
       double mx = apply_M<LPQ>(x, k, &nxt);
       if (k >= N) nxt = 0.0;
-      if (EDGE) {
-        rp = fmax(rp, fabs(nxt - zs));
-        np = fmax(np, fmax(fabs(nxt), fabs(zs)));
+      if (edge) {
+        rp = dmax(rp, fabs(nxt - zs));
+        np = dmax(np, dmax(fabs(nxt), fabs(zs)));
       }
       if (k > N) mx = 0.0;
       double Px = fma(pW, apply_Mt<LPQ>(mx, k), pI * x);
-      if (p2 != 0.0) {   // uniform per group; shuffles below are executed by the whole warp anyway
-        double x1 = shift_down1<LPQ>(x, k), x2 = shift_down1<LPQ>(x1, k);
-        double ee = (k < N - 2) ? (x - 2.0 * x1 + x2) : 0.0;
-        double e1 = shift_up1<LPQ>(ee, k), e2 = shift_up1<LPQ>(e1, k);
+      {
+        const double x1 = shift_down1<LPQ>(x, k), x2 = shift_down1<LPQ>(x1, k);
+        const double ee = (k < N - 2) ? (x - 2.0 * x1 + x2) : 0.0;
+        const double e1 = shift_up1<LPQ>(ee, k), e2 = shift_up1<LPQ>(e1, k);
         Px = fma(p2, ee - 2.0 * e1 + e2, Px);
       }
-      double ey = y3 - y2;
+      const double ey = y3 - y2;
       double Aty = (y0 - y1) + shift_up1<LPQ>(ey, k) - ey;
-      if (EDGE) Aty += apply_Mt_s<LPQ>(ys, k);
+      if (edge) Aty += apply_Mt_s<LPQ>(ys, k);
       double rd = fabs(Px + q + Aty);
-      double nd = fmax(fabs(Px), fmax(fabs(Aty), fabs(q)));
+      double nd = dmax(fabs(Px), dmax(fabs(Aty), fabs(q)));
       rp = group_max<LPQ>(rp); np = group_max<LPQ>(np); rd = group_max<LPQ>(rd); nd = group_max<LPQ>(nd);
-      if (EDGE) {
-        rp = fmax(rp, partner<LPQ>(rp, xch, k, half));
-        np = fmax(np, partner<LPQ>(np, xch, k, half));
-        rd = fmax(rd, partner<LPQ>(rd, xch, k, half));
-        nd = fmax(nd, partner<LPQ>(nd, xch, k, half));
+      if (edge) {
+        rp = dmax(rp, partner<LPQ>(rp, xch, k, half));
+        np = dmax(np, partner<LPQ>(np, xch, k, half));
+        rd = dmax(rd, partner<LPQ>(rd, xch, k, half));
+        nd = dmax(nd, partner<LPQ>(nd, xch, k, half));
       }
       const bool conv = rp <= ip.in_eps_abs + ip.in_eps_rel * np && rd <= ip.in_eps_abs + ip.in_eps_rel * nd;
       if (conv && !done) {
@@ -318,22 +315,21 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       bool refac = false;
       double rn = rho;
       if (!conv && !done && ip.in_adaptive) {
-        double a = rp / fmax(np, 1e-30);
-        double b = fmax(rd / fmax(nd, 1e-30), 1e-30);
-        rn = fmin(fmax(rho * sqrt(a / b), 1e-6), 1e6);
+        const double a = rp / dmax(np, 1e-30);
+        const double b = dmax(rd / dmax(nd, 1e-30), 1e-30);
+        rn = dmin(dmax(rho * sqrt(a / b), 1e-6), 1e6);
         refac = rn > ip.in_adapt_tol * rho || rn < rho / ip.in_adapt_tol;
       }
       // loop exit must be uniform over everything that synchronises inside the loop:
-      // the warp (both groups when LPQ==16) and, for EDGE with LPQ==32, the CTA pair
+      // the warp (both groups when LPQ==16) and, for an edge with LPQ==32, the CTA pair
       // (conv is identical in both halves of an edge by construction).
       if (__all_sync(PIADMM_FULL, done)) break;
       if (__any_sync(PIADMM_FULL, refac)) {
         if (refac) { rho = rn; irho = 1.0 / rho; }
-        build_Kinv<LPQ>(Kinv, N, k, pI + sg, p2, EDGE ? pW + rho : pW, rho, Wsm, rhsbuf);
+        build_Kinv<LPQ>(Kinv, N, k, pI + sg, p2, pW + pWe * rho, rho, Wsm, rhsbuf);
       }
     }
   }
   if (!done) out.x = x;
-  (void)lane;
   return out;
 }

@@ -23,7 +23,7 @@ __device__ __forceinline__ void rollout_nonlinear(const piadmm_params& p, double
 
 // ---- x-update of agent (s,i): casadi/main.py:81-106 --------------------------------------------
 template <int LPQ>
-__device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool valid, int k, int lane,
+__device__ __noinline__ void dev_x_update(const DevCtx& c, int s, int i, bool valid, int k, int lane,
                                              int half, const double* Wsm, double* gbuf, double* xch) {
   const piadmm_params& p = c.p;
   const int N = c.N;
@@ -59,7 +59,7 @@ __device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool
   const double vec = (valid && k <= N) ? (w * e0 + sn * tx - cs * ty) : 0.0;
   const double q = 2.0 * g * apply_Mt<LPQ>(vec, k);
   const double pI = 2.0 * p.Pcost, p2 = valid ? 2.0 : 0.0, pW = valid ? 2.0 * w * g * g : 0.0;
-  InnerOut o = inner_solve<LPQ, false>(p, N, k, lane, half, pI, p2, pW, q, 0.0, 0.0, 0.0, Wsm, gbuf, xch);
+  InnerOut o = inner_solve<LPQ>(p, N, k, half, false, pI, p2, pW, q, 0.0, 0.0, 0.0, Wsm, gbuf, xch);
   const double u = (k < N) ? round_scale(o.x, c.round_u_scale) : 0.0;
   double px, py;
   if (p.pos_nonlinear) {
@@ -90,7 +90,7 @@ __device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool
 // casadi/main.py:121-162 with the convex edge problem (MATLAB ...PI_antiwindup.m:276-304,383-396)
 // and the three dual-update laws.  Writes hat, dual, integ, diff (own side), edge_res, rho_new.
 template <int LPQ>
-__device__ __forceinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0, int v1, int sl0, int sl1,
+__device__ __noinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0, int v1, int sl0, int sl1,
                                              bool last_edge, bool valid, int k, int lane, int half,
                                              const double* Wsm, double* gbuf, double* xch) {
   const piadmm_params& p = c.p;
@@ -141,7 +141,7 @@ __device__ __forceinline__ void dev_z_update(const DevCtx& c, int s, int e, int 
   const double a0 = valid ? -2.0 * g0 * (-lx * sn[0] + ly * cs[0]) : 0.0;
   const double a1 = valid ? 2.0 * g1 * (-lx * sn[1] + ly * cs[1]) : 0.0;
   const double pI = 2.0 * p.Pcost, pW = valid ? rho * g * g : 0.0;
-  InnerOut o = inner_solve<LPQ, true>(p, N, k, lane, half, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch);
+  InnerOut o = inner_solve<LPQ>(p, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch);
   // z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158)
   const double uh = (k < N) ? round_scale(o.x, c.round_edge_scale) : 0.0;
   double hx, hy, hth;

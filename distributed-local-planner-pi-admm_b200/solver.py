@@ -144,6 +144,28 @@ class PIADMMSolver:
                                               self._stream()), "piadmm_step_host")
         return out
 
+    def alloc_host_io(self):
+        """Pinned host tensors for the host-buffer entry point (inputs and outputs of one step)."""
+        S, V, N = self.S, self.V, self.N
+        mk = lambda shape, dt=torch.float64: torch.zeros(shape, dtype=dt).pin_memory()
+        return dict(xt=mk((S, V, 3)), spd=mk((S, V)), refwin=mk((S, V, 2, N + 1)), u=mk((S, V, N)),
+                    pos=mk((S, V, 2, N + 1)), xt_next=mk((S, V, 3)), curr_iter=mk((S,), torch.int32),
+                    n_outer=mk((S,), torch.int32))
+
+    def step_host_tensors(self, io):
+        """piadmm_step_host on (pinned) host tensors from alloc_host_io(): H2D of the inputs, the whole
+        MPC step, D2H of u / pos / xt_next / curr_iter / n_outer, all inside the one C call."""
+        p = lambda t: C.c_void_p(t.data_ptr())
+        self._check(self.lib.piadmm_step_host(self._h, p(io["xt"]), p(io["spd"]), p(io["refwin"]), p(io["u"]),
+                                              p(io["pos"]), p(io["xt_next"]), p(io["curr_iter"]),
+                                              p(io["n_outer"]), self._stream()), "piadmm_step_host")
+
+    @staticmethod
+    def host_io_bytes(io):
+        nb = lambda k: io[k].numel() * io[k].element_size()
+        return (sum(nb(k) for k in ("xt", "spd", "refwin")),
+                sum(nb(k) for k in ("u", "pos", "xt_next", "curr_iter", "n_outer")))
+
     # ------------------------------------------------------------------ outputs
     def residuals(self):
         """(err_rk, err_sk) histories (S, iter_num) and the per-scenario iteration counters."""
