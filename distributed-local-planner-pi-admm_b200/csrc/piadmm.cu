@@ -278,16 +278,40 @@ __global__ void k_plant(const __grid_constant__ DevCtx c) {
 // One pair per scenario runs casadi/main.py:52-181 start to finish: no host round trips, state
 // stays in L1/L2 between phases (each scenario touches ~10 KB).
 template <int LPQ>
+__device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Who<LPQ>& w, const double* Wsm,
+                                                double* gbuf, double* xch);
+
+template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
+  __shared__ int s_next;
   load_W<LPQ>(c, Wsm);
   Who<LPQ> w;
+  // persistent: every pair pulls scenarios from a global counter until the batch is exhausted
+  for (;;) {
+    int s;
+    if (LPQ == 16) {
+      s = 0;
+      if (w.lane == 0) s = atomicAdd(c.queue, 1);
+      s = __shfl_sync(PIADMM_FULL, s, 0);
+    } else {
+      if (threadIdx.x == 0) s_next = atomicAdd(c.queue, 1);
+      __syncthreads();
+      s = s_next;
+      __syncthreads();
+    }
+    if (s >= c.S) break;
+    run_scenario_v2<LPQ>(c, s, w, Wsm, gbuf[w.group_in_cta], xch);
+  }
+}
+
+template <int LPQ>
+__device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Who<LPQ>& w, const double* Wsm,
+                                                double* gbuf, double* xch) {
   const piadmm_params& p = c.p;
   const int N = c.N, k = w.k, half = w.half;
-  const int s = blockIdx.x * pairs_per_cta<LPQ>() + w.pair_in_cta;
-  if (s >= c.S) return;                       // warp-uniform (only possible when LPQ == 16)
   const int i = half, j = half ^ 1;
   const bool lead = half == 0 && k == 0;
   const size_t so = SLOT_OFF(s, i, 0);
@@ -325,7 +349,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_fused_v2(con
 #pragma unroll 1
   for (int i_iter = 0; i_iter < c.I; i_iter++) {
     n_outer++;
-    dev_x_update<LPQ>(c, s, i, true, k, w.lane, half, Wsm, gbuf[w.group_in_cta], xch);
+    dev_x_update<LPQ>(c, s, i, true, k, w.lane, half, Wsm, gbuf, xch);
     pair_sync<LPQ>();
     // ---- collision test, casadi/main.py:110-118
     bool near = false;
@@ -342,7 +366,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_fused_v2(con
     double sk = 0.0, rk = 0.0;
     if (hit) {
       if (k == 0) c.b.nbr[(size_t)s * 2 + i] = j;
-      dev_z_update<LPQ>(c, s, 0, 0, 1, 0, 0, true, true, k, w.lane, half, Wsm, gbuf[w.group_in_cta], xch);
+      dev_z_update<LPQ>(c, s, 0, 0, 1, 0, 0, true, true, k, w.lane, half, Wsm, gbuf, xch);
       pair_sync<LPQ>();
       const double* er = c.edge_res + (size_t)s * c.E * 4;
       const double rho = p.dual_mode == PIADMM_DUAL_PI_OLD ? c.rho_new[s] : c.b.rho_s[s];
@@ -391,6 +415,8 @@ struct piadmm_handle {
   int lpq;
   double* d_W;
   int* d_count;
+  int* d_queue;
+  int fused_grid;
   int64_t launches;
   std::string err;
 };
@@ -464,7 +490,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   }
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
-  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr;
+  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->fused_grid = 0;
   h->c.p = *p; h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
   h->c.N = p->num_ho; h->c.I = p->iter_num;
   h->c.round_u_scale = pow10i(p->round_u); h->c.round_edge_scale = pow10i(p->round_edge);
@@ -504,6 +530,17 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMalloc(&h->c.hits, sizeof(uint32_t) * (size_t)S * V * words)) != cudaSuccess) return fail(ce, "hits");
   if ((ce = cudaMalloc(&h->c.up_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "up_cnt");
   if ((ce = cudaMalloc(&h->d_count, sizeof(int))) != cudaSuccess) return fail(ce, "count");
+  if ((ce = cudaMalloc(&h->d_queue, sizeof(int))) != cudaSuccess) return fail(ce, "queue");
+  h->c.queue = h->d_queue;
+  {
+    cudaDeviceProp prop;
+    int per_sm = 0;
+    if ((ce = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail(ce, "props");
+    if (h->lpq == 16) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_v2<16>, CTA_THREADS, 0);
+    else ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_v2<32>, CTA_THREADS, 0);
+    if (ce != cudaSuccess || per_sm < 1) return fail(ce, "occupancy");
+    h->fused_grid = prop.multiProcessorCount * per_sm;     // one resident wave, persistent CTAs
+  }
   *out = h;
   return PIADMM_OK;
 }
@@ -512,7 +549,7 @@ void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt);
-  cudaFree(h->d_count);
+  cudaFree(h->d_count); cudaFree(h->d_queue);
   delete h;
 }
 
@@ -639,8 +676,12 @@ int piadmm_step(piadmm_handle* h, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   if (h->c.V == 2 && h->c.D == 1) {
     // one persistent kernel for the whole outer loop
-    if (h->lpq == 16) k_fused_v2<16><<<(h->c.S + 1) / 2, CTA_THREADS, 0, st>>>(h->c);
-    else k_fused_v2<32><<<h->c.S, CTA_THREADS, 0, st>>>(h->c);
+    CK(cudaMemsetAsync(h->d_queue, 0, sizeof(int), st));
+    const int pairs = h->lpq == 16 ? 2 : 1;
+    int grid = (h->c.S + pairs - 1) / pairs;
+    if (grid > h->fused_grid) grid = h->fused_grid;
+    if (h->lpq == 16) k_fused_v2<16><<<grid, CTA_THREADS, 0, st>>>(h->c);
+    else k_fused_v2<32><<<grid, CTA_THREADS, 0, st>>>(h->c);
     LAUNCHED();
     return PIADMM_OK;
   }

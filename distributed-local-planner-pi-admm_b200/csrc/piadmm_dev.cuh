@@ -29,6 +29,7 @@ struct DevCtx {
   uint32_t* hits;                          // [S,V,ceil(V/32)] collision bit matrix
   int32_t* up_cnt;                         // [S,V] edges (i,j>i) detected per vehicle
   int i_iter;                              // outer iteration index (phase API)
+  int* queue;                              // work counter of the persistent fused kernel
 };
 
 // ------------------------------------------------------------------ group primitives
@@ -145,27 +146,34 @@ __device__ __forceinline__ double round_scale(double x, double scale) {
 // compile-time register indices: every step rotates the row by one position, so the pivot column
 // is always a[0]; after LPQ steps the rotation has come full circle.  Padded rows/columns (>= N)
 // are identity, for them a step is an exact no-op.
+// a = 0 on the lanes where `me` holds (one predicated CS2R instead of two FSEL)
+__device__ __forceinline__ void zero_if(double& a, int me) {
+  asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %1, 0;\n\t@p mov.f64 %0, 0d0000000000000000;\n\t}" : "+d"(a) : "r"(me));
+}
+
 template <int LPQ>
 __device__ __forceinline__ void gj_step(double (&a)[LPQ], int k, int p, double* rowbuf) {
-  if (k == p) {
-    const double piv = 1.0 / a[0];
+  const int me = k == p;
+  double f = a[0];
+  if (me) {
+    const double piv = 1.0 / f;
     rowbuf[0] = piv;
 #pragma unroll
     for (int j = 1; j < LPQ; j++) rowbuf[j] = a[j] * piv;
   }
   __syncwarp();
-  const bool me = k == p;                        // lane p: new row = the scaled row itself
-  const double f = a[0];
+  // lane p: new row = the scaled row itself = 0 - (-1) * row ; other lanes: a - a[0] * row
+#pragma unroll
+  for (int j = 0; j < LPQ; j++) zero_if(a[j], me);
+  f = me ? -1.0 : f;
+  const double nf = -f;
 #pragma unroll
   for (int j = 0; j < LPQ; j += 2) {             // in place: a[j-1] <- a[j] - f*row[j], a[LPQ-1] <- -f*row[0]
     const double2 r = *reinterpret_cast<const double2*>(rowbuf + j);
-    if (j > 0) a[j - 1] = me ? r.x : fma(-f, r.x, a[j]);
-    a[j] = me ? r.y : fma(-f, r.y, a[j + 1]);
+    if (j > 0) a[j - 1] = fma(nf, r.x, a[j]);
+    a[j] = fma(nf, r.y, a[j + 1]);
   }
-  {
-    const double r0 = rowbuf[0];
-    a[LPQ - 1] = me ? r0 : -f * r0;
-  }
+  a[LPQ - 1] = nf * rowbuf[0];
   __syncwarp();
 }
 
@@ -224,8 +232,8 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
   for (int it = 1; it <= ip.in_max_iter; it++) {
     // ---- rhs = sigma x - q + A'(rho z - y)
     const double e = (rho * z3 - y3) - (rho * z2 - y2);
-    const double em = shift_up1<LPQ>(e, k);
-    double rhs = sg * x - q + ((rho * z0 - y0) - (rho * z1 - y1)) + em - e;
+    double rhs = sg * x - q + ((rho * z0 - y0) - (rho * z1 - y1)) - e;
+    add_if_ge(rhs, __shfl_up_sync(PIADMM_FULL, e, 1, LPQ), k, 1);      // + e_{k-1}
     if (edge) rhs += apply_Mt_s<LPQ>(rho * zs - ys, k);
     rhsbuf[k] = rhs;
     __syncwarp();
