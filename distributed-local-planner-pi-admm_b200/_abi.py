@@ -59,6 +59,7 @@ BUFFER_SPECS = (
     ("veh_inner", C.c_int64, "S"), ("edge_inner", C.c_int64, "S"),
     ("n_veh_solves", _I, "S"), ("n_edge_solves", _I, "S"),
     ("edge_n", _I, "S"), ("edge_ij", _I, "S,E,2"), ("edge_slot", _I, "S,E,2"),
+    ("res_part", _D, "S,2"),
     ("xt_next", _D, "S,V,3"),
 )
 
@@ -136,6 +137,9 @@ _PROTOS = {
     "piadmm_detect_edges": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_z_update": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_residuals": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "piadmm_set_ownership": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "piadmm_residual_partials": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "piadmm_residual_decide": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_num_active": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]),
     "piadmm_step": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_plant_step": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -73,9 +73,8 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(con
   Who<LPQ> w;
   const long a = (long)blockIdx.x * groups_per_cta<LPQ>() + w.group_in_cta;
   const int s = (int)(a / c.V), i = (int)(a % c.V);
-  const bool valid = a < (long)c.S * c.V && !c.b.done[s];
+  const bool valid = a < (long)c.S * c.V && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
   if (!__any_sync(PIADMM_FULL, valid)) return;
-  if (valid && i == 0 && w.k == 0) c.b.n_outer[s] += 1;
   dev_x_update<LPQ>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch);
 }
 
@@ -175,6 +174,7 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
     __syncthreads();
   }
   if (threadIdx.x == 0) {
+    c.b.n_outer[s] += 1;
     c.b.edge_n[s] = base;
     if (base == 0 && c.b.flag[s] == 0) c.b.done[s] = 1;   // "no collision if no edge links": break
     else c.b.flag[s] = 1;
@@ -194,25 +194,50 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(con
   const int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + e) * 2;
   const int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + e) * 2;
   if (eij[0] < 0) return;
+  if (!((eij[0] >= c.own_lo && eij[0] < c.own_hi) || (eij[1] >= c.own_lo && eij[1] < c.own_hi))) return;
   dev_z_update<LPQ>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
                     Wsm, gbuf[w.group_in_cta], xch);
 }
 
-// residuals, stop test, alias latch, last_hat copy: casadi/main.py:165-181.  One CTA per scenario.
-__global__ void k_residuals(const __grid_constant__ DevCtx c) {
-  const int s = blockIdx.x, N = c.N;
+// residuals, casadi/main.py:165-173: rank-local partial sums over the edges whose veh1 is owned.
+__global__ void k_res_partial(const __grid_constant__ DevCtx c) {
+  const int s = blockIdx.x;
   if (c.b.done[s]) return;
   const piadmm_params& p = c.p;
-  __shared__ double red[3][128];
-  __shared__ int decision;
+  __shared__ double red[2][128];
   const int n = c.b.edge_n[s];
   const double rho = (p.dual_mode == PIADMM_DUAL_PI_OLD && n > 0) ? c.rho_new[s] : c.b.rho_s[s];
-  double sk = 0.0, rk = 0.0, bad = 0.0;
+  double sk = 0.0, rk = 0.0;
   for (int e = threadIdx.x; e < n; e += blockDim.x) {
+    const int v0 = c.b.edge_ij[((size_t)s * c.E + e) * 2];
+    if (v0 < c.own_lo || v0 >= c.own_hi) continue;
     const double* er = c.edge_res + ((size_t)s * c.E + e) * 4;
     if (p.residual_global) { sk += sqrt(rho * rho * (er[0] + er[1])); rk += sqrt(er[2] + er[3]); }
     else { sk += 2.0 * sqrt(rho * rho * er[0]); rk += 2.0 * sqrt(er[2]); }
   }
+  red[0][threadIdx.x] = sk; red[1][threadIdx.x] = rk;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o >= 1; o >>= 1) {
+    if ((int)threadIdx.x < o) {
+      red[0][threadIdx.x] += red[0][threadIdx.x + o];
+      red[1][threadIdx.x] += red[1][threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { c.b.res_part[(size_t)s * 2] = red[1][0]; c.b.res_part[(size_t)s * 2 + 1] = red[0][0]; }
+}
+
+// stop test, alias latch, last_hat copy: casadi/main.py:174-181.  One CTA per scenario; res_part holds
+// the (all-reduced) sums.
+__global__ void k_res_decide(const __grid_constant__ DevCtx c) {
+  const int s = blockIdx.x, N = c.N;
+  if (c.b.done[s]) return;
+  const piadmm_params& p = c.p;
+  __shared__ double red[128];
+  __shared__ int decision;
+  const int n = c.b.edge_n[s];
+  const double rho = (p.dual_mode == PIADMM_DUAL_PI_OLD && n > 0) ? c.rho_new[s] : c.b.rho_s[s];
+  double bad = 0.0;
   if (p.stop_dist_test) {
     for (int t = threadIdx.x; t < c.V * c.D; t += blockDim.x) {
       const int i = t / c.D, j = c.b.nbr[(size_t)s * c.V * c.D + t];
@@ -225,22 +250,18 @@ __global__ void k_residuals(const __grid_constant__ DevCtx c) {
       if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) bad = 1.0;
     }
   }
-  red[0][threadIdx.x] = sk; red[1][threadIdx.x] = rk; red[2][threadIdx.x] = bad;
+  red[threadIdx.x] = bad;
   __syncthreads();
   for (int o = blockDim.x / 2; o >= 1; o >>= 1) {
-    if ((int)threadIdx.x < o) {
-      red[0][threadIdx.x] += red[0][threadIdx.x + o];
-      red[1][threadIdx.x] += red[1][threadIdx.x + o];
-      red[2][threadIdx.x] += red[2][threadIdx.x + o];
-    }
+    if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
     __syncthreads();
   }
   if (threadIdx.x == 0) {
-    sk = red[0][0]; rk = red[1][0];
+    const double rk = c.b.res_part[(size_t)s * 2], sk = c.b.res_part[(size_t)s * 2 + 1];
     c.b.err_rk[(size_t)s * c.I + c.i_iter] = rk;
     c.b.err_sk[(size_t)s * c.I + c.i_iter] = sk;
     c.b.rho_s[s] = rho;
-    const bool conv = rk <= p.eps_pri && sk <= p.eps_dual && red[2][0] == 0.0;
+    const bool conv = rk <= p.eps_pri && sk <= p.eps_dual && red[0] == 0.0;
     if (conv) { c.b.curr_iter[s] = c.i_iter + 1; c.b.done[s] = 1; }
     else {
       if (p.dual_res_alias) c.b.aliased[s] = 1;
@@ -493,6 +514,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->fused_grid = 0;
   h->c.p = *p; h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
   h->c.N = p->num_ho; h->c.I = p->iter_num;
+  h->c.own_lo = 0; h->c.own_hi = V;
   h->c.round_u_scale = pow10i(p->round_u); h->c.round_edge_scale = pow10i(p->round_edge);
   h->lpq = p->num_ho <= 15 ? 16 : 32;
   auto fail = [&](cudaError_t e, const char* what) {
@@ -641,12 +663,36 @@ int piadmm_z_update(piadmm_handle* h, void* stream) {
   return PIADMM_OK;
 }
 
-int piadmm_residuals(piadmm_handle* h, void* stream) {
+int piadmm_residual_partials(piadmm_handle* h, void* stream) {
   REQUIRE_BOUND();
   cudaStream_t st = (cudaStream_t)stream;
-  k_residuals<<<h->c.S, 128, 0, st>>>(h->c);
+  k_res_partial<<<h->c.S, 128, 0, st>>>(h->c);
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
+int piadmm_residual_decide(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  cudaStream_t st = (cudaStream_t)stream;
+  k_res_decide<<<h->c.S, 128, 0, st>>>(h->c);
   LAUNCHED();
   h->c.i_iter++;
+  return PIADMM_OK;
+}
+
+int piadmm_residuals(piadmm_handle* h, void* stream) {
+  int rc = piadmm_residual_partials(h, stream);
+  return rc ? rc : piadmm_residual_decide(h, stream);
+}
+
+int piadmm_set_ownership(piadmm_handle* h, int lo, int hi) {
+  if (!h) return PIADMM_E_ARG;
+  if (lo < 0 || hi > h->c.V || lo >= hi) { h->err = "ownership range must satisfy 0 <= lo < hi <= V"; return PIADMM_E_ARG; }
+  if (h->c.p.dual_mode == PIADMM_DUAL_PI_OLD && (lo != 0 || hi != h->c.V)) {
+    h->err = "dual_mode PI_OLD mutates one scene-wide rho and is not supported with vehicle sharding";
+    return PIADMM_E_UNSUPPORTED;
+  }
+  h->c.own_lo = lo; h->c.own_hi = hi;
   return PIADMM_OK;
 }
 

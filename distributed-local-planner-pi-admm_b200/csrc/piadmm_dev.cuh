@@ -29,6 +29,7 @@ struct DevCtx {
   uint32_t* hits;                          // [S,V,ceil(V/32)] collision bit matrix
   int32_t* up_cnt;                         // [S,V] edges (i,j>i) detected per vehicle
   int i_iter;                              // outer iteration index (phase API)
+  int own_lo, own_hi;                      // vehicles x-updated by this rank (multi-GPU vehicle sharding)
   int* queue;                              // work counter of the persistent fused kernel
 };
 

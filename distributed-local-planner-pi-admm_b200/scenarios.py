@@ -44,7 +44,7 @@ def c4_scenarios(S=4096, N=15, seed=4096, step=12, T=50):
     return xt, spd, refwin
 
 
-def c3_intersection(V=64, N=30, seed=64, dt=0.1):
+def c3_intersection(V=64, N=30, seed=64, dt=0.1, r0=12.0, gap=6.0):
     """Config 3: 4-arm intersection, V/4 vehicles per arm heading to the origin."""
     rng = np.random.default_rng(seed)
     per = V // 4
@@ -54,7 +54,7 @@ def c3_intersection(V=64, N=30, seed=64, dt=0.1):
     for arm in range(4):
         ang = arm * np.pi / 2                    # position angle of the arm
         for q in range(per):
-            r = 12.0 + 6.0 * q + rng.uniform(-0.5, 0.5)
+            r = r0 + gap * q + rng.uniform(-0.5, 0.5)
             v = speeds[(arm + q) % 3]
             px, py = r * np.cos(ang), r * np.sin(ang)
             th = np.arctan2(-py, -px)            # heading to the origin

@@ -103,6 +103,17 @@ class PIADMMSolver:
     def update_residuals(self):
         self._check(self.lib.piadmm_residuals(self._h, self._stream()), "piadmm_residuals")
 
+    def set_ownership(self, lo: int, hi: int):
+        """Vehicle sharding: this instance x-updates vehicles [lo, hi) only (see parallel.py)."""
+        self._check(self.lib.piadmm_set_ownership(self._h, int(lo), int(hi)), "piadmm_set_ownership")
+        self.own = (int(lo), int(hi))
+
+    def residual_partials(self):
+        self._check(self.lib.piadmm_residual_partials(self._h, self._stream()), "piadmm_residual_partials")
+
+    def residual_decide(self):
+        self._check(self.lib.piadmm_residual_decide(self._h, self._stream()), "piadmm_residual_decide")
+
     def num_active(self) -> int:
         out = C.c_int32(0)
         self._check(self.lib.piadmm_num_active(self._h, self._stream(), C.byref(out)), "piadmm_num_active")

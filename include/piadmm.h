@@ -119,6 +119,7 @@ typedef struct piadmm_buffers {
   int32_t* edge_n;       /* [S] */
   int32_t* edge_ij;      /* [S,E,2] (veh1 < veh2), sorted */
   int32_t* edge_slot;    /* [S,E,2] slot of veh2 in veh1's table, slot of veh1 in veh2's table */
+  double* res_part;      /* [S,2] rank-local partial residual sums (rk, sk) of the current outer iteration */
   /* plant */
   double* xt_next;       /* [S,V,3] */
 } piadmm_buffers;
@@ -142,7 +143,13 @@ int piadmm_begin_step(piadmm_handle* h, void* stream);   /* casadi/main.py:52-72
 int piadmm_x_update(piadmm_handle* h, void* stream);
 int piadmm_detect_edges(piadmm_handle* h, void* stream);
 int piadmm_z_update(piadmm_handle* h, void* stream);     /* edge problems + dual / PI update */
-int piadmm_residuals(piadmm_handle* h, void* stream);    /* histories, stop flags, alias latch */
+int piadmm_residuals(piadmm_handle* h, void* stream);    /* histories, stop flags, alias latch (= partials + decide) */
+/* vehicle-sharded (multi-GPU) form: this rank x-updates vehicles [lo,hi), solves every edge with an owned
+ * endpoint, and sums the residual terms of the edges whose veh1 it owns into res_part; the caller
+ * all-gathers pos/u rows after x_update and all-reduces (sum) res_part between the two residual calls. */
+int piadmm_set_ownership(piadmm_handle* h, int lo, int hi);
+int piadmm_residual_partials(piadmm_handle* h, void* stream);
+int piadmm_residual_decide(piadmm_handle* h, void* stream);
 int piadmm_num_active(piadmm_handle* h, void* stream, int32_t* host_out); /* scenarios with done==0 (syncs) */
 int piadmm_step(piadmm_handle* h, void* stream);         /* begin_step + all outer iterations, persistent kernel */
 int piadmm_plant_step(piadmm_handle* h, void* stream);

@@ -52,12 +52,9 @@ def _new_rho(rho, rp, rd, n_p, n_d):
     return min(max(rn, 1e-6), 1e6)
 
 
-def solve_box_qp(P, q, s: InnerSettings):
-    """min 1/2 x'Px + q'x  s.t.  A x >= l  with the reference's 4N-2 rows
-    (casadi/PI_ADMM_class.py:172-192).  Returns x, info(dict)."""
+def solve_dense_qp(P, q, A, l, u, s: InnerSettings):
+    """min 1/2 x'Px + q'x  s.t.  l <= A x <= u  (dense OSQP iteration, uniform rho).  Returns x, y, info."""
     n = len(q)
-    A = constraint_matrix(n)
-    l = constraint_lower(n)
     AtA = A.T @ A
     x = np.zeros(n); z = np.zeros(len(l)); y = np.zeros(len(l))
     rho = s.rho0
@@ -70,7 +67,7 @@ def solve_box_qp(P, q, s: InnerSettings):
         zt = A @ xt
         x = s.alpha * xt + (1 - s.alpha) * x
         zr = s.alpha * zt + (1 - s.alpha) * z
-        zn = np.maximum(zr + y / rho, l)
+        zn = np.minimum(np.maximum(zr + y / rho, l), u)
         y = y + rho * (zr - zn)
         z = zn
         if it % s.check == 0:
@@ -87,7 +84,17 @@ def solve_box_qp(P, q, s: InnerSettings):
                     rho = rn
                     K = np.linalg.inv(P + s.sigma * np.eye(n) + rho * AtA)
                     nref += 1
-    return x, dict(iters=it, status=status, refactors=nref, rho=rho)
+    return x, y, dict(iters=it, status=status, refactors=nref, rho=rho)
+
+
+def solve_box_qp(P, q, s: InnerSettings):
+    """min 1/2 x'Px + q'x  s.t.  A x >= l  with the reference's 4N-2 rows
+    (casadi/PI_ADMM_class.py:172-192, passed to OSQP as l = -b, u = +inf).  Returns x, info(dict)."""
+    n = len(q)
+    l = constraint_lower(n)
+    x, y, info = solve_dense_qp(P, q, constraint_matrix(n), l, np.full(len(l), np.inf), s)
+    info["y"] = y
+    return x, info
 
 
 def solve_edge_pair(H, q, a, c, beta, s: InnerSettings):

@@ -106,3 +106,62 @@ def test_create_rejects_bad_arguments():
     with pytest.raises(pa.PIADMMError):
         PIADMMSolver(p, S=1, V=4, D=1)          # al_all needs D >= V-1
     assert lib.piadmm_max_edges(2, 1) == 1
+
+
+# ------------------------------------------------------------------ generic V (configs 3 / 5 shapes)
+def _generic_params(N, inner="default", **kw):
+    p = make_params("matlab_pi", inner, num_ho=N, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5,
+                    al_all=0, iter_num=12)
+    p.update(**kw)
+    return p
+
+
+@pytest.mark.parametrize("V,N,D,r0,gap", [(16, 15, 8, 7.0, 5.0), (64, 30, 8, 12.0, 6.0), (12, 20, 4, 12.0, 6.0),
+                                          (32, 15, 8, 8.0, 4.0)])
+def test_coupled_intersection_matches_oracle(V, N, D, r0, gap):
+    """Config-3-shaped scene (4-arm intersection, active-edge AL term, dual=pi) through the phase kernels."""
+    from pi_admm_b200.scenarios import c3_intersection
+    p = _generic_params(N)
+    xt, spd, refwin = c3_intersection(V=V, N=N, r0=r0, gap=gap)
+    ref = ctwin.step(p, xt, spd, refwin, D=D)
+    sol = PIADMMSolver(p, S=1, V=V, D=D)
+    sol.setup(xt, spd, refwin)
+    sol.iterate()
+    sol.plant_step()
+    got = sol.to_numpy()
+    assert ref["n_edge_solves"].sum() > 0 and (ref["status"] & 4).sum() == 0
+    for k in ("edge_ij", "edge_slot"):
+        n = int(ref["edge_n"][0])
+        assert np.array_equal(got[k][0, :n], ref[k][0, :n])
+    assert_same(got, ref, what=f"c3 V={V} N={N}")
+
+
+def test_vehicle_sharded_lockstep_equals_single(monkeypatch):
+    """Config-5 algorithm (vehicle sharding, all-gather of pos, redundant cross-rank edges, all-reduce of
+    the residual sums) emulated with 2 and 4 'ranks' on one GPU == the unsharded run == the oracle."""
+    from pi_admm_b200.scenarios import c3_intersection
+    from pi_admm_b200.parallel import iterate_lockstep, shard_range
+    V, N, D = 32, 15, 8
+    p = _generic_params(N)
+    xt, spd, refwin = c3_intersection(V=V, N=N, r0=8.0, gap=4.0)
+    ref = ctwin.step(p, xt, spd, refwin, D=D)
+    assert ref["n_edge_solves"].sum() > 100 and ref["status"][0] == 0
+    for world in (2, 4):
+        sols = []
+        for r in range(world):
+            s = PIADMMSolver(p, S=1, V=V, D=D)
+            s.setup(xt, spd, refwin)
+            s.set_ownership(*shard_range(V, r, world))
+            sols.append(s)
+        iterate_lockstep(sols)
+        for r, s in enumerate(sols):
+            s.plant_step()
+            got = s.to_numpy()
+            lo, hi = s.own
+            assert np.array_equal(got["n_outer"], ref["n_outer"]) and np.array_equal(got["curr_iter"], ref["curr_iter"])
+            assert np.array_equal(got["nbr"], ref["nbr"]) and np.array_equal(got["edge_n"], ref["edge_n"])
+            for k in ("u", "pos", "xt_next", "err_rk", "err_sk"):
+                assert rel_err(got[k], ref[k]) <= 1e-6, (world, r, k)
+            for k in ("hat", "dual"):     # slots of the owned vehicles are authoritative on this rank
+                assert rel_err(got[k][:, lo:hi], ref[k][:, lo:hi]) <= 1e-6, (world, r, k)
+            s.close()
