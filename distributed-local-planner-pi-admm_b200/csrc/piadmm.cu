@@ -61,6 +61,7 @@ __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
     c.b.status[t] = 0; c.b.veh_inner[t] = 0; c.b.edge_inner[t] = 0; c.b.n_veh_solves[t] = 0;
     c.b.n_edge_solves[t] = 0; c.b.edge_n[t] = 0;
     c.rho_new[t] = c.b.rho_s[t];
+    c.dist_bad[t] = 0;
   }
 }
 
@@ -69,16 +70,33 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(con
   __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
-  load_W<LPQ>(c, Wsm);
   Who<LPQ> w;
   const long a = (long)blockIdx.x * groups_per_cta<LPQ>() + w.group_in_cta;
   const int s = (int)(a / c.V), i = (int)(a % c.V);
   const bool valid = a < (long)c.S * c.V && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
+  if (!__syncthreads_or(valid)) return;      // nothing to do for the whole CTA: skip the table load
+  load_W<LPQ>(c, Wsm);
   if (!__any_sync(PIADMM_FULL, valid)) return;
   dev_x_update<LPQ>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch);
 }
 
-// hits[s,i,jb] bit jj = 1 iff j = 32*jb+jj > i collides with i (casadi/main.py:110-113)
+// trajectory bounding boxes [S,V,4] = (xmin, xmax, ymin, ymax): cheap reject for the O(V^2) pair test
+__global__ void k_bbox(const __grid_constant__ DevCtx c) {
+  const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= (long)c.S * c.V) return;
+  const int N = c.N;
+  const double* p = c.b.pos + (size_t)a * 2 * (N + 1);
+  double x0 = p[0], x1 = p[0], y0 = p[N + 1], y1 = p[N + 1];
+  for (int k = 1; k <= N; k++) {
+    const double x = p[k], y = p[N + 1 + k];
+    x0 = x < x0 ? x : x0; x1 = x > x1 ? x : x1; y0 = y < y0 ? y : y0; y1 = y > y1 ? y : y1;
+  }
+  double4* o = reinterpret_cast<double4*>(c.bbox) + a;
+  *o = make_double4(x0, x1, y0, y1);
+}
+
+// hits[s,i,jb] bit jj = 1 iff vehicle j = 32*jb+jj collides with i (casadi/main.py:110-113); the
+// matrix is stored symmetric (both (i,j) and (j,i)) so that rows can be scanned per vehicle.
 __global__ void k_hits(const __grid_constant__ DevCtx c) {
   const int N = c.N, words = (c.V + 31) / 32;
   const long wid = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -89,14 +107,21 @@ __global__ void k_hits(const __grid_constant__ DevCtx c) {
   if (c.b.done[s]) return;
   const int j = jb * 32 + lane;
   bool hit = false;
-  if (j > i && j < c.V) {
+  if (j != i && j < c.V) {
     hit = c.p.always_edge != 0;
-    const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
-    const double* pi = c.b.pos + (((size_t)s * c.V + i) * 2) * (N + 1);
-    const double* pj = c.b.pos + (((size_t)s * c.V + j) * 2) * (N + 1);
-    for (int k = 0; k <= N && !hit; k++) {
-      const double dx = pi[k] - pj[k], dy = pi[N + 1 + k] - pj[N + 1 + k];
-      hit = dx * dx + dy * dy < thr;
+    if (!hit) {
+      const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
+      const double4 bi = reinterpret_cast<const double4*>(c.bbox)[(size_t)s * c.V + i];
+      const double4 bj = reinterpret_cast<const double4*>(c.bbox)[(size_t)s * c.V + j];
+      const double gx = fmax(0.0, fmax(bi.x - bj.y, bj.x - bi.y)), gy = fmax(0.0, fmax(bi.z - bj.w, bj.z - bi.w));
+      if (gx * gx + gy * gy < thr) {           // boxes closer than the threshold: exact test
+        const double* pi = c.b.pos + (((size_t)s * c.V + i) * 2) * (N + 1);
+        const double* pj = c.b.pos + (((size_t)s * c.V + j) * 2) * (N + 1);
+        for (int k = 0; k <= N && !hit; k++) {
+          const double dx = pi[k] - pj[k], dy = pi[N + 1 + k] - pj[N + 1 + k];
+          hit = dx * dx + dy * dy < thr;
+        }
+      }
     }
   }
   const unsigned m = __ballot_sync(PIADMM_FULL, hit);
@@ -111,18 +136,20 @@ __global__ void k_slots(const __grid_constant__ DevCtx c) {
   const int s = (int)(a / c.V), i = (int)(a % c.V), words = (c.V + 31) / 32;
   if (c.b.done[s]) return;
   int32_t* nb = c.b.nbr + a * c.D;
-  const uint32_t* H = c.hits + (size_t)s * c.V * words;
+  const uint32_t* H = c.hits + (size_t)a * words;
   int up = 0;
   bool overflow = false;
-  for (int j = 0; j < c.V; j++) {
-    if (j == i) continue;
-    const int lo = j < i ? j : i, hi = j < i ? i : j;
-    if (!((H[(size_t)lo * words + (hi >> 5)] >> (hi & 31)) & 1u)) continue;
-    int slot = -1;
-    for (int d = 0; d < c.D; d++) if (nb[d] == j) { slot = d; break; }
-    if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = j; slot = d; break; }
-    if (slot < 0) { overflow = true; continue; }
-    if (j > i) up++;
+  for (int w = 0; w < words; w++) {
+    uint32_t m = H[w];
+    while (m) {
+      const int j = w * 32 + __ffs(m) - 1;
+      m &= m - 1;
+      int slot = -1;
+      for (int d = 0; d < c.D; d++) if (nb[d] == j) { slot = d; break; }
+      if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = j; slot = d; break; }
+      if (slot < 0) { overflow = true; continue; }
+      if (j > i) up++;
+    }
   }
   c.up_cnt[a] = up;
   if (overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
@@ -151,8 +178,12 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
     int n = base + scan[threadIdx.x] - cnt;
     if (i < c.V && cnt > 0) {
       const int32_t* nbi = c.b.nbr + ((size_t)s * c.V + i) * c.D;
-      for (int j = i + 1; j < c.V; j++) {
-        if (!((H[(size_t)i * words + (j >> 5)] >> (j & 31)) & 1u)) continue;
+      for (int wd = (i + 1) >> 5; wd < words; wd++) {
+       uint32_t m = H[(size_t)i * words + wd];
+       if (wd == ((i + 1) >> 5)) m &= ~0u << ((i + 1) & 31);       // only j > i
+       while (m) {
+        const int j = wd * 32 + __ffs(m) - 1;
+        m &= m - 1;
         const int32_t* nbj = c.b.nbr + ((size_t)s * c.V + j) * c.D;
         int di = -1, dj = -1;
         for (int d = 0; d < c.D; d++) { if (nbi[d] == j) di = d; if (nbj[d] == i) dj = d; }
@@ -167,6 +198,7 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
           eij[0] = i; eij[1] = j; esl[0] = di; esl[1] = dj;
         }
         n++;
+       }
       }
     }
     __syncthreads();
@@ -186,15 +218,16 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(con
   __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
-  load_W<LPQ>(c, Wsm);
   Who<LPQ> w;
   const long pidx = (long)blockIdx.x * pairs_per_cta<LPQ>() + w.pair_in_cta;
   const int s = (int)(pidx / c.E), e = (int)(pidx % c.E);
-  if (s >= c.S || c.b.done[s] || e >= c.b.edge_n[s]) return;   // uniform per pair
+  bool valid = s < c.S && !c.b.done[s] && e < c.b.edge_n[s];     // uniform per pair
   const int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + e) * 2;
   const int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + e) * 2;
-  if (eij[0] < 0) return;
-  if (!((eij[0] >= c.own_lo && eij[0] < c.own_hi) || (eij[1] >= c.own_lo && eij[1] < c.own_hi))) return;
+  if (valid) valid = eij[0] >= 0 && ((eij[0] >= c.own_lo && eij[0] < c.own_hi) || (eij[1] >= c.own_lo && eij[1] < c.own_hi));
+  if (!__syncthreads_or(valid)) return;      // empty CTA: skip the table load
+  load_W<LPQ>(c, Wsm);
+  if (!valid) return;
   dev_z_update<LPQ>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
                     Wsm, gbuf[w.group_in_cta], xch);
 }
@@ -233,35 +266,16 @@ __global__ void k_res_decide(const __grid_constant__ DevCtx c) {
   const int s = blockIdx.x, N = c.N;
   if (c.b.done[s]) return;
   const piadmm_params& p = c.p;
-  __shared__ double red[128];
   __shared__ int decision;
   const int n = c.b.edge_n[s];
   const double rho = (p.dual_mode == PIADMM_DUAL_PI_OLD && n > 0) ? c.rho_new[s] : c.b.rho_s[s];
-  double bad = 0.0;
-  if (p.stop_dist_test) {
-    for (int t = threadIdx.x; t < c.V * c.D; t += blockDim.x) {
-      const int i = t / c.D, j = c.b.nbr[(size_t)s * c.V * c.D + t];
-      if (j <= i) continue;
-      const double* xi = c.b.xt + ((size_t)s * c.V + i) * 3;
-      const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
-      const double vi = c.b.spd[(size_t)s * c.V + i], vj = c.b.spd[(size_t)s * c.V + j];
-      const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
-      const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
-      if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) bad = 1.0;
-    }
-  }
-  red[threadIdx.x] = bad;
-  __syncthreads();
-  for (int o = blockDim.x / 2; o >= 1; o >>= 1) {
-    if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
-    __syncthreads();
-  }
   if (threadIdx.x == 0) {
     const double rk = c.b.res_part[(size_t)s * 2], sk = c.b.res_part[(size_t)s * 2 + 1];
     c.b.err_rk[(size_t)s * c.I + c.i_iter] = rk;
     c.b.err_sk[(size_t)s * c.I + c.i_iter] = sk;
     c.b.rho_s[s] = rho;
-    const bool conv = rk <= p.eps_pri && sk <= p.eps_dual && red[0] == 0.0;
+    const bool conv = rk <= p.eps_pri && sk <= p.eps_dual && c.dist_bad[s] == 0;
+    c.dist_bad[s] = 0;
     if (conv) { c.b.curr_iter[s] = c.i_iter + 1; c.b.done[s] = 1; }
     else {
       if (p.dual_res_alias) c.b.aliased[s] = 1;
@@ -272,9 +286,31 @@ __global__ void k_res_decide(const __grid_constant__ DevCtx c) {
   }
   __syncthreads();
   if (!decision) {
-    const size_t o = (size_t)s * c.V * c.D * 2 * (N + 1), cnt = (size_t)c.V * c.D * 2 * (N + 1);
-    for (size_t t = threadIdx.x; t < cnt; t += blockDim.x) c.b.last_hat[o + t] = c.b.hat[o + t];
+    // last_iter_hat_pos = hat_pos_old: only the slots of this iteration's edges changed
+    const int per = 2 * (N + 1);
+    for (int t = threadIdx.x; t < n * 2 * per; t += blockDim.x) {
+      const int e = t / (2 * per), side = (t / per) & 1, el = t % per;
+      const int v = c.b.edge_ij[((size_t)s * c.E + e) * 2 + side];
+      if (v < 0) continue;
+      const size_t o = ((((size_t)s * c.V + v) * c.D) + c.b.edge_slot[((size_t)s * c.E + e) * 2 + side]) * per + el;
+      c.b.last_hat[o] = c.b.hat[o];
+    }
   }
+}
+
+// MATLAB :202 extra stop condition, evaluated over every allocated neighbour slot (all CTAs of the grid)
+__global__ void k_dist_test(const __grid_constant__ DevCtx c) {
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long)c.S * c.V * c.D) return;
+  const int s = (int)(t / ((long)c.V * c.D)), i = (int)((t / c.D) % c.V), j = c.b.nbr[t];
+  if (j <= i || c.b.done[s]) return;
+  const piadmm_params& p = c.p;
+  const double* xi = c.b.xt + ((size_t)s * c.V + i) * 3;
+  const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
+  const double vi = c.b.spd[(size_t)s * c.V + i], vj = c.b.spd[(size_t)s * c.V + j];
+  const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
+  const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
+  if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) c.dist_bad[s] = 1;
 }
 
 __global__ void k_count_active(const __grid_constant__ DevCtx c, int* out) {
@@ -551,6 +587,9 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMalloc(&h->c.rho_new, sizeof(double) * S)) != cudaSuccess) return fail(ce, "rho_new");
   if ((ce = cudaMalloc(&h->c.hits, sizeof(uint32_t) * (size_t)S * V * words)) != cudaSuccess) return fail(ce, "hits");
   if ((ce = cudaMalloc(&h->c.up_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "up_cnt");
+  if ((ce = cudaMalloc(&h->c.bbox, sizeof(double) * 4 * (size_t)S * V)) != cudaSuccess) return fail(ce, "bbox");
+  if ((ce = cudaMalloc(&h->c.dist_bad, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
+  if ((ce = cudaMemset(h->c.dist_bad, 0, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
   if ((ce = cudaMalloc(&h->d_count, sizeof(int))) != cudaSuccess) return fail(ce, "count");
   if ((ce = cudaMalloc(&h->d_queue, sizeof(int))) != cudaSuccess) return fail(ce, "queue");
   h->c.queue = h->d_queue;
@@ -570,7 +609,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad);
   cudaFree(h->d_count); cudaFree(h->d_queue);
   delete h;
 }
@@ -639,6 +678,8 @@ int piadmm_detect_edges(piadmm_handle* h, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   const int words = (h->c.V + 31) / 32;
   const long warps = (long)h->c.S * h->c.V * words;
+  k_bbox<<<(unsigned)(((long)h->c.S * h->c.V + 127) / 128), 128, 0, st>>>(h->c);
+  LAUNCHED();
   k_hits<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
   const long agents = (long)h->c.S * h->c.V;
@@ -674,6 +715,11 @@ int piadmm_residual_partials(piadmm_handle* h, void* stream) {
 int piadmm_residual_decide(piadmm_handle* h, void* stream) {
   REQUIRE_BOUND();
   cudaStream_t st = (cudaStream_t)stream;
+  if (h->c.p.stop_dist_test) {
+    const long slots = (long)h->c.S * h->c.V * h->c.D;
+    k_dist_test<<<(unsigned)((slots + 255) / 256), 256, 0, st>>>(h->c);
+    LAUNCHED();
+  }
   k_res_decide<<<h->c.S, 128, 0, st>>>(h->c);
   LAUNCHED();
   h->c.i_iter++;

@@ -28,6 +28,8 @@ struct DevCtx {
   double* rho_new;                         // [S] penalty chosen by the last edge (dual_mode PI_OLD)
   uint32_t* hits;                          // [S,V,ceil(V/32)] collision bit matrix
   int32_t* up_cnt;                         // [S,V] edges (i,j>i) detected per vehicle
+  double* bbox;                            // [S,V,4] trajectory bounding boxes (xmin,xmax,ymin,ymax)
+  int* dist_bad;                           // [S] MATLAB :202 distance stop test failed
   int i_iter;                              // outer iteration index (phase API)
   int own_lo, own_hi;                      // vehicles x-updated by this rank (multi-GPU vehicle sharding)
   int* queue;                              // work counter of the persistent fused kernel

@@ -165,3 +165,34 @@ def test_vehicle_sharded_lockstep_equals_single(monkeypatch):
             for k in ("hat", "dual"):     # slots of the owned vehicles are authoritative on this rank
                 assert rel_err(got[k][:, lo:hi], ref[k][:, lo:hi]) <= 1e-6, (world, r, k)
             s.close()
+
+
+# ------------------------------------------------------------------ drop-in script vs golden fixtures
+@pytest.mark.parametrize("fast", [False, True])
+def test_dropin_main_reproduces_golden(fast):
+    """pi_admm_b200/main_intersection.py (the casadi/main.py shaped driver over the class mirror)
+    against tests/golden/c1_python_current_default.json (frozen oracle output)."""
+    import json, os
+    from pi_admm_b200.main_intersection import run
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "c1_python_current_default.json")))
+    out = run(semantics="python_current", inner="osqp_default", fast=fast)
+    assert [int(v) for v in out["iter_his"]] == g["iter_his"]
+    assert out["n_outer"] == g["n_outer"]
+    assert np.allclose(np.array(out["x_vec"]), np.array(g["x_vec"]), rtol=1e-6, atol=1e-9)
+    assert np.allclose(np.array(out["u_vec"]), np.array(g["u_vec"]), rtol=1e-6, atol=1e-9)
+    for a, b in zip(out["err_rk"], g["err_rk"]):
+        assert np.allclose(a, np.array(b), rtol=1e-6, atol=1e-6)
+    assert out["launches"] > 0
+
+
+def test_class_mirror_step_and_mutable_rho():
+    from pi_admm_b200.PI_ADMM_class import PI_ADMM_CASADI
+    P = PI_ADMM_CASADI(semantics="matlab_pi", eps_pri=1.0, eps_dual=1.0)
+    xt = np.array([[-5.2, 0, 0], [0, 10.4, -np.pi / 2]])
+    r1 = P.step(12, xt)
+    P.param.rho = 3.5                      # scripts mutate param.rho (casadi_old_PI_ADMM/main.py:137)
+    r2 = P.step(12, xt)
+    p = P.abi_params()
+    ref = ctwin.step(p, xt[None], np.array([[4.0, 8.0]]), P.ref_window(12)[None])
+    assert r2["n_outer"] == int(ref["n_outer"][0]) and rel_err(r2["primal_u"], ref["u"][0]) <= 1e-6
+    assert rel_err(r1["primal_u"], r2["primal_u"]) > 1e-6
