@@ -303,7 +303,7 @@ def cpu_baseline(p, xt, spd, refwin, S, N):
     cores = ctwin.max_threads()
     ctwin.step(p, xt, spd, refwin, arrs=arrs)
     t0 = time.perf_counter(); reps = 0; solves = 0
-    while time.perf_counter() - t0 < 10.0 and reps < 200:
+    while time.perf_counter() - t0 < 10.0 and reps < 2000:
         r = ctwin.step(p, xt, spd, refwin, arrs=arrs)
         solves += int(r["n_veh_solves"].sum()); reps += 1
     dt = time.perf_counter() - t0
