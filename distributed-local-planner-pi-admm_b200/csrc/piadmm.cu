@@ -31,7 +31,7 @@ __device__ __forceinline__ void pair_sync() {
 
 template <int LPQ>
 __device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) {
-  for (int t = threadIdx.x; t < 2 * LPQ * LPQ; t += blockDim.x) Wsm[t] = c.W[t];
+  for (int t = threadIdx.x; t < PIADMM_NTAB * LPQ * LPQ; t += blockDim.x) Wsm[t] = c.W[t];
   __syncthreads();
 }
 
@@ -67,7 +67,7 @@ __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
 
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(const __grid_constant__ DevCtx c) {
-  __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
+  __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
   Who<LPQ> w;
@@ -215,7 +215,7 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
 
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(const __grid_constant__ DevCtx c) {
-  __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
+  __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
   Who<LPQ> w;
@@ -340,7 +340,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
 
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
-  __shared__ __align__(16) double Wsm[2 * LPQ * LPQ];
+  __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
   __shared__ int s_next;
@@ -561,7 +561,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaSetDevice(device)) != cudaSuccess) return fail(ce, "cudaSetDevice");
   // W = M'M, zero padded to LPQ x LPQ
   const int L = h->lpq, N = p->num_ho;
-  double* W = (double*)calloc((size_t)2 * L * L, sizeof(double));
+  double* W = (double*)calloc((size_t)PIADMM_NTAB * L * L, sizeof(double));
   for (int i = 0; i < N; i++)
     for (int j = 0; j < N; j++) {
       double s = 0;
@@ -576,8 +576,31 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     for (int a = 0; a < 3; a++)
       for (int b = 0; b < 3; b++) W[(size_t)L * L + (r + a) * L + (r + b)] += w[a] * w[b];
   }
-  ce = cudaMalloc(&h->d_W, sizeof(double) * 2 * L * L);
-  if (ce == cudaSuccess) ce = cudaMemcpy(h->d_W, W, sizeof(double) * 2 * L * L, cudaMemcpyHostToDevice);
+  {   // position-space tables of the edge problem: B1 = D'D, B2 = D' T D, T = A'A = 2I + 2 D1'D1
+    double* Dm = (double*)calloc((size_t)N * N, sizeof(double));
+    double* Tm = (double*)calloc((size_t)N * N, sizeof(double));
+    double* TD = (double*)calloc((size_t)N * N, sizeof(double));
+    for (int j = 0; j < N; j++) {
+      Dm[j * N + j] = 1.0;
+      if (j <= N - 2) { if (j >= 1) Dm[j * N + j - 1] = -2.0; if (j >= 2) Dm[j * N + j - 2] = 1.0; }
+    }
+    for (int j = 0; j < N; j++) Tm[j * N + j] = 2.0;
+    for (int r = 0; r + 1 < N; r++) {
+      Tm[r * N + r] += 2.0; Tm[(r + 1) * N + r + 1] += 2.0; Tm[r * N + r + 1] -= 2.0; Tm[(r + 1) * N + r] -= 2.0;
+    }
+    for (int i = 0; i < N; i++)
+      for (int j = 0; j < N; j++) { double s = 0; for (int m = 0; m < N; m++) s += Tm[i * N + m] * Dm[m * N + j]; TD[i * N + j] = s; }
+    for (int i = 0; i < N; i++)
+      for (int j = 0; j < N; j++) {
+        double s1 = 0, s2 = 0;
+        for (int m = 0; m < N; m++) { s1 += Dm[m * N + i] * Dm[m * N + j]; s2 += Dm[m * N + i] * TD[m * N + j]; }
+        W[(size_t)2 * L * L + i * L + j] = s1;
+        W[(size_t)3 * L * L + i * L + j] = s2;
+      }
+    free(Dm); free(Tm); free(TD);
+  }
+  ce = cudaMalloc(&h->d_W, sizeof(double) * PIADMM_NTAB * L * L);
+  if (ce == cudaSuccess) ce = cudaMemcpy(h->d_W, W, sizeof(double) * PIADMM_NTAB * L * L, cudaMemcpyHostToDevice);
   free(W);
   if (ce != cudaSuccess) return fail(ce, "W upload");
   h->c.W = h->d_W;

@@ -142,50 +142,55 @@ __device__ __forceinline__ double round_scale(double x, double scale) {
 }
 
 // ------------------------------------------------------------------ K^-1 in registers
-// Build K = cI*I + c2*D2'D2 + cW*W + cT*T (row k in a[0..LPQ)) and invert it in place by
-// Gauss-Jordan without pivoting (K is SPD).  rowbuf: LPQ doubles of shared memory per group.
+// acc += a*b on the lanes where pred != 0 (one predicated DFMA)
+__device__ __forceinline__ void fma_if(double& acc, double a, double b, int pred) {
+  asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %3, 0;\n\t@p fma.rn.f64 %0, %1, %2, %0;\n\t}" : "+d"(acc) : "d"(a), "d"(b), "r"(pred));
+}
+
+// One step of the in-place Gauss-Jordan inversion of an SPD matrix held one row per lane.
 //
 // The elimination loop is ROLLED (small code, no instruction-cache thrash) and still uses only
 // compile-time register indices: every step rotates the row by one position, so the pivot column
 // is always a[0]; after LPQ steps the rotation has come full circle.  Padded rows/columns (>= N)
 // are identity, for them a step is an exact no-op.
-// a = 0 on the lanes where `me` holds (one predicated CS2R instead of two FSEL)
-__device__ __forceinline__ void zero_if(double& a, int me) {
-  asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %1, 0;\n\t@p mov.f64 %0, 0d0000000000000000;\n\t}" : "+d"(a) : "r"(me));
-}
-
+//   pivot lane p : publishes its raw row (rowbuf[0] = 1/pivot) and clears its registers, so that the
+//                  common update a[j-1] = nf*row[j] + a[j] yields piv*row[j] exactly (nf = piv);
+//   other lanes  : nf = -a[0]*piv:  a[j-1] = a[j] - a[0]*piv*row[j],  a[LPQ-1] = -a[0]*piv.
 template <int LPQ>
 __device__ __forceinline__ void gj_step(double (&a)[LPQ], int k, int p, double* rowbuf) {
-  const int me = k == p;
-  double f = a[0];
-  if (me) {
-    const double piv = 1.0 / f;
-    rowbuf[0] = piv;
+  const double f = a[0];
+  if (k == p) {
+    rowbuf[0] = 1.0 / f;
 #pragma unroll
-    for (int j = 1; j < LPQ; j++) rowbuf[j] = a[j] * piv;
+    for (int j = 1; j < LPQ; j++) rowbuf[j] = a[j];
+#pragma unroll
+    for (int j = 0; j < LPQ; j++) a[j] = 0.0;
   }
   __syncwarp();
-  // lane p: new row = the scaled row itself = 0 - (-1) * row ; other lanes: a - a[0] * row
+  const double piv = rowbuf[0];
+  const double nf = (k == p) ? piv : -f * piv;
 #pragma unroll
-  for (int j = 0; j < LPQ; j++) zero_if(a[j], me);
-  f = me ? -1.0 : f;
-  const double nf = -f;
-#pragma unroll
-  for (int j = 0; j < LPQ; j += 2) {             // in place: a[j-1] <- a[j] - f*row[j], a[LPQ-1] <- -f*row[0]
+  for (int j = 0; j < LPQ; j += 2) {             // in place, increasing j: a[j-1] <- a[j] + nf*row[j]
     const double2 r = *reinterpret_cast<const double2*>(rowbuf + j);
     if (j > 0) a[j - 1] = fma(nf, r.x, a[j]);
     a[j] = fma(nf, r.y, a[j + 1]);
   }
-  a[LPQ - 1] = nf * rowbuf[0];
+  a[LPQ - 1] = nf;
   __syncwarp();
 }
 
+// Shared-memory tables (zero padded LPQ x LPQ, symmetric, read column-wise = conflict free):
+//   0: W  = M'M           1: D2'D2          (vehicle problem, steering space)
+//   2: B1 = D'D           3: B2 = D'(A'A)D  (edge problem, position space; D = second difference map x = D t)
+#define PIADMM_NTAB 4
+
+// Vehicle problem: K = cI*I + c2*D2'D2 + cW*W + cT*T, T = A'A = 2I + 2 D1'D1 (tridiagonal: diag 4 at the
+// ends / 6 inside, off-diagonal -2); inverted in place.  rowbuf: LPQ doubles of shared memory per group.
 template <int LPQ>
-__device__ __forceinline__ void build_Kinv(double (&a)[LPQ], int N, int k, double cI, double c2, double cW,
-                                           double cT, const double* __restrict__ Wsm, double* rowbuf) {
-  // Wsm: two symmetric zero-padded LPQ x LPQ tables, W = M'M and D2'D2 (read column-wise: conflict
-  // free).  T = A'A = 2I + 2 D1'D1 is tridiagonal: diag 4 (ends) / 6, off-diagonal -2.
-  const double* D2sm = Wsm + LPQ * LPQ;
+__device__ __forceinline__ void build_Kinv_vehicle(double (&a)[LPQ], int N, int k, double cI, double c2, double cW,
+                                                   double cT, const double* __restrict__ tabs, double* rowbuf) {
+  const double* Wsm = tabs;
+  const double* D2sm = tabs + LPQ * LPQ;
   const double tdiag = (k == 0 || k == N - 1) ? 4.0 : 6.0;
 #pragma unroll
   for (int j = 0; j < LPQ; j++) {
@@ -199,6 +204,27 @@ __device__ __forceinline__ void build_Kinv(double (&a)[LPQ], int N, int k, doubl
   for (int p = 0; p < LPQ; p++) gj_step<LPQ>(a, k, p, rowbuf);
 }
 
+// Edge half problem in position space: K_t = c1*B1 + cT*B2 + cS*I_s, I_s = identity on lanes <= N-2.
+template <int LPQ>
+__device__ __forceinline__ void build_Kinv_edge(double (&a)[LPQ], int N, int k, double c1, double cT, double cS,
+                                                const double* __restrict__ tabs, double* rowbuf) {
+  const double* B1 = tabs + 2 * LPQ * LPQ;
+  const double* B2 = tabs + 3 * LPQ * LPQ;
+#pragma unroll
+  for (int j = 0; j < LPQ; j++) {
+    double v = fma(c1, B1[j * LPQ + k], cT * B2[j * LPQ + k]);
+    if (j == k && k <= N - 2) v += cS;
+    if (k >= N) v = (j == k) ? 1.0 : 0.0;
+    a[j] = v;
+  }
+#pragma unroll 1
+  for (int p = 0; p < LPQ; p++) gj_step<LPQ>(a, k, p, rowbuf);
+}
+
+// sum_{L>=j} (L-j+1) v_L  (= M'(.) for a vector given on the position rows), v = 0 on masked lanes
+template <int LPQ>
+__device__ __forceinline__ double suffix2(double v, int k) { return incl_suffix<LPQ>(incl_suffix<LPQ>(v, k), k); }
+
 // ------------------------------------------------------------------ inner OSQP-style ADMM
 struct InnerOut {
   double x;
@@ -208,39 +234,54 @@ struct InnerOut {
 
 // One (edge=false) or two coupled (edge=true) half problems per group; see oracle/solver.py.
 //   P = pI*I + p2*D2'D2 + pW*W ; box rows A = [I;-I;-D1;D1] >= -[pi/6,pi/6,pi/9,pi/9]
-//   edge: extra rows s = (M x)_{1..N} (lane L <-> row L+1) coupled with the partner by the prox of
+//   edge: extra position rows s = (M x)_{1..N}, coupled with the partner by the prox of
 //         beta*max(0, c - a0*s0 - a1*s1).  `edge` must be uniform over the pair.
-// rhsbuf: LPQ doubles of shared memory per group, xch: 64 doubles per pair.
+//
+// The edge half problem is iterated in POSITION SPACE: unknown t with x = D t,
+//   t_L = (M x)_{L+2} (L <= N-2),  t_{N-1} = x_{N-1};   x_j = t_j - 2 t_{j-1} + t_{j-2} (j <= N-2).
+// It is the same iteration in other coordinates (K_t = D' K_x D, rhs_t = D' rhs_x, x~ = D t~): identical
+// iterates up to rounding, but M and M' (two chained warp scans each) drop out of the loop: the position
+// rows become the identity (lane L <-> trajectory index L+2; lane N-1 holds the all-zero row of index 1)
+// and D, D' are 3-point stencils.  Termination is still evaluated on the steering-space residuals.
+// cvec follows that lane layout.  rhsbuf: LPQ doubles of shared memory per group, xch: 64 doubles per pair.
 template <int LPQ>
 __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, int k, int half, bool edge,
-                                             double pI, double p2, double pW, double q, double a0, double a1,
-                                             double cvec, const double* __restrict__ Wsm, double* rhsbuf,
-                                             double* xch) {
+                                                double pI, double p2, double pW, double q, double a0, double a1,
+                                                double cvec, const double* __restrict__ tabs, double* rhsbuf,
+                                                double* xch) {
   const double al = ip.in_alpha, sg = ip.in_sigma, oma = 1.0 - al;
   const double l_u = -0.52359877559829887308, l_d = -0.34906585039886591538;  // -pi/6, -pi/9
   double Kinv[LPQ];
   double rho = ip.in_rho0, irho = 1.0 / rho;
   double x = 0.0, z0 = 0.0, z1 = 0.0, z2 = 0.0, z3 = 0.0, y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0;
-  double zs = 0.0, ys = 0.0;
+  double t = 0.0, zs = 0.0, ys = 0.0;
   const double na = edge ? fma(a1, a1, a0 * a0) : 1.0;
   const double a_me = half == 0 ? a0 : a1;
   const bool inner_row = k < N - 1;
-  const double pWe = edge ? 1.0 : 0.0;       // K = P + sigma I + rho (T + [edge] W)
-  build_Kinv<LPQ>(Kinv, N, k, pI + sg, p2, pW + pWe * rho, rho, Wsm, rhsbuf);
+  const int srow = k <= N - 2;               // lane carries a real position row / a second-difference row of D
+  const int d_up1 = srow && k >= 1, d_up2 = srow && k >= 2;          // x_j = t_j - 2 t_{j-1} + t_{j-2}
+  const int d_dn1 = k + 1 <= N - 2, d_dn2 = k + 2 <= N - 2;          // (D'v)_L = v_L - 2 v_{L+1} + v_{L+2}
+  if (edge) build_Kinv_edge<LPQ>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
+  else build_Kinv_vehicle<LPQ>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
   InnerOut out;
   out.x = 0.0; out.iters = ip.in_max_iter; out.status = 1;
   bool done = false;
   int chk = ip.in_check;
 #pragma unroll 1
   for (int it = 1; it <= ip.in_max_iter; it++) {
-    // ---- rhs = sigma x - q + A'(rho z - y)
+    // ---- steering-space right-hand side  v = sigma x - q + A'(rho z - y)
     const double e = (rho * z3 - y3) - (rho * z2 - y2);
     double rhs = sg * x - q + ((rho * z0 - y0) - (rho * z1 - y1)) - e;
     add_if_ge(rhs, __shfl_up_sync(PIADMM_FULL, e, 1, LPQ), k, 1);      // + e_{k-1}
-    if (edge) rhs += apply_Mt_s<LPQ>(rho * zs - ys, k);
+    if (edge) {                                                        // rhs_t = D' v + (rho zs - ys) on position rows
+      const double v1 = __shfl_down_sync(PIADMM_FULL, rhs, 1, LPQ), v2 = __shfl_down_sync(PIADMM_FULL, rhs, 2, LPQ);
+      fma_if(rhs, -2.0, v1, d_dn1);
+      fma_if(rhs, 1.0, v2, d_dn2);
+      fma_if(rhs, 1.0, fma(rho, zs, -ys), srow);
+    }
     rhsbuf[k] = rhs;
     __syncwarp();
-    // ---- x~ = K^-1 rhs  (row k in registers, rhs broadcast from shared memory)
+    // ---- K^-1 rhs  (row k in registers, rhs broadcast from shared memory)
     double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
 #pragma unroll
     for (int j = 0; j < LPQ; j += 4) {
@@ -252,7 +293,14 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       acc3 = fma(Kinv[j + 3], r1.y, acc3);
     }
     __syncwarp();
-    const double xt = (acc0 + acc1) + (acc2 + acc3);
+    double xt = (acc0 + acc1) + (acc2 + acc3);
+    double tt = 0.0;
+    if (edge) {                                                        // x~ = D t~
+      tt = xt;
+      const double u1 = __shfl_up_sync(PIADMM_FULL, tt, 1, LPQ), u2 = __shfl_up_sync(PIADMM_FULL, tt, 2, LPQ);
+      fma_if(xt, -2.0, u1, d_up1);
+      fma_if(xt, 1.0, u2, d_up2);
+    }
     // ---- z~ = A x~, relaxation, projection, dual update
     double d = shift_down1<LPQ>(xt, k) - xt;
     if (!inner_row) d = 0.0;
@@ -267,48 +315,48 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
     zn = dmax(fma(y2, irho, zr2), l_d); y2 = fma(rho, zr2 - zn, y2); z2 = zn;
     zn = dmax(fma(y3, irho, zr3), l_d); y3 = fma(rho, zr3 - zn, y3); z3 = zn;
     if (edge) {
-      double nxt;
-      apply_M<LPQ>(xt, k, &nxt);
-      if (k >= N) nxt = 0.0;          // position rows exist for trajectory indices 1..N only
-      const double zrs = fma(al, nxt, oma * zs);
+      t = fma(al, tt, oma * t);
+      const double st = srow ? tt : 0.0;            // position row value (lane N-1: the zero row)
+      const double zrs = fma(al, st, oma * zs);
       const double vs = fma(ys, irho, zrs);
       const double vo = partner<LPQ>(vs, xch, k, half);
       const double s0 = half == 0 ? vs : vo, s1 = half == 0 ? vo : vs;
       const double tau = fma(a1, s1, a0 * s0);
-      const double t = ip.beta * irho;
+      const double tb = ip.beta * irho;
       double step;
       if (tau >= cvec) step = 0.0;
-      else if (fma(t, na, tau) <= cvec) step = t;
+      else if (fma(tb, na, tau) <= cvec) step = tb;
       else step = (cvec - tau) / na;
       zn = fma(step, a_me, vs);
       ys = fma(rho, zrs - zn, ys);
       zs = zn;
     }
-    // ---- termination / adaptive rho every in_check iterations
+    // ---- termination / adaptive rho every in_check iterations (steering-space residuals)
     if (--chk == 0) {
       chk = ip.in_check;
       double dd = shift_down1<LPQ>(x, k) - x;
       if (!inner_row) dd = 0.0;
       double rp = dmax(dmax(fabs(x - z0), fabs(-x - z1)), dmax(fabs(-dd - z2), fabs(dd - z3)));
       double np = dmax(dmax(fabs(x), fabs(dd)), dmax(dmax(fabs(z0), fabs(z1)), dmax(fabs(z2), fabs(z3))));
-      double nxt;
-      double mx = apply_M<LPQ>(x, k, &nxt);
-      if (k >= N) nxt = 0.0;
+      double Px, Aty;
+      const double ey = y3 - y2;
+      Aty = (y0 - y1) + shift_up1<LPQ>(ey, k) - ey;
       if (edge) {
-        rp = dmax(rp, fabs(nxt - zs));
-        np = dmax(np, dmax(fabs(nxt), fabs(zs)));
-      }
-      if (k > N) mx = 0.0;
-      double Px = fma(pW, apply_Mt<LPQ>(mx, k), pI * x);
-      {
+        const double st = srow ? t : 0.0;           // (M x) on the position rows
+        rp = dmax(rp, fabs(st - zs));
+        np = dmax(np, dmax(fabs(st), fabs(zs)));
+        Px = fma(pW, suffix2<LPQ>(st, k), pI * x);   // P x = pI x + pW M'(M x)
+        Aty += suffix2<LPQ>(srow ? ys : 0.0, k);     // + M' y_s
+      } else {
+        double nxt;
+        double mx = apply_M<LPQ>(x, k, &nxt);
+        if (k > N) mx = 0.0;
+        Px = fma(pW, apply_Mt<LPQ>(mx, k), pI * x);
         const double x1 = shift_down1<LPQ>(x, k), x2 = shift_down1<LPQ>(x1, k);
         const double ee = (k < N - 2) ? (x - 2.0 * x1 + x2) : 0.0;
         const double e1 = shift_up1<LPQ>(ee, k), e2 = shift_up1<LPQ>(e1, k);
         Px = fma(p2, ee - 2.0 * e1 + e2, Px);
       }
-      const double ey = y3 - y2;
-      double Aty = (y0 - y1) + shift_up1<LPQ>(ey, k) - ey;
-      if (edge) Aty += apply_Mt_s<LPQ>(ys, k);
       double rd = fabs(Px + q + Aty);
       double nd = dmax(fabs(Px), dmax(fabs(Aty), fabs(q)));
       rp = group_max<LPQ>(rp); np = group_max<LPQ>(np); rd = group_max<LPQ>(rd); nd = group_max<LPQ>(nd);
@@ -337,7 +385,8 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       if (__all_sync(PIADMM_FULL, done)) break;
       if (__any_sync(PIADMM_FULL, refac)) {
         if (refac) { rho = rn; irho = 1.0 / rho; }
-        build_Kinv<LPQ>(Kinv, N, k, pI + sg, p2, pW + pWe * rho, rho, Wsm, rhsbuf);
+        if (edge) build_Kinv_edge<LPQ>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
+        else build_Kinv_vehicle<LPQ>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
       }
     }
   }

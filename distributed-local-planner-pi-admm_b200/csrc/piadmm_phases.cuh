@@ -135,7 +135,10 @@ __device__ __noinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0,
     cfull = p.dis_thres * p.dis_thres - (base0 + base1 - (lx * lx + ly * ly));
   }
   const double q = rho * g * apply_Mt<LPQ>(vec, k);
-  double cvec = shift_down1<LPQ>(cfull, k);           // lane L <- trajectory index L+1
+  // position-row layout of inner_solve: lane L <= N-2 <-> trajectory index L+2, lane N-1 <-> index 1
+  double cvec = __shfl_down_sync(PIADMM_FULL, cfull, 2, LPQ);
+  const double c_one = __shfl_sync(PIADMM_FULL, cfull, 1, LPQ);
+  if (k == N - 1) cvec = c_one;
   if (!valid || k >= N) cvec = -1e300;
   const double g0 = spd[0] * spd[0] * p.dt * p.dt / p.L, g1 = spd[1] * spd[1] * p.dt * p.dt / p.L;
   const double a0 = valid ? -2.0 * g0 * (-lx * sn[0] + ly * cs[0]) : 0.0;
