@@ -29,11 +29,24 @@ __device__ __forceinline__ void pair_sync() {
   if (LPQ == 16) __syncwarp(); else __syncthreads();
 }
 
+// copy tables [first, first+count) (see PIADMM_NTAB in piadmm_dev.cuh) to shared memory: 16-byte loads,
+// eight in flight per thread before the first store
 template <int LPQ>
-__device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) {
-  for (int t = threadIdx.x; t < PIADMM_NTAB * LPQ * LPQ; t += blockDim.x) Wsm[t] = c.W[t];
+__device__ __forceinline__ void load_tabs(const DevCtx& c, double* Wsm, int first, int count) {
+  const double2* src = reinterpret_cast<const double2*>(c.W + first * LPQ * LPQ);
+  double2* dst = reinterpret_cast<double2*>(Wsm + first * LPQ * LPQ);
+  const int n2 = count * LPQ * LPQ / 2;
+  for (int base = threadIdx.x; base < n2; base += blockDim.x * 8) {
+    double2 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) { const int t = base + u * blockDim.x; if (t < n2) v[u] = __ldg(src + t); }
+#pragma unroll
+    for (int u = 0; u < 8; u++) { const int t = base + u * blockDim.x; if (t < n2) dst[t] = v[u]; }
+  }
   __syncthreads();
 }
+template <int LPQ>
+__device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) { load_tabs<LPQ>(c, Wsm, 0, PIADMM_NTAB); }
 
 // ------------------------------------------------------------------ phase kernels (generic V)
 __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
@@ -71,13 +84,17 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(con
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
   Who<LPQ> w;
-  const long a = (long)blockIdx.x * groups_per_cta<LPQ>() + w.group_in_cta;
-  const int s = (int)(a / c.V), i = (int)(a % c.V);
-  const bool valid = a < (long)c.S * c.V && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
-  if (!__syncthreads_or(valid)) return;      // nothing to do for the whole CTA: skip the table load
-  load_W<LPQ>(c, Wsm);
-  if (!__any_sync(PIADMM_FULL, valid)) return;
-  dev_x_update<LPQ>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch);
+  const long agents = (long)c.S * c.V, items = (agents + groups_per_cta<LPQ>() - 1) / groups_per_cta<LPQ>();
+  bool loaded = false;
+  for (long item = blockIdx.x; item < items; item += gridDim.x) {       // persistent CTAs, grid-stride
+    const long a = item * groups_per_cta<LPQ>() + w.group_in_cta;
+    const int s = (int)(a / c.V), i = (int)(a % c.V);
+    const bool valid = a < agents && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
+    if (!__syncthreads_or(valid)) continue;  // nothing to do for the whole CTA
+    if (!loaded) { load_tabs<LPQ>(c, Wsm, 0, 2); loaded = true; }
+    if (!__any_sync(PIADMM_FULL, valid)) continue;
+    dev_x_update<LPQ>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch);
+  }
 }
 
 // trajectory bounding boxes [S,V,4] = (xmin, xmax, ymin, ymax): cheap reject for the O(V^2) pair test
@@ -219,17 +236,21 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(con
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];
   Who<LPQ> w;
-  const long pidx = (long)blockIdx.x * pairs_per_cta<LPQ>() + w.pair_in_cta;
-  const int s = (int)(pidx / c.E), e = (int)(pidx % c.E);
-  bool valid = s < c.S && !c.b.done[s] && e < c.b.edge_n[s];     // uniform per pair
-  const int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + e) * 2;
-  const int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + e) * 2;
-  if (valid) valid = eij[0] >= 0 && ((eij[0] >= c.own_lo && eij[0] < c.own_hi) || (eij[1] >= c.own_lo && eij[1] < c.own_hi));
-  if (!__syncthreads_or(valid)) return;      // empty CTA: skip the table load
-  load_W<LPQ>(c, Wsm);
-  if (!valid) return;
-  dev_z_update<LPQ>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
-                    Wsm, gbuf[w.group_in_cta], xch);
+  const long pairs = (long)c.S * c.E, items = (pairs + pairs_per_cta<LPQ>() - 1) / pairs_per_cta<LPQ>();
+  bool loaded = false;
+  for (long item = blockIdx.x; item < items; item += gridDim.x) {       // persistent CTAs, grid-stride
+    const long pidx = item * pairs_per_cta<LPQ>() + w.pair_in_cta;
+    const int s = (int)(pidx / c.E), e = (int)(pidx % c.E);
+    bool valid = s < c.S && !c.b.done[s] && e < c.b.edge_n[s];     // uniform per pair
+    const int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + e) * 2;
+    const int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + e) * 2;
+    if (valid) valid = eij[0] >= 0 && ((eij[0] >= c.own_lo && eij[0] < c.own_hi) || (eij[1] >= c.own_lo && eij[1] < c.own_hi));
+    if (!__syncthreads_or(valid)) continue;  // empty CTA
+    if (!loaded) { load_tabs<LPQ>(c, Wsm, 2, 2); loaded = true; }
+    if (!valid) continue;                     // LPQ==16 only: the other pair of the CTA works alone
+    dev_z_update<LPQ>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
+                      Wsm, gbuf[w.group_in_cta], xch);
+  }
 }
 
 // residuals, casadi/main.py:165-173: rank-local partial sums over the edges whose veh1 is owned.
@@ -473,7 +494,7 @@ struct piadmm_handle {
   double* d_W;
   int* d_count;
   int* d_queue;
-  int fused_grid;
+  int fused_grid, x_grid, z_grid;
   int64_t launches;
   std::string err;
 };
@@ -624,6 +645,16 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     else ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_v2<32>, CTA_THREADS, 0);
     if (ce != cudaSuccess || per_sm < 1) return fail(ce, "occupancy");
     h->fused_grid = prop.multiProcessorCount * per_sm;     // one resident wave, persistent CTAs
+    int px = 0, pz = 0;
+    if (h->lpq == 16) {
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&px, k_x_update<16>, CTA_THREADS, 0);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pz, k_z_update<16>, CTA_THREADS, 0);
+    } else {
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&px, k_x_update<32>, CTA_THREADS, 0);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pz, k_z_update<32>, CTA_THREADS, 0);
+    }
+    h->x_grid = prop.multiProcessorCount * (px < 1 ? 1 : px);
+    h->z_grid = prop.multiProcessorCount * (pz < 1 ? 1 : pz);
   }
   *out = h;
   return PIADMM_OK;
@@ -687,10 +718,12 @@ int piadmm_x_update(piadmm_handle* h, void* stream) {
   const long agents = (long)h->c.S * h->c.V;
   if (h->lpq == 16) {
     const int g = groups_per_cta<16>();
-    k_x_update<16><<<(unsigned)((agents + g - 1) / g), CTA_THREADS, 0, st>>>(h->c);
+    long items = (agents + g - 1) / g;
+    k_x_update<16><<<(unsigned)(items < h->x_grid ? items : h->x_grid), CTA_THREADS, 0, st>>>(h->c);
   } else {
     const int g = groups_per_cta<32>();
-    k_x_update<32><<<(unsigned)((agents + g - 1) / g), CTA_THREADS, 0, st>>>(h->c);
+    long items = (agents + g - 1) / g;
+    k_x_update<32><<<(unsigned)(items < h->x_grid ? items : h->x_grid), CTA_THREADS, 0, st>>>(h->c);
   }
   LAUNCHED();
   return PIADMM_OK;
@@ -719,9 +752,10 @@ int piadmm_z_update(piadmm_handle* h, void* stream) {
   const long pairs = (long)h->c.S * h->c.E;
   if (h->lpq == 16) {
     const int g = pairs_per_cta<16>();
-    k_z_update<16><<<(unsigned)((pairs + g - 1) / g), CTA_THREADS, 0, st>>>(h->c);
+    long items = (pairs + g - 1) / g;
+    k_z_update<16><<<(unsigned)(items < h->z_grid ? items : h->z_grid), CTA_THREADS, 0, st>>>(h->c);
   } else {
-    k_z_update<32><<<(unsigned)pairs, CTA_THREADS, 0, st>>>(h->c);
+    k_z_update<32><<<(unsigned)(pairs < h->z_grid ? pairs : h->z_grid), CTA_THREADS, 0, st>>>(h->c);
   }
   LAUNCHED();
   return PIADMM_OK;
