@@ -360,7 +360,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
                                                 double* gbuf, double* xch);
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 7 : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
   __shared__ __align__(16) double xch[64];

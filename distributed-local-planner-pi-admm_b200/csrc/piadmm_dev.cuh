@@ -134,8 +134,17 @@ __device__ __forceinline__ double partner(double mine, double* xch, int k, int h
 }
 
 // max/min without the NaN plumbing of fmax/fmin (inputs are finite): DSETP + 2 SEL
-__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
-__device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
+// (written in PTX so that the compiler does not pattern-match it back into the 7-instruction fmax sequence)
+__device__ __forceinline__ double dmax(double a, double b) {
+  double r;
+  asm("{\n\t.reg .pred p;\n\tsetp.gt.f64 p, %1, %2;\n\tselp.f64 %0, %1, %2, p;\n\t}" : "=d"(r) : "d"(a), "d"(b));
+  return r;
+}
+__device__ __forceinline__ double dmin(double a, double b) {
+  double r;
+  asm("{\n\t.reg .pred p;\n\tsetp.lt.f64 p, %1, %2;\n\tselp.f64 %0, %1, %2, p;\n\t}" : "=d"(r) : "d"(a), "d"(b));
+  return r;
+}
 
 __device__ __forceinline__ double round_scale(double x, double scale) {
   return scale > 0.0 ? rint(x * scale) / scale : x;   // np.around: rint(x*10^d)/10^d
