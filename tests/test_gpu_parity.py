@@ -196,3 +196,62 @@ def test_class_mirror_step_and_mutable_rho():
     ref = ctwin.step(p, xt[None], np.array([[4.0, 8.0]]), P.ref_window(12)[None])
     assert r2["n_outer"] == int(ref["n_outer"][0]) and rel_err(r2["primal_u"], ref["u"][0]) <= 1e-6
     assert rel_err(r1["primal_u"], r2["primal_u"]) > 1e-6
+
+
+# ------------------------------------------------------------------ edge cases
+EDGE_CASES = [
+    ("python_current", dict(num_ho=3), 5),                       # smallest horizon
+    ("python_current", dict(num_ho=31, iter_num=6), 7),          # largest horizon (32-lane groups, all lanes used)
+    ("python_current", dict(num_ho=16), 9),                      # first horizon that needs 32-lane groups
+    ("matlab_pi", dict(num_ho=15, iter_num=1), 6),               # iteration cap reached at once
+    ("matlab_pi", dict(num_ho=15, eps_pri=1e-6, eps_dual=1e-6, iter_num=5), 4),   # never converges: cap
+    ("python_current", dict(in_max_iter=30), 8),                 # inner solver hits max_iter -> status bits
+    ("python_current", dict(in_adaptive=0, in_max_iter=500), 8),
+    ("python_current", dict(round_u=2, round_edge=1), 5),
+    ("matlab_pi", dict(num_ho=12, in_check=10, eps_pri=0.5, eps_dual=0.5), 5),
+    ("python_old_pi", dict(num_ho=9, iter_num=7, round_edge=0), 3),   # old main.py:119 rounds the edge controls to 0 decimals
+]
+
+
+@pytest.mark.parametrize("preset,kw,S", EDGE_CASES)
+@pytest.mark.parametrize("fused", [True, False])
+def test_edge_cases_match_oracle(preset, kw, S, fused):
+    p = make_params(preset, "default", **kw)
+    xt, spd, refwin = c4_scenarios(S=S, N=p.num_ho, seed=21)
+    ref = ctwin.step(p, xt, spd, refwin)
+    got = _run_gpu(p, xt, spd, refwin, fused)
+    assert_same(got, ref, what=f"{preset}/{kw}/fused={fused}")
+    if "in_max_iter" in kw and kw["in_max_iter"] == 30:
+        assert (ref["status"] & 1).any()                          # PIADMM_ST_VEH_MAXITER reported
+
+
+def test_slot_overflow_is_reported():
+    from pi_admm_b200.scenarios import c3_intersection
+    p = _generic_params(15)
+    xt, spd, refwin = c3_intersection(V=16, N=15, r0=5.0, gap=3.0)
+    ref = ctwin.step(p, xt, spd, refwin, D=2)
+    sol = PIADMMSolver(p, S=1, V=16, D=2)
+    sol.setup(xt, spd, refwin)
+    sol.iterate()
+    got = sol.to_numpy()
+    assert ref["status"][0] & 4 and got["status"][0] & 4          # PIADMM_ST_SLOT_OVERFLOW on both
+
+
+def test_large_batch_properties():
+    """BASELINE config-4 size (4096 scenarios): size-independent properties instead of the oracle --
+    steering / rate limits hold, roll-out is consistent with u, a repeated run is bit-identical,
+    and a random subset equals the oracle."""
+    p = make_params("matlab_pi", "default", num_ho=15, eps_pri=0.1, eps_dual=0.1, round_u=4, round_edge=4)
+    xt, spd, refwin = c4_scenarios(S=4096, N=15)
+    a = _run_gpu(p, xt, spd, refwin, True)
+    b = _run_gpu(p, xt, spd, refwin, True)
+    for k in ("u", "pos", "hat", "dual", "err_rk", "n_outer", "veh_inner"):
+        assert np.array_equal(a[k], b[k]), k                       # deterministic
+    u = a["u"]
+    assert np.abs(u).max() <= np.pi / 6 + 2e-3 and np.abs(np.diff(u, axis=2)).max() <= np.pi / 9 + 2e-3  # eps 1e-3 solver
+    assert (a["status"] == 0).all() and (a["n_outer"] >= 1).all()
+    idx = np.random.default_rng(0).choice(4096, 64, replace=False)
+    ref = ctwin.step(p, xt[idx], spd[idx], refwin[idx])
+    for k in ("u", "pos", "err_rk", "xt_next"):
+        assert rel_err(a[k][idx], ref[k]) <= 1e-6, k
+    assert np.array_equal(a["n_outer"][idx], ref["n_outer"])
