@@ -8,6 +8,7 @@
 #include "piadmm_phases.cuh"
 
 #define CTA_THREADS 64
+#define PIADMM_CHUNKS 4   // sub-batches of piadmm_step_host (copies of one overlap the kernels of the others)
 
 // ------------------------------------------------------------------ thread -> (pair, half, k)
 template <int LPQ>
@@ -342,8 +343,8 @@ __global__ void k_count_active(const __grid_constant__ DevCtx c, int* out) {
 }
 
 __global__ void k_plant(const __grid_constant__ DevCtx c) {
-  const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (a >= (long)c.S * c.V) return;
+  const long a = (long)c.s_lo * c.V + (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= (long)c.s_hi * c.V) return;
   const double* xt = c.b.xt + a * 3;
   const double v = c.b.spd[a];
   double* o = c.b.xt_next + a * 3;
@@ -372,15 +373,15 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 7 : 5) k_fused_v2(con
     int s;
     if (LPQ == 16) {
       s = 0;
-      if (w.lane == 0) s = atomicAdd(c.queue, 1);
+      if (w.lane == 0) s = c.s_lo + atomicAdd(c.queue, 1);
       s = __shfl_sync(PIADMM_FULL, s, 0);
     } else {
-      if (threadIdx.x == 0) s_next = atomicAdd(c.queue, 1);
+      if (threadIdx.x == 0) s_next = c.s_lo + atomicAdd(c.queue, 1);
       __syncthreads();
       s = s_next;
       __syncthreads();
     }
-    if (s >= c.S) break;
+    if (s >= c.s_hi) break;
     run_scenario_v2<LPQ>(c, s, w, Wsm, gbuf[w.group_in_cta], xch);
   }
 }
@@ -495,6 +496,9 @@ struct piadmm_handle {
   int* d_count;
   int* d_queue;
   int fused_grid, x_grid, z_grid;
+  cudaStream_t cs[PIADMM_CHUNKS];
+  cudaEvent_t ev_start, ev_done[PIADMM_CHUNKS];
+  bool have_streams;
   int64_t launches;
   std::string err;
 };
@@ -568,10 +572,11 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   }
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
-  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->fused_grid = 0;
+  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->fused_grid = 0; h->have_streams = false;
   h->c.p = *p; h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
   h->c.N = p->num_ho; h->c.I = p->iter_num;
   h->c.own_lo = 0; h->c.own_hi = V;
+  h->c.s_lo = 0; h->c.s_hi = S;
   h->c.round_u_scale = pow10i(p->round_u); h->c.round_edge_scale = pow10i(p->round_edge);
   h->lpq = p->num_ho <= 15 ? 16 : 32;
   auto fail = [&](cudaError_t e, const char* what) {
@@ -635,7 +640,13 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMalloc(&h->c.dist_bad, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
   if ((ce = cudaMemset(h->c.dist_bad, 0, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
   if ((ce = cudaMalloc(&h->d_count, sizeof(int))) != cudaSuccess) return fail(ce, "count");
-  if ((ce = cudaMalloc(&h->d_queue, sizeof(int))) != cudaSuccess) return fail(ce, "queue");
+  if ((ce = cudaMalloc(&h->d_queue, sizeof(int) * (PIADMM_CHUNKS + 1))) != cudaSuccess) return fail(ce, "queue");
+  for (int i = 0; i < PIADMM_CHUNKS; i++) {
+    if ((ce = cudaStreamCreateWithFlags(&h->cs[i], cudaStreamNonBlocking)) != cudaSuccess) return fail(ce, "stream");
+    if ((ce = cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming)) != cudaSuccess) return fail(ce, "event");
+  }
+  if ((ce = cudaEventCreateWithFlags(&h->ev_start, cudaEventDisableTiming)) != cudaSuccess) return fail(ce, "event");
+  h->have_streams = true;
   h->c.queue = h->d_queue;
   {
     cudaDeviceProp prop;
@@ -665,6 +676,10 @@ void piadmm_destroy(piadmm_handle* h) {
   cudaSetDevice(h->device);
   cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad);
   cudaFree(h->d_count); cudaFree(h->d_queue);
+  if (h->have_streams) {
+    for (int i = 0; i < PIADMM_CHUNKS; i++) { cudaStreamDestroy(h->cs[i]); cudaEventDestroy(h->ev_done[i]); }
+    cudaEventDestroy(h->ev_start);
+  }
   delete h;
 }
 
@@ -820,20 +835,24 @@ int piadmm_plant_step(piadmm_handle* h, void* stream) {
   return PIADMM_OK;
 }
 
+// one persistent kernel for the whole outer loop of the scenarios [s_lo, s_hi)
+static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, int* queue) {
+  DevCtx c = h->c;
+  c.s_lo = s_lo; c.s_hi = s_hi; c.queue = queue;
+  CK(cudaMemsetAsync(queue, 0, sizeof(int), st));
+  const int pairs = h->lpq == 16 ? 2 : 1;
+  int grid = (s_hi - s_lo + pairs - 1) / pairs;
+  if (grid > h->fused_grid) grid = h->fused_grid;
+  if (h->lpq == 16) k_fused_v2<16><<<grid, CTA_THREADS, 0, st>>>(c);
+  else k_fused_v2<32><<<grid, CTA_THREADS, 0, st>>>(c);
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
 int piadmm_step(piadmm_handle* h, void* stream) {
   REQUIRE_BOUND();
   cudaStream_t st = (cudaStream_t)stream;
-  if (h->c.V == 2 && h->c.D == 1) {
-    // one persistent kernel for the whole outer loop
-    CK(cudaMemsetAsync(h->d_queue, 0, sizeof(int), st));
-    const int pairs = h->lpq == 16 ? 2 : 1;
-    int grid = (h->c.S + pairs - 1) / pairs;
-    if (grid > h->fused_grid) grid = h->fused_grid;
-    if (h->lpq == 16) k_fused_v2<16><<<grid, CTA_THREADS, 0, st>>>(h->c);
-    else k_fused_v2<32><<<grid, CTA_THREADS, 0, st>>>(h->c);
-    LAUNCHED();
-    return PIADMM_OK;
-  }
+  if (h->c.V == 2 && h->c.D == 1) return launch_fused(h, st, 0, h->c.S, h->d_queue);
   // generic V: phase kernels, one readback of the active-scenario count per outer iteration
   int rc = piadmm_begin_step(h, stream);
   for (int it = 0; it < h->c.I && rc == PIADMM_OK; it++) {
@@ -855,6 +874,36 @@ int piadmm_step_host(piadmm_handle* h, const double* xt, const double* spd, cons
   if (!xt || !spd || !refwin) return PIADMM_E_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   const size_t SV = (size_t)h->c.S * h->c.V, N = h->c.N;
+  if (h->c.V == 2 && h->c.D == 1 && h->c.S >= 64 * PIADMM_CHUNKS) {
+    // Independent scenarios: split the batch into PIADMM_CHUNKS sub-batches on internal streams so that the
+    // H2D / D2H copies of one sub-batch overlap the (latency-bound) kernels of the others.
+    const size_t np1 = N + 1;
+    CK(cudaEventRecord(h->ev_start, st));
+    for (int ch = 0; ch < PIADMM_CHUNKS; ch++) {
+      cudaStream_t cs = h->cs[ch];
+      const int s0 = (int)((long)h->c.S * ch / PIADMM_CHUNKS), s1 = (int)((long)h->c.S * (ch + 1) / PIADMM_CHUNKS);
+      const size_t a0 = (size_t)s0 * 2, na = (size_t)(s1 - s0) * 2;
+      CK(cudaStreamWaitEvent(cs, h->ev_start, 0));
+      CK(cudaMemcpyAsync((double*)h->c.b.xt + a0 * 3, xt + a0 * 3, sizeof(double) * na * 3, cudaMemcpyHostToDevice, cs));
+      CK(cudaMemcpyAsync((double*)h->c.b.spd + a0, spd + a0, sizeof(double) * na, cudaMemcpyHostToDevice, cs));
+      CK(cudaMemcpyAsync((double*)h->c.b.refwin + a0 * 2 * np1, refwin + a0 * 2 * np1, sizeof(double) * na * 2 * np1, cudaMemcpyHostToDevice, cs));
+      int rc = launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch);
+      if (rc) return rc;
+      DevCtx c = h->c;
+      c.s_lo = s0; c.s_hi = s1;
+      k_plant<<<(unsigned)((na + 127) / 128), 128, 0, cs>>>(c);
+      LAUNCHED();
+      if (u_out) CK(cudaMemcpyAsync(u_out + a0 * N, h->c.b.u + a0 * N, sizeof(double) * na * N, cudaMemcpyDeviceToHost, cs));
+      if (pos_out) CK(cudaMemcpyAsync(pos_out + a0 * 2 * np1, h->c.b.pos + a0 * 2 * np1, sizeof(double) * na * 2 * np1, cudaMemcpyDeviceToHost, cs));
+      if (xt_next_out) CK(cudaMemcpyAsync(xt_next_out + a0 * 3, h->c.b.xt_next + a0 * 3, sizeof(double) * na * 3, cudaMemcpyDeviceToHost, cs));
+      if (curr_iter_out) CK(cudaMemcpyAsync(curr_iter_out + s0, h->c.b.curr_iter + s0, sizeof(int32_t) * (s1 - s0), cudaMemcpyDeviceToHost, cs));
+      if (n_outer_out) CK(cudaMemcpyAsync(n_outer_out + s0, h->c.b.n_outer + s0, sizeof(int32_t) * (s1 - s0), cudaMemcpyDeviceToHost, cs));
+      CK(cudaEventRecord(h->ev_done[ch], cs));
+      CK(cudaStreamWaitEvent(st, h->ev_done[ch], 0));
+    }
+    CK(cudaStreamSynchronize(st));
+    return PIADMM_OK;
+  }
   CK(cudaMemcpyAsync((void*)h->c.b.xt, xt, sizeof(double) * SV * 3, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync((void*)h->c.b.spd, spd, sizeof(double) * SV, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync((void*)h->c.b.refwin, refwin, sizeof(double) * SV * 2 * (N + 1), cudaMemcpyHostToDevice, st));

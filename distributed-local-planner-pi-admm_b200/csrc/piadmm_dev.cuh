@@ -33,6 +33,7 @@ struct DevCtx {
   int i_iter;                              // outer iteration index (phase API)
   int own_lo, own_hi;                      // vehicles x-updated by this rank (multi-GPU vehicle sharding)
   int* queue;                              // work counter of the persistent fused kernel
+  int s_lo, s_hi;                          // scenario range of this launch (fused kernel / plant step)
 };
 
 // ------------------------------------------------------------------ group primitives

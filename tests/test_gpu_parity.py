@@ -255,3 +255,16 @@ def test_large_batch_properties():
     for k in ("u", "pos", "err_rk", "xt_next"):
         assert rel_err(a[k][idx], ref[k]) <= 1e-6, k
     assert np.array_equal(a["n_outer"][idx], ref["n_outer"])
+
+
+def test_step_host_chunked_pipeline_equals_device_path():
+    """S >= 256 makes piadmm_step_host split the batch over internal streams (copy/compute overlap)."""
+    p = make_params("matlab_pi", "default", num_ho=15, eps_pri=0.1, eps_dual=0.1)
+    xt, spd, refwin = c4_scenarios(S=301, N=15, seed=5)
+    ref = ctwin.step(p, xt, spd, refwin)
+    sol = PIADMMSolver(p, S=301, V=2)
+    for _ in range(2):
+        out = sol.step_host(xt, spd, refwin)
+        assert np.array_equal(out["n_outer"], ref["n_outer"]) and np.array_equal(out["curr_iter"], ref["curr_iter"])
+        for k in ("u", "pos", "xt_next"):
+            assert rel_err(out[k], ref[k]) <= 1e-6
