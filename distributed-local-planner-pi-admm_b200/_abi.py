@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libpiadmm.so")
+LIB_PATH = os.environ.get("PIADMM_LIB") or os.path.join(_HERE, "csrc", "libpiadmm.so")   # PIADMM_LIB: A/B builds
 
 ABI_VERSION = 1
 DUAL_PLAIN, DUAL_PI, DUAL_PI_OLD = 0, 1, 2
