@@ -146,6 +146,12 @@ _PROTOS = {
     "piadmm_step_host": (C.c_int, [C.c_void_p] + [C.c_void_p] * 8 + [C.c_void_p]),
     "piadmm_launch_count": (C.c_int64, [C.c_void_p]),
     "piadmm_fp64_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    # include/obca_consensus.h (struct pointers passed as void*: obca_consensus.py owns the ctypes mirrors)
+    "obca_lambda_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p]),
+    "obca_residuals": (C.c_int, [C.c_void_p] * 7 + [C.c_void_p]),
+    "obca_check_converge": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_void_p, C.c_void_p]),
+    "obca_iterate_next_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "obca_consensus_tail": (C.c_int, [C.c_void_p] * 5 + [C.c_double] * 3 + [C.c_int32] + [C.c_void_p] * 5),
 }
 EXPORTED_SYMBOLS = tuple(_PROTOS)
 

@@ -15,16 +15,22 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "piadmm.h")
 
 
+HEADER_OBCA = os.path.join(ROOT, "include", "obca_consensus.h")
+
+
 def declared_functions():
-    src = open(HEADER).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(piadmm_[a-z0-9_]+)\s*\(", src)))
+    out = set()
+    for path, prefix in ((HEADER, "piadmm_"), (HEADER_OBCA, "obca_")):
+        src = open(path).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        out |= set(re.findall(r"\b(%s[a-z0-9_]+)\s*\(" % prefix, src))
+    return sorted(out)
 
 
 def test_header_symbols_are_exported_and_bound():
     lib = pa.load_library()
     names = declared_functions()
-    assert len(names) >= 18
+    assert len(names) >= 23 and "obca_consensus_tail" in names
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/piadmm.h but not exported"
     assert set(names) == set(_abi.EXPORTED_SYMBOLS)
@@ -42,6 +48,32 @@ def test_struct_layouts_match_the_c_compiler(tmp_path):
     a, b, c, d = [int(x) for x in subprocess.check_output([str(exe)]).split()]
     assert a == C.sizeof(_abi.Params) and b == C.sizeof(_abi.Buffers)
     assert c == _abi.Params.num_ho.offset and d == _abi.Buffers.xt_next.offset
+
+
+def test_obca_struct_layouts_match_the_c_compiler(tmp_path):
+    from pi_admm_b200 import obca_consensus as oc
+    src = tmp_path / "szo.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "obca_consensus.h"\nint main(void){printf("%zu %zu %zu %zu\\n",'
+                   "sizeof(obca_dims), sizeof(obca_state), offsetof(obca_dims, C), offsetof(obca_state, local_x));return 0;}\n")
+    exe = tmp_path / "szo"
+    subprocess.check_call(["/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc", "-I", os.path.join(ROOT, "include"),
+                           str(src), "-o", str(exe)])
+    a, b, c, d = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert a == C.sizeof(oc.Dims) and b == C.sizeof(oc.State)
+    assert c == oc.Dims.C.offset and d == oc.State.local_x.offset
+
+
+def test_obca_no_cpu_fallback_without_a_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from pi_admm_b200.obca_consensus import OBCAConsensus, Dims, State
+    with pytest.raises(pa.PIADMMError):
+        OBCAConsensus(S=2)
+    lib = pa.load_library()
+    d, st = Dims(1, 2, 7, 5, 4, 14), State(*([8] * 6))    # non-NULL dummies: refused before any dereference
+    assert lib.obca_lambda_update(C.byref(d), C.byref(st), 1.0, None) == -2     # PIADMM_E_CUDA
+    assert lib.obca_lambda_update(None, C.byref(st), 1.0, None) == -1           # PIADMM_E_ARG
 
 
 def test_default_params_agree_in_c_and_python():
