@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(con
     if (!__syncthreads_or(valid)) continue;  // nothing to do for the whole CTA
     if (!loaded) { load_tabs<LPQ>(c, Wsm, 0, 2); loaded = true; }
     if (!__any_sync(PIADMM_FULL, valid)) continue;
-    dev_x_update<LPQ>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch);
+    dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr);
   }
 }
 
@@ -249,8 +249,8 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(con
     if (!__syncthreads_or(valid)) continue;  // empty CTA
     if (!loaded) { load_tabs<LPQ>(c, Wsm, 2, 2); loaded = true; }
     if (!valid) continue;                     // LPQ==16 only: the other pair of the CTA works alone
-    dev_z_update<LPQ>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
-                      Wsm, gbuf[w.group_in_cta], xch);
+    dev_z_update<LPQ, false>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
+                             Wsm, gbuf[w.group_in_cta], xch, nullptr);
   }
 }
 
@@ -356,9 +356,71 @@ __global__ void k_plant(const __grid_constant__ DevCtx c) {
 // ------------------------------------------------------------------ fused V=2 persistent kernel
 // One pair per scenario runs casadi/main.py:52-181 start to finish: no host round trips, state
 // stays in L1/L2 between phases (each scenario touches ~10 KB).
-template <int LPQ>
+template <int LPQ, bool KS>
 __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Who<LPQ>& w, const double* Wsm,
-                                                double* gbuf, double* xch);
+                                                double* gbuf, double* xch, double* krow);
+
+// scenario queue: LPQ==16 one scenario per warp, LPQ==32 one per 64-thread CTA
+template <int LPQ>
+__device__ __forceinline__ int next_scenario(const DevCtx& c, const Who<LPQ>& w, int* s_next) {
+  int s;
+  if (LPQ == 16) {
+    s = 0;
+    if (w.lane == 0) {
+      s = c.s_lo + atomicAdd(c.queue, 1);
+      if (c.order && s < c.s_hi) s = c.order[s];
+    }
+    s = __shfl_sync(PIADMM_FULL, s, 0);
+  } else {
+    if (threadIdx.x == 0) {
+      int q = c.s_lo + atomicAdd(c.queue, 1);
+      if (c.order && q < c.s_hi) q = c.order[q];
+      *s_next = q;
+    }
+    __syncthreads();
+    s = *s_next;
+    __syncthreads();
+  }
+  return s;
+}
+
+// Scheduling hint for the NEXT step of the same scenarios: order[s_lo..s_hi) = the scenarios of the range sorted
+// by the work they needed in this step, longest first (counting sort on a 512-bucket cost histogram, one CTA).
+// Scenario run times differ by up to ~2.7x (outer iterations 1..3, inner iterations 25..225 per solve); with
+// about two scenarios per resident warp slot, starting the long ones first removes most of the tail in which
+// SMs idle while the last warps finish.  Results never depend on the order.
+#define ORDER_BUCKETS 512
+__global__ void __launch_bounds__(1024) k_order(const __grid_constant__ DevCtx c, int* order) {
+  __shared__ unsigned hist[ORDER_BUCKETS];
+  __shared__ unsigned long long cmax;
+  const int n = c.s_hi - c.s_lo;
+  for (int b = threadIdx.x; b < ORDER_BUCKETS; b += blockDim.x) hist[b] = 0;
+  if (threadIdx.x == 0) cmax = 1;
+  __syncthreads();
+  unsigned long long m = 0;
+  for (int t = threadIdx.x; t < n; t += blockDim.x) {
+    const unsigned long long cost = (unsigned long long)c.b.veh_inner[c.s_lo + t] + 4ull * c.b.edge_inner[c.s_lo + t];
+    m = cost > m ? cost : m;
+  }
+  atomicMax(&cmax, m);
+  __syncthreads();
+  const unsigned long long mx = cmax;
+  for (int t = threadIdx.x; t < n; t += blockDim.x) {
+    const unsigned long long cost = (unsigned long long)c.b.veh_inner[c.s_lo + t] + 4ull * c.b.edge_inner[c.s_lo + t];
+    atomicAdd(&hist[ORDER_BUCKETS - 1 - (int)(cost * (ORDER_BUCKETS - 1) / mx)], 1u);   // bucket 0 = longest
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {                     // exclusive scan, 512 entries
+    unsigned run = 0;
+    for (int b = 0; b < ORDER_BUCKETS; b++) { const unsigned v = hist[b]; hist[b] = run; run += v; }
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < n; t += blockDim.x) {
+    const unsigned long long cost = (unsigned long long)c.b.veh_inner[c.s_lo + t] + 4ull * c.b.edge_inner[c.s_lo + t];
+    const unsigned pos = atomicAdd(&hist[ORDER_BUCKETS - 1 - (int)(cost * (ORDER_BUCKETS - 1) / mx)], 1u);
+    order[c.s_lo + pos] = c.s_lo + t;
+  }
+}
 
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 7 : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
@@ -370,25 +432,35 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 7 : 5) k_fused_v2(con
   Who<LPQ> w;
   // persistent: every pair pulls scenarios from a global counter until the batch is exhausted
   for (;;) {
-    int s;
-    if (LPQ == 16) {
-      s = 0;
-      if (w.lane == 0) s = c.s_lo + atomicAdd(c.queue, 1);
-      s = __shfl_sync(PIADMM_FULL, s, 0);
-    } else {
-      if (threadIdx.x == 0) s_next = c.s_lo + atomicAdd(c.queue, 1);
-      __syncthreads();
-      s = s_next;
-      __syncthreads();
-    }
+    const int s = next_scenario<LPQ>(c, w, &s_next);
     if (s >= c.s_hi) break;
-    run_scenario_v2<LPQ>(c, s, w, Wsm, gbuf[w.group_in_cta], xch);
+    run_scenario_v2<LPQ, false>(c, s, w, Wsm, gbuf[w.group_in_cta], xch, nullptr);
   }
 }
 
+// Throughput variant: K^-1 rows in shared memory, tables from global memory (see inner_solve).
+//   LPQ==16: 128-thread CTAs (4 scenario-warps), 7 per SM = 28 warps per SM (4144 scenario slots on 148 SMs)
+//   LPQ==32: 64-thread CTAs (one scenario), up to 12 per SM
+#define KS_THREADS(LPQ) ((LPQ) == 16 ? 128 : 64)
+#define KS_GROUPS(LPQ) (KS_THREADS(LPQ) / (LPQ))
 template <int LPQ>
+__global__ void __launch_bounds__(KS_THREADS(LPQ), LPQ == 16 ? 7 : 12) k_fused_ks(const __grid_constant__ DevCtx c) {
+  __shared__ __align__(16) double krows[KS_GROUPS(LPQ)][LPQ * PIADMM_KROW_STRIDE(LPQ)];
+  __shared__ __align__(16) double gbuf[KS_GROUPS(LPQ)][LPQ];
+  __shared__ __align__(16) double xch[64];
+  __shared__ int s_next;
+  Who<LPQ> w;
+  for (;;) {
+    const int s = next_scenario<LPQ>(c, w, &s_next);
+    if (s >= c.s_hi) break;
+    run_scenario_v2<LPQ, true>(c, s, w, c.W, gbuf[w.group_in_cta], xch,
+                               krows[w.group_in_cta] + w.k * PIADMM_KROW_STRIDE(LPQ));
+  }
+}
+
+template <int LPQ, bool KS>
 __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Who<LPQ>& w, const double* Wsm,
-                                                double* gbuf, double* xch) {
+                                                double* gbuf, double* xch, double* krow) {
   const piadmm_params& p = c.p;
   const int N = c.N, k = w.k, half = w.half;
   const int i = half, j = half ^ 1;
@@ -428,7 +500,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
 #pragma unroll 1
   for (int i_iter = 0; i_iter < c.I; i_iter++) {
     n_outer++;
-    dev_x_update<LPQ>(c, s, i, true, k, w.lane, half, Wsm, gbuf, xch);
+    dev_x_update<LPQ, KS>(c, s, i, true, k, w.lane, half, Wsm, gbuf, xch, krow);
     pair_sync<LPQ>();
     // ---- collision test, casadi/main.py:110-118
     bool near = false;
@@ -445,7 +517,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
     double sk = 0.0, rk = 0.0;
     if (hit) {
       if (k == 0) c.b.nbr[(size_t)s * 2 + i] = j;
-      dev_z_update<LPQ>(c, s, 0, 0, 1, 0, 0, true, true, k, w.lane, half, Wsm, gbuf, xch);
+      dev_z_update<LPQ, KS>(c, s, 0, 0, 1, 0, 0, true, true, k, w.lane, half, Wsm, gbuf, xch, krow);
       pair_sync<LPQ>();
       const double* er = c.edge_res + (size_t)s * c.E * 4;
       const double rho = p.dual_mode == PIADMM_DUAL_PI_OLD ? c.rho_new[s] : c.b.rho_s[s];
@@ -496,6 +568,10 @@ struct piadmm_handle {
   int* d_count;
   int* d_queue;
   int fused_grid, x_grid, z_grid;
+  bool fused_ks;              // fused kernel variant: K^-1 rows in shared memory (k_fused_ks)
+  int* d_order;               // [S] longest-first processing order learnt from the previous step
+  bool use_order;             // PIADMM_LPT=0 disables the hint
+  bool order_valid[PIADMM_CHUNKS + 1];   // per launch range: [0] whole batch, [1+ch] sub-batch ch
   cudaStream_t cs[PIADMM_CHUNKS];
   cudaEvent_t ev_start, ev_done[PIADMM_CHUNKS];
   bool have_streams;
@@ -572,7 +648,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   }
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
-  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->fused_grid = 0; h->have_streams = false;
+  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false;
   h->c.p = *p; h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
   h->c.N = p->num_ho; h->c.I = p->iter_num;
   h->c.own_lo = 0; h->c.own_hi = V;
@@ -641,6 +717,12 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMemset(h->c.dist_bad, 0, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
   if ((ce = cudaMalloc(&h->d_count, sizeof(int))) != cudaSuccess) return fail(ce, "count");
   if ((ce = cudaMalloc(&h->d_queue, sizeof(int) * (PIADMM_CHUNKS + 1))) != cudaSuccess) return fail(ce, "queue");
+  if ((ce = cudaMalloc(&h->d_order, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "order");
+  {
+    const char* lpt = getenv("PIADMM_LPT");
+    h->use_order = !(lpt && strcmp(lpt, "0") == 0);
+    for (int i = 0; i <= PIADMM_CHUNKS; i++) h->order_valid[i] = false;
+  }
   for (int i = 0; i < PIADMM_CHUNKS; i++) {
     if ((ce = cudaStreamCreateWithFlags(&h->cs[i], cudaStreamNonBlocking)) != cudaSuccess) return fail(ce, "stream");
     if ((ce = cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming)) != cudaSuccess) return fail(ce, "event");
@@ -652,7 +734,14 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     cudaDeviceProp prop;
     int per_sm = 0;
     if ((ce = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail(ce, "props");
-    if (h->lpq == 16) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_v2<16>, CTA_THREADS, 0);
+    // A/B switch: "ks" = K^-1 rows in shared memory (twice the resident warps, but the LDS traffic of the
+    // mat-vec then saturates the shared-memory pipe: measured 0.371 ms vs 0.336 ms per step, profiles/r1_history.md)
+    const char* fv = getenv("PIADMM_FUSED");
+    h->fused_ks = fv && strcmp(fv, "ks") == 0;
+    if (h->fused_ks) {
+      if (h->lpq == 16) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_ks<16>, KS_THREADS(16), 0);
+      else ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_ks<32>, KS_THREADS(32), 0);
+    } else if (h->lpq == 16) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_v2<16>, CTA_THREADS, 0);
     else ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_v2<32>, CTA_THREADS, 0);
     if (ce != cudaSuccess || per_sm < 1) return fail(ce, "occupancy");
     h->fused_grid = prop.multiProcessorCount * per_sm;     // one resident wave, persistent CTAs
@@ -675,7 +764,7 @@ void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad);
-  cudaFree(h->d_count); cudaFree(h->d_queue);
+  cudaFree(h->d_count); cudaFree(h->d_queue); cudaFree(h->d_order);
   if (h->have_streams) {
     for (int i = 0; i < PIADMM_CHUNKS; i++) { cudaStreamDestroy(h->cs[i]); cudaEventDestroy(h->ev_done[i]); }
     cudaEventDestroy(h->ev_start);
@@ -836,23 +925,35 @@ int piadmm_plant_step(piadmm_handle* h, void* stream) {
 }
 
 // one persistent kernel for the whole outer loop of the scenarios [s_lo, s_hi)
-static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, int* queue) {
+static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, int* queue, int range_id) {
   DevCtx c = h->c;
   c.s_lo = s_lo; c.s_hi = s_hi; c.queue = queue;
+  // the whole-batch order and the sub-batch orders share d_order: using one invalidates the other
+  c.order = (h->use_order && h->order_valid[range_id]) ? h->d_order : nullptr;
   CK(cudaMemsetAsync(queue, 0, sizeof(int), st));
-  const int pairs = h->lpq == 16 ? 2 : 1;
+  const int pairs = h->lpq == 16 ? (h->fused_ks ? KS_THREADS(16) / 32 : 2) : 1;
   int grid = (s_hi - s_lo + pairs - 1) / pairs;
   if (grid > h->fused_grid) grid = h->fused_grid;
-  if (h->lpq == 16) k_fused_v2<16><<<grid, CTA_THREADS, 0, st>>>(c);
+  if (h->fused_ks) {
+    if (h->lpq == 16) k_fused_ks<16><<<grid, KS_THREADS(16), 0, st>>>(c);
+    else k_fused_ks<32><<<grid, KS_THREADS(32), 0, st>>>(c);
+  } else if (h->lpq == 16) k_fused_v2<16><<<grid, CTA_THREADS, 0, st>>>(c);
   else k_fused_v2<32><<<grid, CTA_THREADS, 0, st>>>(c);
   LAUNCHED();
+  if (h->use_order && s_hi - s_lo >= 2 * grid) {      // learn the order for the next step (needs >1 scenario per slot)
+    k_order<<<1, 1024, 0, st>>>(c, h->d_order);
+    LAUNCHED();
+    if (range_id == 0) { for (int i = 1; i <= PIADMM_CHUNKS; i++) h->order_valid[i] = false; }
+    else h->order_valid[0] = false;
+    h->order_valid[range_id] = true;
+  } else h->order_valid[range_id] = false;
   return PIADMM_OK;
 }
 
 int piadmm_step(piadmm_handle* h, void* stream) {
   REQUIRE_BOUND();
   cudaStream_t st = (cudaStream_t)stream;
-  if (h->c.V == 2 && h->c.D == 1) return launch_fused(h, st, 0, h->c.S, h->d_queue);
+  if (h->c.V == 2 && h->c.D == 1) return launch_fused(h, st, 0, h->c.S, h->d_queue, 0);
   // generic V: phase kernels, one readback of the active-scenario count per outer iteration
   int rc = piadmm_begin_step(h, stream);
   for (int it = 0; it < h->c.I && rc == PIADMM_OK; it++) {
@@ -887,7 +988,7 @@ int piadmm_step_host(piadmm_handle* h, const double* xt, const double* spd, cons
       CK(cudaMemcpyAsync((double*)h->c.b.xt + a0 * 3, xt + a0 * 3, sizeof(double) * na * 3, cudaMemcpyHostToDevice, cs));
       CK(cudaMemcpyAsync((double*)h->c.b.spd + a0, spd + a0, sizeof(double) * na, cudaMemcpyHostToDevice, cs));
       CK(cudaMemcpyAsync((double*)h->c.b.refwin + a0 * 2 * np1, refwin + a0 * 2 * np1, sizeof(double) * na * 2 * np1, cudaMemcpyHostToDevice, cs));
-      int rc = launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch);
+      int rc = launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch, 1 + ch);
       if (rc) return rc;
       DevCtx c = h->c;
       c.s_lo = s0; c.s_hi = s1;

@@ -34,6 +34,7 @@ struct DevCtx {
   int own_lo, own_hi;                      // vehicles x-updated by this rank (multi-GPU vehicle sharding)
   int* queue;                              // work counter of the persistent fused kernel
   int s_lo, s_hi;                          // scenario range of this launch (fused kernel / plant step)
+  const int* order;                        // fused kernel: processing order of [s_lo,s_hi) (longest first), or NULL
 };
 
 // ------------------------------------------------------------------ group primitives
@@ -196,7 +197,11 @@ __device__ __forceinline__ void gj_step(double (&a)[LPQ], int k, int p, double* 
 
 // Vehicle problem: K = cI*I + c2*D2'D2 + cW*W + cT*T, T = A'A = 2I + 2 D1'D1 (tridiagonal: diag 4 at the
 // ends / 6 inside, off-diagonal -2); inverted in place.  rowbuf: LPQ doubles of shared memory per group.
-template <int LPQ>
+template <bool GT>
+__device__ __forceinline__ double tab_ld(const double* p) { return GT ? __ldg(p) : *p; }
+
+// GT: the tables are read from global memory (L1-resident, read-only path) instead of shared memory
+template <int LPQ, bool GT>
 __device__ __forceinline__ void build_Kinv_vehicle(double (&a)[LPQ], int N, int k, double cI, double c2, double cW,
                                                    double cT, const double* __restrict__ tabs, double* rowbuf) {
   const double* Wsm = tabs;
@@ -204,7 +209,7 @@ __device__ __forceinline__ void build_Kinv_vehicle(double (&a)[LPQ], int N, int 
   const double tdiag = (k == 0 || k == N - 1) ? 4.0 : 6.0;
 #pragma unroll
   for (int j = 0; j < LPQ; j++) {
-    double v = fma(cW, Wsm[j * LPQ + k], c2 * D2sm[j * LPQ + k]);
+    double v = fma(cW, tab_ld<GT>(Wsm + j * LPQ + k), c2 * tab_ld<GT>(D2sm + j * LPQ + k));
     if (j == k) v += fma(cT, tdiag, cI);
     if ((j == k + 1 || j == k - 1) && j < N) v = fma(cT, -2.0, v);
     if (k >= N) v = (j == k) ? 1.0 : 0.0;
@@ -215,14 +220,14 @@ __device__ __forceinline__ void build_Kinv_vehicle(double (&a)[LPQ], int N, int 
 }
 
 // Edge half problem in position space: K_t = c1*B1 + cT*B2 + cS*I_s, I_s = identity on lanes <= N-2.
-template <int LPQ>
+template <int LPQ, bool GT>
 __device__ __forceinline__ void build_Kinv_edge(double (&a)[LPQ], int N, int k, double c1, double cT, double cS,
                                                 const double* __restrict__ tabs, double* rowbuf) {
   const double* B1 = tabs + 2 * LPQ * LPQ;
   const double* B2 = tabs + 3 * LPQ * LPQ;
 #pragma unroll
   for (int j = 0; j < LPQ; j++) {
-    double v = fma(c1, B1[j * LPQ + k], cT * B2[j * LPQ + k]);
+    double v = fma(c1, tab_ld<GT>(B1 + j * LPQ + k), cT * tab_ld<GT>(B2 + j * LPQ + k));
     if (j == k && k <= N - 2) v += cS;
     if (k >= N) v = (j == k) ? 1.0 : 0.0;
     a[j] = v;
@@ -254,11 +259,18 @@ struct InnerOut {
 // rows become the identity (lane L <-> trajectory index L+2; lane N-1 holds the all-zero row of index 1)
 // and D, D' are 3-point stencils.  Termination is still evaluated on the steering-space residuals.
 // cvec follows that lane layout.  rhsbuf: LPQ doubles of shared memory per group, xch: 64 doubles per pair.
-template <int LPQ>
+//
+// KS (throughput variant of the fused kernel): the row of K^-1 is kept in SHARED memory (krow: this lane's
+// row, LPQ doubles, rows padded to LPQ+2 so that a quarter-warp LDS.128 is conflict free) instead of
+// registers, and the tables come from global memory.  That halves the register footprint, so that twice
+// as many scenario-warps are resident to hide the dependent FP64 / LDS / SHFL latencies.  The Gauss-Jordan
+// build still runs in registers; around a rebuild the ADMM state is parked in the (then free) row.
+#define PIADMM_KROW_STRIDE(LPQ) ((LPQ) + 2)
+template <int LPQ, bool KS>
 __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, int k, int half, bool edge,
                                                 double pI, double p2, double pW, double q, double a0, double a1,
                                                 double cvec, const double* __restrict__ tabs, double* rhsbuf,
-                                                double* xch) {
+                                                double* xch, double* krow) {
   const double al = ip.in_alpha, sg = ip.in_sigma, oma = 1.0 - al;
   const double l_u = -0.52359877559829887308, l_d = -0.34906585039886591538;  // -pi/6, -pi/9
   double Kinv[LPQ];
@@ -270,23 +282,34 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
   const bool inner_row = k < N - 1;
   const int srow = k <= N - 2;               // lane carries a real position row / a second-difference row of D
   const int d_up1 = srow && k >= 1, d_up2 = srow && k >= 2;          // x_j = t_j - 2 t_{j-1} + t_{j-2}
-  const int d_dn1 = k + 1 <= N - 2, d_dn2 = k + 2 <= N - 2;          // (D'v)_L = v_L - 2 v_{L+1} + v_{L+2}
-  if (edge) build_Kinv_edge<LPQ>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
-  else build_Kinv_vehicle<LPQ>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
+  if (edge) build_Kinv_edge<LPQ, KS>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
+  else build_Kinv_vehicle<LPQ, KS>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
+  if (KS) {
+#pragma unroll
+    for (int j = 0; j < LPQ; j += 2) *reinterpret_cast<double2*>(krow + j) = make_double2(Kinv[j], Kinv[j + 1]);
+  }
   InnerOut out;
   out.x = 0.0; out.iters = ip.in_max_iter; out.status = 1;
   bool done = false;
-  int chk = ip.in_check;
+  // everything the loop body reads is copied out of *ip first: ip points into the kernel parameter block
+  // through a generic pointer, and a load from it inside the loop is a real memory access on the chain
+  const int check_every = ip.in_check;
+  int chk = check_every;
+  int left = ip.in_max_iter;                 // iterations still allowed (counts down: one live register)
+  const double inv_na = 1.0 / na;
+  double tb = ip.beta * irho;                // hinge prox step bound beta / rho
 #pragma unroll 1
-  for (int it = 1; it <= ip.in_max_iter; it++) {
+  for (; left > 0; left--) {
     // ---- steering-space right-hand side  v = sigma x - q + A'(rho z - y)
     const double e = (rho * z3 - y3) - (rho * z2 - y2);
     double rhs = sg * x - q + ((rho * z0 - y0) - (rho * z1 - y1)) - e;
     add_if_ge(rhs, __shfl_up_sync(PIADMM_FULL, e, 1, LPQ), k, 1);      // + e_{k-1}
     if (edge) {                                                        // rhs_t = D' v + (rho zs - ys) on position rows
-      const double v1 = __shfl_down_sync(PIADMM_FULL, rhs, 1, LPQ), v2 = __shfl_down_sync(PIADMM_FULL, rhs, 2, LPQ);
-      fma_if(rhs, -2.0, v1, d_dn1);
-      fma_if(rhs, 1.0, v2, d_dn2);
+      // neighbours beyond lane N-2 must not contribute: zero them at the source (the clamped shuffle of the
+      // last lanes returns their own, zeroed, value), so the two stencil terms need no per-lane predicate
+      const double vm = srow ? rhs : 0.0;
+      const double v1 = __shfl_down_sync(PIADMM_FULL, vm, 1, LPQ), v2 = __shfl_down_sync(PIADMM_FULL, vm, 2, LPQ);
+      rhs = fma(-2.0, v1, rhs) + v2;
       fma_if(rhs, 1.0, fma(rho, zs, -ys), srow);
     }
     rhsbuf[k] = rhs;
@@ -297,10 +320,19 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
     for (int j = 0; j < LPQ; j += 4) {
       const double2 r0 = *reinterpret_cast<const double2*>(rhsbuf + j);
       const double2 r1 = *reinterpret_cast<const double2*>(rhsbuf + j + 2);
-      acc0 = fma(Kinv[j], r0.x, acc0);
-      acc1 = fma(Kinv[j + 1], r0.y, acc1);
-      acc2 = fma(Kinv[j + 2], r1.x, acc2);
-      acc3 = fma(Kinv[j + 3], r1.y, acc3);
+      if (KS) {
+        const double2 k0 = *reinterpret_cast<const double2*>(krow + j);
+        const double2 k1 = *reinterpret_cast<const double2*>(krow + j + 2);
+        acc0 = fma(k0.x, r0.x, acc0);
+        acc1 = fma(k0.y, r0.y, acc1);
+        acc2 = fma(k1.x, r1.x, acc2);
+        acc3 = fma(k1.y, r1.y, acc3);
+      } else {
+        acc0 = fma(Kinv[j], r0.x, acc0);
+        acc1 = fma(Kinv[j + 1], r0.y, acc1);
+        acc2 = fma(Kinv[j + 2], r1.x, acc2);
+        acc3 = fma(Kinv[j + 3], r1.y, acc3);
+      }
     }
     __syncwarp();
     double xt = (acc0 + acc1) + (acc2 + acc3);
@@ -332,18 +364,15 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       const double vo = partner<LPQ>(vs, xch, k, half);
       const double s0 = half == 0 ? vs : vo, s1 = half == 0 ? vo : vs;
       const double tau = fma(a1, s1, a0 * s0);
-      const double tb = ip.beta * irho;
-      double step;
-      if (tau >= cvec) step = 0.0;
-      else if (fma(tb, na, tau) <= cvec) step = tb;
-      else step = (cvec - tau) / na;
+      // prox of beta*max(0, c - a's): step = clamp((c - tau)/|a|^2, 0, beta/rho), branch free
+      const double step = dmin(dmax((cvec - tau) * inv_na, 0.0), tb);
       zn = fma(step, a_me, vs);
       ys = fma(rho, zrs - zn, ys);
       zs = zn;
     }
     // ---- termination / adaptive rho every in_check iterations (steering-space residuals)
     if (--chk == 0) {
-      chk = ip.in_check;
+      chk = check_every;
       double dd = shift_down1<LPQ>(x, k) - x;
       if (!inner_row) dd = 0.0;
       double rp = dmax(dmax(fabs(x - z0), fabs(-x - z1)), dmax(fabs(-dd - z2), fabs(dd - z3)));
@@ -379,7 +408,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       const bool conv = rp <= ip.in_eps_abs + ip.in_eps_rel * np && rd <= ip.in_eps_abs + ip.in_eps_rel * nd;
       if (conv && !done) {
         done = true;
-        out.x = x; out.iters = it; out.status = 0;
+        out.x = x; out.iters = ip.in_max_iter - left + 1; out.status = 0;
       }
       bool refac = false;
       double rn = rho;
@@ -394,9 +423,19 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       // (conv is identical in both halves of an edge by construction).
       if (__all_sync(PIADMM_FULL, done)) break;
       if (__any_sync(PIADMM_FULL, refac)) {
-        if (refac) { rho = rn; irho = 1.0 / rho; }
-        if (edge) build_Kinv_edge<LPQ>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
-        else build_Kinv_vehicle<LPQ>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
+        if (refac) { rho = rn; irho = 1.0 / rho; tb = ip.beta * irho; }
+        if (KS) {      // park the ADMM state in the row that is about to be rebuilt (frees 24 registers for the build)
+          krow[0] = x; krow[1] = z0; krow[2] = z1; krow[3] = z2; krow[4] = z3; krow[5] = y0; krow[6] = y1;
+          krow[7] = y2; krow[8] = y3; krow[9] = t; krow[10] = zs; krow[11] = ys;
+        }
+        if (edge) build_Kinv_edge<LPQ, KS>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
+        else build_Kinv_vehicle<LPQ, KS>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
+        if (KS) {
+          x = krow[0]; z0 = krow[1]; z1 = krow[2]; z2 = krow[3]; z3 = krow[4]; y0 = krow[5]; y1 = krow[6];
+          y2 = krow[7]; y3 = krow[8]; t = krow[9]; zs = krow[10]; ys = krow[11];
+#pragma unroll
+          for (int j = 0; j < LPQ; j += 2) *reinterpret_cast<double2*>(krow + j) = make_double2(Kinv[j], Kinv[j + 1]);
+        }
       }
     }
   }

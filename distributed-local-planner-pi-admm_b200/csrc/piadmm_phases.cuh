@@ -22,9 +22,9 @@ __device__ __forceinline__ void rollout_nonlinear(const piadmm_params& p, double
 }
 
 // ---- x-update of agent (s,i): casadi/main.py:81-106 --------------------------------------------
-template <int LPQ>
+template <int LPQ, bool KS>
 __device__ __noinline__ void dev_x_update(const DevCtx& c, int s, int i, bool valid, int k, int lane,
-                                             int half, const double* Wsm, double* gbuf, double* xch) {
+                                             int half, const double* Wsm, double* gbuf, double* xch, double* krow) {
   const piadmm_params& p = c.p;
   const int N = c.N;
   double x0 = 0.0, y0 = 0.0, th0 = 0.0, v = 1.0, rho = 1.0;
@@ -59,7 +59,7 @@ __device__ __noinline__ void dev_x_update(const DevCtx& c, int s, int i, bool va
   const double vec = (valid && k <= N) ? (w * e0 + sn * tx - cs * ty) : 0.0;
   const double q = 2.0 * g * apply_Mt<LPQ>(vec, k);
   const double pI = 2.0 * p.Pcost, p2 = valid ? 2.0 : 0.0, pW = valid ? 2.0 * w * g * g : 0.0;
-  InnerOut o = inner_solve<LPQ>(p, N, k, half, false, pI, p2, pW, q, 0.0, 0.0, 0.0, Wsm, gbuf, xch);
+  InnerOut o = inner_solve<LPQ, KS>(p, N, k, half, false, pI, p2, pW, q, 0.0, 0.0, 0.0, Wsm, gbuf, xch, krow);
   const double u = (k < N) ? round_scale(o.x, c.round_u_scale) : 0.0;
   double px, py;
   if (p.pos_nonlinear) {
@@ -89,10 +89,10 @@ __device__ __noinline__ void dev_x_update(const DevCtx& c, int s, int i, bool va
 // ---- edge step of edge e = (v0 < v1) of scenario s, half = which endpoint this group owns -------
 // casadi/main.py:121-162 with the convex edge problem (MATLAB ...PI_antiwindup.m:276-304,383-396)
 // and the three dual-update laws.  Writes hat, dual, integ, diff (own side), edge_res, rho_new.
-template <int LPQ>
+template <int LPQ, bool KS>
 __device__ __noinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0, int v1, int sl0, int sl1,
                                              bool last_edge, bool valid, int k, int lane, int half,
-                                             const double* Wsm, double* gbuf, double* xch) {
+                                             const double* Wsm, double* gbuf, double* xch, double* krow) {
   const piadmm_params& p = c.p;
   const int N = c.N;
   int vv[2] = {v0, v1}, sl[2] = {sl0, sl1};
@@ -144,7 +144,7 @@ __device__ __noinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0,
   const double a0 = valid ? -2.0 * g0 * (-lx * sn[0] + ly * cs[0]) : 0.0;
   const double a1 = valid ? 2.0 * g1 * (-lx * sn[1] + ly * cs[1]) : 0.0;
   const double pI = 2.0 * p.Pcost, pW = valid ? rho * g * g : 0.0;
-  InnerOut o = inner_solve<LPQ>(p, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch);
+  InnerOut o = inner_solve<LPQ, KS>(p, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow);
   // z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158)
   const double uh = (k < N) ? round_scale(o.x, c.round_edge_scale) : 0.0;
   double hx, hy, hth;
