@@ -82,7 +82,7 @@ __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
-  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
+  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[64];
   Who<LPQ> w;
   const long agents = (long)c.S * c.V, items = (agents + groups_per_cta<LPQ>() - 1) / groups_per_cta<LPQ>();
@@ -234,7 +234,7 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
-  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
+  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[64];
   Who<LPQ> w;
   const long pairs = (long)c.S * c.E, items = (pairs + pairs_per_cta<LPQ>() - 1) / pairs_per_cta<LPQ>();
@@ -425,7 +425,7 @@ __global__ void __launch_bounds__(1024) k_order(const __grid_constant__ DevCtx c
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 7 : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
-  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][LPQ];
+  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[64];
   __shared__ int s_next;
   load_W<LPQ>(c, Wsm);
@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 7 : 5) k_fused_v2(con
 template <int LPQ>
 __global__ void __launch_bounds__(KS_THREADS(LPQ), LPQ == 16 ? 7 : 12) k_fused_ks(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double krows[KS_GROUPS(LPQ)][LPQ * PIADMM_KROW_STRIDE(LPQ)];
-  __shared__ __align__(16) double gbuf[KS_GROUPS(LPQ)][LPQ];
+  __shared__ __align__(16) double gbuf[KS_GROUPS(LPQ)][2 * LPQ];
   __shared__ __align__(16) double xch[64];
   __shared__ int s_next;
   Who<LPQ> w;

@@ -158,35 +158,49 @@ __device__ __forceinline__ void fma_if(double& acc, double a, double b, int pred
   asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %3, 0;\n\t@p fma.rn.f64 %0, %1, %2, %0;\n\t}" : "+d"(acc) : "d"(a), "d"(b), "r"(pred));
 }
 
-// One step of the in-place Gauss-Jordan inversion of an SPD matrix held one row per lane.
+// One 2x2-BLOCK step of the in-place Gauss-Jordan inversion of an SPD matrix held one row per lane.
 //
-// The elimination loop is ROLLED (small code, no instruction-cache thrash) and still uses only
-// compile-time register indices: every step rotates the row by one position, so the pivot column
-// is always a[0]; after LPQ steps the rotation has come full circle.  Padded rows/columns (>= N)
-// are identity, for them a step is an exact no-op.
-//   pivot lane p : publishes its raw row (rowbuf[0] = 1/pivot) and clears its registers, so that the
-//                  common update a[j-1] = nf*row[j] + a[j] yields piv*row[j] exactly (nf = piv);
-//   other lanes  : nf = -a[0]*piv:  a[j-1] = a[j] - a[0]*piv*row[j],  a[LPQ-1] = -a[0]*piv.
+// Two pivots (rows/columns p, p+1; p even) are eliminated per step, so a build costs LPQ/2 instead of LPQ
+// rounds of "publish pivot rows -> warp barrier -> broadcast read -> reciprocal -> update": the rounds are
+// latency chains (the builds were ~20 % of the fused kernel's time with scalar pivots), the flop count is
+// unchanged.  The loop stays ROLLED with compile-time register indices: every step rotates the row by two
+// positions, so the pivot columns are always a[0], a[1]; after LPQ/2 steps the rotation has come full circle.
+// Padded rows/columns (>= N) are identity and decoupled (a 2x2 block [[a,0],[0,1]] is handled exactly).
+//   pivot lanes    : publish their raw rows and clear their registers, so that the common update
+//                    a[j-2] = c0*rowp[j] + c1*rowq[j] + a[j] yields (B^-1 [rowp; rowq])_j with (c0,c1) = B^-1 row;
+//   other lanes    : (c0,c1) = -[a0 a1] B^-1; the new inverse columns a[LPQ-2], a[LPQ-1] are (c0,c1) for everyone.
+// rowbuf: 2*LPQ doubles of shared memory per group.
 template <int LPQ>
-__device__ __forceinline__ void gj_step(double (&a)[LPQ], int k, int p, double* rowbuf) {
-  const double f = a[0];
-  if (k == p) {
-    rowbuf[0] = 1.0 / f;
+__device__ __forceinline__ void gj_step2(double (&a)[LPQ], int k, int p, double* rowbuf) {
+  const double f0 = a[0], f1 = a[1];
+  const bool piv = (k >> 1) == (p >> 1);
+  if (piv) {
+    double* rb = rowbuf + (k & 1) * LPQ;
 #pragma unroll
-    for (int j = 1; j < LPQ; j++) rowbuf[j] = a[j];
+    for (int j = 0; j < LPQ; j += 2) *reinterpret_cast<double2*>(rb + j) = make_double2(a[j], a[j + 1]);
 #pragma unroll
     for (int j = 0; j < LPQ; j++) a[j] = 0.0;
   }
   __syncwarp();
-  const double piv = rowbuf[0];
-  const double nf = (k == p) ? piv : -f * piv;
-#pragma unroll
-  for (int j = 0; j < LPQ; j += 2) {             // in place, increasing j: a[j-1] <- a[j] + nf*row[j]
-    const double2 r = *reinterpret_cast<const double2*>(rowbuf + j);
-    if (j > 0) a[j - 1] = fma(nf, r.x, a[j]);
-    a[j] = fma(nf, r.y, a[j + 1]);
+  const double2 bp = *reinterpret_cast<const double2*>(rowbuf);         // b00 b01
+  const double2 bq = *reinterpret_cast<const double2*>(rowbuf + LPQ);   // b10 b11
+  const double idet = 1.0 / fma(bp.x, bq.y, -bp.y * bq.x);
+  // non-pivot: (c0,c1) = -[f0 f1] B^-1 = idet * (f1*b10 - f0*b11 , f0*b01 - f1*b00)
+  double c0 = fma(f1, bq.x, -f0 * bq.y), c1 = fma(f0, bp.y, -f1 * bp.x);
+  if (piv) {                                                             // rows of B^-1 = idet*[[b11,-b01],[-b10,b00]]
+    c0 = (k & 1) ? -bq.x : bq.y;
+    c1 = (k & 1) ? bp.x : -bp.y;
   }
-  a[LPQ - 1] = nf;
+  c0 *= idet; c1 *= idet;
+#pragma unroll
+  for (int j = 2; j < LPQ; j += 2) {             // in place, increasing j: a[j-2] <- a[j] + c0*rowp[j] + c1*rowq[j]
+    const double2 rp = *reinterpret_cast<const double2*>(rowbuf + j);
+    const double2 rq = *reinterpret_cast<const double2*>(rowbuf + LPQ + j);
+    a[j - 2] = fma(c0, rp.x, fma(c1, rq.x, a[j]));
+    a[j - 1] = fma(c0, rp.y, fma(c1, rq.y, a[j + 1]));
+  }
+  a[LPQ - 2] = c0;
+  a[LPQ - 1] = c1;
   __syncwarp();
 }
 
@@ -196,7 +210,7 @@ __device__ __forceinline__ void gj_step(double (&a)[LPQ], int k, int p, double* 
 #define PIADMM_NTAB 4
 
 // Vehicle problem: K = cI*I + c2*D2'D2 + cW*W + cT*T, T = A'A = 2I + 2 D1'D1 (tridiagonal: diag 4 at the
-// ends / 6 inside, off-diagonal -2); inverted in place.  rowbuf: LPQ doubles of shared memory per group.
+// ends / 6 inside, off-diagonal -2); inverted in place.  rowbuf: 2*LPQ doubles of shared memory per group.
 template <bool GT>
 __device__ __forceinline__ double tab_ld(const double* p) { return GT ? __ldg(p) : *p; }
 
@@ -216,7 +230,7 @@ __device__ __forceinline__ void build_Kinv_vehicle(double (&a)[LPQ], int N, int 
     a[j] = v;
   }
 #pragma unroll 1
-  for (int p = 0; p < LPQ; p++) gj_step<LPQ>(a, k, p, rowbuf);
+  for (int p = 0; p < LPQ; p += 2) gj_step2<LPQ>(a, k, p, rowbuf);
 }
 
 // Edge half problem in position space: K_t = c1*B1 + cT*B2 + cS*I_s, I_s = identity on lanes <= N-2.
@@ -233,7 +247,7 @@ __device__ __forceinline__ void build_Kinv_edge(double (&a)[LPQ], int N, int k, 
     a[j] = v;
   }
 #pragma unroll 1
-  for (int p = 0; p < LPQ; p++) gj_step<LPQ>(a, k, p, rowbuf);
+  for (int p = 0; p < LPQ; p += 2) gj_step2<LPQ>(a, k, p, rowbuf);
 }
 
 // sum_{L>=j} (L-j+1) v_L  (= M'(.) for a vector given on the position rows), v = 0 on masked lanes
@@ -258,7 +272,8 @@ struct InnerOut {
 // iterates up to rounding, but M and M' (two chained warp scans each) drop out of the loop: the position
 // rows become the identity (lane L <-> trajectory index L+2; lane N-1 holds the all-zero row of index 1)
 // and D, D' are 3-point stencils.  Termination is still evaluated on the steering-space residuals.
-// cvec follows that lane layout.  rhsbuf: LPQ doubles of shared memory per group, xch: 64 doubles per pair.
+// cvec follows that lane layout.  rhsbuf: 2*LPQ doubles of shared memory per group (the mat-vec uses the first
+// LPQ, the K^-1 builds all of it), xch: 64 doubles per pair.
 //
 // KS (throughput variant of the fused kernel): the row of K^-1 is kept in SHARED memory (krow: this lane's
 // row, LPQ doubles, rows padded to LPQ+2 so that a quarter-warp LDS.128 is conflict free) instead of
