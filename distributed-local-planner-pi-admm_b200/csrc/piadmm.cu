@@ -8,6 +8,9 @@
 #include "piadmm_phases.cuh"
 
 #define CTA_THREADS 64
+#ifndef FUSED16_MIN_CTAS
+#define FUSED16_MIN_CTAS 7   // resident CTAs per SM the LPQ==16 fused kernel is compiled for (register budget)
+#endif
 #define PIADMM_CHUNKS 4   // sub-batches of piadmm_step_host (copies of one overlap the kernels of the others)
 
 // ------------------------------------------------------------------ thread -> (pair, half, k)
@@ -390,40 +393,46 @@ __device__ __forceinline__ int next_scenario(const DevCtx& c, const Who<LPQ>& w,
 // about two scenarios per resident warp slot, starting the long ones first removes most of the tail in which
 // SMs idle while the last warps finish.  Results never depend on the order.
 #define ORDER_BUCKETS 512
+__device__ __forceinline__ int order_bucket(const DevCtx& c, int s, float scale) {
+  const float cost = (float)c.b.veh_inner[s] + 4.0f * (float)c.b.edge_inner[s];
+  const int b = ORDER_BUCKETS - 1 - (int)(cost * scale);                 // bucket 0 = longest
+  return b < 0 ? 0 : b;
+}
 __global__ void __launch_bounds__(1024) k_order(const __grid_constant__ DevCtx c, int* order) {
   __shared__ unsigned hist[ORDER_BUCKETS];
-  __shared__ unsigned long long cmax;
-  const int n = c.s_hi - c.s_lo;
+  __shared__ float wmax[32];
+  const int n = c.s_hi - c.s_lo, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int b = threadIdx.x; b < ORDER_BUCKETS; b += blockDim.x) hist[b] = 0;
-  if (threadIdx.x == 0) cmax = 1;
+  float m = 1.0f;
+  for (int t = threadIdx.x; t < n; t += blockDim.x)
+    m = fmaxf(m, (float)c.b.veh_inner[c.s_lo + t] + 4.0f * (float)c.b.edge_inner[c.s_lo + t]);
+  for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(PIADMM_FULL, m, o));
+  if (lane == 0) wmax[warp] = m;
   __syncthreads();
-  unsigned long long m = 0;
-  for (int t = threadIdx.x; t < n; t += blockDim.x) {
-    const unsigned long long cost = (unsigned long long)c.b.veh_inner[c.s_lo + t] + 4ull * c.b.edge_inner[c.s_lo + t];
-    m = cost > m ? cost : m;
+  m = wmax[lane];
+  for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(PIADMM_FULL, m, o));
+  const float scale = (ORDER_BUCKETS - 1) / m;
+  for (int t = threadIdx.x; t < n; t += blockDim.x) atomicAdd(&hist[order_bucket(c, c.s_lo + t, scale)], 1u);
+  __syncthreads();
+  if (warp == 0) {                            // exclusive scan of the 512 bucket counts by one warp
+    unsigned v[ORDER_BUCKETS / 32], tot = 0;
+#pragma unroll
+    for (int i = 0; i < ORDER_BUCKETS / 32; i++) { v[i] = hist[lane * (ORDER_BUCKETS / 32) + i]; tot += v[i]; }
+    unsigned inc = tot;
+    for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(PIADMM_FULL, inc, o); if (lane >= o) inc += t; }
+    unsigned run = inc - tot;
+#pragma unroll
+    for (int i = 0; i < ORDER_BUCKETS / 32; i++) { hist[lane * (ORDER_BUCKETS / 32) + i] = run; run += v[i]; }
   }
-  atomicMax(&cmax, m);
-  __syncthreads();
-  const unsigned long long mx = cmax;
-  for (int t = threadIdx.x; t < n; t += blockDim.x) {
-    const unsigned long long cost = (unsigned long long)c.b.veh_inner[c.s_lo + t] + 4ull * c.b.edge_inner[c.s_lo + t];
-    atomicAdd(&hist[ORDER_BUCKETS - 1 - (int)(cost * (ORDER_BUCKETS - 1) / mx)], 1u);   // bucket 0 = longest
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {                     // exclusive scan, 512 entries
-    unsigned run = 0;
-    for (int b = 0; b < ORDER_BUCKETS; b++) { const unsigned v = hist[b]; hist[b] = run; run += v; }
-  }
   __syncthreads();
   for (int t = threadIdx.x; t < n; t += blockDim.x) {
-    const unsigned long long cost = (unsigned long long)c.b.veh_inner[c.s_lo + t] + 4ull * c.b.edge_inner[c.s_lo + t];
-    const unsigned pos = atomicAdd(&hist[ORDER_BUCKETS - 1 - (int)(cost * (ORDER_BUCKETS - 1) / mx)], 1u);
+    const unsigned pos = atomicAdd(&hist[order_bucket(c, c.s_lo + t, scale)], 1u);
     order[c.s_lo + pos] = c.s_lo + t;
   }
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 7 : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[64];

@@ -309,16 +309,21 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
   // everything the loop body reads is copied out of *ip first: ip points into the kernel parameter block
   // through a generic pointer, and a load from it inside the loop is a real memory access on the chain
   const int check_every = ip.in_check;
-  int chk = check_every;
-  int left = ip.in_max_iter;                 // iterations still allowed (counts down: one live register)
+  int left = ip.in_max_iter;                 // iterations still allowed
   const double inv_na = 1.0 / na;
   double tb = ip.beta * irho;                // hinge prox step bound beta / rho
+  // two nested loops: the hot one counts a block of in_check iterations down in ONE register; `left`, the
+  // termination test and the K^-1 rebuild are touched once per block
 #pragma unroll 1
-  for (; left > 0; left--) {
+  while (left > 0) {
+   const int blk = left < check_every ? left : check_every;
+#pragma unroll 1
+   for (int cnt = blk; cnt > 0; cnt--) {
     // ---- steering-space right-hand side  v = sigma x - q + A'(rho z - y)
     const double e = (rho * z3 - y3) - (rho * z2 - y2);
     double rhs = sg * x - q + ((rho * z0 - y0) - (rho * z1 - y1)) - e;
-    add_if_ge(rhs, __shfl_up_sync(PIADMM_FULL, e, 1, LPQ), k, 1);      // + e_{k-1}
+    // + e_{k-1}: lane 0 reads the last lane of the group, a padded lane (N <= LPQ-1) whose e is exactly 0
+    rhs += __shfl_sync(PIADMM_FULL, e, (k - 1) & (LPQ - 1), LPQ);
     if (edge) {                                                        // rhs_t = D' v + (rho zs - ys) on position rows
       // neighbours beyond lane N-2 must not contribute: zero them at the source (the clamped shuffle of the
       // last lanes returns their own, zeroed, value), so the two stencil terms need no per-lane predicate
@@ -359,7 +364,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       fma_if(xt, 1.0, u2, d_up2);
     }
     // ---- z~ = A x~, relaxation, projection, dual update
-    double d = shift_down1<LPQ>(xt, k) - xt;
+    double d = __shfl_down_sync(PIADMM_FULL, xt, 1, LPQ) - xt;        // the last lane is padded (xt = 0): no clamp needed
     if (!inner_row) d = 0.0;
     const double zr0 = fma(al, xt, oma * z0);
     const double zr1 = fma(-al, xt, oma * z1);
@@ -385,9 +390,10 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       ys = fma(rho, zrs - zn, ys);
       zs = zn;
     }
+   }
+   left -= blk;
     // ---- termination / adaptive rho every in_check iterations (steering-space residuals)
-    if (--chk == 0) {
-      chk = check_every;
+    if (blk == check_every) {
       double dd = shift_down1<LPQ>(x, k) - x;
       if (!inner_row) dd = 0.0;
       double rp = dmax(dmax(fabs(x - z0), fabs(-x - z1)), dmax(fabs(-dd - z2), fabs(dd - z3)));
@@ -423,7 +429,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       const bool conv = rp <= ip.in_eps_abs + ip.in_eps_rel * np && rd <= ip.in_eps_abs + ip.in_eps_rel * nd;
       if (conv && !done) {
         done = true;
-        out.x = x; out.iters = ip.in_max_iter - left + 1; out.status = 0;
+        out.x = x; out.iters = ip.in_max_iter - left; out.status = 0;
       }
       bool refac = false;
       double rn = rho;
