@@ -144,6 +144,8 @@ _PROTOS = {
     "piadmm_step": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_plant_step": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_step_host": (C.c_int, [C.c_void_p] + [C.c_void_p] * 8 + [C.c_void_p]),
+    "piadmm_set_reference": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "piadmm_step_host_at": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 6 + [C.c_void_p]),
     "piadmm_launch_count": (C.c_int64, [C.c_void_p]),
     "piadmm_fp64_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     # include/obca_consensus.h (struct pointers passed as void*: obca_consensus.py owns the ctypes mirrors)

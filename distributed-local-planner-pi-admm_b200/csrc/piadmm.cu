@@ -11,7 +11,7 @@
 #ifndef FUSED16_MIN_CTAS
 #define FUSED16_MIN_CTAS 7   // resident CTAs per SM the LPQ==16 fused kernel is compiled for (register budget)
 #endif
-#define PIADMM_CHUNKS 4   // sub-batches of piadmm_step_host (copies of one overlap the kernels of the others)
+#define PIADMM_CHUNKS 8   // max sub-batches of piadmm_step_host (copies of one overlap the kernels of the others)
 
 // ------------------------------------------------------------------ thread -> (pair, half, k)
 template <int LPQ>
@@ -345,6 +345,19 @@ __global__ void k_count_active(const __grid_constant__ DevCtx c, int* out) {
   if ((threadIdx.x & 31) == 0 && m) atomicAdd(out, __popc(m));
 }
 
+// refwin[s,v,c,k] = ref[s,v,c,*step + k], k = 0..N: the window cost_function_primal slices out of the resident
+// reference (casadi/PI_ADMM_class.py:116-117), scenarios [s_lo,s_hi)
+__global__ void k_refwin(const __grid_constant__ DevCtx c, const double* __restrict__ ref, int T, const int* step) {
+  const int np1 = c.N + 1, st = *step;
+  const size_t rows0 = (size_t)c.s_lo * c.V * 2, n = (size_t)(c.s_hi - c.s_lo) * c.V * 2 * np1;
+  double* out = const_cast<double*>(c.b.refwin);
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = rows0 + t / np1;
+    const int k = (int)(t % np1);
+    out[row * np1 + k] = ref[row * T + st + k];
+  }
+}
+
 __global__ void k_plant(const __grid_constant__ DevCtx c) {
   const long a = (long)c.s_lo * c.V + (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= (long)c.s_hi * c.V) return;
@@ -581,8 +594,20 @@ struct piadmm_handle {
   int* d_order;               // [S] longest-first processing order learnt from the previous step
   bool use_order;             // PIADMM_LPT=0 disables the hint
   bool order_valid[PIADMM_CHUNKS + 1];   // per launch range: [0] whole batch, [1+ch] sub-batch ch
-  cudaStream_t cs[PIADMM_CHUNKS];
-  cudaEvent_t ev_start, ev_done[PIADMM_CHUNKS];
+  cudaStream_t cs[PIADMM_CHUNKS], cs_main;
+  cudaEvent_t ev_start, ev_user, ev_done[PIADMM_CHUNKS];
+  int n_chunks;               // sub-batches used by piadmm_step_host (PIADMM_NCHUNKS, default 2)
+  double* d_ref;              // resident reference trajectories [S,V,2,T] (piadmm_set_reference), library owned
+  int ref_T;
+  int* h_step;                // pinned host word holding num_step of the current piadmm_step_host_at call
+  int* d_step;                //   ... and its device copy (a graph memcpy node refreshes it)
+  // cached CUDA graph of the whole host-buffer step (copies + kernels of all sub-batches): one cudaGraphLaunch
+  // instead of ~45 stream API calls per step
+  bool use_graph;             // PIADMM_GRAPH=0 disables
+  cudaGraphExec_t gexec;
+  const void* gkey[9];        // host pointers + order-validity bits the graph was captured for
+  bool gvalid_after[PIADMM_CHUNKS + 1];
+  int64_t glaunches;
   bool have_streams;
   int64_t launches;
   std::string err;
@@ -617,6 +642,10 @@ static int check_params(const piadmm_params* p, int V, int D, std::string& err) 
   if (p->dual_mode < 0 || p->dual_mode > 2) { err = "bad dual_mode"; return PIADMM_E_ARG; }
   if (p->al_all && D < V - 1) { err = "al_all needs D >= V-1"; return PIADMM_E_ARG; }
   return PIADMM_OK;
+}
+
+static void drop_graph(piadmm_handle* h) {       // kernel arguments are baked into the captured graph
+  if (h->gexec) { cudaGraphExecDestroy(h->gexec); h->gexec = nullptr; }
 }
 
 extern "C" {
@@ -657,7 +686,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   }
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
-  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false;
+  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false; h->gexec = nullptr; h->d_ref = nullptr; h->ref_T = 0; h->h_step = nullptr; h->d_step = nullptr;
   h->c.p = *p; h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
   h->c.N = p->num_ho; h->c.I = p->iter_num;
   h->c.own_lo = 0; h->c.own_hi = V;
@@ -737,6 +766,18 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     if ((ce = cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming)) != cudaSuccess) return fail(ce, "event");
   }
   if ((ce = cudaEventCreateWithFlags(&h->ev_start, cudaEventDisableTiming)) != cudaSuccess) return fail(ce, "event");
+  if ((ce = cudaEventCreateWithFlags(&h->ev_user, cudaEventDisableTiming)) != cudaSuccess) return fail(ce, "event");
+  if ((ce = cudaStreamCreateWithFlags(&h->cs_main, cudaStreamNonBlocking)) != cudaSuccess) return fail(ce, "stream");
+  {
+    const char* e = getenv("PIADMM_NCHUNKS");
+    int n = e ? atoi(e) : 2;
+    h->n_chunks = n < 1 ? 1 : (n > PIADMM_CHUNKS ? PIADMM_CHUNKS : n);
+    e = getenv("PIADMM_GRAPH");
+    h->use_graph = !(e && strcmp(e, "0") == 0);
+    h->gexec = nullptr; h->glaunches = 0;
+  }
+  if ((ce = cudaMallocHost(&h->h_step, sizeof(int))) != cudaSuccess) return fail(ce, "h_step");
+  if ((ce = cudaMalloc(&h->d_step, sizeof(int))) != cudaSuccess) return fail(ce, "d_step");
   h->have_streams = true;
   h->c.queue = h->d_queue;
   {
@@ -773,10 +814,12 @@ void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad);
-  cudaFree(h->d_count); cudaFree(h->d_queue); cudaFree(h->d_order);
+  cudaFree(h->d_count); cudaFree(h->d_queue); cudaFree(h->d_order); cudaFree(h->d_ref); cudaFree(h->d_step);
+  if (h->h_step) cudaFreeHost(h->h_step);
   if (h->have_streams) {
     for (int i = 0; i < PIADMM_CHUNKS; i++) { cudaStreamDestroy(h->cs[i]); cudaEventDestroy(h->ev_done[i]); }
-    cudaEventDestroy(h->ev_start);
+    cudaEventDestroy(h->ev_start); cudaEventDestroy(h->ev_user); cudaStreamDestroy(h->cs_main);
+    if (h->gexec) cudaGraphExecDestroy(h->gexec);
   }
   delete h;
 }
@@ -788,6 +831,7 @@ int piadmm_set_params(piadmm_handle* h, const piadmm_params* p) {
   if (p->num_ho != h->c.N || p->iter_num != h->c.I) { h->err = "num_ho / iter_num are fixed at create time"; return PIADMM_E_ARG; }
   h->c.p = *p;
   h->c.round_u_scale = pow10i(p->round_u); h->c.round_edge_scale = pow10i(p->round_edge);
+  drop_graph(h);
   return PIADMM_OK;
 }
 
@@ -798,6 +842,7 @@ int piadmm_bind(piadmm_handle* h, const piadmm_buffers* b) {
     if (!ptrs[i]) { h->err = "piadmm_bind: NULL buffer at field index " + std::to_string(i); return PIADMM_E_UNBOUND; }
   h->c.b = *b;
   h->bound = true;
+  drop_graph(h);
   return PIADMM_OK;
 }
 
@@ -977,46 +1022,115 @@ int piadmm_step(piadmm_handle* h, void* stream) {
   return rc;
 }
 
-int piadmm_step_host(piadmm_handle* h, const double* xt, const double* spd, const double* refwin,
-                     double* u_out, double* pos_out, double* xt_next_out, int32_t* curr_iter_out,
-                     int32_t* n_outer_out, void* stream) {
-  REQUIRE_BOUND();
-  if (!xt || !spd || !refwin) return PIADMM_E_ARG;
+struct HostStepArgs {
+  const double *xt, *spd, *refwin;     // spd / refwin NULL: resident (bound spd buffer, piadmm_set_reference)
+  double *u_out, *pos_out, *xt_next_out;
+  int32_t *curr_iter_out, *n_outer_out;
+};
+
+// Independent scenarios: the batch is split into n_chunks sub-batches on internal streams (forked from and
+// joined back into `ms`), so that the H2D / D2H copies of one sub-batch overlap the kernels of the others.
+static int enqueue_chunked_host_step(piadmm_handle* h, cudaStream_t ms, const HostStepArgs& a) {
+  const size_t N = h->c.N, np1 = N + 1;
+  const int nch = h->n_chunks;
+  if (!a.refwin) CK(cudaMemcpyAsync(h->d_step, h->h_step, sizeof(int), cudaMemcpyHostToDevice, ms));
+  CK(cudaEventRecord(h->ev_start, ms));
+  for (int ch = 0; ch < nch; ch++) {
+    cudaStream_t cs = h->cs[ch];
+    const int s0 = (int)((long)h->c.S * ch / nch), s1 = (int)((long)h->c.S * (ch + 1) / nch);
+    const size_t a0 = (size_t)s0 * 2, na = (size_t)(s1 - s0) * 2;
+    CK(cudaStreamWaitEvent(cs, h->ev_start, 0));
+    CK(cudaMemcpyAsync((double*)h->c.b.xt + a0 * 3, a.xt + a0 * 3, sizeof(double) * na * 3, cudaMemcpyHostToDevice, cs));
+    if (a.spd) CK(cudaMemcpyAsync((double*)h->c.b.spd + a0, a.spd + a0, sizeof(double) * na, cudaMemcpyHostToDevice, cs));
+    DevCtx c = h->c;
+    c.s_lo = s0; c.s_hi = s1;
+    if (a.refwin) {
+      CK(cudaMemcpyAsync((double*)h->c.b.refwin + a0 * 2 * np1, a.refwin + a0 * 2 * np1, sizeof(double) * na * 2 * np1, cudaMemcpyHostToDevice, cs));
+    } else {
+      k_refwin<<<(unsigned)((na * 2 * np1 + 255) / 256), 256, 0, cs>>>(c, h->d_ref, h->ref_T, h->d_step);
+      LAUNCHED();
+    }
+    int rc = launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch, 1 + ch);
+    if (rc) return rc;
+    k_plant<<<(unsigned)((na + 127) / 128), 128, 0, cs>>>(c);
+    LAUNCHED();
+    if (a.u_out) CK(cudaMemcpyAsync(a.u_out + a0 * N, h->c.b.u + a0 * N, sizeof(double) * na * N, cudaMemcpyDeviceToHost, cs));
+    if (a.pos_out) CK(cudaMemcpyAsync(a.pos_out + a0 * 2 * np1, h->c.b.pos + a0 * 2 * np1, sizeof(double) * na * 2 * np1, cudaMemcpyDeviceToHost, cs));
+    if (a.xt_next_out) CK(cudaMemcpyAsync(a.xt_next_out + a0 * 3, h->c.b.xt_next + a0 * 3, sizeof(double) * na * 3, cudaMemcpyDeviceToHost, cs));
+    if (a.curr_iter_out) CK(cudaMemcpyAsync(a.curr_iter_out + s0, h->c.b.curr_iter + s0, sizeof(int32_t) * (s1 - s0), cudaMemcpyDeviceToHost, cs));
+    if (a.n_outer_out) CK(cudaMemcpyAsync(a.n_outer_out + s0, h->c.b.n_outer + s0, sizeof(int32_t) * (s1 - s0), cudaMemcpyDeviceToHost, cs));
+    CK(cudaEventRecord(h->ev_done[ch], cs));
+    CK(cudaStreamWaitEvent(ms, h->ev_done[ch], 0));
+  }
+  return PIADMM_OK;
+}
+
+static bool pinned_or_null(const void* p) {
+  if (!p) return true;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+
+static int step_host_impl(piadmm_handle* h, const double* xt, const double* spd, const double* refwin,
+                          double* u_out, double* pos_out, double* xt_next_out, int32_t* curr_iter_out,
+                          int32_t* n_outer_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   const size_t SV = (size_t)h->c.S * h->c.V, N = h->c.N;
-  if (h->c.V == 2 && h->c.D == 1 && h->c.S >= 64 * PIADMM_CHUNKS) {
-    // Independent scenarios: split the batch into PIADMM_CHUNKS sub-batches on internal streams so that the
-    // H2D / D2H copies of one sub-batch overlap the (latency-bound) kernels of the others.
-    const size_t np1 = N + 1;
-    CK(cudaEventRecord(h->ev_start, st));
-    for (int ch = 0; ch < PIADMM_CHUNKS; ch++) {
-      cudaStream_t cs = h->cs[ch];
-      const int s0 = (int)((long)h->c.S * ch / PIADMM_CHUNKS), s1 = (int)((long)h->c.S * (ch + 1) / PIADMM_CHUNKS);
-      const size_t a0 = (size_t)s0 * 2, na = (size_t)(s1 - s0) * 2;
-      CK(cudaStreamWaitEvent(cs, h->ev_start, 0));
-      CK(cudaMemcpyAsync((double*)h->c.b.xt + a0 * 3, xt + a0 * 3, sizeof(double) * na * 3, cudaMemcpyHostToDevice, cs));
-      CK(cudaMemcpyAsync((double*)h->c.b.spd + a0, spd + a0, sizeof(double) * na, cudaMemcpyHostToDevice, cs));
-      CK(cudaMemcpyAsync((double*)h->c.b.refwin + a0 * 2 * np1, refwin + a0 * 2 * np1, sizeof(double) * na * 2 * np1, cudaMemcpyHostToDevice, cs));
-      int rc = launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch, 1 + ch);
-      if (rc) return rc;
-      DevCtx c = h->c;
-      c.s_lo = s0; c.s_hi = s1;
-      k_plant<<<(unsigned)((na + 127) / 128), 128, 0, cs>>>(c);
-      LAUNCHED();
-      if (u_out) CK(cudaMemcpyAsync(u_out + a0 * N, h->c.b.u + a0 * N, sizeof(double) * na * N, cudaMemcpyDeviceToHost, cs));
-      if (pos_out) CK(cudaMemcpyAsync(pos_out + a0 * 2 * np1, h->c.b.pos + a0 * 2 * np1, sizeof(double) * na * 2 * np1, cudaMemcpyDeviceToHost, cs));
-      if (xt_next_out) CK(cudaMemcpyAsync(xt_next_out + a0 * 3, h->c.b.xt_next + a0 * 3, sizeof(double) * na * 3, cudaMemcpyDeviceToHost, cs));
-      if (curr_iter_out) CK(cudaMemcpyAsync(curr_iter_out + s0, h->c.b.curr_iter + s0, sizeof(int32_t) * (s1 - s0), cudaMemcpyDeviceToHost, cs));
-      if (n_outer_out) CK(cudaMemcpyAsync(n_outer_out + s0, h->c.b.n_outer + s0, sizeof(int32_t) * (s1 - s0), cudaMemcpyDeviceToHost, cs));
-      CK(cudaEventRecord(h->ev_done[ch], cs));
-      CK(cudaStreamWaitEvent(st, h->ev_done[ch], 0));
+  if (h->c.V == 2 && h->c.D == 1 && h->c.S >= 64 * h->n_chunks) {
+    const HostStepArgs a = {xt, spd, refwin, u_out, pos_out, xt_next_out, curr_iter_out, n_outer_out};
+    cudaStream_t ms = h->cs_main;                 // internal origin stream (the caller's may be the legacy stream,
+    CK(cudaEventRecord(h->ev_user, st));          //  which cannot be captured): ordered after the caller's work
+    CK(cudaStreamWaitEvent(ms, h->ev_user, 0));
+    bool graph = h->use_graph && pinned_or_null(xt) && pinned_or_null(spd) && pinned_or_null(refwin) &&
+                 pinned_or_null(u_out) && pinned_or_null(pos_out) && pinned_or_null(xt_next_out) &&
+                 pinned_or_null(curr_iter_out) && pinned_or_null(n_outer_out);
+    if (graph) {
+      uintptr_t bits = 0;
+      for (int i = 0; i <= PIADMM_CHUNKS; i++) bits |= (uintptr_t)(h->order_valid[i] ? 1 : 0) << i;
+      const void* key[9] = {xt, spd, refwin, u_out, pos_out, xt_next_out, curr_iter_out, n_outer_out, (const void*)bits};
+      if (!h->gexec || memcmp(key, h->gkey, sizeof key) != 0) {
+        drop_graph(h);
+        const int64_t l0 = h->launches;
+        CK(cudaStreamBeginCapture(ms, cudaStreamCaptureModeThreadLocal));
+        const int rc = enqueue_chunked_host_step(h, ms, a);
+        cudaGraph_t g = nullptr;
+        cudaError_t ce = cudaStreamEndCapture(ms, &g);
+        if (rc == PIADMM_OK && ce == cudaSuccess) ce = cudaGraphInstantiate(&h->gexec, g, 0);
+        if (g) cudaGraphDestroy(g);
+        h->glaunches = h->launches - l0;
+        h->launches = l0;
+        if (rc != PIADMM_OK || ce != cudaSuccess) {      // capture unavailable: plain stream path from now on
+          cudaGetLastError();
+          h->gexec = nullptr; h->use_graph = false; graph = false;
+          for (int i = 0; i <= PIADMM_CHUNKS; i++) h->order_valid[i] = false;
+        } else {
+          memcpy(h->gkey, key, sizeof key);
+          for (int i = 0; i <= PIADMM_CHUNKS; i++) h->gvalid_after[i] = h->order_valid[i];
+        }
+      }
+      if (graph) {
+        CK(cudaGraphLaunch(h->gexec, ms));
+        h->launches += h->glaunches;
+        for (int i = 0; i <= PIADMM_CHUNKS; i++) h->order_valid[i] = h->gvalid_after[i];
+      }
     }
-    CK(cudaStreamSynchronize(st));
+    if (!graph) {
+      const int rc = enqueue_chunked_host_step(h, ms, a);
+      if (rc) return rc;
+    }
+    CK(cudaStreamSynchronize(ms));
     return PIADMM_OK;
   }
   CK(cudaMemcpyAsync((void*)h->c.b.xt, xt, sizeof(double) * SV * 3, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync((void*)h->c.b.spd, spd, sizeof(double) * SV, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync((void*)h->c.b.refwin, refwin, sizeof(double) * SV * 2 * (N + 1), cudaMemcpyHostToDevice, st));
+  if (spd) CK(cudaMemcpyAsync((void*)h->c.b.spd, spd, sizeof(double) * SV, cudaMemcpyHostToDevice, st));
+  if (refwin) {
+    CK(cudaMemcpyAsync((void*)h->c.b.refwin, refwin, sizeof(double) * SV * 2 * (N + 1), cudaMemcpyHostToDevice, st));
+  } else {
+    CK(cudaMemcpyAsync(h->d_step, h->h_step, sizeof(int), cudaMemcpyHostToDevice, st));
+    k_refwin<<<(unsigned)((SV * 2 * (N + 1) + 255) / 256), 256, 0, st>>>(h->c, h->d_ref, h->ref_T, h->d_step);
+    LAUNCHED();
+  }
   int rc = piadmm_step(h, stream);
   if (rc) return rc;
   rc = piadmm_plant_step(h, stream);
@@ -1028,6 +1142,43 @@ int piadmm_step_host(piadmm_handle* h, const double* xt, const double* spd, cons
   if (n_outer_out) CK(cudaMemcpyAsync(n_outer_out, h->c.b.n_outer, sizeof(int32_t) * h->c.S, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return PIADMM_OK;
+}
+
+int piadmm_step_host(piadmm_handle* h, const double* xt, const double* spd, const double* refwin,
+                     double* u_out, double* pos_out, double* xt_next_out, int32_t* curr_iter_out,
+                     int32_t* n_outer_out, void* stream) {
+  REQUIRE_BOUND();
+  if (!xt || !spd || !refwin) return PIADMM_E_ARG;
+  return step_host_impl(h, xt, spd, refwin, u_out, pos_out, xt_next_out, curr_iter_out, n_outer_out, stream);
+}
+
+int piadmm_set_reference(piadmm_handle* h, const double* ref, int T, void* stream) {
+  if (!h) return PIADMM_E_ARG;
+  if (!ref || T < h->c.N + 1) { h->err = "piadmm_set_reference: ref is NULL or T < num_ho + 1"; return PIADMM_E_ARG; }
+  CK(cudaSetDevice(h->device));
+  const size_t n = (size_t)h->c.S * h->c.V * 2 * T;
+  if (T != h->ref_T || !h->d_ref) {
+    cudaFree(h->d_ref); h->d_ref = nullptr; h->ref_T = 0;
+    CK(cudaMalloc(&h->d_ref, sizeof(double) * n));
+    drop_graph(h);
+  }
+  CK(cudaMemcpyAsync(h->d_ref, ref, sizeof(double) * n, cudaMemcpyDefault, (cudaStream_t)stream));
+  CK(cudaStreamSynchronize((cudaStream_t)stream));
+  h->ref_T = T;
+  return PIADMM_OK;
+}
+
+int piadmm_step_host_at(piadmm_handle* h, int num_step, const double* xt, double* u_out, double* pos_out,
+                        double* xt_next_out, int32_t* curr_iter_out, int32_t* n_outer_out, void* stream) {
+  REQUIRE_BOUND();
+  if (!xt) return PIADMM_E_ARG;
+  if (!h->d_ref) { h->err = "piadmm_step_host_at: no resident reference (call piadmm_set_reference first)"; return PIADMM_E_UNBOUND; }
+  if (num_step < 0 || num_step + h->c.N + 1 > h->ref_T) {
+    h->err = "piadmm_step_host_at: window [num_step, num_step + num_ho] leaves the reference (casadi/main.py:43)";
+    return PIADMM_E_ARG;
+  }
+  *h->h_step = num_step;
+  return step_host_impl(h, xt, nullptr, nullptr, u_out, pos_out, xt_next_out, curr_iter_out, n_outer_out, stream);
 }
 
 int piadmm_fp64_peak(int device, int iters, double* tflops, double* ms) {

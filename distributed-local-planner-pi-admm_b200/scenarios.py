@@ -35,13 +35,26 @@ def c4_scenarios(S=4096, N=15, seed=4096, step=12, T=50):
     xt[:, 0, 0] = xA0 + 0.1 * step * spd[:, 0]
     xt[:, 1, 1] = yB0 - 0.1 * step * spd[:, 1]
     xt[:, 1, 2] = -np.pi / 2
-    lam = np.linspace(0.0, 1.0, T)[None, :]
-    refA_x = xA0[:, None] * (1 - 2 * lam)
-    refB_y = yB0[:, None] * (1 - 2 * lam)
-    refwin = np.zeros((S, 2, 2, N + 1))
-    refwin[:, 0, 0, :] = refA_x[:, step:step + N + 1]
-    refwin[:, 1, 1, :] = refB_y[:, step:step + N + 1]
+    ref = _c4_reference(xA0, yB0, T)
+    refwin = np.ascontiguousarray(ref[:, :, :, step:step + N + 1])
     return xt, spd, refwin
+
+
+def _c4_reference(xA0, yB0, T):
+    lam = np.linspace(0.0, 1.0, T)[None, :]
+    ref = np.zeros((len(xA0), 2, 2, T))
+    ref[:, 0, 0, :] = xA0[:, None] * (1 - 2 * lam)       # straight line from the start through the mirrored end point
+    ref[:, 1, 1, :] = yB0[:, None] * (1 - 2 * lam)
+    return ref
+
+
+def c4_reference(S=4096, seed=4096, T=50):
+    """Whole reference trajectories (S,2,2,T) of the scenarios c4_scenarios(S, seed=seed) draws: what
+    PI_ADMM_CASADI.ref_traj is for config 1; c4_scenarios returns the window [step, step+N] of it."""
+    rng = np.random.default_rng(seed)
+    xA0 = -10.0 + rng.uniform(-1, 1, S)
+    yB0 = 20.0 + rng.uniform(-2, 2, S)
+    return _c4_reference(xA0, yB0, T)
 
 
 def c3_intersection(V=64, N=30, seed=64, dt=0.1, r0=12.0, gap=6.0):

@@ -171,10 +171,30 @@ class PIADMMSolver:
                                               p(io["pos"]), p(io["xt_next"]), p(io["curr_iter"]),
                                               p(io["n_outer"]), self._stream()), "piadmm_step_host")
 
+    def set_reference(self, ref):
+        """Resident reference trajectories (S,V,2,T) -- numpy or torch, host or device: uploaded once, like
+        ``PI_ADMM_CASADI.ref_traj`` (casadi/PI_ADMM_class.py:31-37); see piadmm_set_reference."""
+        if not torch.is_tensor(ref):
+            ref = torch.from_numpy(np.ascontiguousarray(ref, dtype=np.float64))
+        ref = ref.to(torch.float64).contiguous()
+        if ref.dim() != 4 or tuple(ref.shape[:3]) != (self.S, self.V, 2):
+            raise _abi.PIADMMError(f"reference must have shape ({self.S},{self.V},2,T), got {tuple(ref.shape)}")
+        self._check(self.lib.piadmm_set_reference(self._h, C.c_void_p(ref.data_ptr()), int(ref.shape[3]),
+                                                  self._stream()), "piadmm_set_reference")
+
+    def step_host_at(self, num_step, io):
+        """piadmm_step_host_at on the (pinned) host tensors of alloc_host_io(): per step only io["xt"] goes to
+        the device (the reference window is gathered there from the resident reference, spd is resident);
+        u / pos / xt_next / curr_iter / n_outer come back, all inside the one C call."""
+        p = lambda t: C.c_void_p(t.data_ptr())
+        self._check(self.lib.piadmm_step_host_at(self._h, int(num_step), p(io["xt"]), p(io["u"]), p(io["pos"]),
+                                                 p(io["xt_next"]), p(io["curr_iter"]), p(io["n_outer"]),
+                                                 self._stream()), "piadmm_step_host_at")
+
     @staticmethod
-    def host_io_bytes(io):
+    def host_io_bytes(io, resident_reference=False):
         nb = lambda k: io[k].numel() * io[k].element_size()
-        return (sum(nb(k) for k in ("xt", "spd", "refwin")),
+        return (sum(nb(k) for k in (("xt",) if resident_reference else ("xt", "spd", "refwin"))) + (4 if resident_reference else 0),
                 sum(nb(k) for k in ("u", "pos", "xt_next", "curr_iter", "n_outer")))
 
     # ------------------------------------------------------------------ outputs

@@ -160,6 +160,17 @@ int piadmm_step_host(piadmm_handle* h, const double* xt, const double* spd, cons
                      double* u_out, double* pos_out, double* xt_next_out, int32_t* curr_iter_out,
                      int32_t* n_outer_out, void* stream);
 
+/* Resident reference trajectories.  The reference builds ref_traj once in PI_ADMM_CASADI.__init__
+ * (casadi/PI_ADMM_class.py:31-37) and every MPC step only slices the window [num_step, num_step+num_ho] out of
+ * it (cost_function_primal, :116-117; casadi/main.py:43,84).  piadmm_set_reference copies ref [S,V,2,T]
+ * (host or device pointer; row (s,v,0) = x reference, (s,v,1) = y reference) into library-owned device memory;
+ * piadmm_step_host_at then needs only the plant state xt [S,V,3] per step: the window is gathered on the device,
+ * spd is the bound (device-resident) buffer.  Outputs as piadmm_step_host.  Errors: PIADMM_E_UNBOUND without a
+ * reference, PIADMM_E_ARG when the window leaves the reference (the reference script stops at Nt/dt - num_ho). */
+int piadmm_set_reference(piadmm_handle* h, const double* ref, int T, void* stream);
+int piadmm_step_host_at(piadmm_handle* h, int num_step, const double* xt, double* u_out, double* pos_out,
+                        double* xt_next_out, int32_t* curr_iter_out, int32_t* n_outer_out, void* stream);
+
 /* statistics for the roofline: kernels launched by this handle since creation */
 int64_t piadmm_launch_count(const piadmm_handle* h);
 

@@ -268,3 +268,55 @@ def test_step_host_chunked_pipeline_equals_device_path():
         assert np.array_equal(out["n_outer"], ref["n_outer"]) and np.array_equal(out["curr_iter"], ref["curr_iter"])
         for k in ("u", "pos", "xt_next"):
             assert rel_err(out[k], ref[k]) <= 1e-6
+
+
+def test_step_host_at_resident_reference_closed_loop():
+    """piadmm_set_reference + piadmm_step_host_at: per step only xt goes to the device.  Pinned buffers, so the
+    cached CUDA graph is captured and then replayed with a changing step index and a changing scheduling order;
+    every step is compared with the C twin fed the host-sliced window."""
+    import torch
+    from pi_admm_b200.scenarios import c4_reference
+    S, N = 301, 15
+    p = make_params("matlab_pi", "default", num_ho=N, eps_pri=0.1, eps_dual=0.1)
+    xt, spd, _ = c4_scenarios(S=S, N=N, seed=5, step=10)
+    ref_traj = c4_reference(S=S, seed=5)
+    sol = PIADMMSolver(p, S=S, V=2)
+    sol.setup(xt, spd, np.zeros((S, 2, 2, N + 1)))          # spd becomes resident; the window buffer is overwritten
+    sol.set_reference(ref_traj)
+    io = sol.alloc_host_io()
+    io["xt"].copy_(torch.from_numpy(xt))
+    for step in range(10, 16):
+        sol.step_host_at(step, io)
+        ref = ctwin.step(p, io["xt"].numpy(), spd, np.ascontiguousarray(ref_traj[:, :, :, step:step + N + 1]))
+        assert np.array_equal(io["n_outer"].numpy(), ref["n_outer"]), step
+        assert np.array_equal(io["curr_iter"].numpy(), ref["curr_iter"]), step
+        for k in ("u", "pos", "xt_next"):
+            assert rel_err(io[k].numpy(), ref[k]) <= 1e-6, (step, k)
+        io["xt"].copy_(io["xt_next"])                        # plant step closes the loop (casadi/main.py:185-192)
+    assert ref["n_edge_solves"].sum() > 0
+
+
+def test_step_host_at_argument_errors():
+    import torch
+    from pi_admm_b200.scenarios import c4_reference
+    p = make_params("python_current", "default")
+    xt, spd, refwin = c4_scenarios(S=8, N=p.num_ho, seed=1)
+    sol = PIADMMSolver(p, S=8, V=2)
+    sol.setup(xt, spd, refwin)
+    io = sol.alloc_host_io()
+    with pytest.raises(pa.PIADMMError):                      # no resident reference yet
+        sol.step_host_at(0, io)
+    with pytest.raises(pa.PIADMMError):                      # wrong shape
+        sol.set_reference(np.zeros((8, 2, 50)))
+    sol.set_reference(c4_reference(S=8, seed=1))
+    io["xt"].copy_(torch.from_numpy(xt))
+    sol.step_host_at(34, io)                                 # last admissible step: 34 + 15 + 1 = 50 columns
+    with pytest.raises(pa.PIADMMError):                      # the reference script stops at Nt/dt - num_ho
+        sol.step_host_at(35, io)
+    with pytest.raises(pa.PIADMMError):
+        sol.step_host_at(-1, io)
+    # small batch (not chunked, no graph) agrees with the plain host entry point
+    sol.step_host_at(12, io)
+    out = sol.step_host(xt, spd, refwin)
+    for k in ("u", "pos", "xt_next", "n_outer"):
+        assert np.array_equal(io[k].numpy(), out[k]), k
