@@ -558,6 +558,25 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
     if (p.curr_iter_latest) curr_iter = i_iter + 1;
     pair_sync<LPQ>();
   }
+  if (c.host_out) {
+    // every lane re-reads what it wrote itself (u_k, the two coordinates of point k): no synchronisation needed
+    const size_t uo = ((size_t)s * 2 + i) * N, po = POS_OFF(s, i);
+    if (c.ho_u && k < N) c.ho_u[uo + k] = c.b.u[uo + k];
+    if (c.ho_pos && k <= N) { c.ho_pos[po + k] = c.b.pos[po + k]; c.ho_pos[po + NP1 + k] = c.b.pos[po + NP1 + k]; }
+    if (k == 0) {                              // plant step of vehicle i, casadi/main.py:185-192 (as k_plant)
+      const double* xt = c.b.xt + ((size_t)s * 2 + i) * 3;
+      const double v = c.b.spd[(size_t)s * 2 + i];
+      const double nx = xt[0] + v * cos(xt[2]) * p.dt, ny = xt[1] + v * sin(xt[2]) * p.dt;
+      const double nt = xt[2] + v / p.L * c.b.u[uo] * p.dt;
+      double* o = c.b.xt_next + ((size_t)s * 2 + i) * 3;
+      o[0] = nx; o[1] = ny; o[2] = nt;
+      if (c.ho_xt_next) { double* ho = c.ho_xt_next + ((size_t)s * 2 + i) * 3; ho[0] = nx; ho[1] = ny; ho[2] = nt; }
+    }
+    if (lead) {
+      if (c.ho_curr_iter) c.ho_curr_iter[s] = curr_iter;
+      if (c.ho_n_outer) c.ho_n_outer[s] = n_outer;
+    }
+  }
   if (lead) {
     c.b.flag[s] = flag; c.b.done[s] = 1; c.b.curr_iter[s] = curr_iter; c.b.n_outer[s] = n_outer;
     c.b.edge_n[s] = edge_n;
@@ -604,6 +623,7 @@ struct piadmm_handle {
   // cached CUDA graph of the whole host-buffer step (copies + kernels of all sub-batches): one cudaGraphLaunch
   // instead of ~45 stream API calls per step
   bool use_graph;             // PIADMM_GRAPH=0 disables
+  bool zero_copy;             // PIADMM_ZEROCOPY=0 disables the zero-copy epilogue of the host-buffer entry points
   cudaGraphExec_t gexec;
   const void* gkey[9];        // host pointers + order-validity bits the graph was captured for
   bool gvalid_after[PIADMM_CHUNKS + 1];
@@ -774,6 +794,8 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     h->n_chunks = n < 1 ? 1 : (n > PIADMM_CHUNKS ? PIADMM_CHUNKS : n);
     e = getenv("PIADMM_GRAPH");
     h->use_graph = !(e && strcmp(e, "0") == 0);
+    e = getenv("PIADMM_ZEROCOPY");
+    h->zero_copy = !(e && strcmp(e, "0") == 0);
     h->gexec = nullptr; h->glaunches = 0;
   }
   if ((ce = cudaMallocHost(&h->h_step, sizeof(int))) != cudaSuccess) return fail(ce, "h_step");
@@ -979,9 +1001,21 @@ int piadmm_plant_step(piadmm_handle* h, void* stream) {
 }
 
 // one persistent kernel for the whole outer loop of the scenarios [s_lo, s_hi)
-static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, int* queue, int range_id) {
+struct HostStepArgs {
+  const double *xt, *spd, *refwin;     // spd / refwin NULL: resident (bound spd buffer, piadmm_set_reference)
+  double *u_out, *pos_out, *xt_next_out;
+  int32_t *curr_iter_out, *n_outer_out;
+};
+
+static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, int* queue, int range_id,
+                        const HostStepArgs* zc = nullptr) {
   DevCtx c = h->c;
   c.s_lo = s_lo; c.s_hi = s_hi; c.queue = queue;
+  if (zc) {      // zero-copy epilogue into mapped host memory (device-visible addresses)
+    c.host_out = 1;
+    c.ho_u = zc->u_out; c.ho_pos = zc->pos_out; c.ho_xt_next = zc->xt_next_out;
+    c.ho_curr_iter = zc->curr_iter_out; c.ho_n_outer = zc->n_outer_out;
+  }
   // the whole-batch order and the sub-batch orders share d_order: using one invalidates the other
   c.order = (h->use_order && h->order_valid[range_id]) ? h->d_order : nullptr;
   CK(cudaMemsetAsync(queue, 0, sizeof(int), st));
@@ -1022,17 +1056,15 @@ int piadmm_step(piadmm_handle* h, void* stream) {
   return rc;
 }
 
-struct HostStepArgs {
-  const double *xt, *spd, *refwin;     // spd / refwin NULL: resident (bound spd buffer, piadmm_set_reference)
-  double *u_out, *pos_out, *xt_next_out;
-  int32_t *curr_iter_out, *n_outer_out;
-};
-
 // Independent scenarios: the batch is split into n_chunks sub-batches on internal streams (forked from and
 // joined back into `ms`), so that the H2D / D2H copies of one sub-batch overlap the kernels of the others.
-static int enqueue_chunked_host_step(piadmm_handle* h, cudaStream_t ms, const HostStepArgs& a) {
+// zc != NULL (zero-copy): the kernels store the results themselves into the caller's mapped pinned buffers (zc =
+// their device-visible addresses) while they run: no D2H copies, no plant kernel; with a resident reference the
+// inputs are a few 100 KB and one launch over the whole batch is best.
+static int enqueue_chunked_host_step(piadmm_handle* h, cudaStream_t ms, const HostStepArgs& a, const HostStepArgs* zc) {
   const size_t N = h->c.N, np1 = N + 1;
-  const int nch = h->n_chunks;
+  int nch = (zc && !a.refwin) ? 1 : h->n_chunks;
+  if (h->c.S < 64 * nch) nch = 1;
   if (!a.refwin) CK(cudaMemcpyAsync(h->d_step, h->h_step, sizeof(int), cudaMemcpyHostToDevice, ms));
   CK(cudaEventRecord(h->ev_start, ms));
   for (int ch = 0; ch < nch; ch++) {
@@ -1050,8 +1082,13 @@ static int enqueue_chunked_host_step(piadmm_handle* h, cudaStream_t ms, const Ho
       k_refwin<<<(unsigned)((na * 2 * np1 + 255) / 256), 256, 0, cs>>>(c, h->d_ref, h->ref_T, h->d_step);
       LAUNCHED();
     }
-    int rc = launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch, 1 + ch);
+    int rc = nch == 1 ? launch_fused(h, cs, s0, s1, h->d_queue, 0, zc) : launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch, 1 + ch, zc);
     if (rc) return rc;
+    if (zc) {
+      CK(cudaEventRecord(h->ev_done[ch], cs));
+      CK(cudaStreamWaitEvent(ms, h->ev_done[ch], 0));
+      continue;
+    }
     k_plant<<<(unsigned)((na + 127) / 128), 128, 0, cs>>>(c);
     LAUNCHED();
     if (a.u_out) CK(cudaMemcpyAsync(a.u_out + a0 * N, h->c.b.u + a0 * N, sizeof(double) * na * N, cudaMemcpyDeviceToHost, cs));
@@ -1063,6 +1100,14 @@ static int enqueue_chunked_host_step(piadmm_handle* h, cudaStream_t ms, const Ho
     CK(cudaStreamWaitEvent(ms, h->ev_done[ch], 0));
   }
   return PIADMM_OK;
+}
+
+// device-visible address of a mapped pinned host pointer (NULL stays NULL); false if p is not mapped pinned memory
+static bool mapped_dev_ptr(void* p, void** out) {
+  *out = nullptr;
+  if (!p) return true;
+  if (cudaHostGetDevicePointer(out, p, 0) != cudaSuccess) { cudaGetLastError(); *out = nullptr; return false; }
+  return true;
 }
 
 static bool pinned_or_null(const void* p) {
@@ -1077,23 +1122,30 @@ static int step_host_impl(piadmm_handle* h, const double* xt, const double* spd,
                           int32_t* n_outer_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   const size_t SV = (size_t)h->c.S * h->c.V, N = h->c.N;
-  if (h->c.V == 2 && h->c.D == 1 && h->c.S >= 64 * h->n_chunks) {
-    const HostStepArgs a = {xt, spd, refwin, u_out, pos_out, xt_next_out, curr_iter_out, n_outer_out};
+  const HostStepArgs a = {xt, spd, refwin, u_out, pos_out, xt_next_out, curr_iter_out, n_outer_out};
+  HostStepArgs zc = a;
+  const bool fused = h->c.V == 2 && h->c.D == 1;
+  const bool zero_copy = fused && h->zero_copy && mapped_dev_ptr(u_out, (void**)&zc.u_out) &&
+                         mapped_dev_ptr(pos_out, (void**)&zc.pos_out) && mapped_dev_ptr(xt_next_out, (void**)&zc.xt_next_out) &&
+                         mapped_dev_ptr(curr_iter_out, (void**)&zc.curr_iter_out) &&
+                         mapped_dev_ptr(n_outer_out, (void**)&zc.n_outer_out);
+  if (fused && (zero_copy || h->c.S >= 64 * h->n_chunks)) {
     cudaStream_t ms = h->cs_main;                 // internal origin stream (the caller's may be the legacy stream,
     CK(cudaEventRecord(h->ev_user, st));          //  which cannot be captured): ordered after the caller's work
     CK(cudaStreamWaitEvent(ms, h->ev_user, 0));
     bool graph = h->use_graph && pinned_or_null(xt) && pinned_or_null(spd) && pinned_or_null(refwin) &&
                  pinned_or_null(u_out) && pinned_or_null(pos_out) && pinned_or_null(xt_next_out) &&
                  pinned_or_null(curr_iter_out) && pinned_or_null(n_outer_out);
+    auto enqueue = [&]() { return enqueue_chunked_host_step(h, ms, a, zero_copy ? &zc : nullptr); };
     if (graph) {
-      uintptr_t bits = 0;
+      uintptr_t bits = zero_copy ? (uintptr_t)1 << 20 : 0;
       for (int i = 0; i <= PIADMM_CHUNKS; i++) bits |= (uintptr_t)(h->order_valid[i] ? 1 : 0) << i;
       const void* key[9] = {xt, spd, refwin, u_out, pos_out, xt_next_out, curr_iter_out, n_outer_out, (const void*)bits};
       if (!h->gexec || memcmp(key, h->gkey, sizeof key) != 0) {
         drop_graph(h);
         const int64_t l0 = h->launches;
         CK(cudaStreamBeginCapture(ms, cudaStreamCaptureModeThreadLocal));
-        const int rc = enqueue_chunked_host_step(h, ms, a);
+        const int rc = enqueue();
         cudaGraph_t g = nullptr;
         cudaError_t ce = cudaStreamEndCapture(ms, &g);
         if (rc == PIADMM_OK && ce == cudaSuccess) ce = cudaGraphInstantiate(&h->gexec, g, 0);
@@ -1116,7 +1168,7 @@ static int step_host_impl(piadmm_handle* h, const double* xt, const double* spd,
       }
     }
     if (!graph) {
-      const int rc = enqueue_chunked_host_step(h, ms, a);
+      const int rc = enqueue();
       if (rc) return rc;
     }
     CK(cudaStreamSynchronize(ms));

@@ -35,6 +35,12 @@ struct DevCtx {
   int* queue;                              // work counter of the persistent fused kernel
   int s_lo, s_hi;                          // scenario range of this launch (fused kernel / plant step)
   const int* order;                        // fused kernel: processing order of [s_lo,s_hi) (longest first), or NULL
+  // fused kernel, host-buffer entry points: zero-copy epilogue.  When set, every finished scenario also takes the
+  // plant step and stores its results straight into the caller's pinned (mapped) host buffers, so the D2H traffic
+  // streams out during the kernel instead of as copies after it.  Any pointer may be NULL.
+  int host_out;
+  double *ho_u, *ho_pos, *ho_xt_next;
+  int32_t *ho_curr_iter, *ho_n_outer;
 };
 
 // ------------------------------------------------------------------ group primitives
