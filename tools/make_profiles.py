@@ -48,7 +48,7 @@ def main(tag):
             d[r[ki][:70]].append(float(r[vi].replace(",", "")))
         except ValueError:
             pass
-    step = [k for k in d if "k_fused" in k or "k_plant" in k]
+    step = [k for k in d if "k_fused" in k or "k_order" in k or "k_refwin" in k or "k_plant" in k]
     tot = sum(sum(d[k]) for k in step)
     lines = [f"| `{k}` | {len(v)} | {sum(v) / len(v) / 1e3:.1f} | {'%.3f' % (sum(v) / tot) if k in step else '(not part of a step)'} |"
              for k, v in sorted(d.items(), key=lambda kv: -sum(kv[1]))]
@@ -77,39 +77,49 @@ Files
 | quantity | value |
 |---|---|
 | agent-QP solves/s, inputs resident in HBM (`value`) | **{b['value']:.3e}** ({b['ms_per_step']:.3f} ms per 4096-scenario MPC step: {int(w['agent_qp_solves'])} vehicle QPs + {int(w['edge_solves'])} edge problems, {int(w['veh_inner_iters'] + w['edge_inner_iters'])} inner ADMM iterations, outer iterations mean {w['outer_iters_mean']:.2f}) |
-| end to end through `piadmm_step_host`, pinned host buffers, copies inside (`e2e`) | **{b['e2e']['value']:.3e}** ({b['e2e']['ms_per_step']:.3f} ms; H2D {b['e2e']['h2d_bytes_per_step']} B + D2H {b['e2e']['d2h_bytes_per_step']} B per step) |
+| end to end through `piadmm_step_host_at`, pinned host buffers, reference trajectories resident (`e2e`) | **{b['e2e']['value']:.3e}** ({b['e2e']['ms_per_step']:.3f} ms; H2D {b['e2e']['h2d_bytes_per_step']} B (plant state + step index) + D2H {b['e2e']['d2h_bytes_per_step']} B per step, stored by the kernel into the mapped pinned buffers) |
+| end to end through `piadmm_step_host` (xt, spd and the reference window uploaded every step) | {b['e2e']['full_upload']['value']:.3e} ({b['e2e']['full_upload']['ms_per_step']:.3f} ms; H2D {b['e2e']['full_upload']['h2d_bytes_per_step']} B) |
 | CPU arm (`--impl reference`: oracle C twin = "port", {r['cpu_baseline']['cores']} OpenMP threads of the GPU box) | {r['value']:.3e} solves/s |
 | e2e / CPU arm | {b['e2e']['value'] / r['value']:.1f}x |
-| kernel launches per step | {b['gpu_launches'] // b['steps']} (`k_fused_v2<16>`) |
+| kernel launches per step | {b['gpu_launches'] // b['steps']} (`k_fused_v2<16>` + `k_order`, the longest-first schedule for the next step) |
 | FP64 roofline: algorithmic flops / launch time / repo-measured DFMA peak ({b['roofline']['peak']:.1f} TFLOP/s) | {b['roofline']['achieved']:.2f} TFLOP/s = **{b['roofline']['frac']:.3f}** |
 | ncu (one launch, {m['gpu__time_duration.sum']:.0f} us) | FP64 pipe active {m['sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active']:.1f} % of active cycles; issue slots busy {m['smsp__issue_active.avg.pct_of_peak_sustained_active']:.1f} %; {m['smsp__warps_active.avg.per_cycle_active']:.2f} warps / SM sub-partition active, {m['smsp__warps_eligible.avg.per_cycle_active']:.2f} eligible |
 | ncu DRAM | {rd / 1e6:.2f} MB read + {wr / 1e6:.1f} MB written per launch (the writes are the write-back of the L2-flush buffer); DRAM throughput {m['gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed']:.2f} % of peak: not HBM-bound |
 | clocks during the timed region | {b['clocks']} |
 
-## Launch list (shares of the MPC step = k_fused_v2 + k_plant)
+## Launch list (shares of the MPC step = k_fused_v2 + k_order (+ k_refwin in the end-to-end path))
 
 | kernel | launches | avg us | share of step |
 |---|---|---|---|
 """ + "\n".join(lines) + f"""
 
 `k_fp64_peak` is the one-off peak micro-benchmark after the timed region; torch fill kernels are buffer initialisation
-and the L2 flush (outside the event pairs); `k_plant` runs only in the end-to-end path.  The ncu duration of
-`k_fused_v2<16>` agrees with the CUDA-event time of the bench: the kernel IS the step.
+and the L2 flush (outside the event pairs); `k_refwin` (window gather from the resident reference) runs only in the
+end-to-end path, `k_plant` only in the non-zero-copy host path.  The ncu duration of `k_fused_v2<16>` plus `k_order`
+agrees with the CUDA-event time of the bench: the fused kernel IS the step.
 
 ## Reading of the full capture (what limits the kernel)
 
 {tail}
 
-* 4096 scenario-warps for 2072 resident warp slots (7 CTAs x 2 warps per SM, 128 registers): two rounds of a
-  dependency-latency-bound chain. Issue slots are ~half busy and the FP64 pipe about a quarter: the kernel is
-  **issue / latency bound, not FP64-throughput bound** (stalls: `wait` = fixed-latency dependent FP64 chains,
-  `short_scoreboard` = LDS / SHFL results).  More resident warps were tried (10 and 12 CTAs per SM, 96 / 80
-  registers): the extra spills cost more than the occupancy gives (0.46 / 0.51 ms vs 0.43 ms).
-* Algorithmic flops are ~10 % of the DFMA peak while the pipe is ~27 % busy: the difference is Gauss-Jordan rebuilds
-  of K^-1 (about 2.5 per solve), termination checks, the padded 16th lane and the lock-step wait of the faster
-  vehicle of a warp.
-* Next candidates: pair like vehicles of two scenarios in a warp (the slow vehicle no longer holds the fast one's
-  lanes), cache K^-1(rho0) across outer iterations, shorten the LDS->DFMA chain of the mat-vec.
+* 4096 scenario-warps for 2368 resident warp slots (8 CTAs x 2 warps per SM, 128 registers).  Issue slots are about
+  half busy and the FP64 pipe about a third: the kernel is **dependency-latency bound, not FP64-throughput bound**
+  (stalls: `wait` = fixed-latency dependent FP64 chains, `short_scoreboard` = LDS / SHFL results; in the mat-vec
+  only two of the eight LDS.128 of the right-hand side are in flight at a time because the 32 registers of the
+  K^-1 row leave no room for more).
+* More resident warps do not help: 96 / 80 registers (10 / 12 CTAs per SM) spill in the hot loop (0.348 / 0.407 ms
+  vs 0.319 ms at that commit); K^-1 rows in shared memory (`PIADMM_FUSED=ks`, 72 registers, all 4096 scenarios
+  resident) makes the mat-vec LDS-bound (shared-memory pipe 58 % busy) and is no faster.
+* What did help this round (profiles/r1_history.md): loop-invariant parameter loads hoisted out of the inner loop
+  (they were generic loads from the kernel parameter block on the dependency chain), branch-free hinge prox without
+  a division, 2x2-block Gauss-Jordan builds (half the latency rounds; the builds were ~20 % of the time), nested
+  block counters instead of a spilled loop counter, and a longest-first scenario order learnt from the previous step
+  (scenario work varies 2.7x; elapsed / active SM cycles went from 1.32 to 1.14).
+* Algorithmic flops are ~15 % of the DFMA peak while the pipe is ~35 % busy: the difference is Gauss-Jordan rebuilds
+  of K^-1 (about 1.6 per solve), termination checks, the padded 16th lane and the lock-step wait of the faster
+  vehicle of a warp (16 %).
+* Next candidates: cache K^-1(rho0) across outer iterations (saves one of ~1.6 builds per solve), pair like vehicles
+  of two scenarios in a warp, software-pipeline the right-hand-side loads of the mat-vec.
 """)
     print("profiles/ regenerated from tag", tag)
 
