@@ -107,6 +107,13 @@ class ClockSampler:
         return out
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def run_reference(args, rank, world):
     """CPU arm: oracle C twin on all host cores; rank 0 only."""
     if rank != 0:
@@ -119,13 +126,13 @@ def run_reference(args, rank, world):
     p = bench_params(N)
     xt, spd, refwin = c4_scenarios(S=S, N=N)
     arrs = ctwin.alloc(S, 2, 1, N, p.iter_num)
-    cores = ctwin.max_threads()
+    cores = host_cores()         # all host cores, whatever OMP_NUM_THREADS says (torchrun sets it to 1)
     for _ in range(args.warmup):
-        ctwin.step(p, xt, spd, refwin, arrs=arrs)
+        ctwin.step(p, xt, spd, refwin, arrs=arrs, nthreads=cores)
     t0 = time.perf_counter()
     solves = 0
     for _ in range(args.steps):
-        r = ctwin.step(p, xt, spd, refwin, arrs=arrs)
+        r = ctwin.step(p, xt, spd, refwin, arrs=arrs, nthreads=cores)
         solves += int(r["n_veh_solves"].sum())
     dt = time.perf_counter() - t0
     val = solves / dt
@@ -316,7 +323,7 @@ def main():
                               "outer_iters_max": int(n_outer.max()),
                               "ms_per_mpc_step": ms_per_step},
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:       # reported at N=1 only (rank 0)
             line["cpu_baseline"] = cpu_baseline(p, xt, spd, refwin, S, N)
         print(json.dumps(line))
     if world > 1:
@@ -329,11 +336,11 @@ def cpu_baseline(p, xt, spd, refwin, S, N):
     import __graft_entry__ as ge  # noqa: F401
     from oracle import ctwin
     arrs = ctwin.alloc(S, 2, 1, N, p.iter_num)
-    cores = ctwin.max_threads()
-    ctwin.step(p, xt, spd, refwin, arrs=arrs)
+    cores = host_cores()
+    ctwin.step(p, xt, spd, refwin, arrs=arrs, nthreads=cores)
     t0 = time.perf_counter(); reps = 0; solves = 0
     while time.perf_counter() - t0 < 10.0 and reps < 2000:
-        r = ctwin.step(p, xt, spd, refwin, arrs=arrs)
+        r = ctwin.step(p, xt, spd, refwin, arrs=arrs, nthreads=cores)
         solves += int(r["n_veh_solves"].sum()); reps += 1
     dt = time.perf_counter() - t0
     return {"value": solves / dt, "unit": "solves/s", "cores": cores, "kind": "port",
