@@ -69,6 +69,11 @@ class Buffers(C.Structure):
     _fields_ = [(n, C.c_void_p) for n, _, _ in BUFFER_SPECS]
 
 
+class Histories(C.Structure):
+    """struct piadmm_histories (device pointers, any may be NULL)."""
+    _fields_ = [(n, C.c_void_p) for n in ("x_vec", "theta_vec", "u_vec", "err_rk_his", "iter_his", "n_outer_his")]
+
+
 def max_edges(V: int, D: int) -> int:
     return max(1, V * D // 2)
 
@@ -146,6 +151,7 @@ _PROTOS = {
     "piadmm_step_host": (C.c_int, [C.c_void_p] + [C.c_void_p] * 8 + [C.c_void_p]),
     "piadmm_set_reference": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "piadmm_step_host_at": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 6 + [C.c_void_p]),
+    "piadmm_run_closed_loop": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "piadmm_launch_count": (C.c_int64, [C.c_void_p]),
     "piadmm_fp64_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     # include/obca_consensus.h (struct pointers passed as void*: obca_consensus.py owns the ctypes mirrors)

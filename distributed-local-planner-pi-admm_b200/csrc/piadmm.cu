@@ -358,6 +358,27 @@ __global__ void k_refwin(const __grid_constant__ DevCtx c, const double* __restr
   }
 }
 
+// end of one MPC step of the on-device closed loop: append the histories of casadi/main.py:186,199-201, advance
+// the plant state (xt <- xt_next) and the step index.  t = position of the step in the history arrays.
+__global__ void k_advance(const __grid_constant__ DevCtx c, piadmm_histories o, int t, int* step) {
+  const long a = (long)blockIdx.x * blockDim.x + threadIdx.x, SV = (long)c.S * c.V;
+  if (a == 0) *step += 1;
+  if (a >= SV) return;
+  const int s = (int)(a / c.V);
+  const double* xn = c.b.xt_next + a * 3;
+  double* xt = const_cast<double*>(c.b.xt) + a * 3;
+  const double x = xn[0], y = xn[1], th = xn[2];
+  if (o.x_vec) { o.x_vec[((size_t)t * SV + a) * 2] = x; o.x_vec[((size_t)t * SV + a) * 2 + 1] = y; }
+  if (o.theta_vec) o.theta_vec[(size_t)t * SV + a] = th;
+  if (o.u_vec) o.u_vec[(size_t)t * SV + a] = c.b.u[a * c.N];
+  if (a % c.V == 0) {
+    if (o.iter_his) o.iter_his[(size_t)t * c.S + s] = c.b.curr_iter[s];
+    if (o.n_outer_his) o.n_outer_his[(size_t)t * c.S + s] = c.b.n_outer[s];
+    if (o.err_rk_his) { const int n = c.b.n_outer[s]; o.err_rk_his[(size_t)t * c.S + s] = n > 0 ? c.b.err_rk[(size_t)s * c.I + n - 1] : 0.0; }
+  }
+  xt[0] = x; xt[1] = y; xt[2] = th;
+}
+
 __global__ void k_plant(const __grid_constant__ DevCtx c) {
   const long a = (long)c.s_lo * c.V + (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= (long)c.s_hi * c.V) return;
@@ -1231,6 +1252,40 @@ int piadmm_step_host_at(piadmm_handle* h, int num_step, const double* xt, double
   }
   *h->h_step = num_step;
   return step_host_impl(h, xt, nullptr, nullptr, u_out, pos_out, xt_next_out, curr_iter_out, n_outer_out, stream);
+}
+
+int piadmm_run_closed_loop(piadmm_handle* h, int first_step, int n_steps, const piadmm_histories* out, void* stream) {
+  REQUIRE_BOUND();
+  if (!h->d_ref) { h->err = "piadmm_run_closed_loop: no resident reference (call piadmm_set_reference first)"; return PIADMM_E_UNBOUND; }
+  if (n_steps < 1 || first_step < 0 || first_step + n_steps - 1 + h->c.N + 1 > h->ref_T) {
+    h->err = "piadmm_run_closed_loop: the windows [step, step + num_ho] leave the reference (casadi/main.py:43)";
+    return PIADMM_E_ARG;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  piadmm_histories o;
+  memset(&o, 0, sizeof o);
+  if (out) o = *out;
+  const size_t SV = (size_t)h->c.S * h->c.V, np1 = h->c.N + 1;
+  const bool fused = h->c.V == 2 && h->c.D == 1;
+  *h->h_step = first_step;
+  CK(cudaMemcpyAsync(h->d_step, h->h_step, sizeof(int), cudaMemcpyHostToDevice, st));
+  HostStepArgs none;
+  memset(&none, 0, sizeof none);
+  for (int t = 0; t < n_steps; t++) {
+    k_refwin<<<(unsigned)((SV * 2 * np1 + 255) / 256), 256, 0, st>>>(h->c, h->d_ref, h->ref_T, h->d_step);
+    LAUNCHED();
+    int rc;
+    if (fused) {
+      rc = launch_fused(h, st, 0, h->c.S, h->d_queue, 0, &none);     // host_out with NULL targets: inline plant step
+    } else {
+      rc = piadmm_step(h, stream);
+      if (!rc) rc = piadmm_plant_step(h, stream);
+    }
+    if (rc) return rc;
+    k_advance<<<(unsigned)((SV + 127) / 128), 128, 0, st>>>(h->c, o, t, h->d_step);
+    LAUNCHED();
+  }
+  return PIADMM_OK;
 }
 
 int piadmm_fp64_peak(int device, int iters, double* tflops, double* ms) {

@@ -8,7 +8,9 @@ that built CasADi problems and called ``ca.qpsol("osqp")`` are replaced by calls
     casadi/main.py:121-162  edge loop + dual  ->  sol.z_update()
     casadi/main.py:165-180  residuals / stop  ->  sol.update_residuals()
 
-``fast=True`` runs each MPC step as ONE fused persistent kernel instead (same results).
+``fast=True`` runs each MPC step as ONE fused persistent kernel instead (same results);
+``device_loop=True`` runs the whole receding-horizon loop on the device (piadmm_run_closed_loop: reference
+trajectories resident, plant step and histories in kernels, no host round trip per MPC step).
 Run as a script:  python -m pi_admm_b200.main_intersection
 """
 from __future__ import annotations
@@ -21,7 +23,7 @@ from .PI_ADMM_class import PI_ADMM_CASADI
 
 
 def run(semantics="python_current", inner="osqp_default", fast=False, verbose=False, n_steps=None,
-        png=None, **overrides):
+        png=None, device_loop=False, **overrides):
     # PI_ADMM structure
     PI_ADMM = PI_ADMM_CASADI(semantics=semantics, inner=inner, **overrides)
     # initialize the parameter (casadi/main.py:25)
@@ -36,6 +38,20 @@ def run(semantics="python_current", inner="osqp_default", fast=False, verbose=Fa
     rho = float(PI_ADMM.param.rho)
     t = time.time()
     total_iter = 0
+    if device_loop:
+        V, N = int(PI_ADMM.param.num_veh), int(PI_ADMM.param.num_ho)
+        sol.setup(xt[None], spd, np.zeros((1, V, 2, N + 1)), rho=rho)
+        sol.set_reference(np.ascontiguousarray(PI_ADMM.ref_traj).reshape(1, V, 2, -1))
+        h = {k: v.cpu().numpy() for k, v in sol.run_closed_loop(0, n_steps).items()}
+        iter_his[:n_steps] = h["iter_his"][:, 0]
+        out = dict(x_vec=[h["x_vec"][i, 0].T.copy() for i in range(n_steps)],
+                   theta_vec=[h["theta_vec"][i, 0].copy() for i in range(n_steps)],
+                   u_vec=[h["u_vec"][i, 0].copy() for i in range(n_steps)], iter_his=iter_his,
+                   err_rk=[h["err_rk_his"][i] for i in range(n_steps)], n_outer=h["n_outer_his"][:, 0].tolist(),
+                   elapsed_time=time.time() - t, launches=sol.launch_count)
+        if png:
+            _plot(out["x_vec"], png)
+        return out
     for num_step in range(n_steps):
         # per-step inputs; hat_pos_old / dual_var_old / flag are re-initialised by begin_step (main.py:52-72)
         sol.setup(xt[None], spd, PI_ADMM.ref_window(num_step)[None], rho=rho)

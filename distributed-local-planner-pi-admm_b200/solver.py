@@ -191,6 +191,21 @@ class PIADMMSolver:
                                                  p(io["xt_next"]), p(io["curr_iter"]), p(io["n_outer"]),
                                                  self._stream()), "piadmm_step_host_at")
 
+    def run_closed_loop(self, first_step, n_steps):
+        """n_steps receding-horizon steps of casadi/main.py:43-201 on the device, no host round trip per step
+        (needs set_reference; starts from the plant state given to setup()).  Returns the script's histories as
+        device tensors: x_vec (n,S,V,2), theta_vec (n,S,V), u_vec (n,S,V), iter_his (n,S), n_outer_his (n,S),
+        err_rk_his (n,S)."""
+        n, S, V, dev = int(n_steps), self.S, self.V, self.device
+        f64 = lambda *sh: torch.zeros(sh, dtype=torch.float64, device=dev)
+        i32 = lambda *sh: torch.zeros(sh, dtype=torch.int32, device=dev)
+        out = dict(x_vec=f64(n, S, V, 2), theta_vec=f64(n, S, V), u_vec=f64(n, S, V), err_rk_his=f64(n, S),
+                   iter_his=i32(n, S), n_outer_his=i32(n, S))
+        hs = _abi.Histories(**{k: v.data_ptr() for k, v in out.items()})
+        self._check(self.lib.piadmm_run_closed_loop(self._h, int(first_step), n, C.byref(hs), self._stream()),
+                    "piadmm_run_closed_loop")
+        return out
+
     @staticmethod
     def host_io_bytes(io, resident_reference=False):
         nb = lambda k: io[k].numel() * io[k].element_size()

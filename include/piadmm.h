@@ -171,6 +171,20 @@ int piadmm_set_reference(piadmm_handle* h, const double* ref, int T, void* strea
 int piadmm_step_host_at(piadmm_handle* h, int num_step, const double* xt, double* u_out, double* pos_out,
                         double* xt_next_out, int32_t* curr_iter_out, int32_t* n_outer_out, void* stream);
 
+/* Whole receding-horizon run on the device: n_steps MPC steps of casadi/main.py:43-201 without a
+ * host round trip.  Per step: window gather from the resident reference at num_step = first_step + t, the outer
+ * PI-ADMM loop, the plant step (:185-192), the histories the script appends (:186,199-201) and xt <- xt_next.  The
+ * initial plant state is the bound xt buffer (overwritten: on return it holds the final state).  History arguments are
+ * DEVICE pointers, any may be NULL:
+ *   x_vec [n_steps,S,V,2], theta_vec [n_steps,S,V], u_vec [n_steps,S,V] (first control of the step),
+ *   iter_his [n_steps,S] (curr_iter), n_outer_his [n_steps,S], err_rk_his [n_steps,S] (last primal residual).
+ * Asynchronous on `stream` when V == 2 (fused kernel); the generic-V path synchronises once per outer iteration. */
+typedef struct piadmm_histories {
+  double *x_vec, *theta_vec, *u_vec, *err_rk_his;
+  int32_t *iter_his, *n_outer_his;
+} piadmm_histories;
+int piadmm_run_closed_loop(piadmm_handle* h, int first_step, int n_steps, const piadmm_histories* out, void* stream);
+
 /* statistics for the roofline: kernels launched by this handle since creation */
 int64_t piadmm_launch_count(const piadmm_handle* h);
 

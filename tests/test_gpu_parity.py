@@ -320,3 +320,82 @@ def test_step_host_at_argument_errors():
     out = sol.step_host(xt, spd, refwin)
     for k in ("u", "pos", "xt_next", "n_outer"):
         assert np.array_equal(io[k].numpy(), out[k]), k
+
+
+# ------------------------------------------------------------------ whole receding-horizon run on the device
+GOLDEN_PRESET = {"c1_python_current_default": ("python_current", "default"), "c1_matlab_pi_default": ("matlab_pi", "default"),
+                 "c1_python_old_pi_default": ("python_old_pi", "default"), "c1_python_current_tight": ("python_current", "tight")}
+
+
+@pytest.mark.parametrize("name", sorted(GOLDEN_PRESET))
+def test_run_closed_loop_reproduces_golden_config1(name):
+    """piadmm_run_closed_loop: all 50 - num_ho steps of casadi/main.py:43-201 in one asynchronous call, against the
+    frozen oracle closed loops (tests/golden)."""
+    import json, os
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", name + ".json")))
+    preset, inner = GOLDEN_PRESET[name]
+    p = make_params(preset, inner)
+    N = p.num_ho
+    ref_traj = reference_trajectories()                                  # (2V, 50) rows [x_A; 0; 0; y_B]
+    n_steps = ref_traj.shape[1] - N
+    assert n_steps == len(g["iter_his"])
+    sol = PIADMMSolver(p, S=1, V=2)
+    sol.setup(c1_initial_state()[None], np.array([[4.0, 8.0]]), np.zeros((1, 2, 2, N + 1)))
+    sol.set_reference(ref_traj.reshape(1, 2, 2, -1))
+    h = {k: v.cpu().numpy() for k, v in sol.run_closed_loop(0, n_steps).items()}
+    assert h["iter_his"][:, 0].tolist() == g["iter_his"] and h["n_outer_his"][:, 0].tolist() == g["n_outer"]
+    assert np.allclose(h["x_vec"][:, 0].transpose(0, 2, 1), np.array(g["x_vec"]), rtol=1e-6, atol=1e-9)
+    assert np.allclose(h["theta_vec"][:, 0], np.array(g["theta_vec"]), rtol=1e-6, atol=1e-9)
+    assert np.allclose(h["u_vec"][:, 0], np.array(g["u_vec"]), rtol=1e-6, atol=1e-9)
+    last_rk = [r[-1] if len(r) else 0.0 for r in g["err_rk"]]
+    assert np.allclose(h["err_rk_his"][:, 0], last_rk, rtol=1e-6, atol=1e-6)
+    with pytest.raises(pa.PIADMMError):                                  # one step too many leaves the reference
+        sol.run_closed_loop(0, n_steps + 1)
+
+
+def test_run_closed_loop_batch_equals_stepping():
+    """A batch of perturbed scenarios: the on-device run equals stepping the host entry point (and the C twin)."""
+    from pi_admm_b200.scenarios import c4_reference
+    S, N, first, n = 96, 15, 9, 7
+    p = make_params("matlab_pi", "default", num_ho=N, eps_pri=0.1, eps_dual=0.1)
+    xt0, spd, _ = c4_scenarios(S=S, N=N, seed=8, step=first)
+    ref_traj = c4_reference(S=S, seed=8)
+    sol = PIADMMSolver(p, S=S, V=2)
+    sol.setup(xt0, spd, np.zeros((S, 2, 2, N + 1)))
+    sol.set_reference(ref_traj)
+    h = {k: v.cpu().numpy() for k, v in sol.run_closed_loop(first, n).items()}
+    xt = xt0.copy()
+    for t in range(n):
+        ref = ctwin.step(p, xt, spd, np.ascontiguousarray(ref_traj[:, :, :, first + t:first + t + N + 1]))
+        assert np.array_equal(h["n_outer_his"][t], ref["n_outer"]) and np.array_equal(h["iter_his"][t], ref["curr_iter"]), t
+        assert rel_err(h["x_vec"][t], ref["xt_next"][:, :, :2]) <= 1e-6 and rel_err(h["theta_vec"][t], ref["xt_next"][:, :, 2]) <= 1e-6
+        assert rel_err(h["u_vec"][t], ref["u"][:, :, 0]) <= 1e-6
+        xt = ref["xt_next"].copy()
+    assert rel_err(sol.buf["xt"].cpu().numpy(), xt) <= 1e-6             # the bound state buffer holds the final state
+    assert h["n_outer_his"].max() >= 2
+
+
+def test_run_closed_loop_generic_v():
+    """V > 2 goes through the phase kernels; compared with stepping the same solver by hand."""
+    from pi_admm_b200.scenarios import c3_intersection
+    V, N, D, n = 16, 15, 8, 3
+    p = _generic_params(N)
+    xt, spd, rw0 = c3_intersection(V=V, N=N, r0=7.0, gap=5.0)
+    T = N + 1 + n
+    k = np.arange(T)
+    ref_traj = np.zeros((1, V, 2, T))                                    # constant-speed straight lines (SURVEY 8(d) C3)
+    ref_traj[0, :, 0] = xt[0, :, 0:1] + k * 0.1 * spd[0, :, None] * np.cos(xt[0, :, 2:3])
+    ref_traj[0, :, 1] = xt[0, :, 1:2] + k * 0.1 * spd[0, :, None] * np.sin(xt[0, :, 2:3])
+    assert np.allclose(ref_traj[:, :, :, :N + 1], rw0)
+    a = PIADMMSolver(p, S=1, V=V, D=D)
+    a.setup(xt, spd, rw0); a.set_reference(ref_traj)
+    h = {kk: v.cpu().numpy() for kk, v in a.run_closed_loop(0, n).items()}
+    b = PIADMMSolver(p, S=1, V=V, D=D)
+    x = xt.copy()
+    for t in range(n):
+        b.setup(x, spd, np.ascontiguousarray(ref_traj[:, :, :, t:t + N + 1]))
+        b.iterate(); b.plant_step()
+        o = b.to_numpy()
+        assert np.array_equal(h["n_outer_his"][t], o["n_outer"])
+        assert np.array_equal(h["x_vec"][t], o["xt_next"][:, :, :2]) and np.array_equal(h["u_vec"][t], o["u"][:, :, 0])
+        x = o["xt_next"].copy()
