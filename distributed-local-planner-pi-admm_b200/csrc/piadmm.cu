@@ -86,7 +86,7 @@ template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
-  __shared__ __align__(16) double xch[64];
+  __shared__ __align__(16) double xch[128];
   Who<LPQ> w;
   const long agents = (long)c.S * c.V, items = (agents + groups_per_cta<LPQ>() - 1) / groups_per_cta<LPQ>();
   bool loaded = false;
@@ -116,27 +116,31 @@ __global__ void k_bbox(const __grid_constant__ DevCtx c) {
   *o = make_double4(x0, x1, y0, y1);
 }
 
-// hits[s,i,jb] bit jj = 1 iff vehicle j = 32*jb+jj collides with i (casadi/main.py:110-113); the
-// matrix is stored symmetric (both (i,j) and (j,i)) so that rows can be scanned per vehicle.
+// hits[s,i,jb] bit jj = 1 iff vehicle j = 32*jb+jj collides with i (casadi/main.py:110-113); the matrix is stored
+// symmetric (both (i,j) and (j,i)) so that rows can be scanned per vehicle.  One thread per (i, word of 32 j's) of
+// the UPPER triangle (the test is symmetric): bounding boxes (32 B each, the whole table stays in L1) reject almost
+// every pair, the few hits are OR-ed into both rows of the zeroed matrix.
 __global__ void k_hits(const __grid_constant__ DevCtx c) {
   const int N = c.N, words = (c.V + 31) / 32;
-  const long wid = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long total = (long)c.S * c.V * words;
-  if (wid >= total) return;
-  const int jb = (int)(wid % words), i = (int)((wid / words) % c.V), s = (int)(wid / ((long)words * c.V));
-  if (c.b.done[s]) return;
-  const int j = jb * 32 + lane;
-  bool hit = false;
-  if (j != i && j < c.V) {
-    hit = c.p.always_edge != 0;
+  if (t >= total) return;
+  const int jb = (int)(t % words);
+  const long si = t / words;
+  const int i = (int)(si % c.V), s = (int)(si / c.V);
+  if (jb * 32 + 31 <= i || c.b.done[s]) return;          // no j > i in this word
+  const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
+  const double4* bb = reinterpret_cast<const double4*>(c.bbox) + (size_t)s * c.V;
+  const double4 bi = bb[i];
+  const double* pi = c.b.pos + (((size_t)s * c.V + i) * 2) * (N + 1);
+  uint32_t m = 0;
+  const int j0 = jb * 32, j1 = min(j0 + 32, c.V);
+  for (int j = max(j0, i + 1); j < j1; j++) {
+    bool hit = c.p.always_edge != 0;
     if (!hit) {
-      const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
-      const double4 bi = reinterpret_cast<const double4*>(c.bbox)[(size_t)s * c.V + i];
-      const double4 bj = reinterpret_cast<const double4*>(c.bbox)[(size_t)s * c.V + j];
+      const double4 bj = bb[j];
       const double gx = fmax(0.0, fmax(bi.x - bj.y, bj.x - bi.y)), gy = fmax(0.0, fmax(bi.z - bj.w, bj.z - bi.w));
       if (gx * gx + gy * gy < thr) {           // boxes closer than the threshold: exact test
-        const double* pi = c.b.pos + (((size_t)s * c.V + i) * 2) * (N + 1);
         const double* pj = c.b.pos + (((size_t)s * c.V + j) * 2) * (N + 1);
         for (int k = 0; k <= N && !hit; k++) {
           const double dx = pi[k] - pj[k], dy = pi[N + 1 + k] - pj[N + 1 + k];
@@ -144,15 +148,21 @@ __global__ void k_hits(const __grid_constant__ DevCtx c) {
         }
       }
     }
+    if (hit) {
+      m |= 1u << (j - j0);
+      atomicOr(c.hits + ((size_t)s * c.V + j) * words + (i >> 5), 1u << (i & 31));
+    }
   }
-  const unsigned m = __ballot_sync(PIADMM_FULL, hit);
-  if (lane == 0) c.hits[wid] = m;
+  if (m) atomicOr(c.hits + (size_t)si * words + jb, m);
 }
 
 // per vehicle: allocate neighbour slots for newly colliding vehicles, ascending j (this equals the
 // reference's sequential processing of np.where(edge_mat == 1), row-major)
 __global__ void k_slots(const __grid_constant__ DevCtx c) {
-  const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  // one warp per vehicle: the row of the hit matrix is read 32 words at a time (one coalesced load instead of a
+  // dependent per-thread scan), the rare non-zero words are handed to lane 0 in ascending order
+  const long a = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (a >= (long)c.S * c.V) return;
   const int s = (int)(a / c.V), i = (int)(a % c.V), words = (c.V + 31) / 32;
   if (c.b.done[s]) return;
@@ -160,20 +170,29 @@ __global__ void k_slots(const __grid_constant__ DevCtx c) {
   const uint32_t* H = c.hits + (size_t)a * words;
   int up = 0;
   bool overflow = false;
-  for (int w = 0; w < words; w++) {
-    uint32_t m = H[w];
-    while (m) {
-      const int j = w * 32 + __ffs(m) - 1;
-      m &= m - 1;
-      int slot = -1;
-      for (int d = 0; d < c.D; d++) if (nb[d] == j) { slot = d; break; }
-      if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = j; slot = d; break; }
-      if (slot < 0) { overflow = true; continue; }
-      if (j > i) up++;
+  for (int w0 = 0; w0 < words; w0 += 32) {
+    const uint32_t mine = w0 + lane < words ? H[w0 + lane] : 0u;
+    unsigned nz = __ballot_sync(PIADMM_FULL, mine != 0u);
+    while (nz) {
+      const int src = __ffs(nz) - 1;
+      nz &= nz - 1;
+      uint32_t m = __shfl_sync(PIADMM_FULL, mine, src);
+      if (lane != 0) continue;
+      while (m) {
+        const int j = (w0 + src) * 32 + __ffs(m) - 1;
+        m &= m - 1;
+        int slot = -1;
+        for (int d = 0; d < c.D; d++) if (nb[d] == j) { slot = d; break; }
+        if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = j; slot = d; break; }
+        if (slot < 0) { overflow = true; continue; }
+        if (j > i) up++;
+      }
     }
   }
-  c.up_cnt[a] = up;
-  if (overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
+  if (lane == 0) {
+    c.up_cnt[a] = up;
+    if (overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
+  }
 }
 
 // per scenario: emit the sorted edge list; flag / early-exit logic of casadi/main.py:115-118
@@ -181,37 +200,45 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
   const int s = blockIdx.x, words = (c.V + 31) / 32;
   if (c.b.done[s]) return;
   __shared__ int base;
-  __shared__ int scan[256];
+  __shared__ int wsum[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   if (threadIdx.x == 0) base = 0;
   __syncthreads();
   const uint32_t* H = c.hits + (size_t)s * c.V * words;
   for (int i0 = 0; i0 < c.V; i0 += blockDim.x) {
     const int i = i0 + threadIdx.x;
     const int cnt = i < c.V ? c.up_cnt[(size_t)s * c.V + i] : 0;
-    scan[threadIdx.x] = cnt;
+    int inc = cnt;                                            // CTA-wide exclusive scan: warp scans + scan of warp totals
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(PIADMM_FULL, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) wsum[warp] = inc;
     __syncthreads();
-    for (int o = 1; o < (int)blockDim.x; o <<= 1) {
-      int t = threadIdx.x >= o ? scan[threadIdx.x - o] : 0;
-      __syncthreads();
-      scan[threadIdx.x] += t;
-      __syncthreads();
+    if (warp == 0) {
+      int v = lane < nwarps ? wsum[lane] : 0;
+      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(PIADMM_FULL, v, o); if (lane >= o) v += t; }
+      wsum[lane] = v;
     }
-    int n = base + scan[threadIdx.x] - cnt;
+    __syncthreads();
+    int n = base + (warp ? wsum[warp - 1] : 0) + inc - cnt;
     if (i < c.V && cnt > 0) {
+      // the up-edges of i are among its <= D neighbour slots: test their hit bits (D loads instead of a scan of the
+      // whole row) and emit them in ascending j, the order of np.where(edge_mat == 1)
       const int32_t* nbi = c.b.nbr + ((size_t)s * c.V + i) * c.D;
-      for (int wd = (i + 1) >> 5; wd < words; wd++) {
-       uint32_t m = H[(size_t)i * words + wd];
-       if (wd == ((i + 1) >> 5)) m &= ~0u << ((i + 1) & 31);       // only j > i
-       while (m) {
-        const int j = wd * 32 + __ffs(m) - 1;
-        m &= m - 1;
+      int lastj = i;
+      for (int e = 0; e < cnt; e++) {
+        int j = 0x7fffffff, di = -1;
+        for (int d = 0; d < c.D; d++) {
+          const int cand = nbi[d];
+          if (cand > lastj && cand < j && ((H[(size_t)i * words + (cand >> 5)] >> (cand & 31)) & 1u)) { j = cand; di = d; }
+        }
+        if (di < 0) break;
+        lastj = j;
         const int32_t* nbj = c.b.nbr + ((size_t)s * c.V + j) * c.D;
-        int di = -1, dj = -1;
-        for (int d = 0; d < c.D; d++) { if (nbi[d] == j) di = d; if (nbj[d] == i) dj = d; }
+        int dj = -1;
+        for (int d = 0; d < c.D; d++) if (nbj[d] == i) dj = d;
         if (n >= c.E) continue;
         int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + n) * 2;
         int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + n) * 2;
-        if (di < 0 || dj < 0) {        // slot overflow on the far side (status already set): dead entry
+        if (dj < 0) {                  // slot overflow on the far side (status already set): dead entry
           eij[0] = -1; eij[1] = -1; esl[0] = 0; esl[1] = 0;
           double* er = c.edge_res + ((size_t)s * c.E + n) * 4;
           er[0] = er[1] = er[2] = er[3] = 0.0;
@@ -219,11 +246,10 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
           eij[0] = i; eij[1] = j; esl[0] = di; esl[1] = dj;
         }
         n++;
-       }
       }
     }
     __syncthreads();
-    if (threadIdx.x == blockDim.x - 1) base += scan[threadIdx.x];
+    if (threadIdx.x == 0) base += wsum[nwarps - 1];
     __syncthreads();
   }
   if (threadIdx.x == 0) {
@@ -238,7 +264,7 @@ template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
-  __shared__ __align__(16) double xch[64];
+  __shared__ __align__(16) double xch[128];
   Who<LPQ> w;
   const long pairs = (long)c.S * c.E, items = (pairs + pairs_per_cta<LPQ>() - 1) / pairs_per_cta<LPQ>();
   bool loaded = false;
@@ -469,7 +495,7 @@ template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
-  __shared__ __align__(16) double xch[64];
+  __shared__ __align__(16) double xch[128];
   __shared__ int s_next;
   load_W<LPQ>(c, Wsm);
   Who<LPQ> w;
@@ -490,7 +516,7 @@ template <int LPQ>
 __global__ void __launch_bounds__(KS_THREADS(LPQ), LPQ == 16 ? 7 : 12) k_fused_ks(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double krows[KS_GROUPS(LPQ)][LPQ * PIADMM_KROW_STRIDE(LPQ)];
   __shared__ __align__(16) double gbuf[KS_GROUPS(LPQ)][2 * LPQ];
-  __shared__ __align__(16) double xch[64];
+  __shared__ __align__(16) double xch[128];
   __shared__ int s_next;
   Who<LPQ> w;
   for (;;) {
@@ -937,12 +963,13 @@ int piadmm_detect_edges(piadmm_handle* h, void* stream) {
   const long warps = (long)h->c.S * h->c.V * words;
   k_bbox<<<(unsigned)(((long)h->c.S * h->c.V + 127) / 128), 128, 0, st>>>(h->c);
   LAUNCHED();
-  k_hits<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(h->c);
+  CK(cudaMemsetAsync(h->c.hits, 0, sizeof(uint32_t) * (size_t)warps, st));
+  k_hits<<<(unsigned)((warps + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
   const long agents = (long)h->c.S * h->c.V;
-  k_slots<<<(unsigned)((agents + 127) / 128), 128, 0, st>>>(h->c);
+  k_slots<<<(unsigned)((agents * 32 + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
-  k_edges<<<h->c.S, 128, 0, st>>>(h->c);
+  k_edges<<<h->c.S, h->c.V > 512 ? 1024 : (h->c.V > 128 ? 256 : 128), 0, st>>>(h->c);
   LAUNCHED();
   return PIADMM_OK;
 }

@@ -127,17 +127,36 @@ __device__ __forceinline__ double apply_Mt_s(double ws, int k) {
   return excl_suffix<LPQ>(t, k);
 }
 
-// exchange one double with the partner group of the pair
+// exchange one double with the partner group of the pair.  LPQ==32: through shared memory, DOUBLE BUFFERED (xch =
+// 2 x 64 doubles, `par` selects the buffer and flips): one CTA barrier per exchange instead of two -- the buffer
+// written now is not written again before the barrier of the NEXT exchange, which every thread only reaches after it
+// has read this one.
 template <int LPQ>
-__device__ __forceinline__ double partner(double mine, double* xch, int k, int half) {
+__device__ __forceinline__ double partner(double mine, double* xch, int k, int half, int& par) {
   if (LPQ == 16) {
     return __shfl_xor_sync(PIADMM_FULL, mine, 16);
   } else {
-    xch[half * 32 + k] = mine;
+    double* b = xch + par * 64;
+    par ^= 1;
+    b[half * 32 + k] = mine;
     __syncthreads();
-    double o = xch[(half ^ 1) * 32 + k];
+    return b[(half ^ 1) * 32 + k];
+  }
+}
+// the four group-uniform termination quantities of the partner in one exchange
+template <int LPQ>
+__device__ __forceinline__ void partner_max4(double& a0, double& a1, double& a2, double& a3, double* xch, int k, int half,
+                                             int& par) {
+  if (LPQ == 16) {
+    a0 = fmax(a0, __shfl_xor_sync(PIADMM_FULL, a0, 16)); a1 = fmax(a1, __shfl_xor_sync(PIADMM_FULL, a1, 16));
+    a2 = fmax(a2, __shfl_xor_sync(PIADMM_FULL, a2, 16)); a3 = fmax(a3, __shfl_xor_sync(PIADMM_FULL, a3, 16));
+  } else {
+    double* b = xch + par * 64;
+    par ^= 1;
+    if (k == 0) { double* o = b + half * 32; o[0] = a0; o[1] = a1; o[2] = a2; o[3] = a3; }
     __syncthreads();
-    return o;
+    const double* o = b + (half ^ 1) * 32;
+    a0 = fmax(a0, o[0]); a1 = fmax(a1, o[1]); a2 = fmax(a2, o[2]); a3 = fmax(a3, o[3]);
   }
 }
 
@@ -279,7 +298,7 @@ struct InnerOut {
 // rows become the identity (lane L <-> trajectory index L+2; lane N-1 holds the all-zero row of index 1)
 // and D, D' are 3-point stencils.  Termination is still evaluated on the steering-space residuals.
 // cvec follows that lane layout.  rhsbuf: 2*LPQ doubles of shared memory per group (the mat-vec uses the first
-// LPQ, the K^-1 builds all of it), xch: 64 doubles per pair.
+// LPQ, the K^-1 builds all of it), xch: 2 x 64 doubles per pair.
 //
 // KS (throughput variant of the fused kernel): the row of K^-1 is kept in SHARED memory (krow: this lane's
 // row, LPQ doubles, rows padded to LPQ+2 so that a quarter-warp LDS.128 is conflict free) instead of
@@ -315,6 +334,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
   // everything the loop body reads is copied out of *ip first: ip points into the kernel parameter block
   // through a generic pointer, and a load from it inside the loop is a real memory access on the chain
   const int check_every = ip.in_check;
+  int xpar = 0;                              // buffer parity of the LPQ==32 partner exchange
   int left = ip.in_max_iter;                 // iterations still allowed
   const double inv_na = 1.0 / na;
   double tb = ip.beta * irho;                // hinge prox step bound beta / rho
@@ -387,7 +407,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       const double st = srow ? tt : 0.0;            // position row value (lane N-1: the zero row)
       const double zrs = fma(al, st, oma * zs);
       const double vs = fma(ys, irho, zrs);
-      const double vo = partner<LPQ>(vs, xch, k, half);
+      const double vo = partner<LPQ>(vs, xch, k, half, xpar);
       const double s0 = half == 0 ? vs : vo, s1 = half == 0 ? vo : vs;
       const double tau = fma(a1, s1, a0 * s0);
       // prox of beta*max(0, c - a's): step = clamp((c - tau)/|a|^2, 0, beta/rho), branch free
@@ -427,10 +447,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       double nd = dmax(fabs(Px), dmax(fabs(Aty), fabs(q)));
       rp = group_max<LPQ>(rp); np = group_max<LPQ>(np); rd = group_max<LPQ>(rd); nd = group_max<LPQ>(nd);
       if (edge) {
-        rp = dmax(rp, partner<LPQ>(rp, xch, k, half));
-        np = dmax(np, partner<LPQ>(np, xch, k, half));
-        rd = dmax(rd, partner<LPQ>(rd, xch, k, half));
-        nd = dmax(nd, partner<LPQ>(nd, xch, k, half));
+        partner_max4<LPQ>(rp, np, rd, nd, xch, k, half, xpar);
       }
       const bool conv = rp <= ip.in_eps_abs + ip.in_eps_rel * np && rd <= ip.in_eps_abs + ip.in_eps_rel * nd;
       if (conv && !done) {
