@@ -83,7 +83,7 @@ __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_x_update(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 6) k_x_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];
@@ -261,7 +261,7 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 5) k_z_update(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 6) k_z_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];
@@ -492,7 +492,7 @@ __global__ void __launch_bounds__(1024) k_order(const __grid_constant__ DevCtx c
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 5) k_fused_v2(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 6) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];
