@@ -8,6 +8,9 @@
 #include "piadmm_phases.cuh"
 
 #define CTA_THREADS 64
+#ifndef Z32_MIN_CTAS
+#define Z32_MIN_CTAS 4    // the LPQ==32 edge kernel is latency critical (few concurrent edges): registers over occupancy
+#endif
 #ifndef FUSED16_MIN_CTAS
 #define FUSED16_MIN_CTAS 7   // resident CTAs per SM the LPQ==16 fused kernel is compiled for (register budget)
 #endif
@@ -261,7 +264,7 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 6) k_z_update(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : Z32_MIN_CTAS) k_z_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];

@@ -306,6 +306,12 @@ struct InnerOut {
 // as many scenario-warps are resident to hide the dependent FP64 / LDS / SHFL latencies.  The Gauss-Jordan
 // build still runs in registers; around a rebuild the ADMM state is parked in the (then free) row.
 #define PIADMM_KROW_STRIDE(LPQ) ((LPQ) + 2)
+#ifndef PIADMM_NACC16
+#define PIADMM_NACC16 8
+#endif
+#ifndef PIADMM_NACC32
+#define PIADMM_NACC32 16
+#endif
 template <int LPQ, bool KS>
 __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, int k, int half, bool edge,
                                                 double pI, double p2, double pW, double q, double a0, double a1,
@@ -361,27 +367,35 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
     rhsbuf[k] = rhs;
     __syncwarp();
     // ---- K^-1 rhs  (row k in registers, rhs broadcast from shared memory)
-    double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+    // independent accumulator chains of the mat-vec: the dependent-DFMA depth is LPQ / NACC (+ log2 NACC adds)
+    constexpr int PIADMM_NACC = LPQ == 16 ? PIADMM_NACC16 : PIADMM_NACC32;
+    double acc[PIADMM_NACC];
+#pragma unroll
+    for (int u = 0; u < PIADMM_NACC; u++) acc[u] = 0.0;
 #pragma unroll
     for (int j = 0; j < LPQ; j += 4) {
       const double2 r0 = *reinterpret_cast<const double2*>(rhsbuf + j);
       const double2 r1 = *reinterpret_cast<const double2*>(rhsbuf + j + 2);
+      double k0x, k0y, k1x, k1y;
       if (KS) {
         const double2 k0 = *reinterpret_cast<const double2*>(krow + j);
         const double2 k1 = *reinterpret_cast<const double2*>(krow + j + 2);
-        acc0 = fma(k0.x, r0.x, acc0);
-        acc1 = fma(k0.y, r0.y, acc1);
-        acc2 = fma(k1.x, r1.x, acc2);
-        acc3 = fma(k1.y, r1.y, acc3);
+        k0x = k0.x; k0y = k0.y; k1x = k1.x; k1y = k1.y;
       } else {
-        acc0 = fma(Kinv[j], r0.x, acc0);
-        acc1 = fma(Kinv[j + 1], r0.y, acc1);
-        acc2 = fma(Kinv[j + 2], r1.x, acc2);
-        acc3 = fma(Kinv[j + 3], r1.y, acc3);
+        k0x = Kinv[j]; k0y = Kinv[j + 1]; k1x = Kinv[j + 2]; k1y = Kinv[j + 3];
       }
+      acc[(j + 0) % PIADMM_NACC] = fma(k0x, r0.x, acc[(j + 0) % PIADMM_NACC]);
+      acc[(j + 1) % PIADMM_NACC] = fma(k0y, r0.y, acc[(j + 1) % PIADMM_NACC]);
+      acc[(j + 2) % PIADMM_NACC] = fma(k1x, r1.x, acc[(j + 2) % PIADMM_NACC]);
+      acc[(j + 3) % PIADMM_NACC] = fma(k1y, r1.y, acc[(j + 3) % PIADMM_NACC]);
     }
     __syncwarp();
-    double xt = (acc0 + acc1) + (acc2 + acc3);
+#pragma unroll
+    for (int w = PIADMM_NACC / 2; w >= 1; w >>= 1) {
+#pragma unroll
+      for (int u = 0; u < w; u++) acc[u] += acc[u + w];
+    }
+    double xt = acc[0];
     double tt = 0.0;
     if (edge) {                                                        // x~ = D t~
       tt = xt;
