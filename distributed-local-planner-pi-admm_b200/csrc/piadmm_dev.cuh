@@ -306,9 +306,6 @@ struct InnerOut {
 // as many scenario-warps are resident to hide the dependent FP64 / LDS / SHFL latencies.  The Gauss-Jordan
 // build still runs in registers; around a rebuild the ADMM state is parked in the (then free) row.
 #define PIADMM_KROW_STRIDE(LPQ) ((LPQ) + 2)
-#ifndef PIADMM_WCARRY
-#define PIADMM_WCARRY 1
-#endif
 #ifndef PIADMM_NACC16
 #define PIADMM_NACC16 8
 #endif
@@ -324,11 +321,14 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
   const double l_u = -0.52359877559829887308, l_d = -0.34906585039886591538;  // -pi/6, -pi/9
   double Kinv[LPQ];
   double rho = ip.in_rho0, irho = 1.0 / rho;
-  double x = 0.0, z0 = 0.0, z1 = 0.0, z2 = 0.0, z3 = 0.0, y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0;
-  double t = 0.0, zs = 0.0, ys = 0.0;
-#if PIADMM_WCARRY
-  double g01 = 0.0, ge = 0.0, gs = 0.0;       // (g0 - g1), (g3 - g2), g_s with g = z - y/rho, see the loop head
-#endif
+  // ADMM state per constraint row r: z_r and c_r = (1-alpha) z_r + y_r/rho.  The dual y_r is implicit,
+  // y_r = rho (c_r - (1-alpha) z_r); the recurrences below are OSQP's written in (z, c):
+  //   v = alpha (A x~)_r + c_r,  z' = Pi(v),  y' = rho (v - z')  =>  c' = v - alpha z',  g' = z' - y'/rho = 2 z' - v.
+  // Per iteration and row that is 1 FMA + projection + 2 FMA (instead of relaxation, projection and a separate
+  // dual update), and the loop-carried dependency chain is three FP64 operations shorter.
+  double x = 0.0, z0 = 0.0, z1 = 0.0, z2 = 0.0, z3 = 0.0, c0 = 0.0, c1 = 0.0, c2 = 0.0, c3 = 0.0;
+  double t = 0.0, zs = 0.0, cs = 0.0;
+  double g01 = 0.0, ge = 0.0, gs = 0.0;       // (g0 - g1), (g3 - g2), g_s of the rows of this lane
   const double na = edge ? fma(a1, a1, a0 * a0) : 1.0;
   const double a_me = half == 0 ? a0 : a1;
   const bool inner_row = k < N - 1;
@@ -358,29 +358,16 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
 #pragma unroll 1
    for (int cnt = blk; cnt > 0; cnt--) {
     // ---- steering-space right-hand side  v = sigma x - q + A'(rho z - y)
-#if PIADMM_WCARRY
-    // A'(rho z - y) = rho * A'g with g_r = z_r - y_r/rho = 2 z_r - v_r carried from the projection step below
-    // (v_r = relaxed row value + y_r/rho; y' = rho (v - z') holds for any z'): two dependent FP64 operations
-    // fewer on the chain that wraps around the loop.  e_{k-1}: lane 0 reads the last lane of the group, a padded
-    // lane (N <= LPQ-1) whose e is exactly 0.
+    // A'(rho z - y) = rho A'g.  e_{k-1}: lane 0 reads the last lane of the group, a padded lane (N <= LPQ-1)
+    // whose g is exactly 0.
     double rhs = fma(rho, (g01 - ge) + __shfl_sync(PIADMM_FULL, ge, (k - 1) & (LPQ - 1), LPQ), fma(sg, x, -q));
-#else
-    const double e = (rho * z3 - y3) - (rho * z2 - y2);
-    double rhs = sg * x - q + ((rho * z0 - y0) - (rho * z1 - y1)) - e;
-    // + e_{k-1}: lane 0 reads the last lane of the group, a padded lane (N <= LPQ-1) whose e is exactly 0
-    rhs += __shfl_sync(PIADMM_FULL, e, (k - 1) & (LPQ - 1), LPQ);
-#endif
     if (edge) {                                                        // rhs_t = D' v + (rho zs - ys) on position rows
       // neighbours beyond lane N-2 must not contribute: zero them at the source (the clamped shuffle of the
       // last lanes returns their own, zeroed, value), so the two stencil terms need no per-lane predicate
       const double vm = srow ? rhs : 0.0;
       const double v1 = __shfl_down_sync(PIADMM_FULL, vm, 1, LPQ), v2 = __shfl_down_sync(PIADMM_FULL, vm, 2, LPQ);
       rhs = fma(-2.0, v1, rhs) + v2;
-#if PIADMM_WCARRY
       fma_if(rhs, rho, gs, srow);
-#else
-      fma_if(rhs, 1.0, fma(rho, zs, -ys), srow);
-#endif
     }
     rhsbuf[k] = rhs;
     __syncwarp();
@@ -424,47 +411,33 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
     // ---- z~ = A x~, relaxation, projection, dual update
     double d = __shfl_down_sync(PIADMM_FULL, xt, 1, LPQ) - xt;        // the last lane is padded (xt = 0): no clamp needed
     if (!inner_row) d = 0.0;
-    const double zr0 = fma(al, xt, oma * z0);
-    const double zr1 = fma(-al, xt, oma * z1);
-    const double zr2 = fma(-al, d, oma * z2);
-    const double zr3 = fma(al, d, oma * z3);
     x = fma(al, xt, oma * x);
-    double zn;
-#if PIADMM_WCARRY
     {
-      const double v0 = fma(y0, irho, zr0), v1 = fma(y1, irho, zr1), v2 = fma(y2, irho, zr2), v3 = fma(y3, irho, zr3);
+      const double v0 = fma(al, xt, c0), v1 = fma(-al, xt, c1), v2 = fma(-al, d, c2), v3 = fma(al, d, c3);
       z0 = dmax(v0, l_u); z1 = dmax(v1, l_u); z2 = dmax(v2, l_d); z3 = dmax(v3, l_d);
       g01 = fma(2.0, z0, -v0) - fma(2.0, z1, -v1);
       ge = fma(2.0, z3, -v3) - fma(2.0, z2, -v2);
-      y0 = fma(rho, zr0 - z0, y0); y1 = fma(rho, zr1 - z1, y1); y2 = fma(rho, zr2 - z2, y2); y3 = fma(rho, zr3 - z3, y3);
+      c0 = fma(-al, z0, v0); c1 = fma(-al, z1, v1); c2 = fma(-al, z2, v2); c3 = fma(-al, z3, v3);
     }
-#else
-    zn = dmax(fma(y0, irho, zr0), l_u); y0 = fma(rho, zr0 - zn, y0); z0 = zn;
-    zn = dmax(fma(y1, irho, zr1), l_u); y1 = fma(rho, zr1 - zn, y1); z1 = zn;
-    zn = dmax(fma(y2, irho, zr2), l_d); y2 = fma(rho, zr2 - zn, y2); z2 = zn;
-    zn = dmax(fma(y3, irho, zr3), l_d); y3 = fma(rho, zr3 - zn, y3); z3 = zn;
-#endif
     if (edge) {
       t = fma(al, tt, oma * t);
       const double st = srow ? tt : 0.0;            // position row value (lane N-1: the zero row)
-      const double zrs = fma(al, st, oma * zs);
-      const double vs = fma(ys, irho, zrs);
+      const double vs = fma(al, st, cs);
       const double vo = partner<LPQ>(vs, xch, k, half, xpar);
       const double s0 = half == 0 ? vs : vo, s1 = half == 0 ? vo : vs;
       const double tau = fma(a1, s1, a0 * s0);
       // prox of beta*max(0, c - a's): step = clamp((c - tau)/|a|^2, 0, beta/rho), branch free
       const double step = dmin(dmax((cvec - tau) * inv_na, 0.0), tb);
-      zn = fma(step, a_me, vs);
-#if PIADMM_WCARRY
-      gs = fma(2.0, zn, -vs);
-#endif
-      ys = fma(rho, zrs - zn, ys);
-      zs = zn;
+      zs = fma(step, a_me, vs);
+      gs = fma(2.0, zs, -vs);
+      cs = fma(-al, zs, vs);
     }
    }
    left -= blk;
     // ---- termination / adaptive rho every in_check iterations (steering-space residuals)
     if (blk == check_every) {
+      const double y0 = rho * fma(-oma, z0, c0), y1 = rho * fma(-oma, z1, c1), y2 = rho * fma(-oma, z2, c2),
+                   y3 = rho * fma(-oma, z3, c3), ys = rho * fma(-oma, zs, cs);      // the implicit duals
       double dd = shift_down1<LPQ>(x, k) - x;
       if (!inner_row) dd = 0.0;
       double rp = dmax(dmax(fabs(x - z0), fabs(-x - z1)), dmax(fabs(-dd - z2), fabs(dd - z3)));
@@ -512,23 +485,25 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       // (conv is identical in both halves of an edge by construction).
       if (__all_sync(PIADMM_FULL, done)) break;
       if (__any_sync(PIADMM_FULL, refac)) {
-        if (refac) {
+        if (refac) {       // OSQP keeps (z, y) and changes rho: re-express c and g in the new rho
           rho = rn; irho = 1.0 / rho; tb = ip.beta * irho;
-#if PIADMM_WCARRY
+          c0 = fma(y0, irho, oma * z0); c1 = fma(y1, irho, oma * z1); c2 = fma(y2, irho, oma * z2);
+          c3 = fma(y3, irho, oma * z3); cs = fma(ys, irho, oma * zs);
           g01 = fma(-y0, irho, z0) - fma(-y1, irho, z1);
           ge = fma(-y3, irho, z3) - fma(-y2, irho, z2);
           gs = fma(-ys, irho, zs);
-#endif
         }
         if (KS) {      // park the ADMM state in the row that is about to be rebuilt (frees 24 registers for the build)
-          krow[0] = x; krow[1] = z0; krow[2] = z1; krow[3] = z2; krow[4] = z3; krow[5] = y0; krow[6] = y1;
-          krow[7] = y2; krow[8] = y3; krow[9] = t; krow[10] = zs; krow[11] = ys;
+          krow[0] = x; krow[1] = z0; krow[2] = z1; krow[3] = z2; krow[4] = z3; krow[5] = c0; krow[6] = c1;
+          krow[7] = c2; krow[8] = c3; krow[9] = t; krow[10] = zs; krow[11] = cs; krow[12] = g01; krow[13] = ge;
+          krow[14] = gs;
         }
         if (edge) build_Kinv_edge<LPQ, KS>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
         else build_Kinv_vehicle<LPQ, KS>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
         if (KS) {
-          x = krow[0]; z0 = krow[1]; z1 = krow[2]; z2 = krow[3]; z3 = krow[4]; y0 = krow[5]; y1 = krow[6];
-          y2 = krow[7]; y3 = krow[8]; t = krow[9]; zs = krow[10]; ys = krow[11];
+          x = krow[0]; z0 = krow[1]; z1 = krow[2]; z2 = krow[3]; z3 = krow[4]; c0 = krow[5]; c1 = krow[6];
+          c2 = krow[7]; c3 = krow[8]; t = krow[9]; zs = krow[10]; cs = krow[11]; g01 = krow[12]; ge = krow[13];
+          gs = krow[14];
 #pragma unroll
           for (int j = 0; j < LPQ; j += 2) *reinterpret_cast<double2*>(krow + j) = make_double2(Kinv[j], Kinv[j + 1]);
         }
