@@ -492,6 +492,7 @@ __global__ void __launch_bounds__(1024) k_order(const __grid_constant__ DevCtx c
     const unsigned pos = atomicAdd(&hist[order_bucket(c, c.s_lo + t, scale)], 1u);
     order[c.s_lo + pos] = c.s_lo + t;
   }
+  if (threadIdx.x == 0) *c.queue = 0;          // the fused kernel before this one is done: re-arm its work queue
 }
 
 template <int LPQ>
@@ -663,6 +664,7 @@ struct piadmm_handle {
   int* d_order;               // [S] longest-first processing order learnt from the previous step
   bool use_order;             // PIADMM_LPT=0 disables the hint
   bool order_valid[PIADMM_CHUNKS + 1];   // per launch range: [0] whole batch, [1+ch] sub-batch ch
+  bool queue_armed[PIADMM_CHUNKS + 1];   // the range's work counter was reset on the device by the last k_order
   cudaStream_t cs[PIADMM_CHUNKS], cs_main;
   cudaEvent_t ev_start, ev_user, ev_done[PIADMM_CHUNKS];
   int n_chunks;               // sub-batches used by piadmm_step_host (PIADMM_NCHUNKS, default 2)
@@ -829,7 +831,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   {
     const char* lpt = getenv("PIADMM_LPT");
     h->use_order = !(lpt && strcmp(lpt, "0") == 0);
-    for (int i = 0; i <= PIADMM_CHUNKS; i++) h->order_valid[i] = false;
+    for (int i = 0; i <= PIADMM_CHUNKS; i++) { h->order_valid[i] = false; h->queue_armed[i] = false; }
   }
   for (int i = 0; i < PIADMM_CHUNKS; i++) {
     if ((ce = cudaStreamCreateWithFlags(&h->cs[i], cudaStreamNonBlocking)) != cudaSuccess) return fail(ce, "stream");
@@ -1069,7 +1071,7 @@ static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, i
   }
   // the whole-batch order and the sub-batch orders share d_order: using one invalidates the other
   c.order = (h->use_order && h->order_valid[range_id]) ? h->d_order : nullptr;
-  CK(cudaMemsetAsync(queue, 0, sizeof(int), st));
+  if (!h->queue_armed[range_id]) CK(cudaMemsetAsync(queue, 0, sizeof(int), st));   // else k_order of the last launch did it
   const int pairs = h->lpq == 16 ? (h->fused_ks ? KS_THREADS(16) / 32 : 2) : 1;
   int grid = (s_hi - s_lo + pairs - 1) / pairs;
   if (grid > h->fused_grid) grid = h->fused_grid;
@@ -1085,7 +1087,8 @@ static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, i
     if (range_id == 0) { for (int i = 1; i <= PIADMM_CHUNKS; i++) h->order_valid[i] = false; }
     else h->order_valid[0] = false;
     h->order_valid[range_id] = true;
-  } else h->order_valid[range_id] = false;
+    h->queue_armed[range_id] = true;
+  } else { h->order_valid[range_id] = false; h->queue_armed[range_id] = false; }
   return PIADMM_OK;
 }
 
@@ -1206,7 +1209,7 @@ static int step_host_impl(piadmm_handle* h, const double* xt, const double* spd,
         if (rc != PIADMM_OK || ce != cudaSuccess) {      // capture unavailable: plain stream path from now on
           cudaGetLastError();
           h->gexec = nullptr; h->use_graph = false; graph = false;
-          for (int i = 0; i <= PIADMM_CHUNKS; i++) h->order_valid[i] = false;
+          for (int i = 0; i <= PIADMM_CHUNKS; i++) { h->order_valid[i] = false; h->queue_armed[i] = false; }
         } else {
           memcpy(h->gkey, key, sizeof key);
           for (int i = 0; i <= PIADMM_CHUNKS; i++) h->gvalid_after[i] = h->order_valid[i];
