@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : Z32_MIN_CTAS) k_z
     if (!loaded) { load_tabs<LPQ>(c, Wsm, 2, 2); loaded = true; }
     if (!valid) continue;                     // LPQ==16 only: the other pair of the CTA works alone
     dev_z_update<LPQ, false>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
-                             Wsm, gbuf[w.group_in_cta], xch, nullptr);
+                             Wsm, gbuf[w.group_in_cta], xch, nullptr, false);
   }
 }
 
@@ -590,7 +590,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
     double sk = 0.0, rk = 0.0;
     if (hit) {
       if (k == 0) c.b.nbr[(size_t)s * 2 + i] = j;
-      dev_z_update<LPQ, KS>(c, s, 0, 0, 1, 0, 0, true, true, k, w.lane, half, Wsm, gbuf, xch, krow);
+      dev_z_update<LPQ, KS>(c, s, 0, 0, 1, 0, 0, true, true, k, w.lane, half, Wsm, gbuf, xch, krow, true);
       pair_sync<LPQ>();
       const double* er = c.edge_res + (size_t)s * c.E * 4;
       const double rho = p.dual_mode == PIADMM_DUAL_PI_OLD ? c.rho_new[s] : c.b.rho_s[s];
@@ -828,6 +828,14 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMalloc(&h->d_count, sizeof(int))) != cudaSuccess) return fail(ce, "count");
   if ((ce = cudaMalloc(&h->d_queue, sizeof(int) * (PIADMM_CHUNKS + 1))) != cudaSuccess) return fail(ce, "queue");
   if ((ce = cudaMalloc(&h->d_order, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "order");
+  {   // K^-1(rho0) cache (PIADMM_KCACHE=0 disables): zero keys never match (cI > 0)
+    const char* e = getenv("PIADMM_KCACHE");
+    if (!(e && strcmp(e, "0") == 0)) {
+      const size_t nb = sizeof(double) * (size_t)S * V * 2 * PIADMM_KC_STRIDE(h->lpq);
+      if ((ce = cudaMalloc(&h->c.kcache, nb)) != cudaSuccess) return fail(ce, "kcache");
+      if ((ce = cudaMemset(h->c.kcache, 0, nb)) != cudaSuccess) return fail(ce, "kcache");
+    }
+  }
   {
     const char* lpt = getenv("PIADMM_LPT");
     h->use_order = !(lpt && strcmp(lpt, "0") == 0);
@@ -887,7 +895,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
   cudaFree(h->d_count); cudaFree(h->d_queue); cudaFree(h->d_order); cudaFree(h->d_ref); cudaFree(h->d_step);
   if (h->h_step) cudaFreeHost(h->h_step);
   if (h->have_streams) {

@@ -59,7 +59,8 @@ __device__ __noinline__ void dev_x_update(const DevCtx& c, int s, int i, bool va
   const double vec = (valid && k <= N) ? (w * e0 + sn * tx - cs * ty) : 0.0;
   const double q = 2.0 * g * apply_Mt<LPQ>(vec, k);
   const double pI = 2.0 * p.Pcost, p2 = valid ? 2.0 : 0.0, pW = valid ? 2.0 * w * g * g : 0.0;
-  InnerOut o = inner_solve<LPQ, KS>(p, N, k, half, false, pI, p2, pW, q, 0.0, 0.0, 0.0, Wsm, gbuf, xch, krow);
+  double* kc = (c.kcache && valid) ? c.kcache + (((size_t)s * c.V + i) * 2) * PIADMM_KC_STRIDE(LPQ) : nullptr;
+  InnerOut o = inner_solve<LPQ, KS>(p, N, k, half, false, pI, p2, pW, q, 0.0, 0.0, 0.0, Wsm, gbuf, xch, krow, kc);
   const double u = (k < N) ? round_scale(o.x, c.round_u_scale) : 0.0;
   double px, py;
   if (p.pos_nonlinear) {
@@ -92,7 +93,8 @@ __device__ __noinline__ void dev_x_update(const DevCtx& c, int s, int i, bool va
 template <int LPQ, bool KS>
 __device__ __noinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0, int v1, int sl0, int sl1,
                                              bool last_edge, bool valid, int k, int lane, int half,
-                                             const double* Wsm, double* gbuf, double* xch, double* krow) {
+                                             const double* Wsm, double* gbuf, double* xch, double* krow,
+                                             bool edge_cache) {
   const piadmm_params& p = c.p;
   const int N = c.N;
   int vv[2] = {v0, v1}, sl[2] = {sl0, sl1};
@@ -144,7 +146,10 @@ __device__ __noinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0,
   const double a0 = valid ? -2.0 * g0 * (-lx * sn[0] + ly * cs[0]) : 0.0;
   const double a1 = valid ? 2.0 * g1 * (-lx * sn[1] + ly * cs[1]) : 0.0;
   const double pI = 2.0 * p.Pcost, pW = valid ? rho * g * g : 0.0;
-  InnerOut o = inner_solve<LPQ, KS>(p, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow);
+  // a vehicle can be an endpoint of several edges solved concurrently: the edge entry is used only where every
+  // vehicle has a single writer (edge_cache: the fused V=2 kernel)
+  double* kc = (c.kcache && valid && edge_cache) ? c.kcache + (((size_t)s * c.V + vv[me]) * 2 + 1) * PIADMM_KC_STRIDE(LPQ) : nullptr;
+  InnerOut o = inner_solve<LPQ, KS>(p, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow, kc);
   // z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158)
   const double uh = (k < N) ? round_scale(o.x, c.round_edge_scale) : 0.0;
   double hx, hy, hth;
