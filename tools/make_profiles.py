@@ -115,11 +115,17 @@ agrees with the CUDA-event time of the bench: the fused kernel IS the step.
   a division, 2x2-block Gauss-Jordan builds (half the latency rounds; the builds were ~20 % of the time), nested
   block counters instead of a spilled loop counter, and a longest-first scenario order learnt from the previous step
   (scenario work varies 2.7x; elapsed / active SM cycles went from 1.32 to 1.14).
-* Algorithmic flops are ~15 % of the DFMA peak while the pipe is ~35 % busy: the difference is Gauss-Jordan rebuilds
-  of K^-1 (about 1.6 per solve), termination checks, the padded 16th lane and the lock-step wait of the faster
+* Algorithmic flops are ~18 % of the DFMA peak while the pipe is ~37 % busy: the difference is Gauss-Jordan rebuilds
+  of K^-1 at an adapted rho (about 0.7 per solve), termination checks, the padded 16th lane and the lock-step wait of the faster
   vehicle of a warp (16 %).
-* Next candidates: cache K^-1(rho0) across outer iterations (saves one of ~1.6 builds per solve), pair like vehicles
-  of two scenarios in a warp, software-pipeline the right-hand-side loads of the mat-vec.
+* K^-1(rho0) is cached in global memory across outer iterations and MPC steps (key = the coefficients that define K),
+  so only the rebuilds at an adapted rho remain (~0.7 per solve, ~10 % of the samples).  The 35 MB of cache entries
+  are what the DRAM read figure above consists of (the bench flushes L2 before every step).
+* Sample shares of the current kernel (source page): inner-iteration loops 50 %, per-call prologue / epilogue of the
+  x-update and the edge step 21 % (reference tracking terms, roll-outs, dual / PI update), termination checks 11 %,
+  Gauss-Jordan rebuilds 10 %, scenario initialisation and queue 5 %.
+* Next candidates: pair like vehicles of two scenarios in a warp, rebuild K^-1(rho) from a cached eigen-decomposition
+  of the pencil (K0, A'A) instead of Gauss-Jordan, slimmer termination checks.
 """)
     print("profiles/ regenerated from tag", tag)
 
