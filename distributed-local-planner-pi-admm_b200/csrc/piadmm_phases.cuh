@@ -23,7 +23,7 @@ __device__ __forceinline__ void rollout_nonlinear(const piadmm_params& p, double
 
 // ---- x-update of agent (s,i): casadi/main.py:81-106 --------------------------------------------
 template <int LPQ, bool KS>
-__device__ __noinline__ void dev_x_update(const DevCtx& c, int s, int i, bool valid, int k, int lane,
+__device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool valid, int k, int lane,
                                              int half, const double* Wsm, double* gbuf, double* xch, double* krow) {
   const piadmm_params& p = c.p;
   const int N = c.N;
@@ -91,7 +91,7 @@ __device__ __noinline__ void dev_x_update(const DevCtx& c, int s, int i, bool va
 // casadi/main.py:121-162 with the convex edge problem (MATLAB ...PI_antiwindup.m:276-304,383-396)
 // and the three dual-update laws.  Writes hat, dual, integ, diff (own side), edge_res, rho_new.
 template <int LPQ, bool KS>
-__device__ __noinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0, int v1, int sl0, int sl1,
+__device__ __forceinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0, int v1, int sl0, int sl1,
                                              bool last_edge, bool valid, int k, int lane, int half,
                                              const double* Wsm, double* gbuf, double* xch, double* krow,
                                              bool edge_cache) {
