@@ -8,6 +8,7 @@ import ctypes as C
 import importlib
 import os
 import subprocess
+import sys
 
 import numpy as np
 
@@ -21,7 +22,7 @@ _lib = None
 
 def build(force: bool = False):
     if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(os.path.join(_HERE, "piadmm_ref.c")):
-        subprocess.check_call(["make", "-C", _HERE, "-s"])
+        subprocess.check_call(["make", "-C", _HERE, "-s"], stdout=sys.stderr)
     return _LIB
 
 
