@@ -759,7 +759,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
   h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false; h->gexec = nullptr; h->d_ref = nullptr; h->ref_T = 0; h->h_step = nullptr; h->d_step = nullptr;
-  h->c.p = *p; h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
+  h->c.p = *p; set_inner_consts(h->c.ik, p->in_alpha); h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
   h->c.N = p->num_ho; h->c.I = p->iter_num;
   h->c.own_lo = 0; h->c.own_hi = V;
   h->c.s_lo = 0; h->c.s_hi = S;
@@ -912,6 +912,7 @@ int piadmm_set_params(piadmm_handle* h, const piadmm_params* p) {
   if (rc) return rc;
   if (p->num_ho != h->c.N || p->iter_num != h->c.I) { h->err = "num_ho / iter_num are fixed at create time"; return PIADMM_E_ARG; }
   h->c.p = *p;
+  set_inner_consts(h->c.ik, p->in_alpha);
   h->c.round_u_scale = pow10i(p->round_u); h->c.round_edge_scale = pow10i(p->round_edge);
   drop_graph(h);
   return PIADMM_OK;

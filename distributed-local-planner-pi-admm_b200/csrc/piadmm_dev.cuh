@@ -18,8 +18,21 @@
 
 #define PIADMM_FULL 0xffffffffu
 
+// constants of the inner iteration derived from in_alpha on the host (set_inner_consts): as members of the kernel
+// parameter block they are constant-bank operands of the loop's DFMAs, not registers
+struct InnerK {
+  double ha, b1;        // alpha/2, 1 - alpha/2
+  double alu, ald;      // alpha * l_u, alpha * l_d
+};
+#define PIADMM_L_U (-0.52359877559829887308)   // -pi/6: steering bound rows
+#define PIADMM_L_D (-0.34906585039886591538)   // -pi/9: steering rate rows
+inline void set_inner_consts(InnerK& ik, double alpha) {
+  ik.ha = 0.5 * alpha; ik.b1 = 1.0 - 0.5 * alpha; ik.alu = alpha * PIADMM_L_U; ik.ald = alpha * PIADMM_L_D;
+}
+
 struct DevCtx {
   piadmm_params p;
+  InnerK ik;
   piadmm_buffers b;
   int S, V, D, E, N, I;
   double round_u_scale, round_edge_scale;  // 10^decimals, 0 = no rounding
@@ -326,12 +339,18 @@ struct InnerOut {
 #define PIADMM_NACC32 16
 #endif
 template <int LPQ, bool KS>
-__device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, int k, int half, bool edge,
+__device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const InnerK& ik, int N, int k, int half, bool edge,
                                                 double pI, double p2, double pW, double q, double a0, double a1,
                                                 double cvec, const double* __restrict__ tabs, double* rhsbuf,
                                                 double* xch, double* krow, double* kc) {
   const double al = ip.in_alpha, sg = ip.in_sigma, oma = 1.0 - al;
-  const double l_u = -0.52359877559829887308, l_d = -0.34906585039886591538;  // -pi/6, -pi/9
+  // LPQ == 32 problems (N = 16..31) are latency critical -- few concurrent edge problems, the slowest one of a coupled
+  // scene bounds the outer iteration -- so their edge iteration uses the forms with the shortest loop-carried chain
+  // (one shuffle level less in the right-hand side and in A x~, at ~15 % more instructions); the LPQ == 16 batch
+  // kernels are issue bound and keep the forms with the fewest instructions (measured both ways, r1_history.md).
+  constexpr bool LAT = LPQ == 32;
+  const double ha = ik.ha, b1 = ik.b1, alu = ik.alu, ald = ik.ald;
+  const double l_u = PIADMM_L_U, l_d = PIADMM_L_D;
   double Kinv[LPQ];
   double rho = ip.in_rho0, irho = 1.0 / rho;
   // ADMM state per constraint row r: z_r and c_r = (1-alpha) z_r + y_r/rho.  The dual y_r is implicit,
@@ -339,7 +358,12 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
   //   v = alpha (A x~)_r + c_r,  z' = Pi(v),  y' = rho (v - z')  =>  c' = v - alpha z',  g' = z' - y'/rho = 2 z' - v.
   // Per iteration and row that is 1 FMA + projection + 2 FMA (instead of relaxation, projection and a separate
   // dual update), and the loop-carried dependency chain is three FP64 operations shorter.
-  double x = 0.0, z0 = 0.0, z1 = 0.0, z2 = 0.0, z3 = 0.0, c0 = 0.0, c1 = 0.0, c2 = 0.0, c3 = 0.0;
+  // The bound rows are carried SHIFTED by their bound l: a_r = v_r - l and ch_r = c_r - l, so that
+  //   a = alpha (A x~)_r + ch,   z' = l + max(a, 0) = l + (a + |a|)/2   (never formed in the loop),
+  //   g' = 2 z' - v = l + |a|    (the l cancel in g0 - g1 and g3 - g2),
+  //   ch' = v - alpha z' - l = (1 - alpha/2) a - (alpha/2) |a| - alpha l:
+  // three DFMA and half a DADD per row, no compare / select, and |a| is one operation after the mat-vec result.
+  double x = 0.0, a0r = -l_u, a1r = -l_u, a2r = -l_d, a3r = -l_d, ch0 = -l_u, ch1 = -l_u, ch2 = -l_d, ch3 = -l_d;
   double t = 0.0, zs = 0.0, cs = 0.0;
   double g01 = 0.0, ge = 0.0, gs = 0.0;       // (g0 - g1), (g3 - g2), g_s of the rows of this lane
   const double na = edge ? fma(a1, a1, a0 * a0) : 1.0;
@@ -347,6 +371,8 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
   const bool inner_row = k < N - 1;
   const int srow = k <= N - 2;               // lane carries a real position row / a second-difference row of D
   const int d_up1 = srow && k >= 1, d_up2 = srow && k >= 2;          // x_j = t_j - 2 t_{j-1} + t_{j-2}
+  const int srow_next = k <= N - 3;                                  // the same three predicates for lane k+1
+  const int n_up1 = srow_next, n_up2 = srow_next && k >= 1;
   // K^-1(rho0) depends only on the vehicle (speed), the outer penalty and the inner settings, not on the iterate:
   // it is the same in every outer iteration and every MPC step, so it is cached in global memory (kc: 8 doubles of
   // key = the four coefficients that define K, then the matrix stored so that lane k reads/writes consecutive
@@ -394,13 +420,27 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
     // ---- steering-space right-hand side  v = sigma x - q + A'(rho z - y)
     // A'(rho z - y) = rho A'g.  e_{k-1}: lane 0 reads the last lane of the group, a padded lane (N <= LPQ-1)
     // whose g is exactly 0.
-    double rhs = fma(rho, (g01 - ge) + __shfl_sync(PIADMM_FULL, ge, (k - 1) & (LPQ - 1), LPQ), fma(sg, x, -q));
-    if (edge) {                                                        // rhs_t = D' v + (rho zs - ys) on position rows
-      // neighbours beyond lane N-2 must not contribute: zero them at the source (the clamped shuffle of the
-      // last lanes returns their own, zeroed, value), so the two stencil terms need no per-lane predicate
-      const double vm = srow ? rhs : 0.0;
-      const double v1 = __shfl_down_sync(PIADMM_FULL, vm, 1, LPQ), v2 = __shfl_down_sync(PIADMM_FULL, vm, 2, LPQ);
-      rhs = fma(-2.0, v1, rhs) + v2;
+    double rhs;
+    if (!edge || !LAT) {
+      rhs = fma(rho, (g01 - ge) + __shfl_sync(PIADMM_FULL, ge, (k - 1) & (LPQ - 1), LPQ), fma(sg, x, -q));
+      if (edge) {
+        const double vm = srow ? rhs : 0.0;
+        const double v1 = __shfl_down_sync(PIADMM_FULL, vm, 1, LPQ), v2 = __shfl_down_sync(PIADMM_FULL, vm, 2, LPQ);
+        rhs = fma(-2.0, v1, rhs) + v2;
+        fma_if(rhs, rho, gs, srow);
+      }
+    } else {
+      // rhs_t = D' v + rho g_s on the position rows, with v_k = e_k + f_{k-1} split into its lane-local part
+      // e = rho (g0 - g1 - ge) + sigma x - q and the neighbour part f = rho ge: all four shuffles of the composed
+      // stencil start from lane-local values (one shuffle level on the loop-carried chain instead of two).
+      // Lanes beyond N-2 must not contribute: em / fm are zeroed at the source, and the clamped shuffles of the
+      // last lanes return their own, zeroed, value.
+      const double e = fma(rho, g01 - ge, fma(sg, x, -q)), f = rho * ge;
+      const double em = srow ? e : 0.0, fm = srow_next ? f : 0.0;        // masks of the rows k and k+1
+      const double fu = __shfl_sync(PIADMM_FULL, f, (k - 1) & (LPQ - 1), LPQ);
+      const double e1 = __shfl_down_sync(PIADMM_FULL, em, 1, LPQ), e2 = __shfl_down_sync(PIADMM_FULL, em, 2, LPQ);
+      const double f1 = __shfl_down_sync(PIADMM_FULL, fm, 1, LPQ);
+      rhs = fma(-2.0, e1 + fm, e + fu) + (e2 + f1);
       fma_if(rhs, rho, gs, srow);
     }
     rhsbuf[k] = rhs;
@@ -436,30 +476,46 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
     }
     double xt = acc[0];
     double tt = 0.0;
-    if (edge) {                                                        // x~ = D t~
-      tt = xt;
+    double d;
+    if (!edge || !LAT) {
+      if (edge) {
+        tt = xt;
+        const double u1 = __shfl_up_sync(PIADMM_FULL, tt, 1, LPQ), u2 = __shfl_up_sync(PIADMM_FULL, tt, 2, LPQ);
+        fma_if(xt, -2.0, u1, d_up1);
+        fma_if(xt, 1.0, u2, d_up2);
+      }
+      d = __shfl_down_sync(PIADMM_FULL, xt, 1, LPQ) - xt;              // the last lane is padded (xt = 0): no clamp needed
+    } else {                                                           // x~ = D t~ and its forward difference,
+      tt = xt;                                                         // both straight from the shuffles of t~
       const double u1 = __shfl_up_sync(PIADMM_FULL, tt, 1, LPQ), u2 = __shfl_up_sync(PIADMM_FULL, tt, 2, LPQ);
-      fma_if(xt, -2.0, u1, d_up1);
-      fma_if(xt, 1.0, u2, d_up2);
+      const double dn = __shfl_down_sync(PIADMM_FULL, tt, 1, LPQ);
+      xt = fma(-2.0, d_up1 ? u1 : 0.0, tt) + (d_up2 ? u2 : 0.0);
+      const double xn = fma(-2.0, n_up1 ? tt : 0.0, dn) + (n_up2 ? u1 : 0.0);   // x~_{k+1}
+      d = xn - xt;
     }
-    // ---- z~ = A x~, relaxation, projection, dual update
-    double d = __shfl_down_sync(PIADMM_FULL, xt, 1, LPQ) - xt;        // the last lane is padded (xt = 0): no clamp needed
     if (!inner_row) d = 0.0;
     x = fma(al, xt, oma * x);
     {
-      const double v0 = fma(al, xt, c0), v1 = fma(-al, xt, c1), v2 = fma(-al, d, c2), v3 = fma(al, d, c3);
-      z0 = dmax(v0, l_u); z1 = dmax(v1, l_u); z2 = dmax(v2, l_d); z3 = dmax(v3, l_d);
-      g01 = fma(2.0, z0, -v0) - fma(2.0, z1, -v1);
-      ge = fma(2.0, z3, -v3) - fma(2.0, z2, -v2);
-      c0 = fma(-al, z0, v0); c1 = fma(-al, z1, v1); c2 = fma(-al, z2, v2); c3 = fma(-al, z3, v3);
+      a0r = fma(al, xt, ch0); a1r = fma(-al, xt, ch1); a2r = fma(-al, d, ch2); a3r = fma(al, d, ch3);
+      const double m0 = fabs(a0r), m1 = fabs(a1r), m2 = fabs(a2r), m3 = fabs(a3r);
+      g01 = m0 - m1;
+      ge = m3 - m2;
+      ch0 = fma(b1, a0r, fma(-ha, m0, -alu)); ch1 = fma(b1, a1r, fma(-ha, m1, -alu));
+      ch2 = fma(b1, a2r, fma(-ha, m2, -ald)); ch3 = fma(b1, a3r, fma(-ha, m3, -ald));
     }
     if (edge) {
       t = fma(al, tt, oma * t);
       const double st = srow ? tt : 0.0;            // position row value (lane N-1: the zero row)
       const double vs = fma(al, st, cs);
-      const double vo = partner<LPQ>(vs, xch, k, half, xpar);
-      const double s0 = half == 0 ? vs : vo, s1 = half == 0 ? vo : vs;
-      const double tau = fma(a1, s1, a0 * s0);
+      double tau;
+      if (LAT) {                                    // the halves exchange their products a_me s_me: the sum is
+        const double pm = a_me * vs;                // bitwise the same on both sides, no selects
+        tau = pm + partner<LPQ>(pm, xch, k, half, xpar);
+      } else {
+        const double vo = partner<LPQ>(vs, xch, k, half, xpar);
+        const double s0 = half == 0 ? vs : vo, s1 = half == 0 ? vo : vs;
+        tau = fma(a1, s1, a0 * s0);
+      }
       // prox of beta*max(0, c - a's): step = clamp((c - tau)/|a|^2, 0, beta/rho), branch free
       const double step = dmin(dmax((cvec - tau) * inv_na, 0.0), tb);
       zs = fma(step, a_me, vs);
@@ -470,6 +526,9 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
    left -= blk;
     // ---- termination / adaptive rho every in_check iterations (steering-space residuals)
     if (blk == check_every) {
+      const double z0 = l_u + dmax(a0r, 0.0), z1 = l_u + dmax(a1r, 0.0), z2 = l_d + dmax(a2r, 0.0),
+                   z3 = l_d + dmax(a3r, 0.0);
+      const double c0 = ch0 + l_u, c1 = ch1 + l_u, c2 = ch2 + l_d, c3 = ch3 + l_d;
       const double y0 = rho * fma(-oma, z0, c0), y1 = rho * fma(-oma, z1, c1), y2 = rho * fma(-oma, z2, c2),
                    y3 = rho * fma(-oma, z3, c3), ys = rho * fma(-oma, zs, cs);      // the implicit duals
       double dd = shift_down1<LPQ>(x, k) - x;
@@ -521,22 +580,23 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, int N, 
       if (__any_sync(PIADMM_FULL, refac)) {
         if (refac) {       // OSQP keeps (z, y) and changes rho: re-express c and g in the new rho
           rho = rn; irho = 1.0 / rho; tb = ip.beta * irho;
-          c0 = fma(y0, irho, oma * z0); c1 = fma(y1, irho, oma * z1); c2 = fma(y2, irho, oma * z2);
-          c3 = fma(y3, irho, oma * z3); cs = fma(ys, irho, oma * zs);
+          ch0 = fma(y0, irho, oma * z0) - l_u; ch1 = fma(y1, irho, oma * z1) - l_u;
+          ch2 = fma(y2, irho, oma * z2) - l_d; ch3 = fma(y3, irho, oma * z3) - l_d;
+          cs = fma(ys, irho, oma * zs);
           g01 = fma(-y0, irho, z0) - fma(-y1, irho, z1);
           ge = fma(-y3, irho, z3) - fma(-y2, irho, z2);
           gs = fma(-ys, irho, zs);
         }
         if (KS) {      // park the ADMM state in the row that is about to be rebuilt (frees 24 registers for the build)
-          krow[0] = x; krow[1] = z0; krow[2] = z1; krow[3] = z2; krow[4] = z3; krow[5] = c0; krow[6] = c1;
-          krow[7] = c2; krow[8] = c3; krow[9] = t; krow[10] = zs; krow[11] = cs; krow[12] = g01; krow[13] = ge;
+          krow[0] = x; krow[1] = a0r; krow[2] = a1r; krow[3] = a2r; krow[4] = a3r; krow[5] = ch0; krow[6] = ch1;
+          krow[7] = ch2; krow[8] = ch3; krow[9] = t; krow[10] = zs; krow[11] = cs; krow[12] = g01; krow[13] = ge;
           krow[14] = gs;
         }
         if (edge) build_Kinv_edge<LPQ, KS>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
         else build_Kinv_vehicle<LPQ, KS>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
         if (KS) {
-          x = krow[0]; z0 = krow[1]; z1 = krow[2]; z2 = krow[3]; z3 = krow[4]; c0 = krow[5]; c1 = krow[6];
-          c2 = krow[7]; c3 = krow[8]; t = krow[9]; zs = krow[10]; cs = krow[11]; g01 = krow[12]; ge = krow[13];
+          x = krow[0]; a0r = krow[1]; a1r = krow[2]; a2r = krow[3]; a3r = krow[4]; ch0 = krow[5]; ch1 = krow[6];
+          ch2 = krow[7]; ch3 = krow[8]; t = krow[9]; zs = krow[10]; cs = krow[11]; g01 = krow[12]; ge = krow[13];
           gs = krow[14];
 #pragma unroll
           for (int j = 0; j < LPQ; j += 2) *reinterpret_cast<double2*>(krow + j) = make_double2(Kinv[j], Kinv[j + 1]);

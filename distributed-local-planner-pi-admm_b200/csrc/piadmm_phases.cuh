@@ -60,7 +60,7 @@ __device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool
   const double q = 2.0 * g * apply_Mt<LPQ>(vec, k);
   const double pI = 2.0 * p.Pcost, p2 = valid ? 2.0 : 0.0, pW = valid ? 2.0 * w * g * g : 0.0;
   double* kc = (c.kcache && valid) ? c.kcache + (((size_t)s * c.V + i) * 2) * PIADMM_KC_STRIDE(LPQ) : nullptr;
-  InnerOut o = inner_solve<LPQ, KS>(p, N, k, half, false, pI, p2, pW, q, 0.0, 0.0, 0.0, Wsm, gbuf, xch, krow, kc);
+  InnerOut o = inner_solve<LPQ, KS>(p, c.ik, N, k, half, false, pI, p2, pW, q, 0.0, 0.0, 0.0, Wsm, gbuf, xch, krow, kc);
   const double u = (k < N) ? round_scale(o.x, c.round_u_scale) : 0.0;
   double px, py;
   if (p.pos_nonlinear) {
@@ -149,7 +149,7 @@ __device__ __forceinline__ void dev_z_update(const DevCtx& c, int s, int e, int 
   // a vehicle can be an endpoint of several edges solved concurrently: the edge entry is used only where every
   // vehicle has a single writer (edge_cache: the fused V=2 kernel)
   double* kc = (c.kcache && valid && edge_cache) ? c.kcache + (((size_t)s * c.V + vv[me]) * 2 + 1) * PIADMM_KC_STRIDE(LPQ) : nullptr;
-  InnerOut o = inner_solve<LPQ, KS>(p, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow, kc);
+  InnerOut o = inner_solve<LPQ, KS>(p, c.ik, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow, kc);
   // z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158)
   const double uh = (k < N) ? round_scale(o.x, c.round_edge_scale) : 0.0;
   double hx, hy, hth;
