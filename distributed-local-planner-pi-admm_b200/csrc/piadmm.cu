@@ -495,6 +495,14 @@ __global__ void __launch_bounds__(1024) k_order(const __grid_constant__ DevCtx c
   if (threadIdx.x == 0) *c.queue = 0;          // the fused kernel before this one is done: re-arm its work queue
 }
 
+// Debug build (-DPIADMM_TRACE, tools/trace_step.py): start / end time and SM of every scenario of the last fused launch
+#ifdef PIADMM_TRACE
+__device__ long long g_trace[8192 * 4];
+__device__ __forceinline__ long long gtime() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+extern "C" int piadmm_debug_read_trace(long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_trace, sizeof(long long) * 4 * n);
+}
+#endif
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 6) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
@@ -507,7 +515,16 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 6)
   for (;;) {
     const int s = next_scenario<LPQ>(c, w, &s_next);
     if (s >= c.s_hi) break;
+#ifdef PIADMM_TRACE
+    const long long t0 = gtime();
+#endif
     run_scenario_v2<LPQ, false>(c, s, w, Wsm, gbuf[w.group_in_cta], xch, nullptr);
+#ifdef PIADMM_TRACE
+    if (w.lane == 0 && s < 8192) {
+      unsigned sm; asm("mov.u32 %0, %%smid;" : "=r"(sm));
+      g_trace[s * 4] = t0; g_trace[s * 4 + 1] = gtime(); g_trace[s * 4 + 2] = sm; g_trace[s * 4 + 3] = 0;
+    }
+#endif
   }
 }
 
