@@ -424,7 +424,7 @@ __global__ void k_plant(const __grid_constant__ DevCtx c) {
 // stays in L1/L2 between phases (each scenario touches ~10 KB).
 template <int LPQ, bool KS>
 __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Who<LPQ>& w, const double* Wsm,
-                                                double* gbuf, double* xch, double* krow);
+                                                double* gbuf, double* xch, double* krow, int step);
 
 // scenario queue: LPQ==16 one scenario per warp, LPQ==32 one per 64-thread CTA
 template <int LPQ>
@@ -509,7 +509,10 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 6)
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];
   __shared__ int s_next;
-  load_W<LPQ>(c, Wsm);
+  __shared__ int step_sh;
+  if (c.ref && threadIdx.x == 0) step_sh = *reinterpret_cast<const volatile int*>(c.step);   // overlaps the table load
+  load_W<LPQ>(c, Wsm);                       // (ends with a CTA barrier)
+  const int step = c.ref ? step_sh : 0;
   Who<LPQ> w;
   // persistent: every pair pulls scenarios from a global counter until the batch is exhausted
   for (;;) {
@@ -518,7 +521,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 6)
 #ifdef PIADMM_TRACE
     const long long t0 = gtime();
 #endif
-    run_scenario_v2<LPQ, false>(c, s, w, Wsm, gbuf[w.group_in_cta], xch, nullptr);
+    run_scenario_v2<LPQ, false>(c, s, w, Wsm, gbuf[w.group_in_cta], xch, nullptr, step);
 #ifdef PIADMM_TRACE
     if (w.lane == 0 && s < 8192) {
       unsigned sm; asm("mov.u32 %0, %%smid;" : "=r"(sm));
@@ -544,18 +547,25 @@ __global__ void __launch_bounds__(KS_THREADS(LPQ), LPQ == 16 ? 7 : 12) k_fused_k
     const int s = next_scenario<LPQ>(c, w, &s_next);
     if (s >= c.s_hi) break;
     run_scenario_v2<LPQ, true>(c, s, w, c.W, gbuf[w.group_in_cta], xch,
-                               krows[w.group_in_cta] + w.k * PIADMM_KROW_STRIDE(LPQ));
+                               krows[w.group_in_cta] + w.k * PIADMM_KROW_STRIDE(LPQ), c.ref ? *c.step : 0);
   }
 }
 
 template <int LPQ, bool KS>
 __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Who<LPQ>& w, const double* Wsm,
-                                                double* gbuf, double* xch, double* krow) {
+                                                double* gbuf, double* xch, double* krow, int step) {
   const piadmm_params& p = c.p;
   const int N = c.N, k = w.k, half = w.half;
   const int i = half, j = half ^ 1;
   const bool lead = half == 0 && k == 0;
   const size_t so = SLOT_OFF(s, i, 0);
+  // ---- reference window of vehicle i out of the resident reference (as k_refwin; casadi/PI_ADMM_class.py:116-117)
+  if (c.ref && k <= N) {
+    const size_t row = ((size_t)s * 2 + i) * 2;
+    double* rw = const_cast<double*>(c.b.refwin) + POS_OFF(s, i);
+    rw[k] = c.ref[row * c.ref_T + step + k];
+    rw[NP1 + k] = c.ref[(row + 1) * c.ref_T + step + k];
+  }
   // ---- casadi/main.py:52-72: re-initialise local / edge / dual variables
   if (k <= N) {
     for (int cc = 0; cc < 2; cc++) {
@@ -1087,9 +1097,10 @@ struct HostStepArgs {
 };
 
 static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, int* queue, int range_id,
-                        const HostStepArgs* zc = nullptr) {
+                        const HostStepArgs* zc = nullptr, const int* gather_step = nullptr) {
   DevCtx c = h->c;
   c.s_lo = s_lo; c.s_hi = s_hi; c.queue = queue;
+  if (gather_step) { c.ref = h->d_ref; c.ref_T = h->ref_T; c.step = gather_step; }   // window gather inside the kernel
   if (zc) {      // zero-copy epilogue into mapped host memory (device-visible addresses)
     c.host_out = 1;
     c.ho_u = zc->u_out; c.ho_pos = zc->pos_out; c.ho_xt_next = zc->xt_next_out;
@@ -1145,6 +1156,9 @@ static int enqueue_chunked_host_step(piadmm_handle* h, cudaStream_t ms, const Ho
   const size_t N = h->c.N, np1 = N + 1;
   int nch = (zc && !a.refwin) ? 1 : h->n_chunks;
   if (h->c.S < 64 * nch) nch = 1;
+  // zero-copy step on the resident reference: the fused kernel gathers the windows itself (no gather kernel).  The
+  // step index still travels as a 4-byte copy: 1184 CTAs reading one pinned host word over PCIe took ~0.9 ms.
+  const int* gather = (zc && !a.refwin && nch == 1) ? h->d_step : nullptr;
   if (!a.refwin) CK(cudaMemcpyAsync(h->d_step, h->h_step, sizeof(int), cudaMemcpyHostToDevice, ms));
   CK(cudaEventRecord(h->ev_start, ms));
   for (int ch = 0; ch < nch; ch++) {
@@ -1158,11 +1172,11 @@ static int enqueue_chunked_host_step(piadmm_handle* h, cudaStream_t ms, const Ho
     c.s_lo = s0; c.s_hi = s1;
     if (a.refwin) {
       CK(cudaMemcpyAsync((double*)h->c.b.refwin + a0 * 2 * np1, a.refwin + a0 * 2 * np1, sizeof(double) * na * 2 * np1, cudaMemcpyHostToDevice, cs));
-    } else {
+    } else if (!gather) {
       k_refwin<<<(unsigned)((na * 2 * np1 + 255) / 256), 256, 0, cs>>>(c, h->d_ref, h->ref_T, h->d_step);
       LAUNCHED();
     }
-    int rc = nch == 1 ? launch_fused(h, cs, s0, s1, h->d_queue, 0, zc) : launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch, 1 + ch, zc);
+    int rc = nch == 1 ? launch_fused(h, cs, s0, s1, h->d_queue, 0, zc, gather) : launch_fused(h, cs, s0, s1, h->d_queue + 1 + ch, 1 + ch, zc);
     if (rc) return rc;
     if (zc) {
       CK(cudaEventRecord(h->ev_done[ch], cs));
@@ -1331,12 +1345,12 @@ int piadmm_run_closed_loop(piadmm_handle* h, int first_step, int n_steps, const 
   HostStepArgs none;
   memset(&none, 0, sizeof none);
   for (int t = 0; t < n_steps; t++) {
-    k_refwin<<<(unsigned)((SV * 2 * np1 + 255) / 256), 256, 0, st>>>(h->c, h->d_ref, h->ref_T, h->d_step);
-    LAUNCHED();
     int rc;
-    if (fused) {
-      rc = launch_fused(h, st, 0, h->c.S, h->d_queue, 0, &none);     // host_out with NULL targets: inline plant step
+    if (fused) {     // host_out with NULL targets: inline plant step; the kernel gathers the windows at *d_step itself
+      rc = launch_fused(h, st, 0, h->c.S, h->d_queue, 0, &none, h->d_step);
     } else {
+      k_refwin<<<(unsigned)((SV * 2 * np1 + 255) / 256), 256, 0, st>>>(h->c, h->d_ref, h->ref_T, h->d_step);
+      LAUNCHED();
       rc = piadmm_step(h, stream);
       if (!rc) rc = piadmm_plant_step(h, stream);
     }

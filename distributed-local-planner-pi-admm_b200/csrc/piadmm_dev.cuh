@@ -52,6 +52,11 @@ struct DevCtx {
   // fused kernel, host-buffer entry points: zero-copy epilogue.  When set, every finished scenario also takes the
   // plant step and stores its results straight into the caller's pinned (mapped) host buffers, so the D2H traffic
   // streams out during the kernel instead of as copies after it.  Any pointer may be NULL.
+  // fused kernel with a resident reference (piadmm_set_reference): every scenario gathers its own window
+  // refwin[s,v,c,k] = ref[s,v,c,*step + k] when it starts (no separate gather kernel); `step` is device memory
+  const double* ref;
+  int ref_T;
+  const int* step;
   int host_out;
   double *ho_u, *ho_pos, *ho_xt_next;
   int32_t *ho_curr_iter, *ho_n_outer;
