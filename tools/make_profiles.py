@@ -87,15 +87,15 @@ Files
 | ncu DRAM | {rd / 1e6:.2f} MB read + {wr / 1e6:.1f} MB written per launch (the writes are the write-back of the L2-flush buffer); DRAM throughput {m['gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed']:.2f} % of peak: not HBM-bound |
 | clocks during the timed region | {b['clocks']} |
 
-## Launch list (shares of the MPC step = k_fused_v2 + k_order (+ k_refwin in the end-to-end path))
+## Launch list (shares of the MPC step = k_fused_v2 + k_order)
 
 | kernel | launches | avg us | share of step |
 |---|---|---|---|
 """ + "\n".join(lines) + f"""
 
 `k_fp64_peak` is the one-off peak micro-benchmark after the timed region; torch fill kernels are buffer initialisation
-and the L2 flush (outside the event pairs); `k_refwin` (window gather from the resident reference) runs only in the
-end-to-end path, `k_plant` only in the non-zero-copy host path.  The ncu duration of `k_fused_v2<16>` plus `k_order`
+and the L2 flush (outside the event pairs); with a resident reference the fused kernel gathers the reference windows
+itself (`k_refwin` only remains for the generic-V and non-zero-copy paths, `k_plant` for the non-zero-copy host path).  The ncu duration of `k_fused_v2<16>` plus `k_order`
 agrees with the CUDA-event time of the bench: the fused kernel IS the step.
 
 ## Reading of the full capture (what limits the kernel)
@@ -103,7 +103,7 @@ agrees with the CUDA-event time of the bench: the fused kernel IS the step.
 {tail}
 
 * 4096 scenario-warps for 2368 resident warp slots (8 CTAs x 2 warps per SM, 128 registers).  Issue slots are about
-  half busy and the FP64 pipe about a third: the kernel is **dependency-latency bound, not FP64-throughput bound**
+  half busy and the FP64 pipe 40 %: the kernel is **dependency-latency bound, not FP64-throughput bound**
   (stalls: `wait` = fixed-latency dependent FP64 chains, `short_scoreboard` = LDS / SHFL results; in the mat-vec
   only two of the eight LDS.128 of the right-hand side are in flight at a time because the 32 registers of the
   K^-1 row leave no room for more).
@@ -115,15 +115,19 @@ agrees with the CUDA-event time of the bench: the fused kernel IS the step.
   a division, 2x2-block Gauss-Jordan builds (half the latency rounds; the builds were ~20 % of the time), nested
   block counters instead of a spilled loop counter, and a longest-first scenario order learnt from the previous step
   (scenario work varies 2.7x; elapsed / active SM cycles went from 1.32 to 1.14).
-* Algorithmic flops are ~18 % of the DFMA peak while the pipe is ~37 % busy: the difference is Gauss-Jordan rebuilds
+* Algorithmic flops are ~20 % of the DFMA peak while the pipe is ~40 % busy: the difference is Gauss-Jordan rebuilds
   of K^-1 at an adapted rho (about 0.7 per solve), termination checks, the padded 16th lane and the lock-step wait of the faster
   vehicle of a warp (16 %).
 * K^-1(rho0) is cached in global memory across outer iterations and MPC steps (key = the coefficients that define K),
   so only the rebuilds at an adapted rho remain (~0.7 per solve, ~10 % of the samples).  The 35 MB of cache entries
   are what the DRAM read figure above consists of (the bench flushes L2 before every step).
-* Sample shares of the current kernel (source page): inner-iteration loops 50 %, per-call prologue / epilogue of the
-  x-update and the edge step 21 % (reference tracking terms, roll-outs, dual / PI update), termination checks 11 %,
-  Gauss-Jordan rebuilds 10 %, scenario initialisation and queue 5 %.
+* Sample shares of the current kernel (source page): inner-iteration loops 50 % (vehicle loop 70, edge loop 126 SASS
+  instructions per iteration), per-call prologue / epilogue of the x-update and the edge step 18 % (reference tracking
+  terms, roll-outs, dual / PI update), termination checks 13 %, Gauss-Jordan rebuilds 10 %, scenario initialisation
+  and queue 5 %.
+* What bounds the step is analysed in r1_history.md ("Where the time of a step goes now"): a scenario is a serial
+  chain (~680 cycles per edge iteration alone), the sub-partition saturates at 3-4 such warps (4.1 / 7.4 / 9.5 / 10.7
+  scenarios per us at 1 / 2 / 3 / 4 warps), and the step is two scenario latencies per warp slot.
 * Next candidates: pair like vehicles of two scenarios in a warp, rebuild K^-1(rho) from a cached eigen-decomposition
   of the pencil (K0, A'A) instead of Gauss-Jordan, slimmer termination checks.
 """)
