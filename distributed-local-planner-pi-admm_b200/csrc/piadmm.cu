@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : Z32_MIN_CTAS) k_z
     if (!__syncthreads_or(valid)) continue;  // empty CTA
     if (!loaded) { load_tabs<LPQ>(c, Wsm, 2, 2); loaded = true; }
     if (!valid) continue;                     // LPQ==16 only: the other pair of the CTA works alone
-    dev_z_update<LPQ, false>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
+    dev_z_update<LPQ, false, true>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
                              Wsm, gbuf[w.group_in_cta], xch, nullptr, false);
   }
 }

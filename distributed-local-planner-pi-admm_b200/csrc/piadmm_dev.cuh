@@ -337,13 +337,13 @@ struct InnerOut {
 #define PIADMM_KROW_STRIDE(LPQ) ((LPQ) + 2)
 #define PIADMM_KC_KEY 8                                        // doubles reserved for the key of a K^-1 cache entry
 #define PIADMM_KC_STRIDE(LPQ) (PIADMM_KC_KEY + (LPQ) * (LPQ))  // doubles per cache entry
-#ifndef PIADMM_NACC16
-#define PIADMM_NACC16 8
-#endif
-#ifndef PIADMM_NACC32
-#define PIADMM_NACC32 16
-#endif
-template <int LPQ, bool KS>
+// Independent accumulator chains of the mat-vec K^-1 rhs (LPQ DFMA per lane): NA chains cost NA-1 extra DADD per
+// iteration but shorten the dependent chain to LPQ/NA DFMA + log2(NA) DADD.  The batch kernels are issue bound
+// (FP64 instructions hold the dispatch port for two cycles): fewest instructions win, NA = 4 (N=15: 0.2154 -> 0.2105 ms
+// against 8; N=30: 0.626 -> 0.605 ms against 16).  The generic-V edge kernel is latency bound (few concurrent edge
+// problems, config 5: 7.99 / 8.40 / 8.91 ms with 16 / 8 / 4 chains at N=30): most chains win.
+template <int LPQ, bool LATENCY> __host__ __device__ constexpr int nacc() { return LATENCY ? (LPQ == 16 ? 8 : 16) : 4; }
+template <int LPQ, bool KS, bool LATENCY = false>
 __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const InnerK& ik, int N, int k, int half, bool edge,
                                                 double pI, double p2, double pW, double q, double a0, double a1,
                                                 double cvec, const double* __restrict__ tabs, double* rhsbuf,
@@ -452,7 +452,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
     __syncwarp();
     // ---- K^-1 rhs  (row k in registers, rhs broadcast from shared memory)
     // independent accumulator chains of the mat-vec: the dependent-DFMA depth is LPQ / NACC (+ log2 NACC adds)
-    constexpr int PIADMM_NACC = LPQ == 16 ? PIADMM_NACC16 : PIADMM_NACC32;
+    constexpr int PIADMM_NACC = nacc<LPQ, LATENCY>();
     double acc[PIADMM_NACC];
 #pragma unroll
     for (int u = 0; u < PIADMM_NACC; u++) acc[u] = 0.0;

@@ -90,7 +90,7 @@ __device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool
 // ---- edge step of edge e = (v0 < v1) of scenario s, half = which endpoint this group owns -------
 // casadi/main.py:121-162 with the convex edge problem (MATLAB ...PI_antiwindup.m:276-304,383-396)
 // and the three dual-update laws.  Writes hat, dual, integ, diff (own side), edge_res, rho_new.
-template <int LPQ, bool KS>
+template <int LPQ, bool KS, bool LATENCY = false>
 __device__ __forceinline__ void dev_z_update(const DevCtx& c, int s, int e, int v0, int v1, int sl0, int sl1,
                                              bool last_edge, bool valid, int k, int lane, int half,
                                              const double* Wsm, double* gbuf, double* xch, double* krow,
@@ -149,7 +149,7 @@ __device__ __forceinline__ void dev_z_update(const DevCtx& c, int s, int e, int 
   // a vehicle can be an endpoint of several edges solved concurrently: the edge entry is used only where every
   // vehicle has a single writer (edge_cache: the fused V=2 kernel)
   double* kc = (c.kcache && valid && edge_cache) ? c.kcache + (((size_t)s * c.V + vv[me]) * 2 + 1) * PIADMM_KC_STRIDE(LPQ) : nullptr;
-  InnerOut o = inner_solve<LPQ, KS>(p, c.ik, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow, kc);
+  InnerOut o = inner_solve<LPQ, KS, LATENCY>(p, c.ik, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow, kc);
   // z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158)
   const double uh = (k < N) ? round_scale(o.x, c.round_edge_scale) : 0.0;
   double hx, hy, hth;
