@@ -106,6 +106,17 @@ __device__ __forceinline__ double group_max(double v) {
   for (int o = LPQ / 2; o >= 1; o >>= 1) { double t = __shfl_xor_sync(PIADMM_FULL, v, o); v = v > t ? v : t; }
   return v;
 }
+// group maximum of NON-NEGATIVE finite doubles (norms): their IEEE bit patterns order like unsigned integers, so the
+// maximum is two warp reductions (redux.sync over the group's member mask: high words, then the low words of the
+// lanes that hold the maximal high word) instead of log2(LPQ) rounds of two shuffles, a compare and two selects
+template <int LPQ>
+__device__ __forceinline__ double group_max_nn(double v) {
+  const unsigned mask = LPQ == 32 ? 0xffffffffu : ((threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu);
+  const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+  const unsigned mh = __reduce_max_sync(mask, hi);
+  const unsigned ml = __reduce_max_sync(mask, hi == mh ? lo : 0u);
+  return __hiloint2double((int)mh, (int)ml);
+}
 template <int LPQ>
 __device__ __forceinline__ double group_min(double v) {
 #pragma unroll
@@ -561,7 +572,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
       }
       double rd = fabs(Px + q + Aty);
       double nd = dmax(fabs(Px), dmax(fabs(Aty), fabs(q)));
-      rp = group_max<LPQ>(rp); np = group_max<LPQ>(np); rd = group_max<LPQ>(rd); nd = group_max<LPQ>(nd);
+      rp = group_max_nn<LPQ>(rp); np = group_max_nn<LPQ>(np); rd = group_max_nn<LPQ>(rd); nd = group_max_nn<LPQ>(nd);
       if (edge) {
         partner_max4<LPQ>(rp, np, rd, nd, xch, k, half, xpar);
       }
