@@ -388,6 +388,9 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
   const double a_me = half == 0 ? a0 : a1;
   const bool inner_row = k < N - 1;
   const int srow = k <= N - 2;               // lane carries a real position row / a second-difference row of D
+  // LAT (168 registers): per-lane coefficients instead of selects in the loop; at 128 registers (LPQ == 16) the six
+  // extra registers cost more than the eight selects save (N=15: 0.2120 vs 0.2093 ms; N=30: 0.5925 -> 0.5839 ms)
+  const double al_d = (LAT && !inner_row) ? 0.0 : al, al_s = srow ? al : 0.0;
   const int d_up1 = srow && k >= 1, d_up2 = srow && k >= 2;          // x_j = t_j - 2 t_{j-1} + t_{j-2}
   const int srow_next = k <= N - 3;                                  // the same three predicates for lane k+1
   const int n_up1 = srow_next, n_up2 = srow_next && k >= 1;
@@ -428,6 +431,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
   int left = ip.in_max_iter;                 // iterations still allowed
   const double inv_na = 1.0 / na;
   double tb = ip.beta * irho;                // hinge prox step bound beta / rho
+  double rho_s = srow ? rho : 0.0;           // rho on the position rows, 0 elsewhere
   // two nested loops: the hot one counts a block of in_check iterations down in ONE register; `left`, the
   // termination test and the K^-1 rebuild are touched once per block
 #pragma unroll 1
@@ -459,7 +463,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
       const double e1 = __shfl_down_sync(PIADMM_FULL, em, 1, LPQ), e2 = __shfl_down_sync(PIADMM_FULL, em, 2, LPQ);
       const double f1 = __shfl_down_sync(PIADMM_FULL, fm, 1, LPQ);
       rhs = fma(-2.0, e1 + fm, e + fu) + (e2 + f1);
-      fma_if(rhs, rho, gs, srow);
+      rhs = fma(rho_s, gs, rhs);
     }
     rhsbuf[k] = rhs;
     __syncwarp();
@@ -511,10 +515,10 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
       const double xn = fma(-2.0, n_up1 ? tt : 0.0, dn) + (n_up2 ? u1 : 0.0);   // x~_{k+1}
       d = xn - xt;
     }
-    if (!inner_row) d = 0.0;
+    if (!LAT && !inner_row) d = 0.0;
     x = fma(al, xt, oma * x);
-    {
-      a0r = fma(al, xt, ch0); a1r = fma(-al, xt, ch1); a2r = fma(-al, d, ch2); a3r = fma(al, d, ch3);
+    {   // LAT: al_d = 0 on the lanes without a rate row, their (meaningless) d never enters
+      a0r = fma(al, xt, ch0); a1r = fma(-al, xt, ch1); a2r = fma(-al_d, d, ch2); a3r = fma(al_d, d, ch3);
       const double m0 = fabs(a0r), m1 = fabs(a1r), m2 = fabs(a2r), m3 = fabs(a3r);
       g01 = m0 - m1;
       ge = m3 - m2;
@@ -523,8 +527,8 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
     }
     if (edge) {
       t = fma(al, tt, oma * t);
-      const double st = srow ? tt : 0.0;            // position row value (lane N-1: the zero row)
-      const double vs = fma(al, st, cs);
+      // position row value (lane N-1: the zero row); LAT: al_s = 0 there instead of a select
+      const double vs = LAT ? fma(al_s, tt, cs) : fma(al, srow ? tt : 0.0, cs);
       double tau;
       if (LAT) {                                    // the halves exchange their products a_me s_me: the sum is
         const double pm = a_me * vs;                // bitwise the same on both sides, no selects
@@ -597,7 +601,7 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
       if (__all_sync(PIADMM_FULL, done)) break;
       if (__any_sync(PIADMM_FULL, refac)) {
         if (refac) {       // OSQP keeps (z, y) and changes rho: re-express c and g in the new rho
-          rho = rn; irho = 1.0 / rho; tb = ip.beta * irho;
+          rho = rn; irho = 1.0 / rho; tb = ip.beta * irho; rho_s = srow ? rho : 0.0;
           ch0 = fma(y0, irho, oma * z0) - l_u; ch1 = fma(y1, irho, oma * z1) - l_u;
           ch2 = fma(y2, irho, oma * z2) - l_d; ch3 = fma(y3, irho, oma * z3) - l_d;
           cs = fma(ys, irho, oma * zs);
