@@ -399,3 +399,60 @@ def test_run_closed_loop_generic_v():
         assert np.array_equal(h["n_outer_his"][t], o["n_outer"])
         assert np.array_equal(h["x_vec"][t], o["xt_next"][:, :, :2]) and np.array_equal(h["u_vec"][t], o["u"][:, :, 0])
         x = o["xt_next"].copy()
+
+
+@pytest.mark.parametrize("N,V", [(15, 2), (30, 2), (15, 8)])
+def test_kinv_cache_is_invalidated_by_changed_coefficients(N, V):
+    """The K^-1(rho0) cache is keyed by the coefficients that define K (speed, outer penalty, inner settings).  A handle
+    that has cached one problem set and is then given other speeds / rho / inner sigma must give, bit for bit, what a
+    fresh handle gives (a stale entry would change iterates and iteration counts)."""
+    from pi_admm_b200.scenarios import c3_intersection
+    keys = ("u", "pos", "err_rk", "n_outer", "veh_inner", "edge_inner")
+
+    def inputs(seed, vscale):
+        if V == 2:
+            xt, spd, rw = c4_scenarios(S=48, N=N, seed=seed)
+        else:
+            xt, spd, rw = c3_intersection(V=V, N=N, seed=seed)
+        return xt, np.asarray(spd) * vscale, rw
+
+    def fresh(p, inp, rho=None):
+        s = PIADMMSolver(p, S=inp[0].shape[0], V=V, D=None if V == 2 else 7)
+        s.setup(*inp, rho=rho)
+        s.iterate()
+        out = s.to_numpy()
+        s.close()
+        return out
+
+    kw = dict(num_ho=N, eps_pri=0.1, eps_dual=0.1)
+    if V != 2:
+        kw.update(al_all=0, iter_num=4, eps_pri=0.5, eps_dual=0.5, beta=10.0, Pnorm=1.0, rho=2.0)
+    p = make_params("matlab_pi", "default", **kw)
+    a, b = inputs(3, 1.0), inputs(3, 1.07)
+    sol = PIADMMSolver(p, S=a[0].shape[0], V=V, D=None if V == 2 else 7)
+    sol.setup(*a)
+    sol.iterate(); sol.iterate()                         # second pass runs on cache hits
+    want = fresh(p, a)
+    got = sol.to_numpy()
+    for k in keys:
+        assert np.array_equal(got[k], want[k]), ("hit", k)
+    sol.setup(*b)                                        # other speeds: every vehicle key changes
+    sol.iterate()
+    want, got = fresh(p, b), sol.to_numpy()
+    for k in keys:
+        assert np.array_equal(got[k], want[k]), ("speed", k)
+    rho = np.full(a[0].shape[0], 3.1)
+    sol.setup(*b, rho=rho)                               # other outer penalty
+    sol.iterate()
+    want, got = fresh(p, b, rho=rho), sol.to_numpy()
+    for k in keys:
+        assert np.array_equal(got[k], want[k]), ("rho", k)
+    sol.set_params(in_sigma=2e-6)                        # other inner setting
+    sol.setup(*b, rho=rho)
+    sol.iterate()
+    p2 = make_params("matlab_pi", "default", **kw)
+    p2.update(in_sigma=2e-6)
+    want, got = fresh(p2, b, rho=rho), sol.to_numpy()
+    for k in keys:
+        assert np.array_equal(got[k], want[k]), ("sigma", k)
+    sol.close()
