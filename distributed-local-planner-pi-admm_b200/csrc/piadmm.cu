@@ -685,6 +685,8 @@ struct piadmm_handle {
   int lpq;
   double* d_W;
   int* d_count;
+  int *d_count2, *h_count2;    // piadmm_step (generic V): double-buffered active counts (device / pinned host)
+  cudaEvent_t ev_count[2];
   int* d_queue;
   int fused_grid, x_grid, z_grid;
   bool fused_ks;              // fused kernel variant: K^-1 rows in shared memory (k_fused_ks)
@@ -785,7 +787,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   }
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
-  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false; h->gexec = nullptr; h->d_ref = nullptr; h->ref_T = 0; h->h_step = nullptr; h->d_step = nullptr;
+  h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_count2 = nullptr; h->h_count2 = nullptr; h->ev_count[0] = h->ev_count[1] = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false; h->gexec = nullptr; h->d_ref = nullptr; h->ref_T = 0; h->h_step = nullptr; h->d_step = nullptr;
   h->c.p = *p; set_inner_consts(h->c.ik, p->in_alpha); h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
   h->c.N = p->num_ho; h->c.I = p->iter_num;
   h->c.own_lo = 0; h->c.own_hi = V;
@@ -853,6 +855,10 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMalloc(&h->c.dist_bad, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
   if ((ce = cudaMemset(h->c.dist_bad, 0, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
   if ((ce = cudaMalloc(&h->d_count, sizeof(int))) != cudaSuccess) return fail(ce, "count");
+  if ((ce = cudaMalloc(&h->d_count2, 2 * sizeof(int))) != cudaSuccess) return fail(ce, "count2");
+  if ((ce = cudaMallocHost(&h->h_count2, 2 * sizeof(int))) != cudaSuccess) return fail(ce, "count2");
+  for (int i = 0; i < 2; i++)
+    if ((ce = cudaEventCreateWithFlags(&h->ev_count[i], cudaEventDisableTiming)) != cudaSuccess) return fail(ce, "event");
   if ((ce = cudaMalloc(&h->d_queue, sizeof(int) * (PIADMM_CHUNKS + 1))) != cudaSuccess) return fail(ce, "queue");
   if ((ce = cudaMalloc(&h->d_order, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "order");
   {   // K^-1(rho0) cache (PIADMM_KCACHE=0 disables): zero keys never match (cI > 0)
@@ -923,7 +929,9 @@ void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
-  cudaFree(h->d_count); cudaFree(h->d_queue); cudaFree(h->d_order); cudaFree(h->d_ref); cudaFree(h->d_step);
+  cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
+  for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
+  cudaFree(h->d_queue); cudaFree(h->d_order); cudaFree(h->d_ref); cudaFree(h->d_step);
   if (h->h_step) cudaFreeHost(h->h_step);
   if (h->have_streams) {
     for (int i = 0; i < PIADMM_CHUNKS; i++) { cudaStreamDestroy(h->cs[i]); cudaEventDestroy(h->ev_done[i]); }
@@ -1133,16 +1141,26 @@ int piadmm_step(piadmm_handle* h, void* stream) {
   REQUIRE_BOUND();
   cudaStream_t st = (cudaStream_t)stream;
   if (h->c.V == 2 && h->c.D == 1) return launch_fused(h, st, 0, h->c.S, h->d_queue, 0);
-  // generic V: phase kernels, one readback of the active-scenario count per outer iteration
+  // generic V: phase kernels.  The active-scenario count of every outer iteration is copied to a pinned word
+  // asynchronously and looked at ONE ITERATION LATE: the host has iteration it+1 enqueued before it waits for the
+  // count of iteration it, so the GPU never idles for a host round trip.  At most one superfluous iteration is
+  // enqueued after the last scenario finished; every kernel of it is a no-op (all phases are gated by done[s]).
   int rc = piadmm_begin_step(h, stream);
   for (int it = 0; it < h->c.I && rc == PIADMM_OK; it++) {
     if ((rc = piadmm_x_update(h, stream))) break;
     if ((rc = piadmm_detect_edges(h, stream))) break;
     if ((rc = piadmm_z_update(h, stream))) break;
     if ((rc = piadmm_residuals(h, stream))) break;
-    int32_t act = 0;
-    if ((rc = piadmm_num_active(h, stream, &act))) break;
-    if (act == 0) break;
+    int* cnt = h->d_count2 + (it & 1);
+    CK(cudaMemsetAsync(cnt, 0, sizeof(int), st));
+    k_count_active<<<(h->c.S + 255) / 256, 256, 0, st>>>(h->c, cnt);
+    LAUNCHED();
+    CK(cudaMemcpyAsync(h->h_count2 + (it & 1), cnt, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(h->ev_count[it & 1], st));
+    if (it >= 1) {
+      CK(cudaEventSynchronize(h->ev_count[(it - 1) & 1]));
+      if (h->h_count2[(it - 1) & 1] == 0) break;
+    }
   }
   return rc;
 }
