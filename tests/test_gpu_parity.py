@@ -257,6 +257,27 @@ def test_large_batch_properties():
     assert np.array_equal(a["n_outer"][idx], ref["n_outer"])
 
 
+@pytest.mark.parametrize("N", [15, 30])
+def test_bench_workload_every_scenario_equals_the_oracle(N):
+    """The exact bench workload (BASELINE config 4, 4096 scenarios; N=15 and the N=30 variant, bench parameters):
+    EVERY scenario against the C twin (all host threads): identical outer / inner iteration counts and edge flags,
+    floating point within 1e-6."""
+    import os
+    import bench
+    p = bench.bench_params(N)
+    xt, spd, refwin = c4_scenarios(S=4096, N=N)
+    a = _run_gpu(p, xt, spd, refwin, True)
+    try:
+        nt = len(os.sched_getaffinity(0))
+    except AttributeError:
+        nt = os.cpu_count() or 1
+    ref = ctwin.step(p, xt, spd, refwin, nthreads=nt)
+    for k in ("n_outer", "curr_iter", "veh_inner", "edge_inner", "n_veh_solves", "n_edge_solves", "flag", "status"):
+        assert np.array_equal(a[k], ref[k]), k
+    for k in ("u", "pos", "hat", "dual", "err_rk", "err_sk", "xt_next"):
+        assert rel_err(a[k], ref[k]) <= 1e-6, k
+
+
 def test_step_host_chunked_pipeline_equals_device_path():
     """S >= 256 makes piadmm_step_host split the batch over internal streams (copy/compute overlap)."""
     p = make_params("matlab_pi", "default", num_ho=15, eps_pri=0.1, eps_dual=0.1)
