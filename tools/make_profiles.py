@@ -71,6 +71,11 @@ Files
   `ncu --set full --clock-control none --import-source on -k regex:k_fused -s 3 -c 1` capture; `r1_traffic.json` = its DRAM bytes.
 * `r1_c5_phases.txt` — per-phase CUDA-event times of the generic-V phase kernels (configs 3 and 5 shapes) and the 2-GPU NCCL run.
 * `r1_history.md` — what each optimisation step bought (bench numbers per commit).
+* `r1_scaling.md` — 1 / 2 / 4 / 8 GPU runs (config 4 weak scaling, config 5 vehicle sharding over NCCL).
+* Tools behind the analysis in `r1_history.md`: `tools/single_scenario_latency.py` (one scenario alone on the GPU),
+  `tools/contention.py` (1-4 warps per SM sub-partition), `tools/trace_step.py` (start / end time of every scenario,
+  needs a `-DPIADMM_TRACE` build), `tools/sass_loops.py` (hot loops of the SASS), `tools/c5_phases.py`,
+  `tools/closed_loop_bench.py`.
 
 ## Headline (1 x B200)
 
