@@ -119,6 +119,26 @@ __device__ __forceinline__ double group_max_nn(double v) {
   const unsigned ml = __reduce_max_sync(mask, hi == mh ? lo : 0u);
   return __hiloint2double((int)mh, (int)ml);
 }
+// maxima of FOUR quantities over a 16-lane group in one transposed butterfly: after the xor-8 exchange a lane keeps
+// two of them, after xor-4 one; 9 exchanges + 4 broadcasts instead of 16 exchanges (each = two SHFL + compare + two
+// selects).  Lanes 0-3 / 4-7 / 8-11 / 12-15 of the group end up owning a / b / c / d.
+// pair = true: maxima over both groups of the warp (the two halves of an edge problem), one more exchange.
+__device__ __forceinline__ void group_max4_16(double& a, double& b, double& c, double& d, int k, bool pair) {
+  const bool h8 = k & 8, h4 = k & 4;
+  double m0 = h8 ? c : a, m1 = h8 ? d : b;
+  const double s0 = h8 ? a : c, s1 = h8 ? b : d;
+  const double r0 = __shfl_xor_sync(PIADMM_FULL, s0, 8), r1 = __shfl_xor_sync(PIADMM_FULL, s1, 8);
+  m0 = m0 > r0 ? m0 : r0; m1 = m1 > r1 ? m1 : r1;
+  double m = h4 ? m1 : m0;
+  const double s = h4 ? m0 : m1;
+  const double r = __shfl_xor_sync(PIADMM_FULL, s, 4);
+  m = m > r ? m : r;
+  double t = __shfl_xor_sync(PIADMM_FULL, m, 2); m = m > t ? m : t;
+  t = __shfl_xor_sync(PIADMM_FULL, m, 1); m = m > t ? m : t;
+  if (pair) { t = __shfl_xor_sync(PIADMM_FULL, m, 16); m = m > t ? m : t; }
+  a = __shfl_sync(PIADMM_FULL, m, 0, 16); b = __shfl_sync(PIADMM_FULL, m, 4, 16);
+  c = __shfl_sync(PIADMM_FULL, m, 8, 16); d = __shfl_sync(PIADMM_FULL, m, 12, 16);
+}
 template <int LPQ>
 __device__ __forceinline__ double group_min(double v) {
 #pragma unroll
@@ -578,8 +598,9 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
       }
       double rd = fabs(Px + q + Aty);
       double nd = dmax(fabs(Px), dmax(fabs(Aty), fabs(q)));
-      rp = group_max_nn<LPQ>(rp); np = group_max_nn<LPQ>(np); rd = group_max_nn<LPQ>(rd); nd = group_max_nn<LPQ>(nd);
-      if (edge) {
+      if (LPQ == 16) group_max4_16(rp, np, rd, nd, k, edge);
+      else { rp = group_max_nn<LPQ>(rp); np = group_max_nn<LPQ>(np); rd = group_max_nn<LPQ>(rd); nd = group_max_nn<LPQ>(nd); }
+      if (edge && LPQ == 32) {
         partner_max4<LPQ>(rp, np, rd, nd, xch, k, half, xpar);
       }
       const bool conv = rp <= ip.in_eps_abs + ip.in_eps_rel * np && rd <= ip.in_eps_abs + ip.in_eps_rel * nd;
