@@ -587,10 +587,20 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
         Px = fma(pW, suffix2<LPQ>(st, k), pI * x);   // P x = pI x + pW M'(M x)
         Aty += suffix2<LPQ>(srow ? ys : 0.0, k);     // + M' y_s
       } else {
-        double nxt;
-        double mx = apply_M<LPQ>(x, k, &nxt);
-        if (k > N) mx = 0.0;
-        Px = fma(pW, apply_Mt<LPQ>(mx, k), pI * x);
+        // (M'M x)_k as a dot product with column k of the W table (the one K was built from) instead of four warp
+        // scans (~150 instructions at LPQ == 16).  Deliberately a ROLLED loop: unrolled, its loads next to the live
+        // K^-1 row make ptxas spill (measured: slower than the scans).
+        rhsbuf[k] = x;
+        __syncwarp();
+        double w0 = 0.0, w1 = 0.0;
+#pragma unroll 1
+        for (int j = 0; j < LPQ; j += 2) {
+          const double2 xj = *reinterpret_cast<const double2*>(rhsbuf + j);
+          w0 = fma(tab_ld<KS>(tabs + j * LPQ + k), xj.x, w0);
+          w1 = fma(tab_ld<KS>(tabs + (j + 1) * LPQ + k), xj.y, w1);
+        }
+        __syncwarp();
+        Px = fma(pW, w0 + w1, pI * x);
         const double x1 = shift_down1<LPQ>(x, k), x2 = shift_down1<LPQ>(x1, k);
         const double ee = (k < N - 2) ? (x - 2.0 * x1 + x2) : 0.0;
         const double e1 = shift_up1<LPQ>(ee, k), e2 = shift_up1<LPQ>(e1, k);
