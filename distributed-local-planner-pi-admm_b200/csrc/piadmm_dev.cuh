@@ -429,12 +429,16 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
     } else {
       if (edge) build_Kinv_edge<LPQ, KS>(Kinv, N, k, pI + sg, rho, pW + rho, tabs, rhsbuf);
       else build_Kinv_vehicle<LPQ, KS>(Kinv, N, k, pI + sg, p2, pW, rho, tabs, rhsbuf);
+      // kc is uniform per GROUP only: at LPQ == 16 a warp of the generic-V x-update can hold one group with an entry
+      // and one masked group (finished scenario / vehicle of another rank) without, so the barrier between the
+      // matrix stores and the key store must sit outside the `if (kc)` (a barrier only half the warp reaches pairs
+      // up with the next barrier of the other half, and the halves then read each other's rhs one iteration off)
       if (kc) {
 #pragma unroll
         for (int j = 0; j < LPQ; j++) kc[PIADMM_KC_KEY + j * LPQ + k] = Kinv[j];
-        __syncwarp();
-        if (k == 0) { kc[0] = kI; kc[1] = kB; kc[2] = kW; kc[3] = kT; }
       }
+      __syncwarp();
+      if (kc && k == 0) { kc[0] = kI; kc[1] = kB; kc[2] = kW; kc[3] = kT; }
     }
   }
   if (KS) {

@@ -477,3 +477,57 @@ def test_kinv_cache_is_invalidated_by_changed_coefficients(N, V):
     for k in keys:
         assert np.array_equal(got[k], want[k]), ("sigma", k)
     sol.close()
+
+
+def _ragged_scene(V, N, seeds, far):
+    """S = len(seeds) scenes of V vehicles cut out of c3 intersections; scene `far` is spread out (no collision)."""
+    from pi_admm_b200.scenarios import c3_intersection
+    V4 = 4 * ((V + 3) // 4)
+    parts = []
+    for n, seed in enumerate(seeds):
+        xt, spd, rw = c3_intersection(V=V4, N=N, seed=seed, r0=60.0 if n == far else 7.0, gap=25.0 if n == far else 5.0)
+        parts.append((xt[:, :V], spd[:, :V], rw[:, :V]))
+    return tuple(np.ascontiguousarray(np.concatenate([p[i] for p in parts], axis=0)) for i in range(3))
+
+
+@pytest.mark.parametrize("V,N", [(5, 15), (7, 12), (3, 20)])
+def test_ragged_generic_batch_matches_oracle(V, N):
+    """Odd V and a batch in which one scenario stops after its first outer iteration (no collision): at N <= 15 a warp
+    then holds groups of two different scenarios, one finished and one active (groups masked inside a running warp)."""
+    p = _generic_params(N)
+    xt, spd, refwin = _ragged_scene(V, N, seeds=(3, 4, 5), far=1)
+    ref = ctwin.step(p, xt, spd, refwin, D=V - 1)
+    assert ref["n_outer"][1] == 1 and ref["n_edge_solves"][0] > 0 and ref["n_edge_solves"][2] > 0
+    sol = PIADMMSolver(p, S=3, V=V, D=V - 1)
+    sol.setup(xt, spd, refwin)
+    sol.iterate()
+    sol.plant_step()
+    assert_same(sol.to_numpy(), ref, what=f"ragged V={V} N={N}")
+    sol.close()
+
+
+def test_vehicle_sharding_with_odd_ownership_ranges():
+    """Ownership ranges that split a warp's two groups between ranks (V=6 over ranks of 3 + 3, V=5 over 3 + 2)."""
+    from pi_admm_b200.parallel import iterate_lockstep
+    for V, cuts in ((6, (0, 3, 6)), (5, (0, 3, 5))):
+        N = 15
+        p = _generic_params(N)
+        xt, spd, refwin = _ragged_scene(V, N, seeds=(3,), far=-1)
+        ref = ctwin.step(p, xt, spd, refwin, D=V - 1)
+        assert ref["n_edge_solves"].sum() > 0
+        sols = []
+        for r in range(len(cuts) - 1):
+            s = PIADMMSolver(p, S=1, V=V, D=V - 1)
+            s.setup(xt, spd, refwin)
+            s.set_ownership(cuts[r], cuts[r + 1])
+            sols.append(s)
+        iterate_lockstep(sols)
+        for r, s in enumerate(sols):
+            got = s.to_numpy()
+            lo, hi = s.own
+            assert np.array_equal(got["n_outer"], ref["n_outer"]) and np.array_equal(got["nbr"], ref["nbr"])
+            for k in ("u", "pos", "err_rk", "err_sk"):
+                assert rel_err(got[k], ref[k]) <= 1e-6, (V, r, k)
+            for k in ("hat", "dual"):
+                assert rel_err(got[k][:, lo:hi], ref[k][:, lo:hi]) <= 1e-6, (V, r, k)
+            s.close()
