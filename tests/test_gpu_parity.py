@@ -531,3 +531,33 @@ def test_vehicle_sharding_with_odd_ownership_ranges():
             for k in ("hat", "dual"):
                 assert rel_err(got[k][:, lo:hi], ref[k][:, lo:hi]) <= 1e-6, (V, r, k)
             s.close()
+
+
+GENERIC_PRESETS = [
+    ("python_current", dict(al_all=1, eps_pri=1.0, eps_dual=0.5, dual_res_alias=0), 3, 15),   # AL over every j != i
+    ("python_current", dict(al_all=1), 4, 12),                                    # C1 semantics incl. alias quirk
+    ("python_current", dict(al_all=0, round_u=3, round_edge=2, eps_pri=0.5), 5, 15),
+    ("matlab_pi", dict(al_all=1, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5), 3, 20),
+    ("matlab_pi", dict(al_all=0, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5, PI=0), 6, 15),
+    ("python_old_pi", dict(al_all=0, num_ho=10, iter_num=6), 4, 10),              # scene-wide rho set by the last edge
+    ("python_old_pi", dict(al_all=1, num_ho=15, iter_num=5, trad=1), 3, 15),
+    ("matlab_pi", dict(al_all=0, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5), 1, 15),   # V = 1: no pair at all
+]
+
+
+@pytest.mark.parametrize("preset,kw,V,N", GENERIC_PRESETS)
+def test_generic_v_semantic_presets_match_oracle(preset, kw, V, N):
+    """The three dual-update laws and the AL neighbourhoods through the phase kernels (generic V), on a ragged batch
+    of three scenes (the middle one collision free)."""
+    p = make_params(preset, "default", **dict(dict(num_ho=N, iter_num=8), **kw))
+    xt, spd, refwin = _ragged_scene(V, p.num_ho, seeds=(11, 12, 13), far=1)
+    D = max(1, V - 1)
+    ref = ctwin.step(p, xt, spd, refwin, D=D)
+    if V > 1 and not p.always_edge:
+        assert ref["n_edge_solves"][0] + ref["n_edge_solves"][2] > 0
+    sol = PIADMMSolver(p, S=3, V=V, D=D)
+    sol.setup(xt, spd, refwin)
+    sol.iterate()
+    sol.plant_step()
+    assert_same(sol.to_numpy(), ref, what=f"generic {preset} {kw} V={V}")
+    sol.close()
