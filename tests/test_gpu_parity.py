@@ -561,3 +561,29 @@ def test_generic_v_semantic_presets_match_oracle(preset, kw, V, N):
     sol.plant_step()
     assert_same(sol.to_numpy(), ref, what=f"generic {preset} {kw} V={V}")
     sol.close()
+
+
+def test_run_closed_loop_generic_v_ragged_batch_equals_the_twin():
+    """On-device closed loop through the phase kernels for a ragged batch (odd V, three scenes, one collision free)
+    against stepping the C twin on the host."""
+    V, N, n = 5, 15, 3
+    p = _generic_params(N, iter_num=6)
+    xt, spd, rw0 = _ragged_scene(V, N, seeds=(3, 4, 5), far=1)
+    T = N + 1 + n
+    k = np.arange(T)
+    ref_traj = np.zeros((3, V, 2, T))
+    ref_traj[:, :, 0] = xt[:, :, 0:1] + k * 0.1 * spd[:, :, None] * np.cos(xt[:, :, 2:3])
+    ref_traj[:, :, 1] = xt[:, :, 1:2] + k * 0.1 * spd[:, :, None] * np.sin(xt[:, :, 2:3])
+    assert np.allclose(ref_traj[:, :, :, :N + 1], rw0)
+    sol = PIADMMSolver(p, S=3, V=V, D=V - 1)
+    sol.setup(xt, spd, rw0)
+    sol.set_reference(ref_traj)
+    h = {kk: v.cpu().numpy() for kk, v in sol.run_closed_loop(0, n).items()}
+    sol.close()
+    x = xt.copy()
+    for t in range(n):
+        ref = ctwin.step(p, x, spd, np.ascontiguousarray(ref_traj[:, :, :, t:t + N + 1]), D=V - 1)
+        assert np.array_equal(h["n_outer_his"][t], ref["n_outer"]) and np.array_equal(h["iter_his"][t], ref["curr_iter"]), t
+        assert rel_err(h["x_vec"][t], ref["xt_next"][:, :, :2]) <= 1e-6 and rel_err(h["u_vec"][t], ref["u"][:, :, 0]) <= 1e-6
+        x = ref["xt_next"].copy()
+    assert h["n_outer_his"].max() >= 2

@@ -63,6 +63,25 @@ def phases(N, V=12):
     sol.close()
 
 
+def ragged(N=15, V=5):
+    """Warps that mix a live and a masked group: odd V, a batch with a finished scenario, an odd ownership cut."""
+    p = make_params("matlab_pi", "default", num_ho=N, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5,
+                    al_all=0, iter_num=3)
+    parts = [c3_intersection(V=8, N=N, seed=s, r0=r0, gap=g) for s, r0, g in ((3, 7.0, 5.0), (4, 60.0, 25.0), (5, 7.0, 5.0))]
+    xt, spd, rw = (np.ascontiguousarray(np.concatenate([q[i][:, :V] for q in parts], axis=0)) for i in range(3))
+    sol = PIADMMSolver(p, S=3, V=V, D=V - 1)
+    sol.setup(xt, spd, rw)
+    sol.iterate()
+    torch.cuda.synchronize()
+    assert np.isfinite(sol.to_numpy()["u"]).all()
+    sol.set_ownership(0, 3)
+    sol.begin_step()
+    for _ in range(2):
+        sol.x_update(); sol.detect_edges(); sol.z_update(); sol.residual_partials(); sol.residual_decide()
+    torch.cuda.synchronize()
+    sol.close()
+
+
 def obca(S=5):
     import obca_synth
     from pi_admm_b200.obca_consensus import OBCAConsensus
@@ -83,8 +102,8 @@ def obca(S=5):
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["fused15", "fused30", "phases15", "phases30", "obca"]
+    which = sys.argv[1:] or ["fused15", "fused30", "phases15", "phases30", "ragged", "obca"]
     for w in which:
         {"fused15": lambda: fused(15), "fused30": lambda: fused(30), "phases15": lambda: phases(15),
-         "phases30": lambda: phases(30), "obca": obca}[w]()
+         "phases30": lambda: phases(30), "ragged": ragged, "obca": obca}[w]()
         print("ok", w, flush=True)
