@@ -53,6 +53,18 @@ class Constraints:
         self.m = 4 * rows * N - 2 * rows
 
 
+def check_status(status: int, error_on_fail: bool = True, where: str = ""):
+    """The reference's failure behaviour for one scenario's PIADMM_ST_* bits: a vehicle QP that did not converge
+    raises (CasADi's error_on_fail=True default, casadi/main.py:96-103), an edge problem that did not converge is
+    tolerated (error_on_fail=False, casadi/main.py:145-153); running out of neighbour slots is a sizing error of
+    this implementation and always raises."""
+    if status & _abi.ST_SLOT_OVERFLOW:
+        raise _abi.PIADMMError(f"{where}: a vehicle needed more than D neighbour slots (PIADMM_ST_SLOT_OVERFLOW)")
+    if error_on_fail and status & _abi.ST_VEH_MAXITER:
+        raise RuntimeError(f"{where}: vehicle QP did not converge within in_max_iter inner iterations "
+                           "(PIADMM_ST_VEH_MAXITER; the reference's qpsol raises here, error_on_fail=True)")
+
+
 class PI_ADMM_CASADI(object):
     def __init__(self, semantics: str = "python_current", inner: str = "osqp_default", **overrides):
         # ADMM parameter setting -- casadi/PI_ADMM_class.py:15-28
@@ -65,6 +77,10 @@ class PI_ADMM_CASADI(object):
         self.ref_traj_B = np.vstack((np.zeros_like(y_B), y_B))
         self.ref_traj = np.vstack((self.ref_traj_A, self.ref_traj_B))
         self.semantics, self.inner, self.overrides = semantics, inner, dict(overrides)
+        # casadi/main.py:96 builds the vehicle solver with CasADi's default error_on_fail=True (a failed vehicle QP
+        # raises RuntimeError) and the edge solver with error_on_fail=False (:145-146, a failed edge solve is used
+        # as it is).  step() mirrors that: PIADMM_ST_VEH_MAXITER raises, PIADMM_ST_EDGE_MAXITER is only recorded.
+        self.error_on_fail = True
         self._solver = None
         self._solver_key = None
 
@@ -157,6 +173,7 @@ class PI_ADMM_CASADI(object):
         sol.plant_step()
         o = sol.to_numpy()
         n = int(o["n_outer"][0])
+        check_status(int(o["status"][0]), self.error_on_fail, f"MPC step {num_step}")
         return dict(primal_u=o["u"][0], pos_old=o["pos"][0].reshape(-1, o["pos"].shape[-1]), iter=int(o["curr_iter"][0]),
                     n_outer=n, err_rk=o["err_rk"][0, :n], err_sk=o["err_sk"][0, :n], xt_next=o["xt_next"][0],
                     rho=float(o["rho_s"][0]), hat=o["hat"][0], dual=o["dual"][0], status=int(o["status"][0]))

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PIADMM_LIB") or os.path.join(_HERE, "csrc", "libpiadmm.so")   # PIADMM_LIB: A/B builds
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 DUAL_PLAIN, DUAL_PI, DUAL_PI_OLD = 0, 1, 2
 ST_VEH_MAXITER, ST_EDGE_MAXITER, ST_SLOT_OVERFLOW = 1, 2, 4
 
@@ -71,7 +71,8 @@ class Buffers(C.Structure):
 
 class Histories(C.Structure):
     """struct piadmm_histories (device pointers, any may be NULL)."""
-    _fields_ = [(n, C.c_void_p) for n in ("x_vec", "theta_vec", "u_vec", "err_rk_his", "iter_his", "n_outer_his")]
+    _fields_ = [(n, C.c_void_p) for n in ("x_vec", "theta_vec", "u_vec", "err_rk_his", "iter_his", "n_outer_his",
+                                            "status_his")]
 
 
 def max_edges(V: int, D: int) -> int:

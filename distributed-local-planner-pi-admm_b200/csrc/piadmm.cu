@@ -403,6 +403,7 @@ __global__ void k_advance(const __grid_constant__ DevCtx c, piadmm_histories o, 
   if (a % c.V == 0) {
     if (o.iter_his) o.iter_his[(size_t)t * c.S + s] = c.b.curr_iter[s];
     if (o.n_outer_his) o.n_outer_his[(size_t)t * c.S + s] = c.b.n_outer[s];
+    if (o.status_his) o.status_his[(size_t)t * c.S + s] = c.b.status[s];
     if (o.err_rk_his) { const int n = c.b.n_outer[s]; o.err_rk_his[(size_t)t * c.S + s] = n > 0 ? c.b.err_rk[(size_t)s * c.I + n - 1] : 0.0; }
   }
   xt[0] = x; xt[1] = y; xt[2] = th;

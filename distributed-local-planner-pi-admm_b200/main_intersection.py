@@ -19,7 +19,7 @@ import time
 
 import numpy as np
 
-from .PI_ADMM_class import PI_ADMM_CASADI
+from .PI_ADMM_class import PI_ADMM_CASADI, check_status
 
 
 def run(semantics="python_current", inner="osqp_default", fast=False, verbose=False, n_steps=None,
@@ -43,6 +43,8 @@ def run(semantics="python_current", inner="osqp_default", fast=False, verbose=Fa
         sol.setup(xt[None], spd, np.zeros((1, V, 2, N + 1)), rho=rho)
         sol.set_reference(np.ascontiguousarray(PI_ADMM.ref_traj).reshape(1, V, 2, -1))
         h = {k: v.cpu().numpy() for k, v in sol.run_closed_loop(0, n_steps).items()}
+        for i in range(n_steps):          # failures are reported after the run (the loop never leaves the device)
+            check_status(int(h["status_his"][i, 0]), getattr(PI_ADMM, "error_on_fail", True), f"t_step {i + 1}")
         iter_his[:n_steps] = h["iter_his"][:, 0]
         out = dict(x_vec=[h["x_vec"][i, 0].T.copy() for i in range(n_steps)],
                    theta_vec=[h["theta_vec"][i, 0].copy() for i in range(n_steps)],
@@ -70,6 +72,8 @@ def run(semantics="python_current", inner="osqp_default", fast=False, verbose=Fa
         # finish the iterations of optimization in one time step (main.py:185-201)
         sol.plant_step()
         o = sol.to_numpy()
+        # casadi/main.py:96 vs :145: a failed vehicle QP raises (error_on_fail default), a failed edge solve does not
+        check_status(int(o["status"][0]), getattr(PI_ADMM, "error_on_fail", True), f"t_step {num_step + 1}")
         curr_iter, n_outer = int(o["curr_iter"][0]), int(o["n_outer"][0])
         primal_u = o["u"][0]
         iter_his[num_step] = curr_iter

@@ -200,7 +200,7 @@ class PIADMMSolver:
         f64 = lambda *sh: torch.zeros(sh, dtype=torch.float64, device=dev)
         i32 = lambda *sh: torch.zeros(sh, dtype=torch.int32, device=dev)
         out = dict(x_vec=f64(n, S, V, 2), theta_vec=f64(n, S, V), u_vec=f64(n, S, V), err_rk_his=f64(n, S),
-                   iter_his=i32(n, S), n_outer_his=i32(n, S))
+                   iter_his=i32(n, S), n_outer_his=i32(n, S), status_his=i32(n, S))
         hs = _abi.Histories(**{k: v.data_ptr() for k, v in out.items()})
         self._check(self.lib.piadmm_run_closed_loop(self._h, int(first_step), n, C.byref(hs), self._stream()),
                     "piadmm_run_closed_loop")

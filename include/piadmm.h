@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define PIADMM_ABI_VERSION 1
+#define PIADMM_ABI_VERSION 2
 
 enum {
   PIADMM_OK = 0,
@@ -182,6 +182,7 @@ int piadmm_step_host_at(piadmm_handle* h, int num_step, const double* xt, double
 typedef struct piadmm_histories {
   double *x_vec, *theta_vec, *u_vec, *err_rk_his;
   int32_t *iter_his, *n_outer_his;
+  int32_t *status_his;   /* [n_steps,S] PIADMM_ST_* bits of every step (vehicle / edge solver failures, slot overflow) */
 } piadmm_histories;
 int piadmm_run_closed_loop(piadmm_handle* h, int first_step, int n_steps, const piadmm_histories* out, void* stream);
 

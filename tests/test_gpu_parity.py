@@ -587,3 +587,40 @@ def test_run_closed_loop_generic_v_ragged_batch_equals_the_twin():
         assert rel_err(h["x_vec"][t], ref["xt_next"][:, :, :2]) <= 1e-6 and rel_err(h["u_vec"][t], ref["u"][:, :, 0]) <= 1e-6
         x = ref["xt_next"].copy()
     assert h["n_outer_his"].max() >= 2
+
+
+def test_reference_error_behaviour_vehicle_failure_raises_edge_failure_is_recorded():
+    """casadi/main.py:96-103 builds the vehicle solver with CasADi's error_on_fail default (a failed QP raises
+    RuntimeError) and the edge solver with error_on_fail=False (:145-153).  The class mirror and the drop-in driver
+    do the same with the solver's status bits; the on-device closed loop reports them per step (status_his)."""
+    from pi_admm_b200 import main_intersection
+    from pi_admm_b200.PI_ADMM_class import PI_ADMM_CASADI
+    xt = np.array([[-5.2, 0, 0], [0, 10.4, -np.pi / 2]])
+    P = PI_ADMM_CASADI(in_max_iter=30)                     # no vehicle QP converges within 30 inner iterations
+    with pytest.raises(RuntimeError, match="vehicle QP"):
+        P.step(12, xt)
+    P.error_on_fail = False                                # error_on_fail=False: the step goes through, bits recorded
+    r = P.step(12, xt)
+    assert r["status"] & pa._abi.ST_VEH_MAXITER
+    for kw in (dict(fast=True), dict(fast=False), dict(device_loop=True)):
+        with pytest.raises(RuntimeError, match="vehicle QP"):
+            main_intersection.run(n_steps=14, in_max_iter=30, **kw)
+    out = main_intersection.run(n_steps=3, device_loop=True)             # healthy run: nothing raised
+    assert len(out["u_vec"]) == 3
+    # status_his of the device loop equals the status of stepping
+    S, N = 8, 15
+    p = make_params("python_current", "default", in_max_iter=50)
+    from pi_admm_b200.scenarios import c4_reference
+    xt0, spd, _ = c4_scenarios(S=S, N=N, seed=8, step=10)
+    ref_traj = c4_reference(S=S, seed=8)
+    sol = PIADMMSolver(p, S=S, V=2)
+    sol.setup(xt0, spd, np.zeros((S, 2, 2, N + 1)))
+    sol.set_reference(ref_traj)
+    h = {k: v.cpu().numpy() for k, v in sol.run_closed_loop(10, 3).items()}
+    sol.close()
+    x = xt0.copy()
+    for t in range(3):
+        ref = ctwin.step(p, x, spd, np.ascontiguousarray(ref_traj[:, :, :, 10 + t:10 + t + N + 1]))
+        assert np.array_equal(h["status_his"][t], ref["status"]), t
+        x = ref["xt_next"].copy()
+    assert h["status_his"].any()
