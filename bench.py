@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- agent-QP solves/s of one PI-ADMM MPC step over a batch of synthetic scenarios.
 
-  python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c4|c4n30]
+  python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c4|c4n30|c3|c5]
 
 Workload (config 4 of BASELINE.json): S = 4096 independent two-vehicle intersection
 scenarios PER GPU (weak scaling, no data-path collective), each one MPC step run to PI-ADMM
@@ -9,6 +9,11 @@ convergence by ONE launch of the fused persistent kernel.  One "step" = that MPC
 whole batch; `value` = agent-QP (vehicle x-update) solves per second, all GPUs together, inputs
 resident in HBM; `e2e` = the same through the host-buffer C-ABI entry point piadmm_step_host
 (pinned host inputs -> H2D -> step -> D2H of u/pos/xt_next/iteration counts inside the timed region).
+
+--workload c3 / c5 (not the default, not the driver's line): ONE coupled scene (64-vehicle intersection / 4096-vehicle
+grid, N=30) through the generic-V phase kernels; under torchrun the vehicles are sharded over the ranks (NCCL all-gather
+of pos/u rows + all-reduce of the residual sums per outer iteration), "scaling": "strong".  `ms_per_step` is then the
+BASELINE metric's second half, ms per coupled MPC step.
 
 --impl reference: the reference's CasADi+OSQP stack is not installable here (no wheel, no network),
 so this arm times the oracle's C twin (oracle/piadmm_ref.c, kind "port") on all host cores.
@@ -32,6 +37,39 @@ WORKLOADS = {
     "c4": (4096, 15),
     "c4n30": (4096, 30),
 }
+
+
+COUPLED = {
+    # name: (vehicles, horizon N, neighbour slots D)   -- BASELINE configs 3 and 5, SURVEY.md 8(d)
+    "c3": (64, 30, 8),
+    "c5": (4096, 30, 8),
+}
+
+
+def coupled_params(N):
+    """Synthetic coupled scenes: dual="pi", AL term over activated edges, convex edge problem."""
+    import pi_admm_b200 as pa
+    p = pa.preset("matlab_pi")
+    p.update(num_ho=N, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5, al_all=0, iter_num=12)
+    return p
+
+
+def coupled_scene(name):
+    from pi_admm_b200.scenarios import c3_intersection, c5_grid
+    V, N, D = COUPLED[name]
+    return (c3_intersection(V=V, N=N) if name == "c3" else c5_grid(N=N)), V, N, D
+
+
+def coupled_config(name, V, N, D, world):
+    what = {"c3": "c3: ONE 64-vehicle 4-arm intersection (BASELINE config 3)",
+            "c5": "c5: ONE 4096-vehicle coupled grid scene, 64+64 lanes x 32 vehicles (BASELINE config 5)"}[name]
+    return {"workload": f"{what}, horizon N={N}, one coupled MPC step (outer-iteration cap 12) through the generic-V "
+                        "phase kernels", "vehicles": V, "horizon": N, "neighbour_slots": D,
+            "semantics": "dual=pi (MATLAB PI+anti-windup), AL over activated edges, edge=convex, eps_pri=eps_dual=0.5, "
+                         "inner=osqp_default",
+            "parallelism": "single GPU" if world == 1 else
+                           f"vehicles sharded x{world}, NCCL all-gather of pos/u rows + all-reduce of residual sums per outer iteration",
+            "l2": "L2 flushed (256 MiB write) before every timed step"}
 
 
 def bench_params(N):
@@ -122,6 +160,8 @@ def run_reference(args, rank, world):
     ge.build()
     from oracle import ctwin
     from pi_admm_b200.scenarios import c4_scenarios
+    if args.workload in COUPLED:
+        return run_reference_coupled(args)
     S, N = WORKLOADS[args.workload]
     p = bench_params(N)
     xt, spd, refwin = c4_scenarios(S=S, N=N)
@@ -149,6 +189,34 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
+def run_reference_coupled(args):
+    """CPU arm of the coupled workloads: the C twin's generic-V step on all host cores (a c5 step takes seconds:
+    the run is bounded to ~60 s whatever --steps says, and says so)."""
+    from oracle import ctwin
+    (xt, spd, refwin), V, N, D = coupled_scene(args.workload)
+    p = coupled_params(N)
+    cores = host_cores()
+    t0 = time.perf_counter()
+    r = ctwin.step(p, xt, spd, refwin, D=D, nthreads=cores)              # warm-up, also sizes the run
+    one = time.perf_counter() - t0
+    steps = max(1, min(args.steps, int(60.0 / max(one, 1e-3))))
+    t0 = time.perf_counter()
+    solves = 0
+    for _ in range(steps):
+        r = ctwin.step(p, xt, spd, refwin, D=D, nthreads=cores)
+        solves += int(r["n_veh_solves"].sum())
+    dt = time.perf_counter() - t0
+    val = solves / dt
+    print(json.dumps({
+        "impl": "reference", "metric": "agent-QP solves/s", "value": val, "unit": "solves/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": 1, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": coupled_config(args.workload, V, N, D, 1),
+        "cpu_baseline": {"value": val, "unit": "solves/s", "cores": cores, "kind": "port",
+                         "sample": f"{steps} coupled MPC steps of the whole scene on {cores} OpenMP threads "
+                                   "(oracle/piadmm_ref.c; CasADi+OSQP not installable)"},
+        "e2e": {"value": val, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
 def workload_config(name, S, N, world):
     return {"workload": f"{name}: {S} independent two-vehicle intersection scenarios per GPU (BASELINE config 4), "
                         f"horizon N={N}, one MPC step to PI-ADMM convergence",
@@ -165,7 +233,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS) + sorted(COUPLED))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -202,6 +270,8 @@ def main():
             os.dup2(saved, 1)
             os.close(saved)
 
+    if args.workload in COUPLED:
+        return run_coupled(args, rank, local_rank, world)
     S, N = WORKLOADS[args.workload]
     p = bench_params(N)
     # every rank gets its own S scenarios (different seed per rank: weak scaling, no exchange)
@@ -337,6 +407,129 @@ def main():
         }
         if not args.no_cpu_baseline and world == 1:       # reported at N=1 only (rank 0)
             line["cpu_baseline"] = cpu_baseline(p, xt, spd, refwin, S, N)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_coupled(args, rank, local_rank, world):
+    """--workload c3 / c5: one coupled scene through the phase kernels (generic V).  world > 1: vehicles sharded over the
+    ranks (parallel.VehicleShardedSolver).  Timing: CUDA events around the whole coupled step, max over ranks."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from pi_admm_b200.parallel import VehicleShardedSolver
+    from pi_admm_b200.solver import PIADMMSolver
+    (xt, spd, refwin), V, N, D = coupled_scene(args.workload)
+    p = coupled_params(N)
+    if world > 1:
+        vs = VehicleShardedSolver(p, V, D, device=local_rank)
+        sol, step = vs.sol, vs.iterate
+    else:
+        sol = PIADMMSolver(p, S=1, V=V, D=D, device=local_rank)
+        step = sol.iterate
+    sol.setup(xt, spd, refwin)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=sol.device)
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = sol.launch_count
+    step_ms = []
+    for _ in range(args.steps):
+        flush.fill_(1)                                   # L2 flush, outside the event pair
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        step()                                           # all outer iterations of the coupled MPC step
+        b.record(stream)
+        torch.cuda.synchronize()
+        step_ms.append(a.elapsed_time(b))
+    launches = sol.launch_count - l0
+    out = sol.to_numpy()
+    # ---- end to end (world == 1): host arrays in, step, plant step, results back on the host
+    e2e = None
+    if world == 1:
+        pin = [torch.from_numpy(np.ascontiguousarray(x)).pin_memory() for x in (xt, spd, refwin)]
+        keys = ("u", "pos", "xt_next", "n_outer", "curr_iter")
+        host = {k: torch.empty_like(sol.buf[k], device="cpu").pin_memory() for k in keys}
+
+        def e2e_step():
+            sol.setup(*pin)
+            sol.iterate()
+            sol.plant_step()
+            for k in keys:
+                host[k].copy_(sol.buf[k], non_blocking=True)
+            torch.cuda.synchronize()
+        for _ in range(args.warmup):
+            e2e_step()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        assert np.array_equal(host["u"].numpy(), out["u"]) and np.array_equal(host["n_outer"].numpy(), out["n_outer"])
+        e2e = {"ms_per_step": e2e_ms, "h2d": sum(t.numel() * t.element_size() for t in pin),
+               "d2h": sum(t.numel() * t.element_size() for t in host.values())}
+    clocks = sampler.stop() if rank == 0 else None
+    stats = torch.tensor([sum(step_ms)], dtype=torch.float64, device=sol.device)
+    # every rank books the solves of the vehicles / edges it owns... x-updates: owned vehicles only
+    work = torch.tensor([float(out["n_veh_solves"][0]), float(out["veh_inner"][0])], dtype=torch.float64, device=sol.device)
+    if world > 1:
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        dist.all_reduce(work, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        ms = float(stats[0]) / args.steps
+        n_veh, veh_inner = float(work[0]), float(work[1])
+        n_edge, edge_inner = float(out["n_edge_solves"][0]), float(out["edge_inner"][0])   # world > 1: rank 0's share
+        flops = veh_inner * flops_per_inner_iter(N, False) + edge_inner * flops_per_inner_iter(N, True)
+        tf = C.c_double(0); pm = C.c_double(0)
+        rc = sol.lib.piadmm_fp64_peak(local_rank, 200000, C.byref(tf), C.byref(pm))
+        peak = float(tf.value) if rc == 0 else None
+        ach = flops / (ms * 1e-3) / 1e12
+        line = {
+            "metric": "agent-QP solves/s", "value": n_veh / (ms * 1e-3), "unit": "solves/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": coupled_config(args.workload, V, N, D, world),
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+                         "frac": ach / peak if peak else None, "traffic": None,
+                         "kernel": "whole coupled step (k_x_update + detection + k_z_update + residual kernels)",
+                         "note": "latency bound by construction: every outer iteration waits for the slowest vehicle "
+                                 "QP and the slowest edge problem of the scene (one dependent chain of inner "
+                                 "iterations each); the fraction says how little of the GPU one scene can fill",
+                         "peak_source": "DFMA micro-benchmark of this repo (piadmm_fp64_peak)",
+                         "flops_per_launch": flops},
+            "work_per_step": {"agent_qp_solves": n_veh, "edge_solves": n_edge, "veh_inner_iters": veh_inner,
+                              "edge_inner_iters": edge_inner, "outer_iters": int(out["n_outer"][0]),
+                              "status": int(out["status"][0]), "ms_per_mpc_step": ms}}
+        if e2e:
+            line["e2e"] = {"value": n_veh / (e2e["ms_per_step"] * 1e-3), "unit": "solves/s", "ms_per_step": e2e["ms_per_step"],
+                           "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
+                           "api": "PIADMMSolver.setup (pinned xt, spd, reference window -> device) + iterate + plant_step + "
+                                  "D2H of u, pos, xt_next, n_outer, curr_iter into pinned buffers"}
+        if not args.no_cpu_baseline and world == 1:
+            import __graft_entry__ as ge  # noqa: F401
+            from oracle import ctwin
+            cores = host_cores()
+            t0 = time.perf_counter(); reps = 0; solves = 0
+            while reps == 0 or (time.perf_counter() - t0 < 10.0 and reps < 200):
+                r = ctwin.step(p, xt, spd, refwin, D=D, nthreads=cores)
+                solves += int(r["n_veh_solves"].sum()); reps += 1
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": solves / dt, "unit": "solves/s", "cores": cores, "kind": "port",
+                                    "sample": f"{reps} coupled MPC steps of the same scene (~{dt:.1f} s) with {cores} "
+                                              "OpenMP threads, oracle/piadmm_ref.c"}
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
