@@ -104,19 +104,24 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 6) k_x_update(con
   }
 }
 
-// trajectory bounding boxes [S,V,4] = (xmin, xmax, ymin, ymax): cheap reject for the O(V^2) pair test
+// trajectory bounding boxes [S,V,4] = (xmin, xmax, ymin, ymax): cheap reject for the O(V^2) pair test.
+// One warp per vehicle, lane k = trajectory point k (N+1 <= 32): one coalesced load per coordinate row and a shuffle
+// butterfly instead of a serial 31-point loop of dependent loads per thread (9 us -> ~2 us per launch).
 __global__ void k_bbox(const __grid_constant__ DevCtx c) {
-  const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long a = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (a >= (long)c.S * c.V) return;
-  const int N = c.N;
+  const int N = c.N, k = lane <= N ? lane : 0;             // padded lanes repeat point 0
   const double* p = c.b.pos + (size_t)a * 2 * (N + 1);
-  double x0 = p[0], x1 = p[0], y0 = p[N + 1], y1 = p[N + 1];
-  for (int k = 1; k <= N; k++) {
-    const double x = p[k], y = p[N + 1 + k];
-    x0 = x < x0 ? x : x0; x1 = x > x1 ? x : x1; y0 = y < y0 ? y : y0; y1 = y > y1 ? y : y1;
+  const double x = p[k], y = p[N + 1 + k];
+  double x0 = x, x1 = x, y0 = y, y1 = y;
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    const double a0 = __shfl_xor_sync(PIADMM_FULL, x0, o), a1 = __shfl_xor_sync(PIADMM_FULL, x1, o);
+    const double b0 = __shfl_xor_sync(PIADMM_FULL, y0, o), b1 = __shfl_xor_sync(PIADMM_FULL, y1, o);
+    x0 = a0 < x0 ? a0 : x0; x1 = a1 > x1 ? a1 : x1; y0 = b0 < y0 ? b0 : y0; y1 = b1 > y1 ? b1 : y1;
   }
-  double4* o = reinterpret_cast<double4*>(c.bbox) + a;
-  *o = make_double4(x0, x1, y0, y1);
+  if (lane == 0) reinterpret_cast<double4*>(c.bbox)[a] = make_double4(x0, x1, y0, y1);
 }
 
 // hits[s,i,jb] bit jj = 1 iff vehicle j = 32*jb+jj collides with i (casadi/main.py:110-113); the matrix is stored
@@ -157,6 +162,41 @@ __global__ void k_hits(const __grid_constant__ DevCtx c) {
     }
   }
   if (m) atomicOr(c.hits + (size_t)si * words + jb, m);
+}
+
+// The same test with one WARP per (i, word): lane = one j.  For small scenes (config 3: 64 vehicles = 128 words) the
+// thread-per-word form leaves 128 threads with 32 serial pair tests each (28 us per launch); here every pair has its
+// own lane.  Large scenes (config 5: 8.4 M pairs, almost all rejected by the boxes) keep the thread-per-word form.
+__global__ void k_hits_warp(const __grid_constant__ DevCtx c) {
+  const int N = c.N, words = (c.V + 31) / 32, lane = threadIdx.x & 31;
+  const long t = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (t >= (long)c.S * c.V * words) return;
+  const int jb = (int)(t % words);
+  const long si = t / words;
+  const int i = (int)(si % c.V), s = (int)(si / c.V);
+  if (jb * 32 + 31 <= i || c.b.done[s]) return;          // warp uniform
+  const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
+  const int j = jb * 32 + lane;
+  bool hit = false;
+  if (j > i && j < c.V) {
+    hit = c.p.always_edge != 0;
+    if (!hit) {
+      const double4* bb = reinterpret_cast<const double4*>(c.bbox) + (size_t)s * c.V;
+      const double4 bi = bb[i], bj = bb[j];
+      const double gx = fmax(0.0, fmax(bi.x - bj.y, bj.x - bi.y)), gy = fmax(0.0, fmax(bi.z - bj.w, bj.z - bi.w));
+      if (gx * gx + gy * gy < thr) {
+        const double* pi = c.b.pos + (((size_t)s * c.V + i) * 2) * (N + 1);
+        const double* pj = c.b.pos + (((size_t)s * c.V + j) * 2) * (N + 1);
+        for (int k = 0; k <= N && !hit; k++) {
+          const double dx = pi[k] - pj[k], dy = pi[N + 1 + k] - pj[N + 1 + k];
+          hit = dx * dx + dy * dy < thr;
+        }
+      }
+    }
+  }
+  const unsigned m = __ballot_sync(PIADMM_FULL, hit);
+  if (hit) atomicOr(c.hits + ((size_t)s * c.V + j) * words + (i >> 5), 1u << (i & 31));
+  if (lane == 0 && m) atomicOr(c.hits + (size_t)si * words + jb, m);
 }
 
 // per vehicle: allocate neighbour slots for newly colliding vehicles, ascending j (this equals the
@@ -1011,10 +1051,11 @@ int piadmm_detect_edges(piadmm_handle* h, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   const int words = (h->c.V + 31) / 32;
   const long warps = (long)h->c.S * h->c.V * words;
-  k_bbox<<<(unsigned)(((long)h->c.S * h->c.V + 127) / 128), 128, 0, st>>>(h->c);
+  k_bbox<<<(unsigned)(((long)h->c.S * h->c.V * 32 + 127) / 128), 128, 0, st>>>(h->c);
   LAUNCHED();
   CK(cudaMemsetAsync(h->c.hits, 0, sizeof(uint32_t) * (size_t)warps, st));
-  k_hits<<<(unsigned)((warps + 255) / 256), 256, 0, st>>>(h->c);
+  if (warps <= 148L * 64) k_hits_warp<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(h->c);   // a lane per pair
+  else k_hits<<<(unsigned)((warps + 255) / 256), 256, 0, st>>>(h->c);                                  // a thread per 32 pairs
   LAUNCHED();
   const long agents = (long)h->c.S * h->c.V;
   k_slots<<<(unsigned)((agents * 32 + 255) / 256), 256, 0, st>>>(h->c);
@@ -1055,7 +1096,9 @@ int piadmm_residual_decide(piadmm_handle* h, void* stream) {
     k_dist_test<<<(unsigned)((slots + 255) / 256), 256, 0, st>>>(h->c);
     LAUNCHED();
   }
-  k_res_decide<<<h->c.S, 128, 0, st>>>(h->c);
+  // the last_hat copy of a dense scene is ~7000 elements behind two dependent index loads: 1024 threads per scenario
+  // when there are few scenarios (36 -> ~6 us per launch at config 3), 128 for large batches
+  k_res_decide<<<h->c.S, h->c.S <= 64 ? 1024 : 128, 0, st>>>(h->c);
   LAUNCHED();
   h->c.i_iter++;
   return PIADMM_OK;
