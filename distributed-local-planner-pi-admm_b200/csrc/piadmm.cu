@@ -392,6 +392,79 @@ __global__ void k_res_decide(const __grid_constant__ DevCtx c) {
   }
 }
 
+// Single-rank form of the three kernels above and below (k_res_partial -> k_dist_test -> k_res_decide) plus the
+// active-scenario count, in ONE launch (one CTA per scenario): the phases of a small coupled scene are a few
+// microseconds each, so four launches of dependent tiny kernels are most of their time.  The residual sums are formed
+// exactly as k_res_partial forms them (128 strided partial sums, the same tree), so the histories are bit-identical.
+__global__ void k_res_all(const __grid_constant__ DevCtx c, int* cnt) {
+  const int s = blockIdx.x, N = c.N;
+  if (c.b.done[s]) return;
+  const piadmm_params& p = c.p;
+  __shared__ double red[2][128];
+  __shared__ int bad_sh, decision;
+  const int n = c.b.edge_n[s];
+  const double rho = (p.dual_mode == PIADMM_DUAL_PI_OLD && n > 0) ? c.rho_new[s] : c.b.rho_s[s];
+  if (threadIdx.x == 0) bad_sh = 0;
+  if (threadIdx.x < 128) {
+    double sk = 0.0, rk = 0.0;
+    for (int e = threadIdx.x; e < n; e += 128) {
+      const double* er = c.edge_res + ((size_t)s * c.E + e) * 4;
+      if (p.residual_global) { sk += sqrt(rho * rho * (er[0] + er[1])); rk += sqrt(er[2] + er[3]); }
+      else { sk += 2.0 * sqrt(rho * rho * er[0]); rk += 2.0 * sqrt(er[2]); }
+    }
+    red[0][threadIdx.x] = sk; red[1][threadIdx.x] = rk;
+  }
+  __syncthreads();
+  for (int o = 64; o >= 1; o >>= 1) {
+    if ((int)threadIdx.x < o) {
+      red[0][threadIdx.x] += red[0][threadIdx.x + o];
+      red[1][threadIdx.x] += red[1][threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (p.stop_dist_test) {                      // MATLAB :202 over the allocated neighbour slots of this scenario
+    for (int t = threadIdx.x; t < c.V * c.D; t += blockDim.x) {
+      const int i = t / c.D, j = c.b.nbr[(size_t)s * c.V * c.D + t];
+      if (j <= i) continue;
+      const double* xi = c.b.xt + ((size_t)s * c.V + i) * 3;
+      const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
+      const double vi = c.b.spd[(size_t)s * c.V + i], vj = c.b.spd[(size_t)s * c.V + j];
+      const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
+      const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
+      if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) bad_sh = 1;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double rk = red[1][0], sk = red[0][0];
+    c.b.res_part[(size_t)s * 2] = rk; c.b.res_part[(size_t)s * 2 + 1] = sk;
+    c.b.err_rk[(size_t)s * c.I + c.i_iter] = rk;
+    c.b.err_sk[(size_t)s * c.I + c.i_iter] = sk;
+    c.b.rho_s[s] = rho;
+    const bool conv = rk <= p.eps_pri && sk <= p.eps_dual && bad_sh == 0;
+    bool fin = conv;
+    if (conv) { c.b.curr_iter[s] = c.i_iter + 1; c.b.done[s] = 1; }
+    else {
+      if (p.dual_res_alias) c.b.aliased[s] = 1;
+      if (p.curr_iter_latest) c.b.curr_iter[s] = c.i_iter + 1;
+      if (c.i_iter + 1 >= c.I) { c.b.done[s] = 1; fin = true; }
+    }
+    if (cnt && !fin) atomicAdd(cnt, 1);
+    decision = conv ? 1 : 0;
+  }
+  __syncthreads();
+  if (!decision) {
+    const int per = 2 * (N + 1);
+    for (int t = threadIdx.x; t < n * 2 * per; t += blockDim.x) {
+      const int e = t / (2 * per), side = (t / per) & 1, el = t % per;
+      const int v = c.b.edge_ij[((size_t)s * c.E + e) * 2 + side];
+      if (v < 0) continue;
+      const size_t o = ((((size_t)s * c.V + v) * c.D) + c.b.edge_slot[((size_t)s * c.E + e) * 2 + side]) * per + el;
+      c.b.last_hat[o] = c.b.hat[o];
+    }
+  }
+}
+
 // MATLAB :202 extra stop condition, evaluated over every allocated neighbour slot (all CTAs of the grid)
 __global__ void k_dist_test(const __grid_constant__ DevCtx c) {
   const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1104,7 +1177,18 @@ int piadmm_residual_decide(piadmm_handle* h, void* stream) {
   return PIADMM_OK;
 }
 
+// one launch (k_res_all) when this rank owns every vehicle; cnt (device, zeroed by the caller) receives the number of
+// scenarios that are still active, or is NULL
+static int residuals_single_rank(piadmm_handle* h, cudaStream_t st, int* cnt) {
+  k_res_all<<<h->c.S, h->c.S <= 64 ? 1024 : 128, 0, st>>>(h->c, cnt);
+  LAUNCHED();
+  h->c.i_iter++;
+  return PIADMM_OK;
+}
+
 int piadmm_residuals(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  if (h->c.own_lo == 0 && h->c.own_hi == h->c.V) return residuals_single_rank(h, (cudaStream_t)stream, nullptr);
   int rc = piadmm_residual_partials(h, stream);
   return rc ? rc : piadmm_residual_decide(h, stream);
 }
@@ -1194,11 +1278,15 @@ int piadmm_step(piadmm_handle* h, void* stream) {
     if ((rc = piadmm_x_update(h, stream))) break;
     if ((rc = piadmm_detect_edges(h, stream))) break;
     if ((rc = piadmm_z_update(h, stream))) break;
-    if ((rc = piadmm_residuals(h, stream))) break;
     int* cnt = h->d_count2 + (it & 1);
     CK(cudaMemsetAsync(cnt, 0, sizeof(int), st));
-    k_count_active<<<(h->c.S + 255) / 256, 256, 0, st>>>(h->c, cnt);
-    LAUNCHED();
+    if (h->c.own_lo == 0 && h->c.own_hi == h->c.V) {
+      if ((rc = residuals_single_rank(h, st, cnt))) break;      // residuals + stop test + active count in one launch
+    } else {
+      if ((rc = piadmm_residuals(h, stream))) break;
+      k_count_active<<<(h->c.S + 255) / 256, 256, 0, st>>>(h->c, cnt);
+      LAUNCHED();
+    }
     CK(cudaMemcpyAsync(h->h_count2 + (it & 1), cnt, sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(h->ev_count[it & 1], st));
     if (it >= 1) {
