@@ -1127,7 +1127,8 @@ int piadmm_detect_edges(piadmm_handle* h, void* stream) {
   k_bbox<<<(unsigned)(((long)h->c.S * h->c.V * 32 + 127) / 128), 128, 0, st>>>(h->c);
   LAUNCHED();
   CK(cudaMemsetAsync(h->c.hits, 0, sizeof(uint32_t) * (size_t)warps, st));
-  if (warps <= 148L * 64) k_hits_warp<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(h->c);   // a lane per pair
+  static const int hits_force = getenv("PIADMM_HITS") ? atoi(getenv("PIADMM_HITS")) : 0;   // A/B: 1 = lane per pair, 2 = thread per word
+  if (hits_force == 1 || (hits_force == 0 && warps <= 148L * 64)) k_hits_warp<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(h->c);   // a lane per pair
   else k_hits<<<(unsigned)((warps + 255) / 256), 256, 0, st>>>(h->c);                                  // a thread per 32 pairs
   LAUNCHED();
   const long agents = (long)h->c.S * h->c.V;
