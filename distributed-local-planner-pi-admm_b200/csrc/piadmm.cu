@@ -11,6 +11,18 @@
 #ifndef Z32_MIN_CTAS
 #define Z32_MIN_CTAS 4    // the LPQ==32 edge kernel is latency critical (few concurrent edges): registers over occupancy
 #endif
+#ifndef X32_MIN_CTAS
+#define X32_MIN_CTAS 4    // generic-V x-update, LPQ==32: 250 registers, no spills (6 CTAs = 168 registers spill: config 3 1.32 vs 1.20 ms)
+#endif
+#ifndef Z16_MIN_CTAS
+#define Z16_MIN_CTAS 4    // generic-V edge kernel, LPQ==16: latency critical like Z32 (229 registers, no spills; N=15 grid 9.34 -> 7.75 ms)
+#endif
+#ifndef X16_MIN_CTAS
+#define X16_MIN_CTAS 6    // generic-V x-update, LPQ==16: 166 registers, no spills (8 CTAs = 128 registers spill; N=15 scenes 1.24 -> 1.16 / 7.76 -> 7.61 ms)
+#endif
+#ifndef FUSED32_MIN_CTAS
+#define FUSED32_MIN_CTAS 6   // resident CTAs per SM the LPQ==32 fused kernel is compiled for
+#endif
 #ifndef FUSED16_MIN_CTAS
 #define FUSED16_MIN_CTAS 7   // resident CTAs per SM the LPQ==16 fused kernel is compiled for (register budget)
 #endif
@@ -86,7 +98,7 @@ __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : 6) k_x_update(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? X16_MIN_CTAS : X32_MIN_CTAS) k_x_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];
@@ -304,7 +316,7 @@ __global__ void k_edges(const __grid_constant__ DevCtx c) {
 }
 
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : Z32_MIN_CTAS) k_z_update(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? Z16_MIN_CTAS : Z32_MIN_CTAS) k_z_update(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];
@@ -322,7 +334,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? 8 : Z32_MIN_CTAS) k_z
     if (!loaded) { load_tabs<LPQ>(c, Wsm, 2, 2); loaded = true; }
     if (!valid) continue;                     // LPQ==16 only: the other pair of the CTA works alone
     dev_z_update<LPQ, false, true>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
-                             Wsm, gbuf[w.group_in_cta], xch, nullptr, false);
+                             Wsm, gbuf[w.group_in_cta], xch, nullptr, true);
   }
 }
 
@@ -618,7 +630,7 @@ extern "C" int piadmm_debug_read_trace(long long* host, int n) {
 }
 #endif
 template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : 6) k_fused_v2(const __grid_constant__ DevCtx c) {
+__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : FUSED32_MIN_CTAS) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];

@@ -437,6 +437,11 @@ __device__ __forceinline__ InnerOut inner_solve(const piadmm_params& ip, const I
 #pragma unroll
         for (int j = 0; j < LPQ; j++) kc[PIADMM_KC_KEY + j * LPQ + k] = Kinv[j];
       }
+      // an edge entry is shared by every edge problem of the vehicle (K_t depends on the vehicle's speed and the outer
+      // penalty only), and in the generic-V edge kernel those run concurrently in different CTAs: concurrent writers
+      // store identical bits, and a reader that sees the new key must see the new matrix -> fence between the two
+      // (keys and rows are only ever read after a key match of the same launch, so no stale L1 line can pair up)
+      __threadfence();
       __syncwarp();
       if (kc && k == 0) { kc[0] = kI; kc[1] = kB; kc[2] = kW; kc[3] = kT; }
     }

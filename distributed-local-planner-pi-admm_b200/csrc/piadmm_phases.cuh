@@ -146,8 +146,8 @@ __device__ __forceinline__ void dev_z_update(const DevCtx& c, int s, int e, int 
   const double a0 = valid ? -2.0 * g0 * (-lx * sn[0] + ly * cs[0]) : 0.0;
   const double a1 = valid ? 2.0 * g1 * (-lx * sn[1] + ly * cs[1]) : 0.0;
   const double pI = 2.0 * p.Pcost, pW = valid ? rho * g * g : 0.0;
-  // a vehicle can be an endpoint of several edges solved concurrently: the edge entry is used only where every
-  // vehicle has a single writer (edge_cache: the fused V=2 kernel)
+  // a vehicle can be an endpoint of several edges solved concurrently (generic V): they share the vehicle's edge
+  // entry -- same key, same matrix, identical bits from every writer (see the fence in inner_solve)
   double* kc = (c.kcache && valid && edge_cache) ? c.kcache + (((size_t)s * c.V + vv[me]) * 2 + 1) * PIADMM_KC_STRIDE(LPQ) : nullptr;
   InnerOut o = inner_solve<LPQ, KS, LATENCY>(p, c.ik, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow, kc);
   // z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158)
