@@ -629,8 +629,11 @@ extern "C" int piadmm_debug_read_trace(long long* host, int n) {
   return (int)cudaMemcpyFromSymbol(host, g_trace, sizeof(long long) * 4 * n);
 }
 #endif
-template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? FUSED16_MIN_CTAS : FUSED32_MIN_CTAS) k_fused_v2(const __grid_constant__ DevCtx c) {
+// FEW: the same code compiled for registers instead of occupancy (4 CTAs per SM: ~250 registers, no spills), launched
+// when the batch has at most two CTAs per SM -- config 1 is ONE scenario, i.e. one dependent chain whose spills are
+// pure latency.  Same PTX arithmetic, so results are bit-identical to the throughput build.
+template <int LPQ, bool FEW = false>
+__global__ void __launch_bounds__(CTA_THREADS, FEW ? 4 : (LPQ == 16 ? FUSED16_MIN_CTAS : FUSED32_MIN_CTAS)) k_fused_v2(const __grid_constant__ DevCtx c) {
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];
@@ -815,6 +818,8 @@ struct piadmm_handle {
   cudaEvent_t ev_count[2];
   int* d_queue;
   int fused_grid, x_grid, z_grid;
+  int sm_count;
+  bool fused_few;             // small batches use the registers-over-occupancy build of the fused kernel (PIADMM_FEW=0 disables)
   bool fused_ks;              // fused kernel variant: K^-1 rows in shared memory (k_fused_ks)
   int* d_order;               // [S] longest-first processing order learnt from the previous step
   bool use_order;             // PIADMM_LPT=0 disables the hint
@@ -1029,6 +1034,9 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     // mat-vec then saturates the shared-memory pipe: measured 0.371 ms vs 0.336 ms per step, profiles/r1_history.md)
     const char* fv = getenv("PIADMM_FUSED");
     h->fused_ks = fv && strcmp(fv, "ks") == 0;
+    h->sm_count = prop.multiProcessorCount;
+    const char* few = getenv("PIADMM_FEW");
+    h->fused_few = !(few && strcmp(few, "0") == 0);
     if (h->fused_ks) {
       if (h->lpq == 16) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_ks<16>, KS_THREADS(16), 0);
       else ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_ks<32>, KS_THREADS(32), 0);
@@ -1264,6 +1272,9 @@ static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, i
   if (h->fused_ks) {
     if (h->lpq == 16) k_fused_ks<16><<<grid, KS_THREADS(16), 0, st>>>(c);
     else k_fused_ks<32><<<grid, KS_THREADS(32), 0, st>>>(c);
+  } else if (grid <= 2 * h->sm_count && h->fused_few) {
+    if (h->lpq == 16) k_fused_v2<16, true><<<grid, CTA_THREADS, 0, st>>>(c);
+    else k_fused_v2<32, true><<<grid, CTA_THREADS, 0, st>>>(c);
   } else if (h->lpq == 16) k_fused_v2<16><<<grid, CTA_THREADS, 0, st>>>(c);
   else k_fused_v2<32><<<grid, CTA_THREADS, 0, st>>>(c);
   LAUNCHED();
