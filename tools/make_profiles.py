@@ -66,7 +66,7 @@ Files
   `r1_bench_1gpu_n30.json` — the N=30 variant (`--workload c4n30`).
 * `r1_bench_c3.json`, `r1_bench_c5.json`, `r1_bench_c5_2gpu.json` — `python bench.py --workload c3|c5` (ONE coupled scene through
   the generic-V phase kernels: 64-vehicle intersection 1.21 ms, 4096-vehicle grid 5.76 ms per coupled MPC step; c5 under
-  torchrun on 2 GPUs, vehicles sharded over NCCL: 7.84 ms).
+  torchrun on 2 GPUs, vehicles sharded over NCCL: 6.04 ms).
 * `r1_bench_reference_arm.json` — `python bench.py --impl reference --steps 20 --warmup 2` (oracle C twin, all host cores).
 * `r1_launches_bench.csv` — `ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv` of
   `python bench.py --steps 3 --warmup 3 --no-cpu-baseline` (every launch with its device time).
