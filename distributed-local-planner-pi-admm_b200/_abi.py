@@ -11,7 +11,7 @@ LIB_PATH = os.environ.get("PIADMM_LIB") or os.path.join(_HERE, "csrc", "libpiadm
 
 ABI_VERSION = 2
 DUAL_PLAIN, DUAL_PI, DUAL_PI_OLD = 0, 1, 2
-ST_VEH_MAXITER, ST_EDGE_MAXITER, ST_SLOT_OVERFLOW = 1, 2, 4
+ST_VEH_MAXITER, ST_EDGE_MAXITER, ST_SLOT_OVERFLOW, ST_OUTER_MAXITER, ST_PEER_TIMEOUT = 1, 2, 4, 8, 16
 
 _D = C.c_double
 _I = C.c_int32

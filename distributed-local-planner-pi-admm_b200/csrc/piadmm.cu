@@ -386,7 +386,7 @@ __global__ void k_res_decide(const __grid_constant__ DevCtx c) {
     else {
       if (p.dual_res_alias) c.b.aliased[s] = 1;
       if (p.curr_iter_latest) c.b.curr_iter[s] = c.i_iter + 1;
-      if (c.i_iter + 1 >= c.I) c.b.done[s] = 1;      // iteration cap reached
+      if (c.i_iter + 1 >= c.I) { c.b.done[s] = 1; c.b.status[s] |= PIADMM_ST_OUTER_MAXITER; }      // iteration cap reached
     }
     decision = conv ? 1 : 0;
   }
@@ -459,7 +459,7 @@ __global__ void k_res_all(const __grid_constant__ DevCtx c, int* cnt) {
     else {
       if (p.dual_res_alias) c.b.aliased[s] = 1;
       if (p.curr_iter_latest) c.b.curr_iter[s] = c.i_iter + 1;
-      if (c.i_iter + 1 >= c.I) { c.b.done[s] = 1; fin = true; }
+      if (c.i_iter + 1 >= c.I) { c.b.done[s] = 1; fin = true; c.b.status[s] |= PIADMM_ST_OUTER_MAXITER; }
     }
     if (cnt && !fin) atomicAdd(cnt, 1);
     decision = conv ? 1 : 0;
@@ -715,7 +715,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
     c.rho_new[s] = c.b.rho_s[s];
   }
   pair_sync<LPQ>();
-  int flag = 0, curr_iter = 1, n_outer = 0, edge_n = 0;
+  int flag = 0, curr_iter = 1, n_outer = 0, edge_n = 0, capped = 1;
   const double thr = p.thr_squared ? p.dis_thres * p.dis_thres : p.dis_thres;
   bool dist_ok = true;
   if (p.stop_dist_test) {
@@ -741,7 +741,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
     }
     const bool hit = p.always_edge || group_any<LPQ>(near, w.lane);
     edge_n = hit ? 1 : 0;
-    if (!hit && !flag) break;
+    if (!hit && !flag) { capped = 0; break; }
     flag = 1;
     double sk = 0.0, rk = 0.0;
     if (hit) {
@@ -756,7 +756,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
       if (lead) c.b.rho_s[s] = rho;
     }
     if (lead) { c.b.err_rk[(size_t)s * c.I + i_iter] = rk; c.b.err_sk[(size_t)s * c.I + i_iter] = sk; }
-    if (rk <= p.eps_pri && sk <= p.eps_dual && dist_ok) { curr_iter = i_iter + 1; break; }
+    if (rk <= p.eps_pri && sk <= p.eps_dual && dist_ok) { curr_iter = i_iter + 1; capped = 0; break; }
     if (p.dual_res_alias && lead) c.b.aliased[s] = 1;
     if (k <= N) {
       c.b.last_hat[so + k] = c.b.hat[so + k];
@@ -785,6 +785,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
     }
   }
   if (lead) {
+    if (capped) atomicOr(c.b.status + s, PIADMM_ST_OUTER_MAXITER);
     c.b.flag[s] = flag; c.b.done[s] = 1; c.b.curr_iter[s] = curr_iter; c.b.n_outer[s] = n_outer;
     c.b.edge_n[s] = edge_n;
     if (edge_n) {

@@ -1,0 +1,196 @@
+// piadmm_detect.cuh -- collision-edge detection of casadi/main.py:110-118 for generic V, as device functions shared by
+// the phase kernels (piadmm.cu) and the persistent cooperative kernel (piadmm_coop.cuh).
+//
+// The reference recomputes the dense V x V edge_mat in every outer iteration.  Here the O(V^2) work is done ONCE per
+// MPC step: every trajectory of a step starts at the same plant state and a roll-out of N steps cannot leave a disc
+// around it (reach_radius), so only pairs whose discs come within the collision distance can ever collide in this step.
+// Those pairs form the candidate bit matrix `cand` (k_cand / coop phase 0).  Per outer iteration a warp per vehicle walks
+// the vehicle's candidate row in ascending j, runs the EXACT point-by-point test of the reference on each candidate
+// (lane k = trajectory point k, eight candidates in flight) and allocates neighbour slots for the hits -- ascending
+// partner order per vehicle, which is what the reference's row-major walk over np.where(edge_mat == 1) gives every
+// vehicle.  The result is exact (the candidate set is a superset by construction), and an outer iteration costs
+// O(candidates), not O(V^2).  The round-1 path (bounding boxes + full pair test every iteration, `hits` matrix) is kept
+// behind PIADMM_DETECT=matrix_warp|matrix_thread as the A/B baseline; both feed the same slot / count / emit functions.
+#pragma once
+#include "piadmm_dev.cuh"
+
+// |u| bound assumed by the reach radius of the LINEARISED roll-out (steering is boxed to pi/6 = 0.52 up to the inner
+// solver's tolerance and the 4-decimal rounding; 2 rad is far outside anything a converged QP returns)
+#define PIADMM_U_BOUND 2.0
+
+// every point of every roll-out of a vehicle with speed v lies within this distance of its start
+__host__ __device__ inline double reach_radius(const piadmm_params& p, int N, double v) {
+  const double s = v * N * p.dt;              // non-linear roll-out (casadi/PI_ADMM_class.py:95-101): N steps of length v*dt
+  if (p.pos_nonlinear) return s * (1.0 + 1e-9) + 1e-9;
+  // linearised roll-out (:61-65): k*dt*v along the heading, g*(M u)_k across it, |(M u)_k| <= U k(k-1)/2
+  const double g = v * v * p.dt * p.dt / p.L, lat = g * PIADMM_U_BOUND * 0.5 * N * (N - 1);
+  return sqrt(s * s + lat * lat) * (1.0 + 1e-9) + 1e-9;
+}
+
+// disc[s,i] = (x0, y0, reach, 0) of vehicle (s,i); stored in DevCtx::bbox (unused by the candidate path)
+__device__ __forceinline__ void dev_disc_vehicle(const DevCtx& c, long a) {
+  const double* xt = c.b.xt + a * 3;
+  reinterpret_cast<double4*>(c.bbox)[a] = make_double4(xt[0], xt[1], reach_radius(c.p, c.N, c.b.spd[a]), 0.0);
+}
+
+// word jb of row i of the (symmetric) candidate matrix of scenario s
+__device__ __forceinline__ uint32_t dev_cand_word(const DevCtx& c, int s, int i, int jb) {
+  const double4* disc = reinterpret_cast<const double4*>(c.bbox) + (size_t)s * c.V;
+  const double4 di = disc[i];
+  const double thr_d = c.p.thr_squared ? c.p.dis_thres : sqrt(c.p.dis_thres);   // the distance whose square is the threshold
+  const int j0 = jb * 32, j1 = min(j0 + 32, c.V);
+  uint32_t m = 0;
+  for (int j = j0; j < j1; j++) {
+    if (j == i) continue;
+    bool near = c.p.always_edge != 0;
+    if (!near) {
+      const double4 dj = disc[j];
+      const double dx = di.x - dj.x, dy = di.y - dj.y, rr = (di.z + dj.z + thr_d) * (1.0 + 1e-9);
+      near = dx * dx + dy * dy < rr * rr;
+    }
+    if (near) m |= 1u << (j - j0);
+  }
+  return m;
+}
+
+// One warp, one vehicle: walk row i of `cand` (EXACT: exact test of every candidate) or of `hits` (already exact) in
+// ascending j and find / allocate the neighbour slot of every colliding partner; slot_hit[s,i,d] = 1 for the slots whose
+// partner collides in THIS outer iteration.
+template <bool EXACT>
+__device__ __forceinline__ void dev_slots_vehicle(const DevCtx& c, int s, int i, int lane) {
+  const int N = c.N, np1 = N + 1, words = (c.V + 31) / 32;
+  const size_t a = (size_t)s * c.V + i;
+  int32_t* nb = c.b.nbr + a * c.D;
+  uint8_t* sh = c.slot_hit + a * c.D;
+  for (int d = lane; d < c.D; d += 32) sh[d] = 0;
+  __syncwarp();
+  const uint32_t* row = (EXACT ? c.cand : c.hits) + a * words;
+  const bool test = EXACT && !c.p.always_edge;
+  const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
+  const int k = lane <= N ? lane : 0;                        // padded lanes repeat point 0
+  double xi = 0.0, yi = 0.0;
+  if (test) { const double* pi = c.b.pos + a * 2 * np1; xi = pi[k]; yi = pi[np1 + k]; }
+  bool overflow = false;
+  for (int w0 = 0; w0 < words; w0 += 32) {
+    const uint32_t mine = w0 + lane < words ? row[w0 + lane] : 0u;
+    unsigned nz = __ballot_sync(PIADMM_FULL, mine != 0u);
+    while (nz) {
+      const int src = __ffs(nz) - 1;
+      nz &= nz - 1;
+      uint32_t m = __shfl_sync(PIADMM_FULL, mine, src);
+      const int jbase = (w0 + src) * 32;
+      if (test) {                       // exact tests, eight candidates in flight (16 independent loads per lane)
+        uint32_t rem = m, hits = 0;
+        while (rem) {
+          int jj[8];
+          double xs[8], ys[8];
+#pragma unroll
+          for (int q = 0; q < 8; q++) {
+            jj[q] = -1;
+            if (rem) { jj[q] = __ffs(rem) - 1; rem &= rem - 1; }
+          }
+#pragma unroll
+          for (int q = 0; q < 8; q++) {
+            xs[q] = 0.0; ys[q] = 0.0;
+            if (jj[q] >= 0) {
+              const double* pj = c.b.pos + ((size_t)s * c.V + jbase + jj[q]) * 2 * np1;
+              xs[q] = pj[k]; ys[q] = pj[np1 + k];
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 8; q++) {
+            if (jj[q] >= 0) {           // warp uniform
+              const double dx = xi - xs[q], dy = yi - ys[q];
+              if (__any_sync(PIADMM_FULL, dx * dx + dy * dy < thr)) hits |= 1u << jj[q];
+            }
+          }
+        }
+        m = hits;
+      }
+      if (lane == 0) {
+        while (m) {
+          const int j = jbase + __ffs(m) - 1;
+          m &= m - 1;
+          int slot = -1;
+          for (int d = 0; d < c.D; d++) if (nb[d] == j) { slot = d; break; }
+          if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = j; slot = d; break; }
+          if (slot < 0) overflow = true; else sh[slot] = 1;
+        }
+      }
+    }
+  }
+  if (lane == 0 && overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
+}
+
+// slot of vehicle i in the table of vehicle j, or -1
+__device__ __forceinline__ int dev_far_slot(const DevCtx& c, int s, int j, int i) {
+  const int32_t* nbj = c.b.nbr + ((size_t)s * c.V + j) * c.D;
+  int dj = -1;
+  for (int d = 0; d < c.D; d++) if (nbj[d] == i) dj = d;
+  return dj;
+}
+
+// number of edges (i, j > i) of this outer iteration: the partner collides now and BOTH tables hold a slot (a pair
+// with a full table on either side is dropped, status already set -- as find_or_alloc_slot in the oracle)
+__device__ __forceinline__ int dev_count_vehicle(const DevCtx& c, int s, int i) {
+  const size_t a = (size_t)s * c.V + i;
+  const int32_t* nb = c.b.nbr + a * c.D;
+  const uint8_t* sh = c.slot_hit + a * c.D;
+  int cnt = 0;
+  for (int d = 0; d < c.D; d++) {
+    const int j = nb[d];
+    if (j > i && sh[d] && dev_far_slot(c, s, j, i) >= 0) cnt++;
+  }
+  return cnt;
+}
+
+// emit the `cnt` edges of vehicle i at edge_ij / edge_slot [n0, n0 + cnt), ascending j (the order of
+// np.where(edge_mat == 1), casadi/main.py:121)
+__device__ __forceinline__ void dev_emit_vehicle(const DevCtx& c, int s, int i, int n0, int cnt) {
+  const size_t a = (size_t)s * c.V + i;
+  const int32_t* nb = c.b.nbr + a * c.D;
+  const uint8_t* sh = c.slot_hit + a * c.D;
+  int n = n0, lastj = i, emitted = 0;
+  while (emitted < cnt) {
+    int j = 0x7fffffff, di = -1;
+    for (int d = 0; d < c.D; d++) {
+      const int cand = nb[d];
+      if (sh[d] && cand > lastj && cand < j) { j = cand; di = d; }
+    }
+    if (di < 0) break;
+    lastj = j;
+    const int dj = dev_far_slot(c, s, j, i);
+    if (dj < 0) continue;
+    int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + n) * 2;
+    int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + n) * 2;
+    eij[0] = i; eij[1] = j; esl[0] = di; esl[1] = dj;
+    n++; emitted++;
+  }
+}
+
+// end of the detection of scenario s with n edges: casadi/main.py:115-118 ("no collision if no edge links": break)
+__device__ __forceinline__ void dev_edges_done(const DevCtx& c, int s, int n) {
+  c.b.n_outer[s] += 1;
+  c.b.edge_n[s] = n;
+  if (n == 0 && c.b.flag[s] == 0) c.b.done[s] = 1;
+  else c.b.flag[s] = 1;
+}
+
+// exclusive scan over the threads of a CTA (blockDim.x a multiple of 32, <= 1024); wsum: 32 ints of shared memory.
+// Returns the exclusive prefix of v; *total = sum over the CTA.
+__device__ __forceinline__ int cta_excl_scan(int v, int* wsum, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  int inc = v;
+  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(PIADMM_FULL, inc, o); if (lane >= o) inc += t; }
+  __syncthreads();                       // wsum may still be read from a previous call
+  if (lane == 31) wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int w = lane < nwarps ? wsum[lane] : 0;
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(PIADMM_FULL, w, o); if (lane >= o) w += t; }
+    wsum[lane] = w;
+  }
+  __syncthreads();
+  *total = wsum[nwarps - 1];
+  return (warp ? wsum[warp - 1] : 0) + inc - v;
+}

@@ -80,19 +80,33 @@ def c3_intersection(V=64, N=30, seed=64, dt=0.1, r0=12.0, gap=6.0):
     return xt, spd, refwin
 
 
-def c5_grid(lanes=64, per_lane=32, N=30, seed=4096, dt=0.1, lane_gap=20.0):
+def c5_grid(lanes=64, per_lane=32, N=30, seed=4096, dt=0.1, lane_gap=20.0, clear=3.0):
     """Config 5: `lanes` east-bound lanes (y = gap*r) and `lanes` south-bound lanes (x = gap*c),
-    `per_lane` vehicles each, along-lane spacing 20 + U(-3,3)."""
+    `per_lane` vehicles each, along-lane spacing 20 + U(-3,3).
+
+    clear > 0 (default): rejection rule -- a spacing draw is repeated while it would START the vehicle within `clear`
+    metres (along its lane) of a crossing point.  Without it (clear=0, the round-1 generator) 15 east/south pairs start
+    already inside dis_thres (minimum 0.84 m); the first two trajectory points do not depend on the steering sequence,
+    so no plan can repair those pairs and their hinge terms stay active for ever.  With clear=3 every pair is at
+    least 3*sqrt(2) = 4.2 m apart at t=0; the conflicts that remain are the ones steering can resolve."""
     rng = np.random.default_rng(seed)
     V = 2 * lanes * per_lane
     xt = np.zeros((1, V, 3)); spd = np.zeros((1, V)); refwin = np.zeros((1, V, 2, N + 1))
     speeds = (4.0, 6.0, 8.0)
     k = np.arange(N + 1)
+
+    def advance(pos, sign):
+        while True:
+            nxt = pos + sign * (20.0 + rng.uniform(-3, 3))
+            c = round(nxt / lane_gap)
+            if clear <= 0 or not (0 <= c < lanes) or abs(nxt - lane_gap * c) >= clear:
+                return nxt
+
     i = 0
     for r in range(lanes):                       # east-bound
         pos = -10.0
         for q in range(per_lane):
-            pos += 20.0 + rng.uniform(-3, 3)
+            pos = advance(pos, +1.0)
             v = speeds[(r + q) % 3]
             xt[0, i] = (pos, lane_gap * r, 0.0); spd[0, i] = v
             refwin[0, i, 0] = pos + k * dt * v; refwin[0, i, 1] = lane_gap * r
@@ -100,7 +114,7 @@ def c5_grid(lanes=64, per_lane=32, N=30, seed=4096, dt=0.1, lane_gap=20.0):
     for c in range(lanes):                       # south-bound
         pos = lane_gap * lanes + 10.0
         for q in range(per_lane):
-            pos -= 20.0 + rng.uniform(-3, 3)
+            pos = advance(pos, -1.0)
             v = speeds[(c + q) % 3]
             xt[0, i] = (lane_gap * c, pos, -np.pi / 2); spd[0, i] = v
             refwin[0, i, 0] = lane_gap * c; refwin[0, i, 1] = pos - k * dt * v

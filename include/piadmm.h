@@ -54,7 +54,10 @@ enum { PIADMM_DUAL_PLAIN = 0, PIADMM_DUAL_PI = 1, PIADMM_DUAL_PI_OLD = 2 };
 enum {
   PIADMM_ST_VEH_MAXITER = 1,   /* a vehicle QP hit in_max_iter (reference: CasADi raises) */
   PIADMM_ST_EDGE_MAXITER = 2,  /* an edge problem hit in_max_iter (reference: error_on_fail=False) */
-  PIADMM_ST_SLOT_OVERFLOW = 4  /* a vehicle needed more than D neighbour slots */
+  PIADMM_ST_SLOT_OVERFLOW = 4, /* a vehicle needed more than D neighbour slots (the pair is dropped) */
+  PIADMM_ST_OUTER_MAXITER = 8, /* the outer loop ended at iter_num without passing the stop test (casadi/main.py:78
+                                  just falls out of its for loop; curr_iter then keeps its last value) */
+  PIADMM_ST_PEER_TIMEOUT = 16  /* multi-GPU persistent kernel: a peer did not arrive at a barrier in time */
 };
 
 typedef struct piadmm_params {

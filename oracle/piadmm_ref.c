@@ -22,10 +22,14 @@
  */
 #include <math.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #ifdef _OPENMP
 #include <omp.h>
+static int omp_thread_id(void) { return omp_get_thread_num(); }
+#else
+static int omp_thread_id(void) { return 0; }
 #endif
 #include "../include/piadmm.h"
 
@@ -416,68 +420,109 @@ static void begin_scenario(const piadmm_params* p, const piadmm_buffers* b, int 
   (void)E;
 }
 
-static void x_update_scenario(const piadmm_params* p, const consts_t* c, const piadmm_buffers* b, int s, int V,
-                              int D, half_t* h) {
+static void x_update_vehicle(const piadmm_params* p, const consts_t* c, const piadmm_buffers* b, int s, int i, int V,
+                             int D, half_t* h, int* it_out, int* st_out) {
   const int N = p->num_ho;
   const double rho = b->rho_s[s];
-  for (int i = 0; i < V; i++) {
-    const double* xt = b->xt + ((size_t)s * V + i) * 3;
-    const double v = b->spd[(size_t)s * V + i];
-    const double* rw = b->refwin + POS_OFF(s, i);
-    const double sn = sin(xt[2]), cs = cos(xt[2]), g = v * v * p->dt * p->dt / p->L;
-    double tx[NMAX + 1], ty[NMAX + 1], vec[NMAX + 1];
-    int deg = 0;
-    for (int k = 0; k <= N; k++) { tx[k] = p->Pnorm * rw[k]; ty[k] = p->Pnorm * rw[NP1 + k]; }
-    for (int d = 0; d < D; d++) {
-      if (b->nbr[((size_t)s * V + i) * D + d] < 0) continue;
-      deg++;
-      const double* hat = b->hat + SLOT_OFF(s, i, d);
-      const double* du = b->dual + SLOT_OFF(s, i, d);
-      for (int k = 0; k <= N; k++) {
-        tx[k] += 0.5 * rho * (hat[k] - du[k]);
-        ty[k] += 0.5 * rho * (hat[NP1 + k] - du[NP1 + k]);
-      }
+  const double* xt = b->xt + ((size_t)s * V + i) * 3;
+  const double v = b->spd[(size_t)s * V + i];
+  const double* rw = b->refwin + POS_OFF(s, i);
+  const double sn = sin(xt[2]), cs = cos(xt[2]), g = v * v * p->dt * p->dt / p->L;
+  double tx[NMAX + 1], ty[NMAX + 1], vec[NMAX + 1];
+  int deg = 0;
+  for (int k = 0; k <= N; k++) { tx[k] = p->Pnorm * rw[k]; ty[k] = p->Pnorm * rw[NP1 + k]; }
+  for (int d = 0; d < D; d++) {
+    if (b->nbr[((size_t)s * V + i) * D + d] < 0) continue;
+    deg++;
+    const double* hat = b->hat + SLOT_OFF(s, i, d);
+    const double* du = b->dual + SLOT_OFF(s, i, d);
+    for (int k = 0; k <= N; k++) {
+      tx[k] += 0.5 * rho * (hat[k] - du[k]);
+      ty[k] += 0.5 * rho * (hat[NP1 + k] - du[NP1 + k]);
     }
-    const double w = p->Pnorm + 0.5 * rho * deg;
-    const double e0 = -sn * xt[0] + cs * xt[1];
-    for (int k = 0; k <= N; k++) vec[k] = w * e0 + sn * tx[k] - cs * ty[k];
-    apply_Mt(N, vec, h->q);
-    for (int k = 0; k < N; k++) h->q[k] *= 2.0 * g;
-    h->pI = 2.0 * p->Pcost; h->p2 = 2.0; h->pW = 2.0 * w * g * g;
-    int st;
-    int it = solve_vehicle(p, c, h, &st);
-    b->veh_inner[s] += it; b->n_veh_solves[s] += 1;
-    if (st) b->status[s] |= PIADMM_ST_VEH_MAXITER;
-    double* u = b->u + ((size_t)s * V + i) * N;
-    for (int k = 0; k < N; k++) u[k] = round_dec(h->x[k], p->round_u);
-    double* pos = b->pos + POS_OFF(s, i);
-    if (p->pos_nonlinear) rollout_nonlinear(p, N, xt, v, u, pos, pos + NP1, NULL);
-    else rollout_linear(p, N, xt, v, u, pos, pos + NP1);
   }
+  const double w = p->Pnorm + 0.5 * rho * deg;
+  const double e0 = -sn * xt[0] + cs * xt[1];
+  for (int k = 0; k <= N; k++) vec[k] = w * e0 + sn * tx[k] - cs * ty[k];
+  apply_Mt(N, vec, h->q);
+  for (int k = 0; k < N; k++) h->q[k] *= 2.0 * g;
+  h->pI = 2.0 * p->Pcost; h->p2 = 2.0; h->pW = 2.0 * w * g * g;
+  *it_out = solve_vehicle(p, c, h, st_out);
+  double* u = b->u + ((size_t)s * V + i) * N;
+  for (int k = 0; k < N; k++) u[k] = round_dec(h->x[k], p->round_u);
+  double* pos = b->pos + POS_OFF(s, i);
+  if (p->pos_nonlinear) rollout_nonlinear(p, N, xt, v, u, pos, pos + NP1, NULL);
+  else rollout_linear(p, N, xt, v, u, pos, pos + NP1);
 }
 
-static void detect_scenario(const piadmm_params* p, const piadmm_buffers* b, int s, int V, int D, int E) {
+/* `pool` = one half_t pair per OpenMP thread; inner != 0: the vehicles of this ONE scenario are spread over the
+ * threads (coupled scenes, S < threads), else the caller already runs scenarios in parallel */
+static void x_update_scenario(const piadmm_params* p, const consts_t* c, const piadmm_buffers* b, int s, int V,
+                              int D, half_t** pool, int inner) {
+  long tot_it = 0; int any_st = 0, max_it = 0;
+  if (inner) {
+#pragma omp parallel for schedule(dynamic, 8) reduction(+ : tot_it) reduction(| : any_st) reduction(max : max_it)
+    for (int i = 0; i < V; i++) {
+      int it, st;
+      x_update_vehicle(p, c, b, s, i, V, D, pool[2 * omp_thread_id()], &it, &st);
+      tot_it += it; any_st |= st;
+      if (it > max_it) max_it = it;
+    }
+  } else {
+    for (int i = 0; i < V; i++) {
+      int it, st;
+      x_update_vehicle(p, c, b, s, i, V, D, pool[2 * omp_thread_id()], &it, &st);
+      tot_it += it; any_st |= st;
+      if (it > max_it) max_it = it;
+    }
+  }
+  if (getenv("PIADMM_REF_DEBUG"))
+    fprintf(stderr, "[ref] scenario %d outer %d: %d vehicle QPs, inner iterations sum %ld max %d\n", s, (int)b->n_outer[s], V, tot_it, max_it);
+  b->veh_inner[s] += tot_it; b->n_veh_solves[s] += V;
+  if (any_st) b->status[s] |= PIADMM_ST_VEH_MAXITER;
+}
+
+/* casadi/main.py:110-118.  The pair test fills a V x V bitmap (in parallel over rows when `inner`), the slot allocation
+ * then walks it in row-major order = the order of np.where(edge_mat == 1). */
+static void detect_scenario(const piadmm_params* p, const piadmm_buffers* b, int s, int V, int D, int E,
+                            uint8_t* hitmap, int inner) {
   const int N = p->num_ho;
   const double thr = p->thr_squared ? p->dis_thres * p->dis_thres : p->dis_thres;
-  int n = 0;
-  for (int i = 0; i < V; i++)
+  const size_t rowb = ((size_t)V + 7) / 8;
+#pragma omp parallel for schedule(dynamic, 16) if (inner)
+  for (int i = 0; i < V; i++) {
+    uint8_t* row = hitmap + (size_t)i * rowb;
+    memset(row, 0, rowb);
+    const double* pi = b->pos + POS_OFF(s, i);
     for (int j = i + 1; j < V; j++) {
-      const double* pi = b->pos + POS_OFF(s, i);
       const double* pj = b->pos + POS_OFF(s, j);
       int hit = p->always_edge;
       for (int k = 0; k <= N && !hit; k++) {
         double dx = pi[k] - pj[k], dy = pi[NP1 + k] - pj[NP1 + k];
         if (dx * dx + dy * dy < thr) hit = 1;
       }
-      if (!hit) continue;
-      int32_t* ni = b->nbr + ((size_t)s * V + i) * D;
-      int32_t* nj = b->nbr + ((size_t)s * V + j) * D;
-      int di = find_or_alloc_slot(ni, D, j), dj = find_or_alloc_slot(nj, D, i);
-      if (di < 0 || dj < 0 || n >= E) { b->status[s] |= PIADMM_ST_SLOT_OVERFLOW; continue; }
-      b->edge_ij[((size_t)s * E + n) * 2 + 0] = i; b->edge_ij[((size_t)s * E + n) * 2 + 1] = j;
-      b->edge_slot[((size_t)s * E + n) * 2 + 0] = di; b->edge_slot[((size_t)s * E + n) * 2 + 1] = dj;
-      n++;
+      if (hit) row[j >> 3] |= (uint8_t)(1u << (j & 7));
     }
+  }
+  int n = 0;
+  for (int i = 0; i < V; i++) {
+    const uint8_t* row = hitmap + (size_t)i * rowb;
+    for (size_t w = (size_t)(i + 1) >> 3; w < rowb; w++) {
+      uint8_t m = row[w];
+      while (m) {
+        const int bit = __builtin_ctz(m);
+        m &= (uint8_t)(m - 1);
+        const int j = (int)(w * 8) + bit;
+        int32_t* ni = b->nbr + ((size_t)s * V + i) * D;
+        int32_t* nj = b->nbr + ((size_t)s * V + j) * D;
+        int di = find_or_alloc_slot(ni, D, j), dj = find_or_alloc_slot(nj, D, i);
+        if (di < 0 || dj < 0 || n >= E) { b->status[s] |= PIADMM_ST_SLOT_OVERFLOW; continue; }
+        b->edge_ij[((size_t)s * E + n) * 2 + 0] = i; b->edge_ij[((size_t)s * E + n) * 2 + 1] = j;
+        b->edge_slot[((size_t)s * E + n) * 2 + 0] = di; b->edge_slot[((size_t)s * E + n) * 2 + 1] = dj;
+        n++;
+      }
+    }
+  }
   b->edge_n[s] = n;
 }
 
@@ -508,90 +553,108 @@ static void dual_side(const piadmm_params* p, int N, double rho, double kP, doub
   }
 }
 
-static void z_update_scenario(const piadmm_params* p, const consts_t* c, const piadmm_buffers* b, int s, int V,
-                              int D, int E, half_t* h0, half_t* h1) {
+/* edge problem e of scenario s + its dual / PI update (edges of one outer iteration are independent of each other:
+ * every directed slot belongs to exactly one edge, all edges see the same penalty) */
+static void z_update_edge(const piadmm_params* p, const consts_t* c, const piadmm_buffers* b, int s, int e, int V,
+                          int D, int E, half_t* h0, half_t* h1, int* it_out, int* st_out, double* rho_next) {
   const int N = p->num_ho;
-  const int n = b->edge_n[s];
   half_t* hh[2] = {h0, h1};
-  double rho_next = b->rho_s[s];
-  for (int e = 0; e < n; e++) {
-    const double rho = b->rho_s[s];   /* all edges of one outer iteration see the same penalty */
-    int vv[2] = {b->edge_ij[((size_t)s * E + e) * 2], b->edge_ij[((size_t)s * E + e) * 2 + 1]};
-    int sl[2] = {b->edge_slot[((size_t)s * E + e) * 2], b->edge_slot[((size_t)s * E + e) * 2 + 1]};
-    double seed[2][2], a[2], base[2][NMAX + 1], cvec[NMAX];
-    const double* xt[2]; double spd[2];
-    for (int r = 0; r < 2; r++) {
-      xt[r] = b->xt + ((size_t)s * V + vv[r]) * 3;
-      spd[r] = b->spd[(size_t)s * V + vv[r]];
-      seed[r][0] = round_dec(xt[r][0] + p->dt * spd[r] * cos(xt[r][2]), 4);   /* casadi/main.py:48-49 */
-      seed[r][1] = round_dec(xt[r][1] + p->dt * spd[r] * sin(xt[r][2]), 4);
-    }
-    const double lx = seed[1][0] - seed[0][0], ly = seed[1][1] - seed[0][1];
-    for (int r = 0; r < 2; r++) {
-      const double sn = sin(xt[r][2]), cs = cos(xt[r][2]), v = spd[r], g = v * v * p->dt * p->dt / p->L;
-      const double* pos = b->pos + POS_OFF(s, vv[r]);
-      const double* du = b->dual + SLOT_OFF(s, vv[r], sl[r]);
-      double vec[NMAX + 1];
-      const double sign = r == 0 ? -1.0 : 1.0;
-      for (int k = 0; k <= N; k++) {
-        const double xb = xt[r][0] + k * p->dt * v * cs, yb = xt[r][1] + k * p->dt * v * sn;
-        const double ex = pos[k] + du[k] - xb, ey = pos[NP1 + k] + du[NP1 + k] - yb;
-        vec[k] = sn * ex - cs * ey;
-        base[r][k] = sign * 2.0 * (lx * xb + ly * yb);
-      }
-      apply_Mt(N, vec, hh[r]->q);
-      for (int k = 0; k < N; k++) hh[r]->q[k] *= rho * g;
-      hh[r]->pI = 2.0 * p->Pcost; hh[r]->p2 = 0.0; hh[r]->pW = rho * g * g;
-      a[r] = sign * 2.0 * g * (-lx * sn + ly * cs);
-    }
-    for (int k = 1; k <= N; k++)
-      cvec[k - 1] = p->dis_thres * p->dis_thres - (base[0][k] + base[1][k] - (lx * lx + ly * ly));
-    int st;
-    int it = solve_edge(p, c, h0, h1, a[0], a[1], cvec, &st);
-    b->edge_inner[s] += it; b->n_edge_solves[s] += 1;
-    if (st) b->status[s] |= PIADMM_ST_EDGE_MAXITER;
-    /* z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158) */
-    double uh[2][NMAX];
-    for (int r = 0; r < 2; r++) {
-      for (int k = 0; k < N; k++) uh[r][k] = round_dec(hh[r]->x[k], p->round_edge);
-      double* hat = b->hat + SLOT_OFF(s, vv[r], sl[r]);
-      rollout_nonlinear(p, N, xt[r], spd[r], uh[r], hat, hat + NP1, NULL);
-      if (p->dual_res_alias && b->aliased[s])
-        memcpy(b->last_hat + SLOT_OFF(s, vv[r], sl[r]), hat, sizeof(double) * 2 * NP1);
-    }
-    /* gains */
-    double kP = 0.0, kI = p->kI < 0.0 ? rho : p->kI, rho_dual = rho;
-    if (p->dual_mode == PIADMM_DUAL_PI) {
-      const double* p0 = b->pos + POS_OFF(s, vv[0]);
-      const double* p1 = b->pos + POS_OFF(s, vv[1]);
-      double dmin = INFINITY;
-      for (int k = 0; k <= N; k++) {
-        double dx = p0[k] - p1[k], dy = p0[NP1 + k] - p1[NP1 + k];
-        double d = sqrt(dx * dx + dy * dy);
-        if (d < dmin) dmin = d;
-      }
-      kP = p->theta1 - p->theta2 / (1.0 + exp(-dmin));
-    } else if (p->dual_mode == PIADMM_DUAL_PI_OLD) {
-      double px[2][NMAX + 1], py[2][NMAX + 1];
-      for (int r = 0; r < 2; r++)
-        rollout_nonlinear(p, N, xt[r], spd[r], b->u + ((size_t)s * V + vv[r]) * N, px[r], py[r], NULL);
-      double dmin = INFINITY;
-      for (int k = 0; k <= N; k++) {
-        double dx = px[0][k] - px[1][k], dy = py[0][k] - py[1][k];
-        double d = sqrt(dx * dx + dy * dy);
-        if (d < dmin) dmin = d;
-      }
-      kP = p->KP_num / dmin; if (kP > p->KP_max) kP = p->KP_max;
-      double rn = p->rho_num / dmin; if (rn > p->rho_max) rn = p->rho_max; if (rn < p->rho_min) rn = p->rho_min;
-      rho_dual = rn;      /* old main.py:137: rho is updated before the dual update */
-      rho_next = rn;
-    }
-    for (int r = 0; r < 2; r++) {
-      size_t o = SLOT_OFF(s, vv[r], sl[r]);
-      dual_side(p, N, rho_dual, kP, kI, b->pos + POS_OFF(s, vv[r]), b->hat + o, b->dual + o, b->integ + o,
-                b->diff + o);
-    }
+  const double rho = b->rho_s[s];   /* all edges of one outer iteration see the same penalty */
+  int vv[2] = {b->edge_ij[((size_t)s * E + e) * 2], b->edge_ij[((size_t)s * E + e) * 2 + 1]};
+  int sl[2] = {b->edge_slot[((size_t)s * E + e) * 2], b->edge_slot[((size_t)s * E + e) * 2 + 1]};
+  double seed[2][2], a[2], base[2][NMAX + 1], cvec[NMAX];
+  const double* xt[2]; double spd[2];
+  for (int r = 0; r < 2; r++) {
+    xt[r] = b->xt + ((size_t)s * V + vv[r]) * 3;
+    spd[r] = b->spd[(size_t)s * V + vv[r]];
+    seed[r][0] = round_dec(xt[r][0] + p->dt * spd[r] * cos(xt[r][2]), 4);   /* casadi/main.py:48-49 */
+    seed[r][1] = round_dec(xt[r][1] + p->dt * spd[r] * sin(xt[r][2]), 4);
   }
+  const double lx = seed[1][0] - seed[0][0], ly = seed[1][1] - seed[0][1];
+  for (int r = 0; r < 2; r++) {
+    const double sn = sin(xt[r][2]), cs = cos(xt[r][2]), v = spd[r], g = v * v * p->dt * p->dt / p->L;
+    const double* pos = b->pos + POS_OFF(s, vv[r]);
+    const double* du = b->dual + SLOT_OFF(s, vv[r], sl[r]);
+    double vec[NMAX + 1];
+    const double sign = r == 0 ? -1.0 : 1.0;
+    for (int k = 0; k <= N; k++) {
+      const double xb = xt[r][0] + k * p->dt * v * cs, yb = xt[r][1] + k * p->dt * v * sn;
+      const double ex = pos[k] + du[k] - xb, ey = pos[NP1 + k] + du[NP1 + k] - yb;
+      vec[k] = sn * ex - cs * ey;
+      base[r][k] = sign * 2.0 * (lx * xb + ly * yb);
+    }
+    apply_Mt(N, vec, hh[r]->q);
+    for (int k = 0; k < N; k++) hh[r]->q[k] *= rho * g;
+    hh[r]->pI = 2.0 * p->Pcost; hh[r]->p2 = 0.0; hh[r]->pW = rho * g * g;
+    a[r] = sign * 2.0 * g * (-lx * sn + ly * cs);
+  }
+  for (int k = 1; k <= N; k++)
+    cvec[k - 1] = p->dis_thres * p->dis_thres - (base[0][k] + base[1][k] - (lx * lx + ly * ly));
+  int st;
+  *it_out = solve_edge(p, c, h0, h1, a[0], a[1], cvec, &st);
+  *st_out = st;
+  /* z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158) */
+  double uh[2][NMAX];
+  for (int r = 0; r < 2; r++) {
+    for (int k = 0; k < N; k++) uh[r][k] = round_dec(hh[r]->x[k], p->round_edge);
+    double* hat = b->hat + SLOT_OFF(s, vv[r], sl[r]);
+    rollout_nonlinear(p, N, xt[r], spd[r], uh[r], hat, hat + NP1, NULL);
+    if (p->dual_res_alias && b->aliased[s])
+      memcpy(b->last_hat + SLOT_OFF(s, vv[r], sl[r]), hat, sizeof(double) * 2 * NP1);
+  }
+  /* gains */
+  double kP = 0.0, kI = p->kI < 0.0 ? rho : p->kI, rho_dual = rho;
+  if (p->dual_mode == PIADMM_DUAL_PI) {
+    const double* p0 = b->pos + POS_OFF(s, vv[0]);
+    const double* p1 = b->pos + POS_OFF(s, vv[1]);
+    double dmin = INFINITY;
+    for (int k = 0; k <= N; k++) {
+      double dx = p0[k] - p1[k], dy = p0[NP1 + k] - p1[NP1 + k];
+      double d = sqrt(dx * dx + dy * dy);
+      if (d < dmin) dmin = d;
+    }
+    kP = p->theta1 - p->theta2 / (1.0 + exp(-dmin));
+  } else if (p->dual_mode == PIADMM_DUAL_PI_OLD) {
+    double px[2][NMAX + 1], py[2][NMAX + 1];
+    for (int r = 0; r < 2; r++)
+      rollout_nonlinear(p, N, xt[r], spd[r], b->u + ((size_t)s * V + vv[r]) * N, px[r], py[r], NULL);
+    double dmin = INFINITY;
+    for (int k = 0; k <= N; k++) {
+      double dx = px[0][k] - px[1][k], dy = py[0][k] - py[1][k];
+      double d = sqrt(dx * dx + dy * dy);
+      if (d < dmin) dmin = d;
+    }
+    kP = p->KP_num / dmin; if (kP > p->KP_max) kP = p->KP_max;
+    double rn = p->rho_num / dmin; if (rn > p->rho_max) rn = p->rho_max; if (rn < p->rho_min) rn = p->rho_min;
+    rho_dual = rn;      /* old main.py:137: rho is updated before the dual update */
+    *rho_next = rn;
+  }
+  for (int r = 0; r < 2; r++) {
+    size_t o = SLOT_OFF(s, vv[r], sl[r]);
+    dual_side(p, N, rho_dual, kP, kI, b->pos + POS_OFF(s, vv[r]), b->hat + o, b->dual + o, b->integ + o,
+              b->diff + o);
+  }
+}
+
+static void z_update_scenario(const piadmm_params* p, const consts_t* c, const piadmm_buffers* b, int s, int V,
+                              int D, int E, half_t** pool, int inner) {
+  const int n = b->edge_n[s];
+  double rho_next = b->rho_s[s];
+  long tot_it = 0; int any_st = 0, max_it = 0;
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : tot_it) reduction(| : any_st) reduction(max : max_it) if (inner)
+  for (int e = 0; e < n; e++) {
+    int it, st;
+    double rn = 0.0;
+    half_t** hp = pool + 2 * omp_thread_id();
+    z_update_edge(p, c, b, s, e, V, D, E, hp[0], hp[1], &it, &st, &rn);
+    tot_it += it; any_st |= st;
+    if (it > max_it) max_it = it;
+    if (e == n - 1 && p->dual_mode == PIADMM_DUAL_PI_OLD) rho_next = rn;   /* old main.py:137: the last edge's rho stays */
+  }
+  if (getenv("PIADMM_REF_DEBUG"))
+    fprintf(stderr, "[ref] scenario %d outer %d: %d edges, inner iterations sum %ld max %d\n", s, (int)b->n_outer[s], n, tot_it, max_it);
+  b->edge_inner[s] += tot_it; b->n_edge_solves[s] += n;
+  if (any_st) b->status[s] |= PIADMM_ST_EDGE_MAXITER;
   b->rho_s[s] = rho_next;
 }
 
@@ -664,38 +727,45 @@ int piadmm_ref_max_threads(void) {
 }
 
 /* One MPC step for S scenarios: begin_step + outer loop + plant step.  All pointers in *b are HOST
- * pointers.  nthreads <= 0 -> OpenMP default. */
+ * pointers.  nthreads <= 0 -> OpenMP default.  Batches (S >= threads) run scenarios in parallel; coupled scenes
+ * (S < threads) run the vehicles / pair-test rows / edges of one scenario in parallel.  Results do not depend on the
+ * thread count (no floating-point reduction crosses threads). */
 int piadmm_ref_step(const piadmm_params* p, const piadmm_buffers* b, int S, int V, int D, int nthreads) {
   if (!p || !b || p->num_ho < 3 || p->num_ho > NMAX || V < 1 || D < 1) return PIADMM_E_ARG;
   if (p->al_all && D < V - 1) return PIADMM_E_ARG;
   const int E = piadmm_ref_max_edges(V, D);
   consts_t* c = (consts_t*)malloc(sizeof(consts_t));
   build_consts(c, p->num_ho);
+  int nt = 1;
 #ifdef _OPENMP
   if (nthreads > 0) omp_set_num_threads(nthreads);
+  nt = omp_get_max_threads();
 #endif
-#pragma omp parallel
-  {
-    half_t* h0 = (half_t*)malloc(sizeof(half_t));
-    half_t* h1 = (half_t*)malloc(sizeof(half_t));
-#pragma omp for schedule(dynamic, 4)
-    for (int s = 0; s < S; s++) {
-      begin_scenario(p, b, s, V, D, E);
-      for (int i_iter = 0; i_iter < p->iter_num; i_iter++) {
-        b->n_outer[s] += 1;
-        x_update_scenario(p, c, b, s, V, D, h0);
-        detect_scenario(p, b, s, V, D, E);
-        if (b->edge_n[s] == 0 && b->flag[s] == 0) break;
-        b->flag[s] = 1;
-        z_update_scenario(p, c, b, s, V, D, E, h0, h1);
-        residual_scenario(p, b, s, V, D, E, i_iter);
-        if (b->done[s]) break;
-      }
-      b->done[s] = 1;
-      plant_scenario(p, b, s, V);
+  const int inner = S < nt && V >= 16;   /* tiny scenes: not worth a parallel region per phase */
+  half_t** pool = (half_t**)malloc(sizeof(half_t*) * 2 * nt);
+  for (int t = 0; t < 2 * nt; t++) pool[t] = (half_t*)malloc(sizeof(half_t));
+  const size_t mapb = (size_t)V * (((size_t)V + 7) / 8);
+  uint8_t* hitmaps = (uint8_t*)malloc(mapb * (inner ? 1 : nt));
+#pragma omp parallel for schedule(dynamic, 4) if (!inner)
+  for (int s = 0; s < S; s++) {
+    uint8_t* hitmap = hitmaps + (inner ? 0 : mapb * omp_thread_id());
+    begin_scenario(p, b, s, V, D, E);
+    for (int i_iter = 0; i_iter < p->iter_num; i_iter++) {
+      b->n_outer[s] += 1;
+      x_update_scenario(p, c, b, s, V, D, pool, inner);
+      detect_scenario(p, b, s, V, D, E, hitmap, inner);
+      if (b->edge_n[s] == 0 && b->flag[s] == 0) break;
+      b->flag[s] = 1;
+      z_update_scenario(p, c, b, s, V, D, E, pool, inner);
+      residual_scenario(p, b, s, V, D, E, i_iter);
+      if (b->done[s]) break;
     }
-    free(h0); free(h1);
+    if (!b->done[s] && b->n_outer[s] == p->iter_num && b->flag[s]) b->status[s] |= PIADMM_ST_OUTER_MAXITER;
+    b->done[s] = 1;
+    plant_scenario(p, b, s, V);
   }
+  for (int t = 0; t < 2 * nt; t++) free(pool[t]);
+  free(pool); free(hitmaps);
   free(c);
   return PIADMM_OK;
 }
