@@ -47,10 +47,15 @@ COUPLED = {
 
 
 def coupled_params(N):
-    """Synthetic coupled scenes: dual="pi", AL term over activated edges, convex edge problem."""
+    """Synthetic coupled scenes: dual="pi" (per-directed-edge integrators, clamp +-30 with
+    back-calculation), AL term over activated edges, convex edge problem, the reference's outer cap of 100
+    (casadi/PI_ADMM_class.py:25).  Gains: kI = 1.5, kP = 0 -- with the reference's own gains (kI = rho = 2, sigmoid
+    kP in [2, 3.5], MATLAB :21-23,160) the outer loop does not reach consensus on many-edge scenes (profiles/r2_convergence.md,
+    tools/coupled_gain_scan.py): every kP > 0 we scanned slows it down or destabilises it."""
     import pi_admm_b200 as pa
     p = pa.preset("matlab_pi")
-    p.update(num_ho=N, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5, al_all=0, iter_num=12)
+    p.update(num_ho=N, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5, al_all=0, iter_num=100,
+             kI=1.5, theta1=0.0, theta2=0.0)
     return p
 
 
@@ -63,10 +68,10 @@ def coupled_scene(name):
 def coupled_config(name, V, N, D, world):
     what = {"c3": "c3: ONE 64-vehicle 4-arm intersection (BASELINE config 3)",
             "c5": "c5: ONE 4096-vehicle coupled grid scene, 64+64 lanes x 32 vehicles (BASELINE config 5)"}[name]
-    return {"workload": f"{what}, horizon N={N}, one coupled MPC step (outer-iteration cap 12) through the generic-V "
-                        "phase kernels", "vehicles": V, "horizon": N, "neighbour_slots": D,
-            "semantics": "dual=pi (MATLAB PI+anti-windup), AL over activated edges, edge=convex, eps_pri=eps_dual=0.5, "
-                         "inner=osqp_default",
+    return {"workload": f"{what}, horizon N={N}, one coupled MPC step to PI-ADMM convergence (outer cap 100)",
+            "vehicles": V, "horizon": N, "neighbour_slots": D,
+            "semantics": "dual=pi (per-edge integrators, clamp +-30 + back-calculation; kI=1.5, kP=0), AL over activated edges, "
+                         "edge=convex, eps_pri=eps_dual=0.5, inner=osqp_default",
             "parallelism": "single GPU" if world == 1 else
                            f"vehicles sharded x{world}, NCCL all-gather of pos/u rows + all-reduce of residual sums per outer iteration",
             "l2": "L2 flushed (256 MiB write) before every timed step"}
@@ -156,9 +161,8 @@ def run_reference(args, rank, world):
     """CPU arm: oracle C twin on all host cores; rank 0 only."""
     if rank != 0:
         return
-    import __graft_entry__ as ge
-    ge.build()
-    from oracle import ctwin
+    from oracle import ctwin          # builds oracle/libpiadmm_ref.so if missing; the CUDA library is NOT loaded in this arm
+    ctwin.build()
     from pi_admm_b200.scenarios import c4_scenarios
     if args.workload in COUPLED:
         return run_reference_coupled(args)
@@ -219,7 +223,8 @@ def run_reference_coupled(args):
 
 def workload_config(name, S, N, world):
     return {"workload": f"{name}: {S} independent two-vehicle intersection scenarios per GPU (BASELINE config 4), "
-                        f"horizon N={N}, one MPC step to PI-ADMM convergence",
+                        f"horizon N={N}, one MPC step to PI-ADMM convergence (on these inputs: <= 2-3 outer iterations, every "
+                        "scenario leaves the loop through the reference's empty-edge rule; see work_per_step.rank0)",
             "scenarios_per_gpu": S, "vehicles_per_scenario": 2, "horizon": N,
             "semantics": "C1 constants (casadi/PI_ADMM_class.py:15-28), dual=pi (MATLAB PI+anti-windup), "
                          "edge=convex, eps_pri=eps_dual=0.1, inner=osqp_default (eps 1e-3, adaptive rho)",
@@ -235,6 +240,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS) + sorted(COUPLED))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-coupled", action="store_true", help="skip the coupled (config 5 / 3) records of the default line")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -342,6 +348,14 @@ def main():
         assert np.array_equal(io[k].numpy(), out[k]), f"e2e output {k} differs from the device-resident run"
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- the coupled scenes (BASELINE configs 5 and 3): config 5 on ALL ranks of this run (vehicle-sharded, strong
+    # scaling), config 3 at N=1.  Reported beside the config-4 headline as `coupled`.
+    coupled = None
+    if not args.no_coupled:
+        coupled = {"c5": measure_coupled("c5", args, rank, local_rank, world)}
+        if world == 1:
+            coupled["c3"] = measure_coupled("c3", args, rank, local_rank, world)
+
     # ---- max over ranks, sums of work ------------------------------------------------------
     stats = torch.tensor([total_ms, e2e_s * 1e3, e2e_full_s * 1e3], dtype=torch.float64, device=sol.device)
     work = torch.tensor([n_veh, n_edge, veh_inner, edge_inner], dtype=torch.float64, device=sol.device)
@@ -403,7 +417,8 @@ def main():
             "work_per_step": {"agent_qp_solves": g_veh, "edge_solves": g_edge, "veh_inner_iters": g_vi,
                               "edge_inner_iters": g_ei, "outer_iters_mean": float(n_outer.mean()),
                               "outer_iters_max": int(n_outer.max()),
-                              "ms_per_mpc_step": ms_per_step},
+                              "ms_per_mpc_step": ms_per_step, "rank0": exit_summary(out, p)},
+            "coupled": coupled,
         }
         if not args.no_cpu_baseline and world == 1:       # reported at N=1 only (rank 0)
             line["cpu_baseline"] = cpu_baseline(p, xt, spd, refwin, S, N)
@@ -413,123 +428,179 @@ def main():
         dist.destroy_process_group()
 
 
-def run_coupled(args, rank, local_rank, world):
-    """--workload c3 / c5: one coupled scene through the phase kernels (generic V).  world > 1: vehicles sharded over the
-    ranks (parallel.VehicleShardedSolver).  Timing: CUDA events around the whole coupled step, max over ranks."""
+def exit_summary(out, p):
+    """How the scenarios left the outer loop (casadi/main.py:115-118 empty edge list / :174-178 stop test / the cap)."""
+    n_outer = np.asarray(out["n_outer"]).reshape(-1)
+    status = np.asarray(out["status"]).reshape(-1)
+    edge_n = np.asarray(out["edge_n"]).reshape(-1)
+    flag = np.asarray(out["flag"]).reshape(-1)
+    rk = np.asarray(out["err_rk"]).reshape(len(n_outer), -1)
+    sk = np.asarray(out["err_sk"]).reshape(len(n_outer), -1)
+    last = np.clip(n_outer - 1, 0, rk.shape[1] - 1)
+    rk_l = rk[np.arange(len(n_outer)), last]; sk_l = sk[np.arange(len(n_outer)), last]
+    cap = (status & 8) != 0
+    never = (flag == 0) & ~cap                                  # no collision ever seen: break in the first iteration
+    empty = (edge_n == 0) & (flag != 0) & ~cap                  # the edge list emptied: residuals exactly 0
+    stop = ~cap & ~never & ~empty
+    hist = {int(k): int(v) for k, v in zip(*np.unique(n_outer, return_counts=True))}
+    return {"exit": {"stop_test_with_active_edges": int(stop.sum()), "empty_edge_list": int(empty.sum()),
+                     "no_collision_at_all": int(never.sum()), "iteration_cap": int(cap.sum())},
+            "converged": bool(not cap.any()), "outer_iters_hist": hist,
+            "residual_at_exit": {"err_rk_max": float(rk_l.max()), "err_sk_max": float(sk_l.max()),
+                                 "eps_pri": float(p.eps_pri), "eps_dual": float(p.eps_dual)},
+            "outer_cap": int(p.iter_num)}
+
+
+def measure_coupled(name, args, rank, local_rank, world, with_cpu=True):
+    """One coupled scene (c3 / c5) on `world` ranks: vehicles in the spatial order, sharded by strips
+    (parallel.VehicleShardedSolver; world == 1: the same numbering on one GPU).  Device-timed steps (L2 flushed, barrier
+    on both sides, max over ranks), end-to-end steps from host arrays, exit / convergence summary, a checksum of the
+    results (bit-identical for every world size), and at world == 1 the CPU port timed and used as the checker."""
     import ctypes as C
+    import hashlib
     import torch
     import torch.distributed as dist
     from pi_admm_b200.parallel import VehicleShardedSolver
-    from pi_admm_b200.solver import PIADMMSolver
-    (xt, spd, refwin), V, N, D = coupled_scene(args.workload)
+    (xt, spd, refwin), V, N, D = coupled_scene(name)
     p = coupled_params(N)
-    if world > 1:
-        vs = VehicleShardedSolver(p, V, D, device=local_rank)
-        sol, step = vs.sol, vs.iterate
-    else:
-        sol = PIADMMSolver(p, S=1, V=V, D=D, device=local_rank)
-        step = sol.iterate
-    sol.setup(xt, spd, refwin)
+    vs = VehicleShardedSolver(p, V, D, device=local_rank)
+    sol = vs.sol
+    vs.setup(xt, spd, refwin)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=sol.device)
     stream = torch.cuda.current_stream()
+    steps, warmup = max(1, args.steps), max(3, args.warmup)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step()
+    for _ in range(warmup):
+        vs.iterate()
     barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     l0 = sol.launch_count
     step_ms = []
-    for _ in range(args.steps):
+    for _ in range(steps):
         flush.fill_(1)                                   # L2 flush, outside the event pair
         barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
-        step()                                           # all outer iterations of the coupled MPC step
+        vs.iterate()                                     # all outer iterations of the coupled MPC step
         b.record(stream)
         torch.cuda.synchronize()
         step_ms.append(a.elapsed_time(b))
     launches = sol.launch_count - l0
-    out = sol.to_numpy()
-    # ---- end to end (world == 1): host arrays in, step, plant step, results back on the host
-    e2e = None
-    if world == 1:
-        pin = [torch.from_numpy(np.ascontiguousarray(x)).pin_memory() for x in (xt, spd, refwin)]
-        keys = ("u", "pos", "xt_next", "n_outer", "curr_iter")
-        host = {k: torch.empty_like(sol.buf[k], device="cpu").pin_memory() for k in keys}
+    vs.plant_step()
+    out = vs.results()
+    raw = sol.to_numpy()
+    # ---- end to end: host arrays in (H2D inside setup), step, plant step, results back on the host
+    h2d = sum(np.asarray(x).nbytes for x in (xt, spd, refwin))
+    keys = ("u", "pos", "xt_next", "n_outer", "curr_iter")
+    host = {k: torch.empty_like(sol.buf[k], device="cpu").pin_memory() for k in keys}
 
-        def e2e_step():
-            sol.setup(*pin)
-            sol.iterate()
-            sol.plant_step()
-            for k in keys:
-                host[k].copy_(sol.buf[k], non_blocking=True)
-            torch.cuda.synchronize()
-        for _ in range(args.warmup):
-            e2e_step()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            e2e_step()
-        e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
-        assert np.array_equal(host["u"].numpy(), out["u"]) and np.array_equal(host["n_outer"].numpy(), out["n_outer"])
-        e2e = {"ms_per_step": e2e_ms, "h2d": sum(t.numel() * t.element_size() for t in pin),
-               "d2h": sum(t.numel() * t.element_size() for t in host.values())}
-    clocks = sampler.stop() if rank == 0 else None
-    stats = torch.tensor([sum(step_ms)], dtype=torch.float64, device=sol.device)
-    # every rank books the solves of the vehicles / edges it owns... x-updates: owned vehicles only
-    work = torch.tensor([float(out["n_veh_solves"][0]), float(out["veh_inner"][0])], dtype=torch.float64, device=sol.device)
+    def e2e_step():
+        vs.setup(xt, spd, refwin)
+        vs.iterate()
+        vs.plant_step()
+        for k in keys:
+            host[k].copy_(sol.buf[k], non_blocking=True)
+        torch.cuda.synchronize()
+    for _ in range(warmup):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e2e_step()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / steps
+    assert np.array_equal(host["u"].numpy(), raw["u"]), "coupled e2e results differ from the device-timed run"
+    stats = torch.tensor([sum(step_ms) / steps, e2e_ms], dtype=torch.float64, device=sol.device)
+    work = torch.tensor([float(raw["n_veh_solves"][0]), float(raw["veh_inner"][0]), float(raw["n_edge_solves"][0]),
+                         float(raw["edge_inner"][0])], dtype=torch.float64, device=sol.device)
     if world > 1:
         dist.all_reduce(stats, op=dist.ReduceOp.MAX)
         dist.all_reduce(work, op=dist.ReduceOp.SUM)
+    ms, e2e_ms = float(stats[0]), float(stats[1])
+    n_veh, veh_inner, n_edge, edge_inner = [float(x) for x in work.tolist()]
+    rec = None
     if rank == 0:
-        ms = float(stats[0]) / args.steps
-        n_veh, veh_inner = float(work[0]), float(work[1])
-        n_edge, edge_inner = float(out["n_edge_solves"][0]), float(out["edge_inner"][0])   # world > 1: rank 0's share
         flops = veh_inner * flops_per_inner_iter(N, False) + edge_inner * flops_per_inner_iter(N, True)
         tf = C.c_double(0); pm = C.c_double(0)
         rc = sol.lib.piadmm_fp64_peak(local_rank, 200000, C.byref(tf), C.byref(pm))
         peak = float(tf.value) if rc == 0 else None
         ach = flops / (ms * 1e-3) / 1e12
-        line = {
-            "metric": "agent-QP solves/s", "value": n_veh / (ms * 1e-3), "unit": "solves/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": coupled_config(args.workload, V, N, D, world),
-            "gpu_launches": int(launches), "clocks": clocks,
-            "roofline": {"bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
-                         "frac": ach / peak if peak else None, "traffic": None,
-                         "kernel": "whole coupled step (k_x_update + detection + k_z_update + residual kernels)",
-                         "note": "latency bound by construction: every outer iteration waits for the slowest vehicle "
-                                 "QP and the slowest edge problem of the scene (one dependent chain of inner "
-                                 "iterations each); the fraction says how little of the GPU one scene can fill",
-                         "peak_source": "DFMA micro-benchmark of this repo (piadmm_fp64_peak)",
-                         "flops_per_launch": flops},
-            "work_per_step": {"agent_qp_solves": n_veh, "edge_solves": n_edge, "veh_inner_iters": veh_inner,
-                              "edge_inner_iters": edge_inner, "outer_iters": int(out["n_outer"][0]),
-                              "status": int(out["status"][0]), "ms_per_mpc_step": ms}}
-        if e2e:
-            line["e2e"] = {"value": n_veh / (e2e["ms_per_step"] * 1e-3), "unit": "solves/s", "ms_per_step": e2e["ms_per_step"],
-                           "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
-                           "api": "PIADMMSolver.setup (pinned xt, spd, reference window -> device) + iterate + plant_step + "
-                                  "D2H of u, pos, xt_next, n_outer, curr_iter into pinned buffers"}
-        if not args.no_cpu_baseline and world == 1:
-            import __graft_entry__ as ge  # noqa: F401
+        sha = hashlib.sha256(np.ascontiguousarray(out["u"]).tobytes() + np.ascontiguousarray(out["pos"]).tobytes()).hexdigest()
+        stored = None
+        try:
+            stored = json.load(open(os.path.join(ROOT, "profiles", "r2_coupled_checksums.json"))).get(name)
+        except Exception:
+            pass
+        what = {"c3": "c3: ONE 64-vehicle 4-arm intersection (BASELINE config 3)",
+                "c5": "c5: ONE 4096-vehicle coupled grid scene, 64+64 lanes x 32 vehicles (BASELINE config 5; generator with the "
+                      "rejection rule clear=3 m: no pair starts inside dis_thres)"}[name]
+        rec = {"workload": f"{what}, horizon N={N}, one coupled MPC step to PI-ADMM convergence (outer cap {p.iter_num})",
+               "vehicles": V, "horizon": N, "neighbour_slots": D, "n_gpus": world, "scaling": "strong",
+               "semantics": "dual=pi (per-edge integrators, clamp +-30 + back-calculation; kI=1.5, kP=0: profiles/r2_convergence.md), "
+                            "AL over activated edges, edge=convex, eps_pri=eps_dual=0.5, inner=osqp_default",
+               "parallelism": "single GPU, persistent cooperative kernel" if world == 1 else
+                              f"vehicles sharded x{world} by spatial strips; exchange={vs.exchange}" +
+                              (f" [{vs.exchange_note}]" if vs.exchange_note else ""),
+               "exchange": vs.exchange, "ms_per_step": ms, "steps": steps, "warmup": warmup,
+               "agent_qp_solves_per_s": n_veh / (ms * 1e-3), "edge_qp_solves_per_s": n_edge / (ms * 1e-3),
+               "gpu_launches_per_step": launches / steps,
+               "l2": "L2 flushed (256 MiB write) before every timed step",
+               "e2e": {"ms_per_step": e2e_ms, "value": n_veh / (e2e_ms * 1e-3), "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
+                       "d2h_bytes_per_step": int(sum(t.numel() * t.element_size() for t in host.values())),
+                       "api": "VehicleShardedSolver.setup (host xt, spd, reference window -> device) + iterate + plant_step + D2H "
+                              "of u, pos, xt_next, n_outer, curr_iter into pinned buffers"},
+               "work_per_step": {"agent_qp_solves": n_veh, "edge_solves_incl_redundant_cut_edges": n_edge,
+                                 "veh_inner_iters": veh_inner, "edge_inner_iters": edge_inner,
+                                 "outer_iters": int(out["n_outer"][0]), "status": int(out["status"][0])},
+               "roofline": {"bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if peak else None,
+                            "flops_per_step": flops, "kernel": "k_coop (whole coupled step)",
+                            "note": "one scene = a few hundred microseconds of dependent phases; the fraction says how little of "
+                                    "the GPU one coupled scene can fill, the batched config-4 line is the throughput figure",
+                            "peak_source": "DFMA micro-benchmark of this repo (piadmm_fp64_peak)"},
+               "result_sha256": sha, "matches_stored_checksum": (sha == stored) if stored else None}
+        rec.update(exit_summary(out, p))
+        if with_cpu and world == 1 and not args.no_cpu_baseline:
             from oracle import ctwin
             cores = host_cores()
             t0 = time.perf_counter(); reps = 0; solves = 0
-            while reps == 0 or (time.perf_counter() - t0 < 10.0 and reps < 200):
+            while reps == 0 or (time.perf_counter() - t0 < 8.0 and reps < 200):
                 r = ctwin.step(p, xt, spd, refwin, D=D, nthreads=cores)
                 solves += int(r["n_veh_solves"].sum()); reps += 1
             dt = time.perf_counter() - t0
-            line["cpu_baseline"] = {"value": solves / dt, "unit": "solves/s", "cores": cores, "kind": "port",
-                                    "sample": f"{reps} coupled MPC steps of the same scene (~{dt:.1f} s) with {cores} "
-                                              "OpenMP threads, oracle/piadmm_ref.c"}
+            rel = lambda a_, b_: float(np.abs(a_ - b_).max() / max(1.0, np.abs(b_).max()))
+            rec["cpu_baseline"] = {"value": solves / dt, "unit": "solves/s", "ms_per_step": 1e3 * dt / reps, "cores": cores,
+                                   "kind": "port", "sample": f"{reps} coupled MPC steps of the same scene (~{dt:.1f} s) with "
+                                                             f"{cores} OpenMP threads, oracle/piadmm_ref.c"}
+            rec["parity_vs_cpu_port"] = {"outer_iters_equal": bool(np.array_equal(out["n_outer"], r["n_outer"])),
+                                         "u_rel_err": rel(out["u"], r["u"]), "pos_rel_err": rel(out["pos"], r["pos"]),
+                                         "err_rk_rel_err": rel(out["err_rk"], r["err_rk"])}
+    barrier()
+    vs.close()
+    return rec
+
+
+def run_coupled(args, rank, local_rank, world):
+    """--workload c3 / c5: the coupled record as its own line (`ms_per_step` = the BASELINE metric's second half)."""
+    import torch.distributed as dist
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    rec = measure_coupled(args.workload, args, rank, local_rank, world)
+    clocks = sampler.stop() if rank == 0 else None
+    if rank == 0:
+        line = {"metric": "agent-QP solves/s", "value": rec["agent_qp_solves_per_s"], "unit": "solves/s", "n_gpus": world,
+                "steps": rec["steps"], "warmup": rec["warmup"], "ms_per_step": rec["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {k: rec[k] for k in ("workload", "vehicles", "horizon", "neighbour_slots", "semantics", "parallelism", "l2")},
+                "gpu_launches": int(round(rec["gpu_launches_per_step"] * rec["steps"])), "clocks": clocks}
+        for k in ("e2e", "roofline", "work_per_step", "exit", "converged", "outer_iters_hist", "residual_at_exit", "outer_cap",
+                  "result_sha256", "matches_stored_checksum", "cpu_baseline", "parity_vs_cpu_port", "exchange"):
+            if k in rec:
+                line[k] = rec[k]
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

@@ -9,8 +9,9 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PIADMM_LIB") or os.path.join(_HERE, "csrc", "libpiadmm.so")   # PIADMM_LIB: A/B builds
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 DUAL_PLAIN, DUAL_PI, DUAL_PI_OLD = 0, 1, 2
+PEER_HANDLE_BYTES = 64
 ST_VEH_MAXITER, ST_EDGE_MAXITER, ST_SLOT_OVERFLOW, ST_OUTER_MAXITER, ST_PEER_TIMEOUT = 1, 2, 4, 8, 16
 
 _D = C.c_double
@@ -148,6 +149,9 @@ _PROTOS = {
     "piadmm_residual_decide": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_num_active": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]),
     "piadmm_step": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "piadmm_peer_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "piadmm_peer_connect": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "piadmm_peer_disconnect": (C.c_int, [C.c_void_p]),
     "piadmm_plant_step": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_step_host": (C.c_int, [C.c_void_p] + [C.c_void_p] * 8 + [C.c_void_p]),
     "piadmm_set_reference": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),

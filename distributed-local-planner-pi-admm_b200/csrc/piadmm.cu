@@ -5,7 +5,9 @@
 #include <cstring>
 #include <cmath>
 #include <string>
+#include <algorithm>
 #include "piadmm_phases.cuh"
+#include "piadmm_detect.cuh"
 
 #define CTA_THREADS 64
 #ifndef Z32_MIN_CTAS
@@ -66,6 +68,8 @@ __device__ __forceinline__ void load_tabs(const DevCtx& c, double* Wsm, int firs
 }
 template <int LPQ>
 __device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) { load_tabs<LPQ>(c, Wsm, 0, PIADMM_NTAB); }
+
+#include "piadmm_coop.cuh"
 
 // ------------------------------------------------------------------ phase kernels (generic V)
 __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
@@ -211,108 +215,47 @@ __global__ void k_hits_warp(const __grid_constant__ DevCtx c) {
   if (lane == 0 && m) atomicOr(c.hits + (size_t)si * words + jb, m);
 }
 
-// per vehicle: allocate neighbour slots for newly colliding vehicles, ascending j (this equals the
-// reference's sequential processing of np.where(edge_mat == 1), row-major)
-__global__ void k_slots(const __grid_constant__ DevCtx c) {
-  // one warp per vehicle: the row of the hit matrix is read 32 words at a time (one coalesced load instead of a
-  // dependent per-thread scan), the rare non-zero words are handed to lane 0 in ascending order
-  const long a = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (a >= (long)c.S * c.V) return;
-  const int s = (int)(a / c.V), i = (int)(a % c.V), words = (c.V + 31) / 32;
-  if (c.b.done[s]) return;
-  int32_t* nb = c.b.nbr + a * c.D;
-  const uint32_t* H = c.hits + (size_t)a * words;
-  int up = 0;
-  bool overflow = false;
-  for (int w0 = 0; w0 < words; w0 += 32) {
-    const uint32_t mine = w0 + lane < words ? H[w0 + lane] : 0u;
-    unsigned nz = __ballot_sync(PIADMM_FULL, mine != 0u);
-    while (nz) {
-      const int src = __ffs(nz) - 1;
-      nz &= nz - 1;
-      uint32_t m = __shfl_sync(PIADMM_FULL, mine, src);
-      if (lane != 0) continue;
-      while (m) {
-        const int j = (w0 + src) * 32 + __ffs(m) - 1;
-        m &= m - 1;
-        int slot = -1;
-        for (int d = 0; d < c.D; d++) if (nb[d] == j) { slot = d; break; }
-        if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = j; slot = d; break; }
-        if (slot < 0) { overflow = true; continue; }
-        if (j > i) up++;
-      }
-    }
-  }
-  if (lane == 0) {
-    c.up_cnt[a] = up;
-    if (overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
-  }
+// ---- candidate pairs of the MPC step (piadmm_detect.cuh): reach discs, then the symmetric candidate bit matrix
+__global__ void k_disc(const __grid_constant__ DevCtx c) {
+  const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a < (long)c.S * c.V) dev_disc_vehicle(c, a);
+}
+__global__ void k_cand(const __grid_constant__ DevCtx c) {
+  const int words = (c.V + 31) / 32;
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long)c.S * c.V * words) return;
+  const int jb = (int)(t % words);
+  const long si = t / words;
+  c.cand[t] = dev_cand_word(c, (int)(si / c.V), (int)(si % c.V), jb);
 }
 
-// per scenario: emit the sorted edge list; flag / early-exit logic of casadi/main.py:115-118
-__global__ void k_edges(const __grid_constant__ DevCtx c) {
-  const int s = blockIdx.x, words = (c.V + 31) / 32;
+// per vehicle (one warp): exact test of the candidates (EXACT) / walk of the hit matrix, neighbour slots in ascending j
+// (this equals the reference's sequential processing of np.where(edge_mat == 1), row-major)
+template <bool EXACT>
+__global__ void k_slots(const __grid_constant__ DevCtx c) {
+  const long a = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (a >= (long)c.S * c.V) return;
+  const int s = (int)(a / c.V), i = (int)(a % c.V);
   if (c.b.done[s]) return;
-  __shared__ int base;
+  dev_slots_vehicle<EXACT>(c, s, i, threadIdx.x & 31);
+}
+
+// per scenario: count the valid edges per vehicle, scan, emit the sorted edge list; flag / early-exit logic of
+// casadi/main.py:115-118
+__global__ void k_edges(const __grid_constant__ DevCtx c) {
+  const int s = blockIdx.x;
+  if (c.b.done[s]) return;
   __shared__ int wsum[32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  if (threadIdx.x == 0) base = 0;
-  __syncthreads();
-  const uint32_t* H = c.hits + (size_t)s * c.V * words;
+  int base = 0;
   for (int i0 = 0; i0 < c.V; i0 += blockDim.x) {
     const int i = i0 + threadIdx.x;
-    const int cnt = i < c.V ? c.up_cnt[(size_t)s * c.V + i] : 0;
-    int inc = cnt;                                            // CTA-wide exclusive scan: warp scans + scan of warp totals
-    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(PIADMM_FULL, inc, o); if (lane >= o) inc += t; }
-    if (lane == 31) wsum[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-      int v = lane < nwarps ? wsum[lane] : 0;
-      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(PIADMM_FULL, v, o); if (lane >= o) v += t; }
-      wsum[lane] = v;
-    }
-    __syncthreads();
-    int n = base + (warp ? wsum[warp - 1] : 0) + inc - cnt;
-    if (i < c.V && cnt > 0) {
-      // the up-edges of i are among its <= D neighbour slots: test their hit bits (D loads instead of a scan of the
-      // whole row) and emit them in ascending j, the order of np.where(edge_mat == 1)
-      const int32_t* nbi = c.b.nbr + ((size_t)s * c.V + i) * c.D;
-      int lastj = i;
-      for (int e = 0; e < cnt; e++) {
-        int j = 0x7fffffff, di = -1;
-        for (int d = 0; d < c.D; d++) {
-          const int cand = nbi[d];
-          if (cand > lastj && cand < j && ((H[(size_t)i * words + (cand >> 5)] >> (cand & 31)) & 1u)) { j = cand; di = d; }
-        }
-        if (di < 0) break;
-        lastj = j;
-        const int32_t* nbj = c.b.nbr + ((size_t)s * c.V + j) * c.D;
-        int dj = -1;
-        for (int d = 0; d < c.D; d++) if (nbj[d] == i) dj = d;
-        if (n >= c.E) continue;
-        int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + n) * 2;
-        int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + n) * 2;
-        if (dj < 0) {                  // slot overflow on the far side (status already set): dead entry
-          eij[0] = -1; eij[1] = -1; esl[0] = 0; esl[1] = 0;
-          double* er = c.edge_res + ((size_t)s * c.E + n) * 4;
-          er[0] = er[1] = er[2] = er[3] = 0.0;
-        } else {
-          eij[0] = i; eij[1] = j; esl[0] = di; esl[1] = dj;
-        }
-        n++;
-      }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) base += wsum[nwarps - 1];
-    __syncthreads();
+    const int cnt = i < c.V ? dev_count_vehicle(c, s, i) : 0;
+    int total;
+    const int off = cta_excl_scan(cnt, wsum, &total);
+    if (cnt > 0) dev_emit_vehicle(c, s, i, base + off, cnt);
+    base += total;
   }
-  if (threadIdx.x == 0) {
-    c.b.n_outer[s] += 1;
-    c.b.edge_n[s] = base;
-    if (base == 0 && c.b.flag[s] == 0) c.b.done[s] = 1;   // "no collision if no edge links": break
-    else c.b.flag[s] = 1;
-  }
+  if (threadIdx.x == 0) dev_edges_done(c, s, base);
 }
 
 template <int LPQ>
@@ -409,72 +352,11 @@ __global__ void k_res_decide(const __grid_constant__ DevCtx c) {
 // microseconds each, so four launches of dependent tiny kernels are most of their time.  The residual sums are formed
 // exactly as k_res_partial forms them (128 strided partial sums, the same tree), so the histories are bit-identical.
 __global__ void k_res_all(const __grid_constant__ DevCtx c, int* cnt) {
-  const int s = blockIdx.x, N = c.N;
+  const int s = blockIdx.x;
   if (c.b.done[s]) return;
-  const piadmm_params& p = c.p;
   __shared__ double red[2][128];
-  __shared__ int bad_sh, decision;
-  const int n = c.b.edge_n[s];
-  const double rho = (p.dual_mode == PIADMM_DUAL_PI_OLD && n > 0) ? c.rho_new[s] : c.b.rho_s[s];
-  if (threadIdx.x == 0) bad_sh = 0;
-  if (threadIdx.x < 128) {
-    double sk = 0.0, rk = 0.0;
-    for (int e = threadIdx.x; e < n; e += 128) {
-      const double* er = c.edge_res + ((size_t)s * c.E + e) * 4;
-      if (p.residual_global) { sk += sqrt(rho * rho * (er[0] + er[1])); rk += sqrt(er[2] + er[3]); }
-      else { sk += 2.0 * sqrt(rho * rho * er[0]); rk += 2.0 * sqrt(er[2]); }
-    }
-    red[0][threadIdx.x] = sk; red[1][threadIdx.x] = rk;
-  }
-  __syncthreads();
-  for (int o = 64; o >= 1; o >>= 1) {
-    if ((int)threadIdx.x < o) {
-      red[0][threadIdx.x] += red[0][threadIdx.x + o];
-      red[1][threadIdx.x] += red[1][threadIdx.x + o];
-    }
-    __syncthreads();
-  }
-  if (p.stop_dist_test) {                      // MATLAB :202 over the allocated neighbour slots of this scenario
-    for (int t = threadIdx.x; t < c.V * c.D; t += blockDim.x) {
-      const int i = t / c.D, j = c.b.nbr[(size_t)s * c.V * c.D + t];
-      if (j <= i) continue;
-      const double* xi = c.b.xt + ((size_t)s * c.V + i) * 3;
-      const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
-      const double vi = c.b.spd[(size_t)s * c.V + i], vj = c.b.spd[(size_t)s * c.V + j];
-      const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
-      const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
-      if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) bad_sh = 1;
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) {
-    const double rk = red[1][0], sk = red[0][0];
-    c.b.res_part[(size_t)s * 2] = rk; c.b.res_part[(size_t)s * 2 + 1] = sk;
-    c.b.err_rk[(size_t)s * c.I + c.i_iter] = rk;
-    c.b.err_sk[(size_t)s * c.I + c.i_iter] = sk;
-    c.b.rho_s[s] = rho;
-    const bool conv = rk <= p.eps_pri && sk <= p.eps_dual && bad_sh == 0;
-    bool fin = conv;
-    if (conv) { c.b.curr_iter[s] = c.i_iter + 1; c.b.done[s] = 1; }
-    else {
-      if (p.dual_res_alias) c.b.aliased[s] = 1;
-      if (p.curr_iter_latest) c.b.curr_iter[s] = c.i_iter + 1;
-      if (c.i_iter + 1 >= c.I) { c.b.done[s] = 1; fin = true; c.b.status[s] |= PIADMM_ST_OUTER_MAXITER; }
-    }
-    if (cnt && !fin) atomicAdd(cnt, 1);
-    decision = conv ? 1 : 0;
-  }
-  __syncthreads();
-  if (!decision) {
-    const int per = 2 * (N + 1);
-    for (int t = threadIdx.x; t < n * 2 * per; t += blockDim.x) {
-      const int e = t / (2 * per), side = (t / per) & 1, el = t % per;
-      const int v = c.b.edge_ij[((size_t)s * c.E + e) * 2 + side];
-      if (v < 0) continue;
-      const size_t o = ((((size_t)s * c.V + v) * c.D) + c.b.edge_slot[((size_t)s * c.E + e) * 2 + side]) * per + el;
-      c.b.last_hat[o] = c.b.hat[o];
-    }
-  }
+  __shared__ int ish[2];
+  dev_res_all(c, s, c.i_iter, cnt, red, ish);       // piadmm_coop.cuh: the same statements the cooperative kernel runs
 }
 
 // MATLAB :202 extra stop condition, evaluated over every allocated neighbour slot (all CTAs of the grid)
@@ -843,8 +725,31 @@ struct piadmm_handle {
   int64_t glaunches;
   bool have_streams;
   int64_t launches;
+  // persistent cooperative kernel for generic V (piadmm_coop.cuh); PIADMM_COOP=0 selects the phase kernels
+  bool use_coop;
+  int coop_grid_max;          // co-resident CTAs of k_coop<lpq>
+  int* d_nactive;             // [2]
+  // vehicle-sharded multi-GPU exchange (piadmm_peer_export / piadmm_peer_connect)
+  char* xblk;                 // library-owned exchange block of THIS rank: pos | u | edge_res | flags | epoch | aborted
+  bool peer_on;
+  void* peer_base[PIADMM_MAX_PEERS];   // the peers' exchange blocks as mapped into this process (cudaIpcOpenMemHandle)
+  PeerCtx peer;
   std::string err;
 };
+
+// layout of an exchange block (S == 1): doubles first, then the barrier words
+struct XblkLayout { size_t pos, u, er, flags, epoch, aborted, bytes; };
+static XblkLayout xblk_layout(int V, int N, int E) {
+  XblkLayout L;
+  L.pos = 0;
+  L.u = L.pos + sizeof(double) * (size_t)V * 2 * (N + 1);
+  L.er = L.u + sizeof(double) * (size_t)V * N;
+  L.flags = L.er + sizeof(double) * (size_t)E * 4;
+  L.epoch = L.flags + sizeof(unsigned long long) * PIADMM_MAX_PEERS;
+  L.aborted = L.epoch + sizeof(unsigned long long);
+  L.bytes = L.aborted + 16;
+  return L;
+}
 
 static thread_local std::string g_create_err;
 
@@ -920,6 +825,9 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
   h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_count2 = nullptr; h->h_count2 = nullptr; h->ev_count[0] = h->ev_count[1] = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false; h->gexec = nullptr; h->d_ref = nullptr; h->ref_T = 0; h->h_step = nullptr; h->d_step = nullptr;
+  h->use_coop = true; h->coop_grid_max = 0; h->d_nactive = nullptr; h->xblk = nullptr; h->peer_on = false;
+  memset(&h->peer, 0, sizeof h->peer);
+  for (int i = 0; i < PIADMM_MAX_PEERS; i++) h->peer_base[i] = nullptr;
   h->c.p = *p; set_inner_consts(h->c.ik, p->in_alpha); h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
   h->c.N = p->num_ho; h->c.I = p->iter_num;
   h->c.own_lo = 0; h->c.own_hi = V;
@@ -982,6 +890,18 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMemset(h->c.edge_res, 0, sizeof(double) * (size_t)S * h->c.E * 4)) != cudaSuccess) return fail(ce, "edge_res");
   if ((ce = cudaMalloc(&h->c.rho_new, sizeof(double) * S)) != cudaSuccess) return fail(ce, "rho_new");
   if ((ce = cudaMalloc(&h->c.hits, sizeof(uint32_t) * (size_t)S * V * words)) != cudaSuccess) return fail(ce, "hits");
+  if ((ce = cudaMalloc(&h->c.cand, sizeof(uint32_t) * (size_t)S * V * words)) != cudaSuccess) return fail(ce, "cand");
+  if ((ce = cudaMalloc(&h->c.slot_hit, (size_t)S * V * D)) != cudaSuccess) return fail(ce, "slot_hit");
+  if ((ce = cudaMemset(h->c.slot_hit, 0, (size_t)S * V * D)) != cudaSuccess) return fail(ce, "slot_hit");
+  {   // A/B: PIADMM_DETECT = cand (default) | matrix_warp | matrix_thread ; PIADMM_HITS=1|2 is the round-1 spelling of the last two
+    const char* e = getenv("PIADMM_DETECT");
+    const char* e2 = getenv("PIADMM_HITS");
+    h->c.detect_mode = 0;
+    if (e && strcmp(e, "matrix_warp") == 0) h->c.detect_mode = 1;
+    else if (e && strcmp(e, "matrix_thread") == 0) h->c.detect_mode = 2;
+    else if (e && strcmp(e, "matrix") == 0) h->c.detect_mode = (long)S * V * words <= 9472 ? 1 : 2;
+    else if (!e && e2 && atoi(e2) >= 1 && atoi(e2) <= 2) h->c.detect_mode = atoi(e2);
+  }
   if ((ce = cudaMalloc(&h->c.up_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "up_cnt");
   if ((ce = cudaMalloc(&h->c.bbox, sizeof(double) * 4 * (size_t)S * V)) != cudaSuccess) return fail(ce, "bbox");
   if ((ce = cudaMalloc(&h->c.dist_bad, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
@@ -1055,6 +975,15 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     }
     h->x_grid = prop.multiProcessorCount * (px < 1 ? 1 : px);
     h->z_grid = prop.multiProcessorCount * (pz < 1 ? 1 : pz);
+    int pc = 0;
+    if (h->lpq == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pc, k_coop<16>, CTA_THREADS, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pc, k_coop<32>, CTA_THREADS, 0);
+    int coop_ok = 0;
+    cudaDeviceGetAttribute(&coop_ok, cudaDevAttrCooperativeLaunch, device);
+    h->coop_grid_max = prop.multiProcessorCount * (pc < 1 ? 0 : pc);
+    const char* ce_ = getenv("PIADMM_COOP");
+    h->use_coop = coop_ok && h->coop_grid_max > 0 && !(ce_ && strcmp(ce_, "0") == 0);
+    if ((ce = cudaMalloc(&h->d_nactive, 2 * sizeof(int))) != cudaSuccess) return fail(ce, "nactive");
   }
   *out = h;
   return PIADMM_OK;
@@ -1063,9 +992,11 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
   cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
   for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
+  piadmm_peer_disconnect(h);
+  cudaFree(h->xblk); cudaFree(h->d_nactive);
   cudaFree(h->d_queue); cudaFree(h->d_order); cudaFree(h->d_ref); cudaFree(h->d_step);
   if (h->h_step) cudaFreeHost(h->h_step);
   if (h->have_streams) {
@@ -1114,12 +1045,23 @@ int64_t piadmm_launch_count(const piadmm_handle* h) { return h ? h->launches : 0
     CK(cudaGetLastError());     \
   } while (0)
 
+// candidate pairs of this MPC step (detect_mode 0): once per step, from the plant state
+static int build_candidates(piadmm_handle* h, cudaStream_t st) {
+  const long agents = (long)h->c.S * h->c.V, wtot = agents * ((h->c.V + 31) / 32);
+  k_disc<<<(unsigned)((agents + 255) / 256), 256, 0, st>>>(h->c);
+  LAUNCHED();
+  k_cand<<<(unsigned)((wtot + 255) / 256), 256, 0, st>>>(h->c);
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
 int piadmm_begin_step(piadmm_handle* h, void* stream) {
   REQUIRE_BOUND();
   cudaStream_t st = (cudaStream_t)stream;
   h->c.i_iter = 0;
-  k_begin_step<<<148 * 4, 256, 0, st>>>(h->c);
+  k_begin_step<<<h->sm_count * 4, 256, 0, st>>>(h->c);
   LAUNCHED();
+  if (h->c.detect_mode == 0) return build_candidates(h, st);   // (the fused V=2 kernel never comes through here)
   return PIADMM_OK;
 }
 
@@ -1144,17 +1086,20 @@ int piadmm_detect_edges(piadmm_handle* h, void* stream) {
   REQUIRE_BOUND();
   cudaStream_t st = (cudaStream_t)stream;
   const int words = (h->c.V + 31) / 32;
-  const long warps = (long)h->c.S * h->c.V * words;
-  k_bbox<<<(unsigned)(((long)h->c.S * h->c.V * 32 + 127) / 128), 128, 0, st>>>(h->c);
-  LAUNCHED();
-  CK(cudaMemsetAsync(h->c.hits, 0, sizeof(uint32_t) * (size_t)warps, st));
-  static const int hits_force = getenv("PIADMM_HITS") ? atoi(getenv("PIADMM_HITS")) : 0;   // A/B: 1 = lane per pair, 2 = thread per word
-  if (hits_force == 1 || (hits_force == 0 && warps <= 148L * 64)) k_hits_warp<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(h->c);   // a lane per pair
-  else k_hits<<<(unsigned)((warps + 255) / 256), 256, 0, st>>>(h->c);                                  // a thread per 32 pairs
-  LAUNCHED();
-  const long agents = (long)h->c.S * h->c.V;
-  k_slots<<<(unsigned)((agents * 32 + 255) / 256), 256, 0, st>>>(h->c);
-  LAUNCHED();
+  const long agents = (long)h->c.S * h->c.V, warps = agents * words;
+  if (h->c.detect_mode == 0) {
+    k_slots<true><<<(unsigned)((agents * 32 + 255) / 256), 256, 0, st>>>(h->c);
+    LAUNCHED();
+  } else {                      // round-1 path: bounding boxes + the full pair test in every outer iteration
+    k_bbox<<<(unsigned)((agents * 32 + 127) / 128), 128, 0, st>>>(h->c);
+    LAUNCHED();
+    CK(cudaMemsetAsync(h->c.hits, 0, sizeof(uint32_t) * (size_t)warps, st));
+    if (h->c.detect_mode == 1) k_hits_warp<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(h->c);   // a lane per pair
+    else k_hits<<<(unsigned)((warps + 255) / 256), 256, 0, st>>>(h->c);                                    // a thread per 32 pairs
+    LAUNCHED();
+    k_slots<false><<<(unsigned)((agents * 32 + 255) / 256), 256, 0, st>>>(h->c);
+    LAUNCHED();
+  }
   k_edges<<<h->c.S, h->c.V > 512 ? 1024 : (h->c.V > 128 ? 256 : 128), 0, st>>>(h->c);
   LAUNCHED();
   return PIADMM_OK;
@@ -1290,10 +1235,109 @@ static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, i
   return PIADMM_OK;
 }
 
+// ---- vehicle-sharded multi-GPU exchange: library-owned exchange block, exported / mapped with CUDA IPC
+int piadmm_peer_export(piadmm_handle* h, void* handle_out) {
+  if (!h || !handle_out) return PIADMM_E_ARG;
+  if (h->c.S != 1) { h->err = "the peer exchange shards ONE coupled scene (S == 1)"; return PIADMM_E_UNSUPPORTED; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == PIADMM_PEER_HANDLE_BYTES, "handle size");
+  CK(cudaSetDevice(h->device));
+  const XblkLayout L = xblk_layout(h->c.V, h->c.N, h->c.E);
+  if (!h->xblk) {
+    CK(cudaMalloc(&h->xblk, L.bytes));
+    CK(cudaMemset(h->xblk, 0, L.bytes));
+    CK(cudaDeviceSynchronize());
+  }
+  cudaIpcMemHandle_t ih;
+  CK(cudaIpcGetMemHandle(&ih, h->xblk));
+  memcpy(handle_out, &ih, sizeof ih);
+  return PIADMM_OK;
+}
+
+int piadmm_peer_disconnect(piadmm_handle* h) {
+  if (!h) return PIADMM_E_ARG;
+  if (h->peer_on) cudaSetDevice(h->device);
+  for (int r = 0; r < PIADMM_MAX_PEERS; r++) {
+    if (h->peer_base[r]) { cudaIpcCloseMemHandle(h->peer_base[r]); h->peer_base[r] = nullptr; }
+  }
+  h->peer_on = false;
+  memset(&h->peer, 0, sizeof h->peer);
+  return PIADMM_OK;
+}
+
+int piadmm_peer_connect(piadmm_handle* h, int rank, int world, const void* handles) {
+  if (!h || !handles) return PIADMM_E_ARG;
+  if (world < 2 || world > PIADMM_MAX_PEERS || rank < 0 || rank >= world) { h->err = "piadmm_peer_connect: 2 <= world <= 8, 0 <= rank < world"; return PIADMM_E_ARG; }
+  if (!h->xblk) { h->err = "piadmm_peer_connect: call piadmm_peer_export first"; return PIADMM_E_UNBOUND; }
+  if (!h->use_coop || h->c.detect_mode != 0) { h->err = "the peer exchange needs the cooperative kernel (PIADMM_COOP / PIADMM_DETECT defaults)"; return PIADMM_E_UNSUPPORTED; }
+  CK(cudaSetDevice(h->device));
+  piadmm_peer_disconnect(h);
+  const XblkLayout L = xblk_layout(h->c.V, h->c.N, h->c.E);
+  const cudaIpcMemHandle_t* ih = reinterpret_cast<const cudaIpcMemHandle_t*>(handles);
+  PeerCtx pc;
+  memset(&pc, 0, sizeof pc);
+  pc.rank = rank; pc.world = world;
+  for (int r = 0; r < world; r++) {
+    char* base = h->xblk;
+    if (r != rank) {
+      void* q = nullptr;
+      cudaError_t e = cudaIpcOpenMemHandle(&q, ih[r], cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        h->err = std::string("cudaIpcOpenMemHandle (rank ") + std::to_string(r) + "): " + cudaGetErrorString(e);
+        cudaGetLastError();
+        piadmm_peer_disconnect(h);
+        return PIADMM_E_CUDA;
+      }
+      h->peer_base[r] = q;
+      base = (char*)q;
+    }
+    pc.pos[r] = (double*)(base + L.pos); pc.u[r] = (double*)(base + L.u); pc.edge_res[r] = (double*)(base + L.er);
+    pc.flags[r] = (unsigned long long*)(base + L.flags);
+  }
+  pc.epoch = (unsigned long long*)(h->xblk + L.epoch);
+  pc.aborted = (int*)(h->xblk + L.aborted);
+  const char* to = getenv("PIADMM_PEER_TIMEOUT_MS");
+  pc.timeout_ns = (unsigned long long)(to ? atoll(to) : 20000) * 1000000ull;
+  h->peer = pc;
+  h->peer_on = true;
+  return PIADMM_OK;
+}
+
+// the whole outer loop in ONE cooperative launch (piadmm_coop.cuh)
+static int launch_coop(piadmm_handle* h, cudaStream_t st) {
+  DevCtx c = h->c;
+  CoopArgs a;
+  memset(&a, 0, sizeof a);
+  a.n_active = h->d_nactive;
+  if (h->peer_on) {
+    const XblkLayout L = xblk_layout(c.V, c.N, c.E);
+    a.peer = h->peer;
+    a.peer.user_pos = h->c.b.pos; a.peer.user_u = h->c.b.u;
+    c.b.pos = (double*)(h->xblk + L.pos); c.b.u = (double*)(h->xblk + L.u); c.edge_res = (double*)(h->xblk + L.er);
+  }
+  const long agents = (long)c.S * c.V, pairs = (long)c.S * c.E;
+  long want;
+  if (h->lpq == 16) want = std::max((agents + 3) / 4, (pairs + 1) / 2);
+  else want = std::max((agents + 1) / 2, pairs);
+  int grid = (int)std::min<long>(h->coop_grid_max, std::max<long>(want, 1));
+  void* args[2] = {&c, &a};
+  if (h->lpq == 16) CK(cudaLaunchCooperativeKernel((void*)k_coop<16>, dim3(grid), dim3(CTA_THREADS), args, 0, st));
+  else CK(cudaLaunchCooperativeKernel((void*)k_coop<32>, dim3(grid), dim3(CTA_THREADS), args, 0, st));
+  LAUNCHED();
+  return PIADMM_OK;
+}
+
 int piadmm_step(piadmm_handle* h, void* stream) {
   REQUIRE_BOUND();
   cudaStream_t st = (cudaStream_t)stream;
   if (h->c.V == 2 && h->c.D == 1) return launch_fused(h, st, 0, h->c.S, h->d_queue, 0);
+  const bool partial = h->c.own_lo != 0 || h->c.own_hi != h->c.V;
+  if (partial && !h->peer_on) {
+    h->err = "piadmm_step on a vehicle-sharded handle needs the peer exchange (piadmm_peer_connect); without it drive the "
+             "phase entry points and reduce res_part between piadmm_residual_partials and piadmm_residual_decide";
+    return PIADMM_E_UNSUPPORTED;
+  }
+  if (h->use_coop && h->c.detect_mode == 0) return launch_coop(h, st);
+  if (h->peer_on) { h->err = "peer exchange without the cooperative kernel"; return PIADMM_E_UNSUPPORTED; }
   // generic V: phase kernels.  The active-scenario count of every outer iteration is copied to a pinned word
   // asynchronously and looked at ONE ITERATION LATE: the host has iteration it+1 enqueued before it waits for the
   // count of iteration it, so the GPU never idles for a host round trip.  At most one superfluous iteration is

@@ -1,0 +1,323 @@
+// piadmm_coop.cuh -- the whole outer PI-ADMM loop of casadi/main.py:52-181 for ANY number of vehicles as ONE persistent
+// cooperative kernel (north_star (c): "one persistent kernel runs all outer iterations without host round-trips").
+//
+//   phase 0   re-initialisation (:52-72), reach discs, candidate matrix            -> grid barrier
+//   per outer iteration
+//     x       vehicle QPs of the owned vehicles (:81-106)  [+ peer stores]          -> grid barrier (cross-GPU when sharded)
+//     slots   exact collision test of the candidates, neighbour slots (:110-113)    -> grid barrier
+//     count   valid edges per vehicle                                               -> grid barrier
+//     edges   sorted edge list, flag / early exit (:115-118)                        -> grid barrier
+//     z       edge problems + dual / PI update (:121-162)  [+ peer stores]          -> grid barrier (cross-GPU when sharded)
+//     decide  residuals, stop test, histories, last_hat copy (:165-181)             -> grid barrier
+//   loop exit on the device when no scenario is active any more.
+//
+// Vehicle-sharded multi-GPU form (config 5): the SAME kernel runs on every rank with an ownership range; the exchange is
+// fused into the compute phases -- the x phase stores every owned pos_old / primal_u row straight into every peer's
+// exchange block over NVLink (peer-mapped memory), the z phase does the same with the per-edge residual terms of the
+// edges whose veh1 it owns -- and the two grid barriers that follow them are extended to all ranks by flags in peer
+// memory.  No NCCL call, no host round trip inside the step.  Every rank sums the same per-edge terms in the same
+// order, so stop decisions and histories are bit-identical on all ranks and for every world size.
+#pragma once
+#include <cooperative_groups.h>
+#include "piadmm_detect.cuh"
+
+namespace cg = cooperative_groups;
+
+#define PIADMM_MAX_PEERS 8
+
+struct PeerCtx {
+  int rank, world;                               // world <= 1: single GPU, nothing below is used
+  double* pos[PIADMM_MAX_PEERS];                 // [V,2,N+1] exchange copy of pos_old on rank r (as mapped in this process)
+  double* u[PIADMM_MAX_PEERS];                   // [V,N]
+  double* edge_res[PIADMM_MAX_PEERS];            // [E,4]
+  unsigned long long* flags[PIADMM_MAX_PEERS];   // [PIADMM_MAX_PEERS] barrier epochs signalled TO rank r, indexed by sender
+  unsigned long long* epoch;                     // local: barrier epoch reached by the previous launch
+  int* aborted;                                  // local: a barrier timed out (later barriers do not spin)
+  unsigned long long timeout_ns;
+  double *user_pos, *user_u;                     // the caller's bound buffers: filled from the exchange block at the end
+};
+
+struct CoopArgs {
+  int* n_active;                                 // [2] scenarios still active after the decide phase (double buffered)
+  PeerCtx peer;
+};
+
+__device__ __forceinline__ unsigned long long coop_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Grid barrier extended to all ranks: every thread fences its peer stores system-wide, the grid meets, one thread per
+// peer publishes the new epoch in that peer's flag row and waits for the peer's epoch in its own row, the grid meets
+// again.  A peer that does not arrive within timeout_ns sets PIADMM_ST_PEER_TIMEOUT and stops all further waiting (the
+// kernel then runs to its end with meaningless results instead of hanging the GPU).
+__device__ __forceinline__ void coop_cross_barrier(cg::grid_group& grid, const DevCtx& c, const PeerCtx& pc,
+                                                   unsigned long long& epoch) {
+  if (pc.world <= 1) { grid.sync(); return; }
+  __threadfence_system();
+  grid.sync();
+  epoch++;
+  if (blockIdx.x == 0 && (int)threadIdx.x < pc.world && (int)threadIdx.x != pc.rank) {
+    const int r = threadIdx.x;
+    unsigned long long* dst = pc.flags[r] + pc.rank;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(epoch) : "memory");
+    const unsigned long long* src = pc.flags[pc.rank] + r;
+    const unsigned long long t0 = coop_now_ns();
+    unsigned long long seen = 0;
+    int spins = 0;
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(src) : "memory");
+      if (seen >= epoch) break;
+      if ((++spins & 63) == 0) {
+        if (*reinterpret_cast<volatile int*>(pc.aborted)) break;
+        if (coop_now_ns() - t0 > pc.timeout_ns) {
+          *reinterpret_cast<volatile int*>(pc.aborted) = 1;
+          atomicOr(c.b.status, PIADMM_ST_PEER_TIMEOUT);
+          break;
+        }
+      }
+    }
+  }
+  grid.sync();
+}
+
+// ---- decide phase of scenario s by one CTA (any blockDim >= 64): residual sums (casadi/main.py:165-173), MATLAB :202
+// distance test, stop decision, histories, alias latch, last_iter_hat_pos copy (:174-181).  The sums are formed as 128
+// strided partial sums and one binary tree whatever the CTA size, so k_res_all (128 / 1024 threads) and the cooperative
+// kernel (64 threads) produce bit-identical histories.  red: 2 x 128 doubles, ish: 2 ints of shared memory.
+__device__ __forceinline__ void dev_res_all(const DevCtx& c, int s, int i_iter, int* cnt, double (*red)[128], int* ish) {
+  const piadmm_params& p = c.p;
+  const int N = c.N, T = blockDim.x, t = threadIdx.x;
+  const int n = c.b.edge_n[s];
+  const double rho = (p.dual_mode == PIADMM_DUAL_PI_OLD && n > 0) ? c.rho_new[s] : c.b.rho_s[s];
+  if (t == 0) ish[0] = 0;
+  for (int q = t; q < 128; q += T) {
+    double sk = 0.0, rk = 0.0;
+    for (int e = q; e < n; e += 128) {
+      const double* er = c.edge_res + ((size_t)s * c.E + e) * 4;
+      if (p.residual_global) { sk += sqrt(rho * rho * (er[0] + er[1])); rk += sqrt(er[2] + er[3]); }
+      else { sk += 2.0 * sqrt(rho * rho * er[0]); rk += 2.0 * sqrt(er[2]); }
+    }
+    red[0][q] = sk; red[1][q] = rk;
+  }
+  __syncthreads();
+  for (int o = 64; o >= 1; o >>= 1) {
+    for (int q = t; q < o; q += T) { red[0][q] += red[0][q + o]; red[1][q] += red[1][q + o]; }
+    __syncthreads();
+  }
+  if (p.stop_dist_test) {                      // MATLAB :202 over the allocated neighbour slots of this scenario
+    for (int q = t; q < c.V * c.D; q += T) {
+      const int i = q / c.D, j = c.b.nbr[(size_t)s * c.V * c.D + q];
+      if (j <= i) continue;
+      const double* xi = c.b.xt + ((size_t)s * c.V + i) * 3;
+      const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
+      const double vi = c.b.spd[(size_t)s * c.V + i], vj = c.b.spd[(size_t)s * c.V + j];
+      const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
+      const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
+      if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) ish[0] = 1;
+    }
+    __syncthreads();
+  }
+  if (t == 0) {
+    const double rk = red[1][0], sk = red[0][0];
+    c.b.res_part[(size_t)s * 2] = rk; c.b.res_part[(size_t)s * 2 + 1] = sk;
+    c.b.err_rk[(size_t)s * c.I + i_iter] = rk;
+    c.b.err_sk[(size_t)s * c.I + i_iter] = sk;
+    c.b.rho_s[s] = rho;
+    const bool conv = rk <= p.eps_pri && sk <= p.eps_dual && ish[0] == 0;
+    bool fin = conv;
+    if (conv) { c.b.curr_iter[s] = i_iter + 1; c.b.done[s] = 1; }
+    else {
+      if (p.dual_res_alias) c.b.aliased[s] = 1;
+      if (p.curr_iter_latest) c.b.curr_iter[s] = i_iter + 1;
+      if (i_iter + 1 >= c.I) { c.b.done[s] = 1; fin = true; c.b.status[s] |= PIADMM_ST_OUTER_MAXITER; }
+    }
+    if (cnt && !fin) atomicAdd(cnt, 1);
+    ish[1] = conv ? 1 : 0;
+  }
+  __syncthreads();
+  if (!ish[1]) {       // last_iter_hat_pos = hat_pos_old: only the slots of this iteration's edges changed
+    const int per = 2 * (N + 1);
+    for (int q = t; q < n * 2 * per; q += T) {
+      const int e = q / (2 * per), side = (q / per) & 1, el = q % per;
+      const int v = c.b.edge_ij[((size_t)s * c.E + e) * 2 + side];
+      if (v < 0) continue;
+      const size_t o = ((((size_t)s * c.V + v) * c.D) + c.b.edge_slot[((size_t)s * c.E + e) * 2 + side]) * per + el;
+      c.b.last_hat[o] = c.b.hat[o];
+    }
+  }
+  __syncthreads();     // red / ish are reused by the next scenario of this CTA
+}
+
+// ------------------------------------------------------------------ the persistent cooperative kernel
+// (Who, load_tabs, groups_per_cta, pairs_per_cta, CTA_THREADS: piadmm.cu, defined before this file is included)
+#ifndef COOP_MIN_CTAS
+#define COOP_MIN_CTAS 4   // registers over occupancy, as the generic-V phase kernels (x and z bodies are both inlined here)
+#endif
+
+template <int LPQ>
+__global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __grid_constant__ DevCtx c,
+                                                                       const __grid_constant__ CoopArgs ca) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
+  __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
+  __shared__ __align__(16) double xch[128];
+  __shared__ double red[2][128];
+  __shared__ int ish[34];
+  Who<LPQ> w;
+  const PeerCtx& pc = ca.peer;
+  const bool sharded = pc.world > 1;
+  const int N = c.N, np1 = N + 1;
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+  const long agents = (long)c.S * c.V;
+  const int words = (c.V + 31) / 32;
+  unsigned long long epoch = sharded ? *pc.epoch : 0ull;
+  load_tabs<LPQ>(c, Wsm, 0, PIADMM_NTAB);                // (ends with a CTA barrier)
+
+  // ---- phase 0: casadi/main.py:52-72.  pos / u are only zeroed for the owned vehicles: the rows of the others are
+  // written by their owners' x phase, which may already be running on a faster rank.
+  {
+    const size_t n_slot = (size_t)agents * c.D * 2 * np1;
+    for (size_t t = tid; t < n_slot; t += nth) {
+      c.b.hat[t] = 0.0; c.b.dual[t] = 0.0; c.b.integ[t] = 0.0; c.b.diff[t] = 0.0; c.b.last_hat[t] = 0.0;
+    }
+    const size_t own_n = (size_t)(c.own_hi - c.own_lo);
+    for (size_t t = tid; t < (size_t)c.S * own_n * 2 * np1; t += nth) {
+      const size_t s = t / (own_n * 2 * np1), r = t % (own_n * 2 * np1);
+      c.b.pos[(s * c.V + c.own_lo) * 2 * np1 + r] = 0.0;
+    }
+    for (size_t t = tid; t < (size_t)c.S * own_n * N; t += nth) {
+      const size_t s = t / (own_n * N), r = t % (own_n * N);
+      c.b.u[(s * c.V + c.own_lo) * N + r] = 0.0;
+    }
+    for (size_t t = tid; t < (size_t)agents * c.D; t += nth) {
+      const int d = (int)(t % c.D), i = (int)((t / c.D) % c.V);
+      int j = -1;
+      if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;
+      c.b.nbr[t] = j;
+      c.slot_hit[t] = 0;
+    }
+    for (size_t t = tid; t < (size_t)c.S * c.I; t += nth) { c.b.err_rk[t] = 0.0; c.b.err_sk[t] = 0.0; }
+    for (size_t t = tid; t < (size_t)c.S; t += nth) {
+      c.b.flag[t] = 0; c.b.done[t] = 0; c.b.aliased[t] = 0; c.b.curr_iter[t] = 1; c.b.n_outer[t] = 0;
+      c.b.status[t] = 0; c.b.veh_inner[t] = 0; c.b.edge_inner[t] = 0; c.b.n_veh_solves[t] = 0;
+      c.b.n_edge_solves[t] = 0; c.b.edge_n[t] = 0;
+      c.rho_new[t] = c.b.rho_s[t];
+      c.dist_bad[t] = 0;
+    }
+    for (size_t t = tid; t < (size_t)agents; t += nth) dev_disc_vehicle(c, (long)t);
+  }
+  grid.sync();
+  for (size_t t = tid; t < (size_t)agents * words; t += nth) {
+    const int jb = (int)(t % words);
+    const size_t si = t / words;
+    c.cand[t] = dev_cand_word(c, (int)(si / c.V), (int)(si % c.V), jb);
+  }
+  // (the candidate matrix is first read in the slots phase, behind the barrier that ends the x phase)
+
+#pragma unroll 1
+  for (int it = 0; it < c.I; it++) {
+    if (tid == 0) ca.n_active[it & 1] = 0;
+    // ---- x-update of the owned vehicles, casadi/main.py:81-106
+    {
+      const long items = (agents + groups_per_cta<LPQ>() - 1) / groups_per_cta<LPQ>();
+      for (long item = blockIdx.x; item < items; item += gridDim.x) {
+        const long a = item * groups_per_cta<LPQ>() + w.group_in_cta;
+        const int s = (int)(a / c.V), i = (int)(a % c.V);
+        const bool valid = a < agents && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
+        if (!__syncthreads_or(valid)) continue;
+        if (!__any_sync(PIADMM_FULL, valid)) continue;
+        dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr);
+        if (sharded && valid) {       // fused exchange: this lane's point / control of the row, to every peer
+          const size_t po = ((size_t)s * c.V + i) * 2 * np1, uo = ((size_t)s * c.V + i) * N;
+          const int k = w.k;
+          const double px = k <= N ? c.b.pos[po + k] : 0.0, py = k <= N ? c.b.pos[po + np1 + k] : 0.0;
+          const double uk = k < N ? c.b.u[uo + k] : 0.0;
+          for (int r = 0; r < pc.world; r++) {
+            if (r == pc.rank) continue;
+            if (k <= N) { pc.pos[r][po + k] = px; pc.pos[r][po + np1 + k] = py; }
+            if (k < N) pc.u[r][uo + k] = uk;
+          }
+        }
+      }
+    }
+    coop_cross_barrier(grid, c, pc, epoch);
+    // ---- collision edges, casadi/main.py:110-118
+    for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {
+      const int s = (int)(a / c.V), i = (int)(a % c.V);
+      if (!c.b.done[s]) dev_slots_vehicle<true>(c, s, i, w.lane);
+    }
+    grid.sync();
+    for (long a = (long)tid; a < agents; a += (long)nth) {
+      const int s = (int)(a / c.V);
+      c.up_cnt[a] = c.b.done[s] ? 0 : dev_count_vehicle(c, s, (int)(a % c.V));
+    }
+    grid.sync();
+    {
+      const int chunks = (c.V + CTA_THREADS - 1) / CTA_THREADS;
+      for (long item = blockIdx.x; item < (long)c.S * chunks; item += gridDim.x) {
+        const int s = (int)(item / chunks), ch = (int)(item % chunks);
+        if (c.b.done[s]) continue;                                    // CTA uniform
+        const int32_t* uc = c.up_cnt + (size_t)s * c.V;
+        int part = 0;
+        for (int v = threadIdx.x; v < ch * CTA_THREADS; v += CTA_THREADS) part += uc[v];
+        int base, total;
+        cta_excl_scan(part, ish, &base);                              // base = edges of all lower vehicles
+        const int i = ch * CTA_THREADS + threadIdx.x;
+        const int cnt = i < c.V ? uc[i] : 0;
+        const int off = cta_excl_scan(cnt, ish, &total);
+        if (cnt > 0) dev_emit_vehicle(c, s, i, base + off, cnt);
+        if (ch == chunks - 1 && threadIdx.x == 0) dev_edges_done(c, s, base + total);
+      }
+    }
+    grid.sync();
+    // ---- edge problems + dual / PI update, casadi/main.py:121-162 (every edge with an owned endpoint)
+    {
+      const long pairs = (long)c.S * c.E, items = (pairs + pairs_per_cta<LPQ>() - 1) / pairs_per_cta<LPQ>();
+      for (long item = blockIdx.x; item < items; item += gridDim.x) {
+        const long pidx = item * pairs_per_cta<LPQ>() + w.pair_in_cta;
+        const int s = (int)(pidx / c.E), e = (int)(pidx % c.E);
+        // all pairs of this CTA lie in the same scenario or beyond its edge list: cheap CTA-uniform skip of the tail
+        if (pairs_per_cta<LPQ>() == 1 && (s >= c.S || c.b.done[s] || e >= c.b.edge_n[s])) continue;
+        bool valid = s < c.S && !c.b.done[s] && e < c.b.edge_n[s];
+        const int32_t* eij = c.b.edge_ij + ((size_t)s * c.E + e) * 2;
+        const int32_t* esl = c.b.edge_slot + ((size_t)s * c.E + e) * 2;
+        int v0 = -1, v1 = -1;
+        if (valid) {
+          v0 = eij[0]; v1 = eij[1];
+          valid = v0 >= 0 && ((v0 >= c.own_lo && v0 < c.own_hi) || (v1 >= c.own_lo && v1 < c.own_hi));
+        }
+        if (!__syncthreads_or(valid)) continue;
+        if (!valid) continue;                     // LPQ==16 only: the other pair of the CTA works alone
+        dev_z_update<LPQ, false, true>(c, s, e, v0, v1, esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane,
+                                       w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr, true);
+        if (sharded && w.k == 0 && v0 >= c.own_lo && v0 < c.own_hi) {   // residual terms of this half, to every peer
+          const size_t eo = ((size_t)s * c.E + e) * 4;
+          const double ss = c.edge_res[eo + w.half], rr = c.edge_res[eo + 2 + w.half];
+          for (int r = 0; r < pc.world; r++) {
+            if (r == pc.rank) continue;
+            pc.edge_res[r][eo + w.half] = ss; pc.edge_res[r][eo + 2 + w.half] = rr;
+          }
+        }
+      }
+    }
+    coop_cross_barrier(grid, c, pc, epoch);
+    // ---- residuals + stop test, casadi/main.py:165-181
+    for (int s = blockIdx.x; s < c.S; s += gridDim.x) {
+      if (c.b.done[s]) continue;
+      dev_res_all(c, s, it, ca.n_active + (it & 1), red, ish);
+    }
+    grid.sync();
+    if (*reinterpret_cast<volatile int*>(ca.n_active + (it & 1)) == 0) break;     // grid uniform
+  }
+  if (sharded) {
+    // results into the caller's buffers (the exchange block is overwritten by the peers' next step), then one more
+    // barrier over all ranks: nobody starts the next step before everybody has copied out
+    const size_t n_pos = (size_t)agents * 2 * np1, n_u = (size_t)agents * N;
+    if (pc.user_pos) for (size_t t = tid; t < n_pos; t += nth) pc.user_pos[t] = c.b.pos[t];
+    if (pc.user_u) for (size_t t = tid; t < n_u; t += nth) pc.user_u[t] = c.b.u[t];
+    coop_cross_barrier(grid, c, pc, epoch);
+    if (tid == 0) *pc.epoch = epoch;
+  }
+}

@@ -39,9 +39,12 @@ struct DevCtx {
   const double* W;                         // [2][LPQ*LPQ]: M'M and D2'D2, zero padded, row stride LPQ
   double* edge_res;                        // [S,E,4] ss0, ss1, rr0, rr1 of the current outer iteration
   double* rho_new;                         // [S] penalty chosen by the last edge (dual_mode PI_OLD)
-  uint32_t* hits;                          // [S,V,ceil(V/32)] collision bit matrix
-  int32_t* up_cnt;                         // [S,V] edges (i,j>i) detected per vehicle
-  double* bbox;                            // [S,V,4] trajectory bounding boxes (xmin,xmax,ymin,ymax)
+  uint32_t* hits;                          // [S,V,ceil(V/32)] collision bit matrix (matrix detection modes)
+  uint32_t* cand;                          // [S,V,ceil(V/32)] candidate pairs of this MPC step (piadmm_detect.cuh)
+  uint8_t* slot_hit;                       // [S,V,D] the partner in this slot collides in the current outer iteration
+  int32_t* up_cnt;                         // [S,V] edges (i,j>i) of the current outer iteration per vehicle
+  double* bbox;                            // [S,V,4] trajectory bounding boxes (xmin,xmax,ymin,ymax) / reach discs (x0,y0,R,0)
+  int detect_mode;                         // 0 candidate rows (default), 1 full pair test lane-per-pair, 2 thread-per-word
   int* dist_bad;                           // [S] MATLAB :202 distance stop test failed
   int i_iter;                              // outer iteration index (phase API)
   int own_lo, own_hi;                      // vehicles x-updated by this rank (multi-GPU vehicle sharding)

@@ -108,6 +108,21 @@ class PIADMMSolver:
         self._check(self.lib.piadmm_set_ownership(self._h, int(lo), int(hi)), "piadmm_set_ownership")
         self.own = (int(lo), int(hi))
 
+    def peer_export(self) -> bytes:
+        """CUDA IPC handle of this rank's exchange block (piadmm_peer_export)."""
+        buf = C.create_string_buffer(_abi.PEER_HANDLE_BYTES)
+        self._check(self.lib.piadmm_peer_export(self._h, buf), "piadmm_peer_export")
+        return buf.raw
+
+    def peer_connect(self, rank: int, world: int, handles: bytes):
+        """Map the exchange blocks of all ranks (`handles` = world x PEER_HANDLE_BYTES, rank order)."""
+        assert len(handles) == world * _abi.PEER_HANDLE_BYTES
+        self._check(self.lib.piadmm_peer_connect(self._h, int(rank), int(world), C.c_char_p(handles)),
+                    "piadmm_peer_connect")
+
+    def peer_disconnect(self):
+        self._check(self.lib.piadmm_peer_disconnect(self._h), "piadmm_peer_disconnect")
+
     def residual_partials(self):
         self._check(self.lib.piadmm_residual_partials(self._h, self._stream()), "piadmm_residual_partials")
 

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define PIADMM_ABI_VERSION 2
+#define PIADMM_ABI_VERSION 3
 
 enum {
   PIADMM_OK = 0,
@@ -156,6 +156,19 @@ int piadmm_residual_decide(piadmm_handle* h, void* stream);
 int piadmm_num_active(piadmm_handle* h, void* stream, int32_t* host_out); /* scenarios with done==0 (syncs) */
 int piadmm_step(piadmm_handle* h, void* stream);         /* begin_step + all outer iterations, persistent kernel */
 int piadmm_plant_step(piadmm_handle* h, void* stream);
+
+/* Vehicle-sharded multi-GPU step without NCCL in the data path (config 5; there is no reference counterpart: the
+ * reference's "communication" is Python variable passing, casadi/main.py:75-77).  Every rank creates a handle for the
+ * whole scene (S == 1), sets its ownership range, exports a library-owned exchange block as a CUDA IPC handle
+ * (PIADMM_PEER_HANDLE_BYTES bytes), the caller all-gathers the handles of all ranks (torch.distributed) and every rank
+ * maps its peers' blocks.  piadmm_step then runs the persistent cooperative kernel on every rank: owned pos_old /
+ * primal_u rows and per-edge residual terms are stored straight into the peers' blocks over NVLink, two of the grid
+ * barriers per outer iteration span all ranks (flags in peer memory).  All ranks must call piadmm_step collectively.
+ * A peer that does not arrive within PIADMM_PEER_TIMEOUT_MS (default 20000) sets PIADMM_ST_PEER_TIMEOUT. */
+#define PIADMM_PEER_HANDLE_BYTES 64
+int piadmm_peer_export(piadmm_handle* h, void* handle_out);
+int piadmm_peer_connect(piadmm_handle* h, int rank, int world, const void* handles /* world x PIADMM_PEER_HANDLE_BYTES */);
+int piadmm_peer_disconnect(piadmm_handle* h);
 
 /* host-buffer convenience path (what a ctypes caller without torch uses; copies inside):
  * runs begin_step + the whole outer loop + plant step for host inputs and returns host outputs. */

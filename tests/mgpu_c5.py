@@ -1,63 +1,80 @@
-"""Multi-GPU check (run under torchrun on N GPUs, NCCL): config-5-style vehicle-sharded consensus
-over NVLink against the oracle's C twin, and config-4 scenario sharding.  Not collected by pytest
-(needs >1 GPU):  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/mgpu_c5.py"""
+"""Multi-GPU check + timing of the vehicle-sharded coupled step (BASELINE config 5), run under torchrun:
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node G --master-addr 127.0.0.1 --master-port 29511 tests/mgpu_c5.py
+
+For both exchanges (peer-mapped persistent kernel, NCCL baseline): the full 4096-vehicle scene on G ranks against the
+oracle's C twin (rank 0 computes it, everybody compares), results bit-identical across ranks, then device-timed steps
+(L2 flushed, barrier on both sides, max over ranks).  One JSON line per exchange on rank 0.  Not collected by pytest
+(no test_ prefix): pytest's multi-rank case is tests/test_gpu_coupled.py::test_vehicle_sharded_two_ranks_equal_twin."""
+import json
 import os
 import sys
-import time
 
 import numpy as np
 import torch
 import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import bench  # noqa: E402
+from pi_admm_b200.parallel import VehicleShardedSolver, cut_edges  # noqa: E402
+from util import rel_err  # noqa: E402
 
 
 def main():
-    rank = int(os.environ["RANK"]); local = int(os.environ["LOCAL_RANK"]); world = int(os.environ["WORLD_SIZE"])
+    rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(local)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    from oracle import ctwin
-    from util import make_params, rel_err
-    from pi_admm_b200.parallel import VehicleShardedSolver
-    from pi_admm_b200.scenarios import c3_intersection, c5_grid
-    V, N, D = 64, 30, 8
-    p = make_params("matlab_pi", "default", num_ho=N, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5,
-                    al_all=0, iter_num=12)
-    xt, spd, rw = c3_intersection(V=V, N=N)
-    vs = VehicleShardedSolver(p, V, D, device=local)
-    vs.setup(xt, spd, rw)
-    vs.iterate()
-    torch.cuda.synchronize()
-    got = vs.sol.to_numpy()
-    ref = ctwin.step(p, xt, spd, rw, D=D)
-    ok = np.array_equal(got["n_outer"], ref["n_outer"]) and np.array_equal(got["curr_iter"], ref["curr_iter"])
-    errs = {k: rel_err(got[k], ref[k]) for k in ("u", "pos", "err_rk", "err_sk")}
-    errs["hat_owned"] = rel_err(got["hat"][:, vs.lo:vs.hi], ref["hat"][:, vs.lo:vs.hi])
-    ok = ok and max(errs.values()) <= 1e-6
-    print(f"[rank {rank}/{world}] c3-sharded V={V}: ok={ok} n_outer={got['n_outer']} edges={int(ref['n_edge_solves'][0])} errs={errs}", flush=True)
-    # config 5 at full size: timing of the coupled step (device events, max over ranks)
-    xt, spd, rw = c5_grid(N=30)
-    V5 = xt.shape[1]
-    vs5 = VehicleShardedSolver(p, V5, 8, device=local)
-    vs5.setup(xt, spd, rw)
-    vs5.iterate()                       # warm-up
-    torch.cuda.synchronize(); dist.barrier()
-    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    e0.record(); vs5.iterate(); e1.record(); torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    g5 = vs5.sol.to_numpy()
-    solves = torch.tensor([float(g5["n_veh_solves"][0])], device="cuda", dtype=torch.float64)
-    dist.all_reduce(solves)
+    name = os.environ.get("MGPU_SCENE", "c5")
+    steps = int(os.environ.get("MGPU_STEPS", "10"))
+    (xt, spd, refwin), V, N, D = bench.coupled_scene(name)
+    p = bench.coupled_params(N)
+    ref = None
     if rank == 0:
-        print(f"c5 V={V5} N=30 on {world} GPUs: {ms.item():.2f} ms per coupled MPC step, n_outer={int(g5['n_outer'][0])}, "
-              f"agent-QP solves={int(solves.item())} -> {solves.item() / ms.item() * 1e3:.3e} solves/s, "
-              f"edges last iter={int(g5['edge_n'][0])}, status={int(g5['status'][0])}", flush=True)
-    allok = torch.tensor([1.0 if ok else 0.0], device="cuda")
-    dist.all_reduce(allok, op=dist.ReduceOp.MIN)
-    dist.barrier(); dist.destroy_process_group()
-    sys.exit(0 if allok.item() == 1.0 else 1)
+        from oracle import ctwin
+        ref = ctwin.step(p, xt, spd, refwin, D=D, nthreads=len(os.sched_getaffinity(0)))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")
+    stream = torch.cuda.current_stream()
+    for exchange in ("peer", "nccl"):
+        vs = VehicleShardedSolver(p, V, D, device=local, exchange=exchange)
+        vs.setup(xt, spd, refwin)
+        for _ in range(3):
+            vs.iterate()
+        vs.plant_step()
+        out = vs.results()
+        # bit-identical across ranks: compare a checksum of u / pos / histories
+        h = torch.tensor([float(np.frombuffer(out[k].tobytes(), dtype=np.uint8).astype(np.float64).sum()) for k in ("u", "pos", "err_rk")],
+                         dtype=torch.float64, device=f"cuda:{local}")
+        hs = [torch.zeros_like(h) for _ in range(world)]
+        dist.all_gather(hs, h)
+        same = all(bool(torch.equal(hs[0], x)) for x in hs)
+        ms = []
+        for _ in range(steps):
+            flush.fill_(1)
+            dist.barrier(); torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream); vs.iterate(); b.record(stream)
+            torch.cuda.synchronize()
+            ms.append(a.elapsed_time(b))
+        t = torch.tensor([float(np.mean(ms))], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            err = {k: rel_err(out[k], ref[k]) for k in ("u", "pos", "xt_next", "err_rk", "err_sk")}
+            ok = (np.array_equal(out["n_outer"], ref["n_outer"]) and np.array_equal(out["edge_n"], ref["edge_n"])
+                  and max(err.values()) <= 1e-6 and same)
+            n = int(ref["edge_n"][0])
+            print(json.dumps({"scene": name, "world": world, "exchange_requested": exchange, "exchange": vs.exchange,
+                              "note": vs.exchange_note, "ms_per_step": float(t.item()), "outer_iters": int(out["n_outer"][0]),
+                              "status": int(out["status"][0]), "parity_vs_cpu_port": ok, "rel_err": err,
+                              "identical_across_ranks": same,
+                              "cut_edges_last_iter": cut_edges(vs.perm, ref["edge_ij"][0, :n], world)}), flush=True)
+            assert ok, (exchange, err, same)
+        dist.barrier()
+        vs.close()
+    dist.destroy_process_group()
 
 
 if __name__ == "__main__":
