@@ -27,7 +27,7 @@ class Params(C.Structure):
         "in_rho0", "in_sigma", "in_alpha", "in_eps_abs", "in_eps_rel", "in_adapt_tol")] + [(n, _I) for n in (
         "num_ho", "iter_num", "dual_mode", "thr_squared", "dual_res_alias", "stop_dist_test",
         "pos_nonlinear", "curr_iter_latest", "round_u", "round_edge", "al_all", "always_edge",
-        "residual_global", "PI", "windup", "trad", "in_max_iter", "in_check", "in_adaptive")]
+        "residual_global", "PI", "windup", "trad", "in_max_iter", "in_check", "in_adaptive", "x_memo")]
 
     def copy(self):
         o = Params()
@@ -101,7 +101,7 @@ def default_params() -> Params:
              num_ho=15, iter_num=100, dual_mode=DUAL_PLAIN, thr_squared=0, dual_res_alias=1,
              stop_dist_test=0, pos_nonlinear=0, curr_iter_latest=0, round_u=4, round_edge=4, al_all=1,
              always_edge=0, residual_global=0, PI=1, windup=1, trad=0, in_max_iter=4000, in_check=25,
-             in_adaptive=1)
+             in_adaptive=1, x_memo=1)
     return p
 
 

@@ -75,21 +75,12 @@ __device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) { load_tabs
 __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
   const int N = c.N;
-  const size_t n_slot = (size_t)c.S * c.V * c.D * 2 * (N + 1);
-  for (size_t t = tid; t < n_slot; t += nth) {
-    c.b.hat[t] = 0.0; c.b.dual[t] = 0.0; c.b.integ[t] = 0.0; c.b.diff[t] = 0.0; c.b.last_hat[t] = 0.0;
-  }
+  dev_begin_slots(c, tid >> 5, nth >> 5, threadIdx.x & 31);
+  for (size_t t = tid; t < (size_t)c.S * c.V; t += nth) c.veh_dirty[t] = 1;
   const size_t n_pos = (size_t)c.S * c.V * 2 * (N + 1);
   for (size_t t = tid; t < n_pos; t += nth) c.b.pos[t] = 0.0;
   const size_t n_u = (size_t)c.S * c.V * N;
   for (size_t t = tid; t < n_u; t += nth) c.b.u[t] = 0.0;
-  const size_t n_nbr = (size_t)c.S * c.V * c.D;
-  for (size_t t = tid; t < n_nbr; t += nth) {
-    const int d = (int)(t % c.D), i = (int)((t / c.D) % c.V);
-    int j = -1;
-    if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;
-    c.b.nbr[t] = j;
-  }
   const size_t n_h = (size_t)c.S * c.I;
   for (size_t t = tid; t < n_h; t += nth) { c.b.err_rk[t] = 0.0; c.b.err_sk[t] = 0.0; }
   for (size_t t = tid; t < (size_t)c.S; t += nth) {
@@ -112,11 +103,13 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? X16_MIN_CTAS : X32_MI
   for (long item = blockIdx.x; item < items; item += gridDim.x) {       // persistent CTAs, grid-stride
     const long a = item * groups_per_cta<LPQ>() + w.group_in_cta;
     const int s = (int)(a / c.V), i = (int)(a % c.V);
-    const bool valid = a < agents && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
+    bool valid = a < agents && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
+    if (valid && dev_memo_on(c)) valid = c.veh_dirty[a] != 0;       // unchanged QP: u / pos_old stay as they are
     if (!__syncthreads_or(valid)) continue;  // nothing to do for the whole CTA
     if (!loaded) { load_tabs<LPQ>(c, Wsm, 0, 2); loaded = true; }
     if (!__any_sync(PIADMM_FULL, valid)) continue;
     dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr);
+    if (valid && w.k == 0) c.veh_dirty[a] = 0;
   }
 }
 
@@ -278,6 +271,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? Z16_MIN_CTAS : Z32_MI
     if (!valid) continue;                     // LPQ==16 only: the other pair of the CTA works alone
     dev_z_update<LPQ, false, true>(c, s, e, eij[0], eij[1], esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane, w.half,
                              Wsm, gbuf[w.group_in_cta], xch, nullptr, true);
+    if (w.k == 0) c.veh_dirty[(size_t)s * c.V + eij[w.half]] = 1;       // this endpoint's QP changed
   }
 }
 
@@ -608,10 +602,13 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
     const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
     dist_ok = sqrt(dx * dx + dy * dy) > p.dis_thres;
   }
+  const bool memo = dev_memo_on(c);
+  bool dirty = true;                            // x_memo: both QPs change together (one edge) or not at all
 #pragma unroll 1
   for (int i_iter = 0; i_iter < c.I; i_iter++) {
     n_outer++;
-    dev_x_update<LPQ, KS>(c, s, i, true, k, w.lane, half, Wsm, gbuf, xch, krow);
+    if (dirty || !memo) dev_x_update<LPQ, KS>(c, s, i, true, k, w.lane, half, Wsm, gbuf, xch, krow);
+    dirty = false;
     pair_sync<LPQ>();
     // ---- collision test, casadi/main.py:110-118
     bool near = false;
@@ -629,6 +626,7 @@ __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Wh
     if (hit) {
       if (k == 0) c.b.nbr[(size_t)s * 2 + i] = j;
       dev_z_update<LPQ, KS>(c, s, 0, 0, 1, 0, 0, true, true, k, w.lane, half, Wsm, gbuf, xch, krow, true);
+      dirty = true;
       pair_sync<LPQ>();
       const double* er = c.edge_res + (size_t)s * c.E * 4;
       const double rho = p.dual_mode == PIADMM_DUAL_PI_OLD ? c.rho_new[s] : c.b.rho_s[s];
@@ -804,7 +802,7 @@ void piadmm_default_params(piadmm_params* p) {
   p->thr_squared = 0; p->dual_res_alias = 1; p->stop_dist_test = 0; p->pos_nonlinear = 0;
   p->curr_iter_latest = 0; p->round_u = 4; p->round_edge = 4; p->al_all = 1; p->always_edge = 0;
   p->residual_global = 0; p->PI = 1; p->windup = 1; p->trad = 0;
-  p->in_max_iter = 4000; p->in_check = 25; p->in_adaptive = 1;
+  p->in_max_iter = 4000; p->in_check = 25; p->in_adaptive = 1; p->x_memo = 1;
 }
 
 const char* piadmm_last_error(const piadmm_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
@@ -902,6 +900,8 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     else if (e && strcmp(e, "matrix") == 0) h->c.detect_mode = (long)S * V * words <= 9472 ? 1 : 2;
     else if (!e && e2 && atoi(e2) >= 1 && atoi(e2) <= 2) h->c.detect_mode = atoi(e2);
   }
+  if ((ce = cudaMalloc(&h->c.veh_dirty, (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_dirty");
+  if ((ce = cudaMemset(h->c.veh_dirty, 1, (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_dirty");
   if ((ce = cudaMalloc(&h->c.up_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "up_cnt");
   if ((ce = cudaMalloc(&h->c.bbox, sizeof(double) * 4 * (size_t)S * V)) != cudaSuccess) return fail(ce, "bbox");
   if ((ce = cudaMalloc(&h->c.dist_bad, sizeof(int) * (size_t)S)) != cudaSuccess) return fail(ce, "dist_bad");
@@ -992,7 +992,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
   cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
   for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
   piadmm_peer_disconnect(h);
@@ -1025,6 +1025,7 @@ int piadmm_bind(piadmm_handle* h, const piadmm_buffers* b) {
   for (size_t i = 0; i < sizeof(piadmm_buffers) / sizeof(void*); i++)
     if (!ptrs[i]) { h->err = "piadmm_bind: NULL buffer at field index " + std::to_string(i); return PIADMM_E_UNBOUND; }
   h->c.b = *b;
+  h->c.slots_dirty = 1;
   h->bound = true;
   drop_graph(h);
   return PIADMM_OK;
@@ -1061,6 +1062,7 @@ int piadmm_begin_step(piadmm_handle* h, void* stream) {
   h->c.i_iter = 0;
   k_begin_step<<<h->sm_count * 4, 256, 0, st>>>(h->c);
   LAUNCHED();
+  h->c.slots_dirty = 0;
   if (h->c.detect_mode == 0) return build_candidates(h, st);   // (the fused V=2 kernel never comes through here)
   return PIADMM_OK;
 }
@@ -1323,6 +1325,7 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
   if (h->lpq == 16) CK(cudaLaunchCooperativeKernel((void*)k_coop<16>, dim3(grid), dim3(CTA_THREADS), args, 0, st));
   else CK(cudaLaunchCooperativeKernel((void*)k_coop<32>, dim3(grid), dim3(CTA_THREADS), args, 0, st));
   LAUNCHED();
+  h->c.slots_dirty = 0;
   return PIADMM_OK;
 }
 

@@ -86,6 +86,9 @@ __device__ __forceinline__ void coop_cross_barrier(cg::grid_group& grid, const D
 // distance test, stop decision, histories, alias latch, last_iter_hat_pos copy (:174-181).  The sums are formed as 128
 // strided partial sums and one binary tree whatever the CTA size, so k_res_all (128 / 1024 threads) and the cooperative
 // kernel (64 threads) produce bit-identical histories.  red: 2 x 128 doubles, ish: 2 ints of shared memory.
+// COPY = false: the last_hat copy is left to the caller (the cooperative kernel spreads it over the whole grid:
+// ~45 000 elements behind two dependent index loads are 0.7 ms for the 64 threads of one CTA at config 5).
+template <bool COPY = true>
 __device__ __forceinline__ void dev_res_all(const DevCtx& c, int s, int i_iter, int* cnt, double (*red)[128], int* ish) {
   const piadmm_params& p = c.p;
   const int N = c.N, T = blockDim.x, t = threadIdx.x;
@@ -137,7 +140,7 @@ __device__ __forceinline__ void dev_res_all(const DevCtx& c, int s, int i_iter, 
     ish[1] = conv ? 1 : 0;
   }
   __syncthreads();
-  if (!ish[1]) {       // last_iter_hat_pos = hat_pos_old: only the slots of this iteration's edges changed
+  if (COPY && !ish[1]) {       // last_iter_hat_pos = hat_pos_old: only the slots of this iteration's edges changed
     const int per = 2 * (N + 1);
     for (int q = t; q < n * 2 * per; q += T) {
       const int e = q / (2 * per), side = (q / per) & 1, el = q % per;
@@ -173,15 +176,13 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
   const long agents = (long)c.S * c.V;
   const int words = (c.V + 31) / 32;
   unsigned long long epoch = sharded ? *pc.epoch : 0ull;
+  const bool memo = dev_memo_on(c);
   load_tabs<LPQ>(c, Wsm, 0, PIADMM_NTAB);                // (ends with a CTA barrier)
 
   // ---- phase 0: casadi/main.py:52-72.  pos / u are only zeroed for the owned vehicles: the rows of the others are
   // written by their owners' x phase, which may already be running on a faster rank.
   {
-    const size_t n_slot = (size_t)agents * c.D * 2 * np1;
-    for (size_t t = tid; t < n_slot; t += nth) {
-      c.b.hat[t] = 0.0; c.b.dual[t] = 0.0; c.b.integ[t] = 0.0; c.b.diff[t] = 0.0; c.b.last_hat[t] = 0.0;
-    }
+    dev_begin_slots(c, tid >> 5, nth >> 5, w.lane);
     const size_t own_n = (size_t)(c.own_hi - c.own_lo);
     for (size_t t = tid; t < (size_t)c.S * own_n * 2 * np1; t += nth) {
       const size_t s = t / (own_n * 2 * np1), r = t % (own_n * 2 * np1);
@@ -191,13 +192,6 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
       const size_t s = t / (own_n * N), r = t % (own_n * N);
       c.b.u[(s * c.V + c.own_lo) * N + r] = 0.0;
     }
-    for (size_t t = tid; t < (size_t)agents * c.D; t += nth) {
-      const int d = (int)(t % c.D), i = (int)((t / c.D) % c.V);
-      int j = -1;
-      if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;
-      c.b.nbr[t] = j;
-      c.slot_hit[t] = 0;
-    }
     for (size_t t = tid; t < (size_t)c.S * c.I; t += nth) { c.b.err_rk[t] = 0.0; c.b.err_sk[t] = 0.0; }
     for (size_t t = tid; t < (size_t)c.S; t += nth) {
       c.b.flag[t] = 0; c.b.done[t] = 0; c.b.aliased[t] = 0; c.b.curr_iter[t] = 1; c.b.n_outer[t] = 0;
@@ -206,7 +200,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
       c.rho_new[t] = c.b.rho_s[t];
       c.dist_bad[t] = 0;
     }
-    for (size_t t = tid; t < (size_t)agents; t += nth) dev_disc_vehicle(c, (long)t);
+    for (size_t t = tid; t < (size_t)agents; t += nth) { dev_disc_vehicle(c, (long)t); c.veh_dirty[t] = 1; }
   }
   grid.sync();
   for (size_t t = tid; t < (size_t)agents * words; t += nth) {
@@ -219,16 +213,33 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
 #pragma unroll 1
   for (int it = 0; it < c.I; it++) {
     if (tid == 0) ca.n_active[it & 1] = 0;
+    if (it > 0) {
+      // last_iter_hat_pos = hat_pos_old (casadi/main.py:180) for the scenarios that go on, spread over the grid; the
+      // edge list of the previous iteration is intact until the edges phase, last_hat is next read in the z phase
+      const int per = 2 * np1;
+      for (int s = 0; s < c.S; s++) {
+        if (c.b.done[s]) continue;
+        const size_t tot = (size_t)c.b.edge_n[s] * 2 * per;
+        for (size_t q = tid; q < tot; q += nth) {
+          const int e = (int)(q / (2 * per)), side = (int)((q / per) & 1), el = (int)(q % per);
+          const int v = c.b.edge_ij[((size_t)s * c.E + e) * 2 + side];
+          const size_t o = ((((size_t)s * c.V + v) * c.D) + c.b.edge_slot[((size_t)s * c.E + e) * 2 + side]) * per + el;
+          c.b.last_hat[o] = c.b.hat[o];
+        }
+      }
+    }
     // ---- x-update of the owned vehicles, casadi/main.py:81-106
     {
       const long items = (agents + groups_per_cta<LPQ>() - 1) / groups_per_cta<LPQ>();
       for (long item = blockIdx.x; item < items; item += gridDim.x) {
         const long a = item * groups_per_cta<LPQ>() + w.group_in_cta;
         const int s = (int)(a / c.V), i = (int)(a % c.V);
-        const bool valid = a < agents && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
+        bool valid = a < agents && !c.b.done[s] && i >= c.own_lo && i < c.own_hi;
+        if (valid && memo) valid = c.veh_dirty[a] != 0;             // unchanged QP: u / pos_old (here and on the peers) stay
         if (!__syncthreads_or(valid)) continue;
         if (!__any_sync(PIADMM_FULL, valid)) continue;
         dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr);
+        if (valid && w.k == 0) c.veh_dirty[a] = 0;
         if (sharded && valid) {       // fused exchange: this lane's point / control of the row, to every peer
           const size_t po = ((size_t)s * c.V + i) * 2 * np1, uo = ((size_t)s * c.V + i) * N;
           const int k = w.k;
@@ -292,6 +303,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
         if (!valid) continue;                     // LPQ==16 only: the other pair of the CTA works alone
         dev_z_update<LPQ, false, true>(c, s, e, v0, v1, esl[0], esl[1], e == c.b.edge_n[s] - 1, true, w.k, w.lane,
                                        w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr, true);
+        if (w.k == 0) c.veh_dirty[(size_t)s * c.V + (w.half ? v1 : v0)] = 1;      // this endpoint's QP changed
         if (sharded && w.k == 0 && v0 >= c.own_lo && v0 < c.own_hi) {   // residual terms of this half, to every peer
           const size_t eo = ((size_t)s * c.E + e) * 4;
           const double ss = c.edge_res[eo + w.half], rr = c.edge_res[eo + 2 + w.half];
@@ -306,7 +318,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
     // ---- residuals + stop test, casadi/main.py:165-181
     for (int s = blockIdx.x; s < c.S; s += gridDim.x) {
       if (c.b.done[s]) continue;
-      dev_res_all(c, s, it, ca.n_active + (it & 1), red, ish);
+      dev_res_all<false>(c, s, it, ca.n_active + (it & 1), red, ish);
     }
     grid.sync();
     if (*reinterpret_cast<volatile int*>(ca.n_active + (it & 1)) == 0) break;     // grid uniform

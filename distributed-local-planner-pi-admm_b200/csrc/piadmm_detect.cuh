@@ -27,6 +27,36 @@ __host__ __device__ inline double reach_radius(const piadmm_params& p, int N, do
   return sqrt(s * s + lat * lat) * (1.0 + 1e-9) + 1e-9;
 }
 
+// casadi/main.py:56-63 for the per-slot arrays (hat, dual, integ, diff, last_hat = 0) and the slot tables, one WARP per
+// slot.  Only slots that were allocated in the previous step (nbr >= 0) are written: an unallocated slot is never
+// touched by any phase, so it still holds the zeros of the step before (invariant: nbr < 0  =>  the slot is zero;
+// slots_dirty forces the full pass after piadmm_bind).  Config 5 has 32768 slots of 2.5 KB and a few hundred in use:
+// 81 MB of stores per MPC step become < 2 MB.
+__device__ __forceinline__ void dev_begin_slots(const DevCtx& c, size_t warp_id, size_t n_warps, int lane) {
+  const int per = 2 * (c.N + 1);
+  const size_t n_slots = (size_t)c.S * c.V * c.D;
+  for (size_t t = warp_id; t < n_slots; t += n_warps) {
+    const bool used = c.slots_dirty || c.b.nbr[t] >= 0;
+    __syncwarp();
+    if (used) {
+      for (int el = lane; el < per; el += 32) {
+        const size_t o = t * per + el;
+        c.b.hat[o] = 0.0; c.b.dual[o] = 0.0; c.b.integ[o] = 0.0; c.b.diff[o] = 0.0; c.b.last_hat[o] = 0.0;
+      }
+    }
+    if (lane == 0) {
+      const int d = (int)(t % c.D), i = (int)((t / c.D) % c.V);
+      int j = -1;
+      if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;      // AL over every j != i: slots pre-assigned, ascending
+      c.b.nbr[t] = j;
+      c.slot_hit[t] = 0;
+    }
+  }
+}
+
+// x_memo (include/piadmm.h): solve vehicle a in this outer iteration?
+__device__ __forceinline__ bool dev_memo_on(const DevCtx& c) { return c.p.x_memo && c.p.dual_mode != PIADMM_DUAL_PI_OLD; }
+
 // disc[s,i] = (x0, y0, reach, 0) of vehicle (s,i); stored in DevCtx::bbox (unused by the candidate path)
 __device__ __forceinline__ void dev_disc_vehicle(const DevCtx& c, long a) {
   const double* xt = c.b.xt + a * 3;

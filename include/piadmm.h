@@ -86,6 +86,11 @@ typedef struct piadmm_params {
   int32_t residual_global; /* old main.py:154-155 */
   int32_t PI, windup, trad;/* MATLAB :24-25 ; old main.py:18 */
   int32_t in_max_iter, in_check, in_adaptive;
+  int32_t x_memo;          /* 1: a vehicle QP whose inputs did not change since its last solve in this MPC step (no slot of
+                              the vehicle was touched by an edge problem) is not solved again -- the reference re-solves
+                              every vehicle in every outer iteration (casadi/main.py:81) and gets the identical u; exact.
+                              n_veh_solves / veh_inner then count the solves that were executed.  Off with dual_mode PI_OLD
+                              (rho changes between iterations). */
 } piadmm_params;
 
 /* Device buffers owned by the caller.  Shapes in comments. */

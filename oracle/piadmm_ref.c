@@ -385,7 +385,7 @@ void piadmm_ref_default_params(piadmm_params* p) {
   p->thr_squared = 0; p->dual_res_alias = 1; p->stop_dist_test = 0; p->pos_nonlinear = 0;
   p->curr_iter_latest = 0; p->round_u = 4; p->round_edge = 4; p->al_all = 1; p->always_edge = 0;
   p->residual_global = 0; p->PI = 1; p->windup = 1; p->trad = 0;
-  p->in_max_iter = 4000; p->in_check = 25; p->in_adaptive = 1;
+  p->in_max_iter = 4000; p->in_check = 25; p->in_adaptive = 1; p->x_memo = 1;
 }
 
 /* ---- indexing helpers over the piadmm_buffers layout (host pointers here) ---- */
@@ -457,28 +457,37 @@ static void x_update_vehicle(const piadmm_params* p, const consts_t* c, const pi
 
 /* `pool` = one half_t pair per OpenMP thread; inner != 0: the vehicles of this ONE scenario are spread over the
  * threads (coupled scenes, S < threads), else the caller already runs scenarios in parallel */
+/* x_memo: dirty[i] != 0 <=> the QP of vehicle i changed since its last solve in this MPC step (set for everybody at the
+ * start of the step and by every edge problem for its two endpoints); clean vehicles keep u / pos_old as they are */
+static int memo_on(const piadmm_params* p) { return p->x_memo && p->dual_mode != PIADMM_DUAL_PI_OLD; }
+
 static void x_update_scenario(const piadmm_params* p, const consts_t* c, const piadmm_buffers* b, int s, int V,
-                              int D, half_t** pool, int inner) {
-  long tot_it = 0; int any_st = 0, max_it = 0;
+                              int D, half_t** pool, int inner, uint8_t* dirty) {
+  long tot_it = 0; int any_st = 0, max_it = 0, n_solved = 0;
+  const int memo = memo_on(p);
   if (inner) {
-#pragma omp parallel for schedule(dynamic, 8) reduction(+ : tot_it) reduction(| : any_st) reduction(max : max_it)
+#pragma omp parallel for schedule(dynamic, 8) reduction(+ : tot_it, n_solved) reduction(| : any_st) reduction(max : max_it)
     for (int i = 0; i < V; i++) {
       int it, st;
+      if (memo && !dirty[i]) continue;
+      dirty[i] = 0;
       x_update_vehicle(p, c, b, s, i, V, D, pool[2 * omp_thread_id()], &it, &st);
-      tot_it += it; any_st |= st;
+      tot_it += it; any_st |= st; n_solved++;
       if (it > max_it) max_it = it;
     }
   } else {
     for (int i = 0; i < V; i++) {
       int it, st;
+      if (memo && !dirty[i]) continue;
+      dirty[i] = 0;
       x_update_vehicle(p, c, b, s, i, V, D, pool[2 * omp_thread_id()], &it, &st);
-      tot_it += it; any_st |= st;
+      tot_it += it; any_st |= st; n_solved++;
       if (it > max_it) max_it = it;
     }
   }
   if (getenv("PIADMM_REF_DEBUG"))
-    fprintf(stderr, "[ref] scenario %d outer %d: %d vehicle QPs, inner iterations sum %ld max %d\n", s, (int)b->n_outer[s], V, tot_it, max_it);
-  b->veh_inner[s] += tot_it; b->n_veh_solves[s] += V;
+    fprintf(stderr, "[ref] scenario %d outer %d: %d vehicle QPs, inner iterations sum %ld max %d\n", s, (int)b->n_outer[s], n_solved, tot_it, max_it);
+  b->veh_inner[s] += tot_it; b->n_veh_solves[s] += n_solved;
   if (any_st) b->status[s] |= PIADMM_ST_VEH_MAXITER;
 }
 
@@ -637,15 +646,19 @@ static void z_update_edge(const piadmm_params* p, const consts_t* c, const piadm
 }
 
 static void z_update_scenario(const piadmm_params* p, const consts_t* c, const piadmm_buffers* b, int s, int V,
-                              int D, int E, half_t** pool, int inner) {
+                              int D, int E, half_t** pool, int inner, uint8_t* dirty) {
   const int n = b->edge_n[s];
+  for (int e = 0; e < n; e++) {
+    dirty[b->edge_ij[((size_t)s * E + e) * 2]] = 1; dirty[b->edge_ij[((size_t)s * E + e) * 2 + 1]] = 1;
+  }
   double rho_next = b->rho_s[s];
   long tot_it = 0; int any_st = 0, max_it = 0;
+  const int outer_tid = omp_thread_id();      /* !inner: the region below is serialised and would report thread 0 */
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : tot_it) reduction(| : any_st) reduction(max : max_it) if (inner)
   for (int e = 0; e < n; e++) {
     int it, st;
     double rn = 0.0;
-    half_t** hp = pool + 2 * omp_thread_id();
+    half_t** hp = pool + 2 * (inner ? omp_thread_id() : outer_tid);
     z_update_edge(p, c, b, s, e, V, D, E, hp[0], hp[1], &it, &st, &rn);
     tot_it += it; any_st |= st;
     if (it > max_it) max_it = it;
@@ -746,17 +759,20 @@ int piadmm_ref_step(const piadmm_params* p, const piadmm_buffers* b, int S, int 
   for (int t = 0; t < 2 * nt; t++) pool[t] = (half_t*)malloc(sizeof(half_t));
   const size_t mapb = (size_t)V * (((size_t)V + 7) / 8);
   uint8_t* hitmaps = (uint8_t*)malloc(mapb * (inner ? 1 : nt));
+  uint8_t* dirty_all = (uint8_t*)malloc((size_t)S * V);
 #pragma omp parallel for schedule(dynamic, 4) if (!inner)
   for (int s = 0; s < S; s++) {
     uint8_t* hitmap = hitmaps + (inner ? 0 : mapb * omp_thread_id());
+    uint8_t* dirty = dirty_all + (size_t)s * V;
+    memset(dirty, 1, V);
     begin_scenario(p, b, s, V, D, E);
     for (int i_iter = 0; i_iter < p->iter_num; i_iter++) {
       b->n_outer[s] += 1;
-      x_update_scenario(p, c, b, s, V, D, pool, inner);
+      x_update_scenario(p, c, b, s, V, D, pool, inner, dirty);
       detect_scenario(p, b, s, V, D, E, hitmap, inner);
       if (b->edge_n[s] == 0 && b->flag[s] == 0) break;
       b->flag[s] = 1;
-      z_update_scenario(p, c, b, s, V, D, E, pool, inner);
+      z_update_scenario(p, c, b, s, V, D, E, pool, inner, dirty);
       residual_scenario(p, b, s, V, D, E, i_iter);
       if (b->done[s]) break;
     }
@@ -765,7 +781,7 @@ int piadmm_ref_step(const piadmm_params* p, const piadmm_buffers* b, int S, int 
     plant_scenario(p, b, s, V);
   }
   for (int t = 0; t < 2 * nt; t++) free(pool[t]);
-  free(pool); free(hitmaps);
+  free(pool); free(hitmaps); free(dirty_all);
   free(c);
   return PIADMM_OK;
 }

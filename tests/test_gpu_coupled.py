@@ -30,9 +30,10 @@ def _run(p, xt, spd, refwin, D, fused=None):
     sol = PIADMMSolver(p, S=xt.shape[0], V=xt.shape[1], D=D)
     sol.setup(xt, spd, refwin)
     sol.iterate(fused=fused)
+    launches = sol.launch_count
     sol.plant_step()
     out = sol.to_numpy()
-    out["_launches"] = sol.launch_count
+    out["_launches"] = launches
     sol.close()
     return out
 
@@ -99,6 +100,21 @@ def test_cooperative_kernel_equals_phase_kernels_bit_for_bit(monkeypatch, V, N, 
         assert np.array_equal(a[k], b[k]), k
     ref = ctwin.step(p, xt, spd, refwin, D=D)
     assert_same(a, ref, what=f"coop c3 V={V}")
+
+
+@pytest.mark.parametrize("coop", ["1", "0"])
+def test_x_memo_is_exact_on_the_gpu(monkeypatch, coop):
+    """x_memo=1 (skip vehicle QPs whose inputs did not change) gives bit for bit what x_memo=0 gives, with fewer solves."""
+    monkeypatch.setenv("PIADMM_COOP", coop)
+    xt, spd, refwin = c5_grid(lanes=8, per_lane=16, N=30, seed=2, clear=0.0)
+    p1 = bench.coupled_params(30).update(iter_num=6)
+    p0 = bench.coupled_params(30).update(iter_num=6, x_memo=0)
+    a, b = _run(p1, xt, spd, refwin, 8), _run(p0, xt, spd, refwin, 8)
+    for k in ("u", "pos", "hat", "dual", "err_rk", "err_sk", "n_outer", "edge_n", "nbr", "edge_inner", "xt_next"):
+        assert np.array_equal(a[k], b[k]), k
+    assert a["n_veh_solves"][0] < b["n_veh_solves"][0]
+    assert_same(a, ctwin.step(p1, xt, spd, refwin, D=8), what="memo on")
+    assert_same(b, ctwin.step(p0, xt, spd, refwin, D=8), what="memo off")
 
 
 def test_cooperative_kernel_ragged_batch(monkeypatch):
