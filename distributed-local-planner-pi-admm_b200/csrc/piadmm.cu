@@ -212,6 +212,9 @@ __global__ void k_hits_warp(const __grid_constant__ DevCtx c) {
 __global__ void k_disc(const __grid_constant__ DevCtx c) {
   const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (a < (long)c.S * c.V) dev_disc_vehicle(c, a);
+  const int words = (c.V + 31) / 32;
+  const long wb = a >> 5;                                  // warp -> (scenario, block of 32 vehicles)
+  if (wb < (long)c.S * words) dev_block_box(c, (int)(wb / words), (int)(wb % words), threadIdx.x & 31);
 }
 __global__ void k_cand(const __grid_constant__ DevCtx c) {
   const int words = (c.V + 31) / 32;
@@ -900,6 +903,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     else if (e && strcmp(e, "matrix") == 0) h->c.detect_mode = (long)S * V * words <= 9472 ? 1 : 2;
     else if (!e && e2 && atoi(e2) >= 1 && atoi(e2) <= 2) h->c.detect_mode = atoi(e2);
   }
+  if ((ce = cudaMalloc(&h->c.blockbox, sizeof(double) * 4 * (size_t)S * words)) != cudaSuccess) return fail(ce, "blockbox");
   if ((ce = cudaMalloc(&h->c.veh_dirty, (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_dirty");
   if ((ce = cudaMemset(h->c.veh_dirty, 1, (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_dirty");
   if ((ce = cudaMalloc(&h->c.up_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "up_cnt");
@@ -992,7 +996,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
   cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
   for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
   piadmm_peer_disconnect(h);
@@ -1049,7 +1053,8 @@ int64_t piadmm_launch_count(const piadmm_handle* h) { return h ? h->launches : 0
 // candidate pairs of this MPC step (detect_mode 0): once per step, from the plant state
 static int build_candidates(piadmm_handle* h, cudaStream_t st) {
   const long agents = (long)h->c.S * h->c.V, wtot = agents * ((h->c.V + 31) / 32);
-  k_disc<<<(unsigned)((agents + 255) / 256), 256, 0, st>>>(h->c);
+  const long nt_disc = std::max(agents, (long)h->c.S * ((h->c.V + 31) / 32) * 32);
+  k_disc<<<(unsigned)((nt_disc + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
   k_cand<<<(unsigned)((wtot + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
@@ -1321,6 +1326,8 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
   if (h->lpq == 16) want = std::max((agents + 3) / 4, (pairs + 1) / 2);
   else want = std::max((agents + 1) / 2, pairs);
   int grid = (int)std::min<long>(h->coop_grid_max, std::max<long>(want, 1));
+  int rc = build_candidates(h, st);          // reads xt / spd only
+  if (rc) return rc;
   void* args[2] = {&c, &a};
   if (h->lpq == 16) CK(cudaLaunchCooperativeKernel((void*)k_coop<16>, dim3(grid), dim3(CTA_THREADS), args, 0, st));
   else CK(cudaLaunchCooperativeKernel((void*)k_coop<32>, dim3(grid), dim3(CTA_THREADS), args, 0, st));

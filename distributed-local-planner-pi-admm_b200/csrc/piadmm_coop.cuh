@@ -174,7 +174,6 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
   const int N = c.N, np1 = N + 1;
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
   const long agents = (long)c.S * c.V;
-  const int words = (c.V + 31) / 32;
   unsigned long long epoch = sharded ? *pc.epoch : 0ull;
   const bool memo = dev_memo_on(c);
   load_tabs<LPQ>(c, Wsm, 0, PIADMM_NTAB);                // (ends with a CTA barrier)
@@ -200,15 +199,11 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
       c.rho_new[t] = c.b.rho_s[t];
       c.dist_bad[t] = 0;
     }
-    for (size_t t = tid; t < (size_t)agents; t += nth) { dev_disc_vehicle(c, (long)t); c.veh_dirty[t] = 1; }
+    for (size_t t = tid; t < (size_t)agents; t += nth) c.veh_dirty[t] = 1;
   }
+  // (the candidate matrix of this MPC step was built by k_disc + k_cand right before this launch: an O(V^2/32) pass that
+  //  wants the whole machine at full occupancy, not the 8 warps per SM of this kernel)
   grid.sync();
-  for (size_t t = tid; t < (size_t)agents * words; t += nth) {
-    const int jb = (int)(t % words);
-    const size_t si = t / words;
-    c.cand[t] = dev_cand_word(c, (int)(si / c.V), (int)(si % c.V), jb);
-  }
-  // (the candidate matrix is first read in the slots phase, behind the barrier that ends the x phase)
 
 #pragma unroll 1
   for (int it = 0; it < c.I; it++) {

@@ -63,13 +63,39 @@ __device__ __forceinline__ void dev_disc_vehicle(const DevCtx& c, long a) {
   reinterpret_cast<double4*>(c.bbox)[a] = make_double4(xt[0], xt[1], reach_radius(c.p, c.N, c.b.spd[a]), 0.0);
 }
 
-// word jb of row i of the (symmetric) candidate matrix of scenario s
+// blockbox[s,jb] = (xmin, xmax, ymin, ymax) over the reach discs of the vehicles 32*jb .. 32*jb+31 of scenario s: one
+// warp per block, computed from xt / spd directly (no dependence on dev_disc_vehicle having run)
+__device__ __forceinline__ void dev_block_box(const DevCtx& c, int s, int jb, int lane) {
+  const int j = jb * 32 + lane;
+  double x0 = 1e300, x1 = -1e300, y0 = 1e300, y1 = -1e300;
+  if (j < c.V) {
+    const size_t a = (size_t)s * c.V + j;
+    const double* xt = c.b.xt + a * 3;
+    const double r = reach_radius(c.p, c.N, c.b.spd[a]);
+    x0 = xt[0] - r; x1 = xt[0] + r; y0 = xt[1] - r; y1 = xt[1] + r;
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    x0 = fmin(x0, __shfl_xor_sync(PIADMM_FULL, x0, o)); x1 = fmax(x1, __shfl_xor_sync(PIADMM_FULL, x1, o));
+    y0 = fmin(y0, __shfl_xor_sync(PIADMM_FULL, y0, o)); y1 = fmax(y1, __shfl_xor_sync(PIADMM_FULL, y1, o));
+  }
+  if (lane == 0) reinterpret_cast<double4*>(c.blockbox)[(size_t)s * ((c.V + 31) / 32) + jb] = make_double4(x0, x1, y0, y1);
+}
+
+// word jb of row i of the (symmetric) candidate matrix of scenario s.  Two levels: the disc of i against the box of the
+// whole block first (one test rejects 32 pairs; with vehicles in a spatial order almost every word goes this way).
 __device__ __forceinline__ uint32_t dev_cand_word(const DevCtx& c, int s, int i, int jb) {
   const double4* disc = reinterpret_cast<const double4*>(c.bbox) + (size_t)s * c.V;
   const double4 di = disc[i];
   const double thr_d = c.p.thr_squared ? c.p.dis_thres : sqrt(c.p.dis_thres);   // the distance whose square is the threshold
   const int j0 = jb * 32, j1 = min(j0 + 32, c.V);
   uint32_t m = 0;
+  if (!c.p.always_edge) {
+    const double4 bb = reinterpret_cast<const double4*>(c.blockbox)[(size_t)s * ((c.V + 31) / 32) + jb];
+    const double gx = fmax(0.0, fmax(bb.x - di.x, di.x - bb.y)), gy = fmax(0.0, fmax(bb.z - di.y, di.y - bb.w));
+    const double rr = (di.z + thr_d) * (1.0 + 1e-9);      // (the discs' own radii are inside the box)
+    if (gx * gx + gy * gy >= rr * rr) return 0u;
+  }
   for (int j = j0; j < j1; j++) {
     if (j == i) continue;
     bool near = c.p.always_edge != 0;

@@ -44,6 +44,7 @@ struct DevCtx {
   uint8_t* slot_hit;                       // [S,V,D] the partner in this slot collides in the current outer iteration
   int32_t* up_cnt;                         // [S,V] edges (i,j>i) of the current outer iteration per vehicle
   double* bbox;                            // [S,V,4] trajectory bounding boxes (xmin,xmax,ymin,ymax) / reach discs (x0,y0,R,0)
+  double* blockbox;                        // [S,ceil(V/32),4] bounding box of the reach discs of 32 consecutive vehicles
   uint8_t* veh_dirty;                      // [S,V] x_memo: the vehicle's QP changed since its last solve in this step
   int slots_dirty;                         // the slot arrays may hold anything (first step after piadmm_bind): zero all of them
   int detect_mode;                         // 0 candidate rows (default), 1 full pair test lane-per-pair, 2 thread-per-word
