@@ -158,6 +158,7 @@ _PROTOS = {
     "piadmm_step_host_at": (C.c_int, [C.c_void_p, C.c_int] + [C.c_void_p] * 6 + [C.c_void_p]),
     "piadmm_run_closed_loop": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "piadmm_launch_count": (C.c_int64, [C.c_void_p]),
+    "piadmm_debug_coop_trace": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "piadmm_fp64_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     # include/obca_consensus.h (struct pointers passed as void*: obca_consensus.py owns the ctypes mirrors)
     "obca_lambda_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p]),

@@ -730,6 +730,7 @@ struct piadmm_handle {
   bool use_coop;
   int coop_grid_max;          // co-resident CTAs of k_coop<lpq>
   int* d_nactive;             // [2]
+  long long* d_trace;         // piadmm_debug_coop_trace
   // vehicle-sharded multi-GPU exchange (piadmm_peer_export / piadmm_peer_connect)
   char* xblk;                 // library-owned exchange block of THIS rank: pos | u | edge_res | flags | epoch | aborted
   bool peer_on;
@@ -826,7 +827,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
   h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_count2 = nullptr; h->h_count2 = nullptr; h->ev_count[0] = h->ev_count[1] = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false; h->gexec = nullptr; h->d_ref = nullptr; h->ref_T = 0; h->h_step = nullptr; h->d_step = nullptr;
-  h->use_coop = true; h->coop_grid_max = 0; h->d_nactive = nullptr; h->xblk = nullptr; h->peer_on = false;
+  h->use_coop = true; h->coop_grid_max = 0; h->d_nactive = nullptr; h->d_trace = nullptr; h->xblk = nullptr; h->peer_on = false;
   memset(&h->peer, 0, sizeof h->peer);
   for (int i = 0; i < PIADMM_MAX_PEERS; i++) h->peer_base[i] = nullptr;
   h->c.p = *p; set_inner_consts(h->c.ik, p->in_alpha); h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
@@ -1000,7 +1001,7 @@ void piadmm_destroy(piadmm_handle* h) {
   cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
   for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
   piadmm_peer_disconnect(h);
-  cudaFree(h->xblk); cudaFree(h->d_nactive);
+  cudaFree(h->xblk); cudaFree(h->d_nactive); cudaFree(h->d_trace);
   cudaFree(h->d_queue); cudaFree(h->d_order); cudaFree(h->d_ref); cudaFree(h->d_step);
   if (h->h_step) cudaFreeHost(h->h_step);
   if (h->have_streams) {
@@ -1309,12 +1310,28 @@ int piadmm_peer_connect(piadmm_handle* h, int rank, int world, const void* handl
   return PIADMM_OK;
 }
 
+int piadmm_debug_coop_trace(piadmm_handle* h, int64_t* host_out, int n) {
+  if (!h) return PIADMM_E_ARG;
+  CK(cudaSetDevice(h->device));
+  if (!h->d_trace) {
+    CK(cudaMalloc(&h->d_trace, sizeof(long long) * PIADMM_COOP_TRACE_MAX));
+    CK(cudaMemset(h->d_trace, 0, sizeof(long long) * PIADMM_COOP_TRACE_MAX));
+  }
+  if (host_out && n > 0) {
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(host_out, h->d_trace, sizeof(long long) * (size_t)std::min(n, PIADMM_COOP_TRACE_MAX), cudaMemcpyDeviceToHost));
+  }
+  return PIADMM_OK;
+}
+
 // the whole outer loop in ONE cooperative launch (piadmm_coop.cuh)
 static int launch_coop(piadmm_handle* h, cudaStream_t st) {
   DevCtx c = h->c;
   CoopArgs a;
   memset(&a, 0, sizeof a);
   a.n_active = h->d_nactive;
+  a.trace = h->d_trace;
+  if (h->d_trace) CK(cudaMemsetAsync(h->d_trace, 0, sizeof(long long), st));
   if (h->peer_on) {
     const XblkLayout L = xblk_layout(c.V, c.N, c.E);
     a.peer = h->peer;

@@ -37,7 +37,9 @@ struct PeerCtx {
   double *user_pos, *user_u;                     // the caller's bound buffers: filled from the exchange block at the end
 };
 
+#define PIADMM_COOP_TRACE_MAX 1024
 struct CoopArgs {
+  long long* trace;                              // debug (piadmm_debug_coop_trace): globaltimer at every phase boundary, or NULL
   int* n_active;                                 // [2] scenarios still active after the decide phase (double buffered)
   PeerCtx peer;
 };
@@ -88,7 +90,9 @@ __device__ __forceinline__ void coop_cross_barrier(cg::grid_group& grid, const D
 // kernel (64 threads) produce bit-identical histories.  red: 2 x 128 doubles, ish: 2 ints of shared memory.
 // COPY = false: the last_hat copy is left to the caller (the cooperative kernel spreads it over the whole grid:
 // ~45 000 elements behind two dependent index loads are 0.7 ms for the 64 threads of one CTA at config 5).
-template <bool COPY = true>
+// DIST = false: the MATLAB :202 distance test was evaluated by the caller into c.dist_bad[s] (the cooperative kernel
+// does it per vehicle in its count phase: V*D slots are 0.25 ms for one 64-thread CTA at config 5).
+template <bool COPY = true, bool DIST = true>
 __device__ __forceinline__ void dev_res_all(const DevCtx& c, int s, int i_iter, int* cnt, double (*red)[128], int* ish) {
   const piadmm_params& p = c.p;
   const int N = c.N, T = blockDim.x, t = threadIdx.x;
@@ -109,7 +113,8 @@ __device__ __forceinline__ void dev_res_all(const DevCtx& c, int s, int i_iter, 
     for (int q = t; q < o; q += T) { red[0][q] += red[0][q + o]; red[1][q] += red[1][q + o]; }
     __syncthreads();
   }
-  if (p.stop_dist_test) {                      // MATLAB :202 over the allocated neighbour slots of this scenario
+  if (!DIST) { if (t == 0 && c.dist_bad[s]) ish[0] = 1; __syncthreads(); }
+  if (DIST && p.stop_dist_test) {              // MATLAB :202 over the allocated neighbour slots of this scenario
     for (int q = t; q < c.V * c.D; q += T) {
       const int i = q / c.D, j = c.b.nbr[(size_t)s * c.V * c.D + q];
       if (j <= i) continue;
@@ -159,6 +164,14 @@ __device__ __forceinline__ void dev_res_all(const DevCtx& c, int s, int i_iter, 
 #define COOP_MIN_CTAS 4   // registers over occupancy, as the generic-V phase kernels (x and z bodies are both inlined here)
 #endif
 
+#define COOP_TRACE()                                                                  \
+  do {                                                                                \
+    if (ca.trace && tid == 0) {                                                       \
+      const int n_ = (int)ca.trace[0];                                                \
+      if (n_ < PIADMM_COOP_TRACE_MAX - 2) { ca.trace[1 + n_] = (long long)coop_now_ns(); ca.trace[0] = n_ + 1; } \
+    }                                                                                 \
+  } while (0)
+
 template <int LPQ>
 __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __grid_constant__ DevCtx c,
                                                                        const __grid_constant__ CoopArgs ca) {
@@ -177,6 +190,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
   unsigned long long epoch = sharded ? *pc.epoch : 0ull;
   const bool memo = dev_memo_on(c);
   load_tabs<LPQ>(c, Wsm, 0, PIADMM_NTAB);                // (ends with a CTA barrier)
+  COOP_TRACE();                                          // [0] start
 
   // ---- phase 0: casadi/main.py:52-72.  pos / u are only zeroed for the owned vehicles: the rows of the others are
   // written by their owners' x phase, which may already be running on a faster rank.
@@ -204,10 +218,13 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
   // (the candidate matrix of this MPC step was built by k_disc + k_cand right before this launch: an O(V^2/32) pass that
   //  wants the whole machine at full occupancy, not the 8 warps per SM of this kernel)
   grid.sync();
+  COOP_TRACE();                                          // [1] begin done; then 7 stamps per outer iteration:
+                                                         //     x, slots, count, edges, z, (cross barrier), decide
 
 #pragma unroll 1
   for (int it = 0; it < c.I; it++) {
     if (tid == 0) ca.n_active[it & 1] = 0;
+    for (size_t t = tid; t < (size_t)c.S; t += nth) c.dist_bad[t] = 0;      // set again in the count phase
     if (it > 0) {
       // last_iter_hat_pos = hat_pos_old (casadi/main.py:180) for the scenarios that go on, spread over the grid; the
       // edge list of the previous iteration is intact until the edges phase, last_hat is next read in the z phase
@@ -249,17 +266,22 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
       }
     }
     coop_cross_barrier(grid, c, pc, epoch);
+    COOP_TRACE();
     // ---- collision edges, casadi/main.py:110-118
     for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {
       const int s = (int)(a / c.V), i = (int)(a % c.V);
       if (!c.b.done[s]) dev_slots_vehicle<true>(c, s, i, w.lane);
     }
     grid.sync();
+    COOP_TRACE();
     for (long a = (long)tid; a < agents; a += (long)nth) {
-      const int s = (int)(a / c.V);
-      c.up_cnt[a] = c.b.done[s] ? 0 : dev_count_vehicle(c, s, (int)(a % c.V));
+      const int s = (int)(a / c.V), i = (int)(a % c.V);
+      if (c.b.done[s]) { c.up_cnt[a] = 0; continue; }
+      c.up_cnt[a] = dev_count_vehicle(c, s, i);
+      if (c.p.stop_dist_test && dev_dist_bad_vehicle(c, s, i)) c.dist_bad[s] = 1;      // MATLAB :202
     }
     grid.sync();
+    COOP_TRACE();
     {
       const int chunks = (c.V + CTA_THREADS - 1) / CTA_THREADS;
       for (long item = blockIdx.x; item < (long)c.S * chunks; item += gridDim.x) {
@@ -278,6 +300,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
       }
     }
     grid.sync();
+    COOP_TRACE();
     // ---- edge problems + dual / PI update, casadi/main.py:121-162 (every edge with an owned endpoint)
     {
       const long pairs = (long)c.S * c.E, items = (pairs + pairs_per_cta<LPQ>() - 1) / pairs_per_cta<LPQ>();
@@ -309,13 +332,16 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
         }
       }
     }
+    COOP_TRACE();                                        // z phase done on this rank (before the barrier)
     coop_cross_barrier(grid, c, pc, epoch);
+    COOP_TRACE();
     // ---- residuals + stop test, casadi/main.py:165-181
     for (int s = blockIdx.x; s < c.S; s += gridDim.x) {
       if (c.b.done[s]) continue;
-      dev_res_all<false>(c, s, it, ca.n_active + (it & 1), red, ish);
+      dev_res_all<false, false>(c, s, it, ca.n_active + (it & 1), red, ish);
     }
     grid.sync();
+    COOP_TRACE();
     if (*reinterpret_cast<volatile int*>(ca.n_active + (it & 1)) == 0) break;     // grid uniform
   }
   if (sharded) {

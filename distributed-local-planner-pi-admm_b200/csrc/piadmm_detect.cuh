@@ -186,6 +186,25 @@ __device__ __forceinline__ int dev_far_slot(const DevCtx& c, int s, int j, int i
   return dj;
 }
 
+// MATLAB ...PI_antiwindup.m:202 for the allocated slots (i, j > i) of vehicle i: is the one-step-ahead distance
+// dis_vec(2) of any pair NOT larger than dis_thres?  (depends on the plant state only)
+__device__ __forceinline__ bool dev_dist_bad_vehicle(const DevCtx& c, int s, int i) {
+  const piadmm_params& p = c.p;
+  const int32_t* nb = c.b.nbr + ((size_t)s * c.V + i) * c.D;
+  bool bad = false;
+  for (int d = 0; d < c.D; d++) {
+    const int j = nb[d];
+    if (j <= i) continue;
+    const double* xi = c.b.xt + ((size_t)s * c.V + i) * 3;
+    const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
+    const double vi = c.b.spd[(size_t)s * c.V + i], vj = c.b.spd[(size_t)s * c.V + j];
+    const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
+    const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
+    if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) bad = true;
+  }
+  return bad;
+}
+
 // number of edges (i, j > i) of this outer iteration: the partner collides now and BOTH tables hold a slot (a pair
 // with a full table on either side is dropped, status already set -- as find_or_alloc_slot in the oracle)
 __device__ __forceinline__ int dev_count_vehicle(const DevCtx& c, int s, int i) {

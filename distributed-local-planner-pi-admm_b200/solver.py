@@ -123,6 +123,13 @@ class PIADMMSolver:
     def peer_disconnect(self):
         self._check(self.lib.piadmm_peer_disconnect(self._h), "piadmm_peer_disconnect")
 
+    def coop_trace(self):
+        """Phase timeline (ns, relative to the kernel start) of the last cooperative launch; the first call enables it."""
+        buf = np.zeros(1024, dtype=np.int64)
+        self._check(self.lib.piadmm_debug_coop_trace(self._h, buf.ctypes.data_as(C.c_void_p), 1024), "piadmm_debug_coop_trace")
+        n = int(buf[0])
+        return (buf[1:1 + n] - buf[1]) if n else buf[:0]
+
     def residual_partials(self):
         self._check(self.lib.piadmm_residual_partials(self._h, self._stream()), "piadmm_residual_partials")
 

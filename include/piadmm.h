@@ -207,6 +207,12 @@ typedef struct piadmm_histories {
 } piadmm_histories;
 int piadmm_run_closed_loop(piadmm_handle* h, int first_step, int n_steps, const piadmm_histories* out, void* stream);
 
+/* Debug: phase timeline of the LAST cooperative launch (generic V).  The first call enables the trace; later calls copy
+ * out[0] = number of stamps, out[1..] = %globaltimer (ns) at the kernel start, after the re-initialisation, and then
+ * seven per outer iteration: after the x phase (+ exchange barrier), slots, count, edges, z phase, its exchange
+ * barrier, decide.  n <= 1024. */
+int piadmm_debug_coop_trace(piadmm_handle* h, int64_t* host_out, int n);
+
 /* statistics for the roofline: kernels launched by this handle since creation */
 int64_t piadmm_launch_count(const piadmm_handle* h);
 

@@ -34,8 +34,16 @@ def main():
     p = bench.coupled_params(N)
     ref = None
     if rank == 0:
+        # the twin in the kernels' (spatial) vehicle numbering: the residual's veh1 side depends on the numbering
         from oracle import ctwin
-        ref = ctwin.step(p, xt, spd, refwin, D=D, nthreads=len(os.sched_getaffinity(0)))
+        from pi_admm_b200.parallel import spatial_order
+        pm = spatial_order(xt)
+        inv = np.empty_like(pm); inv[pm] = np.arange(V)
+        r = ctwin.step(p, np.ascontiguousarray(xt[:, pm]), np.ascontiguousarray(np.broadcast_to(spd, (1, V))[:, pm]),
+                       np.ascontiguousarray(refwin[:, pm]), D=D, nthreads=len(os.sched_getaffinity(0)))
+        ref = {k: r[k][:, inv] for k in ("u", "pos", "xt_next")}
+        ref.update({k: r[k] for k in ("n_outer", "edge_n", "err_rk", "err_sk")})
+        ref["edge_ij"] = pm[r["edge_ij"]]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")
     stream = torch.cuda.current_stream()
     for exchange in ("peer", "nccl"):
