@@ -76,7 +76,7 @@ __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
   const int N = c.N;
   dev_begin_slots(c, tid >> 5, nth >> 5, threadIdx.x & 31);
-  for (size_t t = tid; t < (size_t)c.S * c.V; t += nth) c.veh_dirty[t] = 1;
+  for (size_t t = tid; t < (size_t)c.S * c.V; t += nth) { c.veh_dirty[t] = 1; c.veh_stamp[t] = -1; }
   const size_t n_pos = (size_t)c.S * c.V * 2 * (N + 1);
   for (size_t t = tid; t < n_pos; t += nth) c.b.pos[t] = 0.0;
   const size_t n_u = (size_t)c.S * c.V * N;
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(CTA_THREADS, LPQ == 16 ? X16_MIN_CTAS : X32_MI
     if (!loaded) { load_tabs<LPQ>(c, Wsm, 0, 2); loaded = true; }
     if (!__any_sync(PIADMM_FULL, valid)) continue;
     dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr);
-    if (valid && w.k == 0) c.veh_dirty[a] = 0;
+    if (valid && w.k == 0) { c.veh_dirty[a] = 0; c.veh_stamp[a] = c.i_iter; }
   }
 }
 
@@ -224,6 +224,10 @@ __global__ void k_cand(const __grid_constant__ DevCtx c) {
   const long si = t / words;
   c.cand[t] = dev_cand_word(c, (int)(si / c.V), (int)(si % c.V), jb);
 }
+__global__ void k_cand_list(const __grid_constant__ DevCtx c) {
+  const long a = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (a < (long)c.S * c.V) dev_cand_list_vehicle(c, (int)(a / c.V), (int)(a % c.V), threadIdx.x & 31);
+}
 
 // per vehicle (one warp): exact test of the candidates (EXACT) / walk of the hit matrix, neighbour slots in ascending j
 // (this equals the reference's sequential processing of np.where(edge_mat == 1), row-major)
@@ -233,7 +237,7 @@ __global__ void k_slots(const __grid_constant__ DevCtx c) {
   if (a >= (long)c.S * c.V) return;
   const int s = (int)(a / c.V), i = (int)(a % c.V);
   if (c.b.done[s]) return;
-  dev_slots_vehicle<EXACT>(c, s, i, threadIdx.x & 31);
+  dev_slots<EXACT>(c, s, i, threadIdx.x & 31, c.i_iter);
 }
 
 // per scenario: count the valid edges per vehicle, scan, emit the sorted edge list; flag / early-exit logic of
@@ -904,6 +908,10 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     else if (e && strcmp(e, "matrix") == 0) h->c.detect_mode = (long)S * V * words <= 9472 ? 1 : 2;
     else if (!e && e2 && atoi(e2) >= 1 && atoi(e2) <= 2) h->c.detect_mode = atoi(e2);
   }
+  if ((ce = cudaMalloc(&h->c.cand_list, sizeof(int32_t) * (size_t)S * V * PIADMM_CAND_CAP)) != cudaSuccess) return fail(ce, "cand_list");
+  if ((ce = cudaMalloc(&h->c.cand_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "cand_cnt");
+  if ((ce = cudaMemset(h->c.cand_cnt, 0xff, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "cand_cnt");
+  if ((ce = cudaMalloc(&h->c.veh_stamp, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_stamp");
   if ((ce = cudaMalloc(&h->c.blockbox, sizeof(double) * 4 * (size_t)S * words)) != cudaSuccess) return fail(ce, "blockbox");
   if ((ce = cudaMalloc(&h->c.veh_dirty, (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_dirty");
   if ((ce = cudaMemset(h->c.veh_dirty, 1, (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_dirty");
@@ -997,7 +1005,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.cand_list); cudaFree(h->c.cand_cnt); cudaFree(h->c.veh_stamp); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
   cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
   for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
   piadmm_peer_disconnect(h);
@@ -1058,6 +1066,8 @@ static int build_candidates(piadmm_handle* h, cudaStream_t st) {
   k_disc<<<(unsigned)((nt_disc + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
   k_cand<<<(unsigned)((wtot + 255) / 256), 256, 0, st>>>(h->c);
+  LAUNCHED();
+  k_cand_list<<<(unsigned)((agents * 32 + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
   return PIADMM_OK;
 }

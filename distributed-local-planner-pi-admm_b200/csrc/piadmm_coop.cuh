@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
       c.rho_new[t] = c.b.rho_s[t];
       c.dist_bad[t] = 0;
     }
-    for (size_t t = tid; t < (size_t)agents; t += nth) c.veh_dirty[t] = 1;
+    for (size_t t = tid; t < (size_t)agents; t += nth) { c.veh_dirty[t] = 1; c.veh_stamp[t] = -1; }
   }
   // (the candidate matrix of this MPC step was built by k_disc + k_cand right before this launch: an O(V^2/32) pass that
   //  wants the whole machine at full occupancy, not the 8 warps per SM of this kernel)
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
         if (!__syncthreads_or(valid)) continue;
         if (!__any_sync(PIADMM_FULL, valid)) continue;
         dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr);
-        if (valid && w.k == 0) c.veh_dirty[a] = 0;
+        if (valid && w.k == 0) { c.veh_dirty[a] = 0; c.veh_stamp[a] = it; }
         if (sharded && valid) {       // fused exchange: this lane's point / control of the row, to every peer
           const size_t po = ((size_t)s * c.V + i) * 2 * np1, uo = ((size_t)s * c.V + i) * N;
           const int k = w.k;
@@ -270,15 +270,14 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
     // ---- collision edges, casadi/main.py:110-118
     for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {
       const int s = (int)(a / c.V), i = (int)(a % c.V);
-      if (!c.b.done[s]) dev_slots_vehicle<true>(c, s, i, w.lane);
+      if (!c.b.done[s]) dev_slots<true>(c, s, i, w.lane, it);
     }
     grid.sync();
     COOP_TRACE();
-    for (long a = (long)tid; a < agents; a += (long)nth) {
+    for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {           // a warp per vehicle, lane = slot
       const int s = (int)(a / c.V), i = (int)(a % c.V);
-      if (c.b.done[s]) { c.up_cnt[a] = 0; continue; }
-      c.up_cnt[a] = dev_count_vehicle(c, s, i);
-      if (c.p.stop_dist_test && dev_dist_bad_vehicle(c, s, i)) c.dist_bad[s] = 1;      // MATLAB :202
+      if (c.b.done[s]) { if (w.lane == 0) c.up_cnt[a] = 0; continue; }
+      dev_count_vehicle_warp(c, s, i, w.lane);                                    // + MATLAB :202 distance flag
     }
     grid.sync();
     COOP_TRACE();

@@ -178,6 +178,143 @@ __device__ __forceinline__ void dev_slots_vehicle(const DevCtx& c, int s, int i,
   if (lane == 0 && overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
 }
 
+__device__ __forceinline__ int dev_far_slot(const DevCtx& c, int s, int j, int i);
+
+// candidate list of vehicle (s,i) out of its bit row: one warp, ascending j (once per MPC step)
+__device__ __forceinline__ void dev_cand_list_vehicle(const DevCtx& c, int s, int i, int lane) {
+  const int words = (c.V + 31) / 32;
+  const size_t a = (size_t)s * c.V + i;
+  const uint32_t* row = c.cand + a * words;
+  int32_t* lst = c.cand_list + a * PIADMM_CAND_CAP;
+  int n = 0;
+  for (int w0 = 0; w0 < words; w0 += 32) {
+    const uint32_t mine = w0 + lane < words ? row[w0 + lane] : 0u;
+    // exclusive prefix of the popcounts: where this lane's candidates go
+    const int pc = __popc(mine);
+    int inc = pc;
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(PIADMM_FULL, inc, o); if (lane >= o) inc += t; }
+    int at = n + inc - pc;
+    uint32_t m = mine;
+    while (m) {
+      const int j = (w0 + lane) * 32 + __ffs(m) - 1;
+      m &= m - 1;
+      if (at < PIADMM_CAND_CAP) lst[at] = j;
+      at++;
+    }
+    n += __shfl_sync(PIADMM_FULL, inc, 31);
+  }
+  if (lane == 0) c.cand_cnt[a] = n <= PIADMM_CAND_CAP ? n : -1;
+}
+
+// Slot phase over the candidate LIST (the default): lane q holds candidate q.  Only pairs with a recomputed trajectory
+// on either side are tested again (veh_stamp == it: the x phase of this outer iteration solved the vehicle; vehicles of
+// other ranks count as recomputed) -- the state of every other pair (slot_hit of its slot, or "no slot") is the one of
+// the previous outer iteration and still exact.  With x_memo most vehicles of a large scene rest after the first
+// iteration, and so do their pairs.
+__device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, int i, int lane, int it) {
+  const int N = c.N, np1 = N + 1;
+  const size_t a = (size_t)s * c.V + i, sv = (size_t)s * c.V;
+  int32_t* nb = c.b.nbr + a * c.D;
+  uint8_t* sh = c.slot_hit + a * c.D;
+  const int cnt = c.cand_cnt[a];
+  const bool test = !c.p.always_edge;
+  const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
+  const int k = lane <= N ? lane : 0;                        // padded lanes repeat point 0
+  const double* pi = c.b.pos + a * 2 * np1;
+  const double xi = pi[k], yi = pi[np1 + k];
+  const bool moved_i = c.veh_stamp[a] == it || i < c.own_lo || i >= c.own_hi;
+  bool overflow = false;
+  for (int base = 0; base < cnt; base += 32) {
+    const int q = base + lane;
+    const int j = q < cnt ? c.cand_list[a * PIADMM_CAND_CAP + q] : -1;
+    bool need = false;
+    if (j >= 0) need = moved_i || c.veh_stamp[sv + j] == it || j < c.own_lo || j >= c.own_hi;
+    const unsigned mask = __ballot_sync(PIADMM_FULL, need);
+    unsigned hits = test ? 0u : mask;
+    if (test) {                         // exact tests, eight pairs in flight (16 independent loads per lane)
+      unsigned rem = mask;
+      while (rem) {
+        int src[8], jq[8];
+        double xs[8], ys[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+          src[u] = -1;
+          if (rem) { src[u] = __ffs(rem) - 1; rem &= rem - 1; }
+          jq[u] = __shfl_sync(PIADMM_FULL, j, src[u] < 0 ? 0 : src[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+          xs[u] = 0.0; ys[u] = 0.0;
+          if (src[u] >= 0) { const double* pj = c.b.pos + (sv + jq[u]) * 2 * np1; xs[u] = pj[k]; ys[u] = pj[np1 + k]; }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+          if (src[u] >= 0) {            // warp uniform
+            const double dx = xi - xs[u], dy = yi - ys[u];
+            if (__any_sync(PIADMM_FULL, dx * dx + dy * dy < thr)) hits |= 1u << src[u];
+          }
+        }
+      }
+    }
+    unsigned rem = mask;                // slot tables, ascending j (= the order of the list)
+    while (rem) {
+      const int b = __ffs(rem) - 1;
+      rem &= rem - 1;
+      const int jb = __shfl_sync(PIADMM_FULL, j, b);
+      if (lane == 0) {
+        int slot = -1;
+        for (int d = 0; d < c.D; d++) if (nb[d] == jb) { slot = d; break; }
+        if ((hits >> b) & 1u) {
+          if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = jb; slot = d; break; }
+          if (slot < 0) overflow = true; else sh[slot] = 1;
+        } else if (slot >= 0) sh[slot] = 0;
+      }
+    }
+  }
+  if (lane == 0 && overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
+}
+
+// slot phase of one vehicle: candidate list, bit row of `cand` when the list overflowed, or the `hits` matrix
+template <bool EXACT>
+__device__ __forceinline__ void dev_slots(const DevCtx& c, int s, int i, int lane, int it) {
+  if (EXACT && c.cand_cnt[(size_t)s * c.V + i] >= 0) dev_slots_vehicle_list(c, s, i, lane, it);
+  else dev_slots_vehicle<EXACT>(c, s, i, lane);
+}
+
+// valid up-edges of vehicle i (dev_count_vehicle) and its MATLAB :202 distance flag, one WARP per vehicle: lane = slot
+__device__ __forceinline__ void dev_count_vehicle_warp(const DevCtx& c, int s, int i, int lane) {
+  const size_t a = (size_t)s * c.V + i;
+  const int32_t* nb = c.b.nbr + a * c.D;
+  const uint8_t* sh = c.slot_hit + a * c.D;
+  const piadmm_params& p = c.p;
+  int cnt = 0;
+  bool bad = false;
+  for (int d0 = 0; d0 < c.D; d0 += 32) {
+    const int d = d0 + lane;
+    bool ok = false;
+    if (d < c.D) {
+      const int j = nb[d];
+      if (j > i) {
+        if (sh[d]) ok = dev_far_slot(c, s, j, i) >= 0;
+        if (p.stop_dist_test) {
+          const double* xi = c.b.xt + a * 3;
+          const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
+          const double vi = c.b.spd[a], vj = c.b.spd[(size_t)s * c.V + j];
+          const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
+          const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
+          if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) bad = true;
+        }
+      }
+    }
+    cnt += __popc(__ballot_sync(PIADMM_FULL, ok));
+  }
+  bad = __any_sync(PIADMM_FULL, bad);
+  if (lane == 0) {
+    c.up_cnt[a] = cnt;
+    if (bad) c.dist_bad[s] = 1;
+  }
+}
+
 // slot of vehicle i in the table of vehicle j, or -1
 __device__ __forceinline__ int dev_far_slot(const DevCtx& c, int s, int j, int i) {
   const int32_t* nbj = c.b.nbr + ((size_t)s * c.V + j) * c.D;

@@ -30,6 +30,7 @@ inline void set_inner_consts(InnerK& ik, double alpha) {
   ik.ha = 0.5 * alpha; ik.b1 = 1.0 - 0.5 * alpha; ik.alu = alpha * PIADMM_L_U; ik.ald = alpha * PIADMM_L_D;
 }
 
+#define PIADMM_CAND_CAP 64
 struct DevCtx {
   piadmm_params p;
   InnerK ik;
@@ -44,6 +45,9 @@ struct DevCtx {
   uint8_t* slot_hit;                       // [S,V,D] the partner in this slot collides in the current outer iteration
   int32_t* up_cnt;                         // [S,V] edges (i,j>i) of the current outer iteration per vehicle
   double* bbox;                            // [S,V,4] trajectory bounding boxes (xmin,xmax,ymin,ymax) / reach discs (x0,y0,R,0)
+  int32_t* cand_list;                      // [S,V,PIADMM_CAND_CAP] candidate partners of every vehicle, ascending
+  int32_t* cand_cnt;                       // [S,V] their number, or -1: more than the cap, walk the bit row instead
+  int32_t* veh_stamp;                      // [S,V] outer iteration in which the vehicle's trajectory was last recomputed
   double* blockbox;                        // [S,ceil(V/32),4] bounding box of the reach discs of 32 consecutive vehicles
   uint8_t* veh_dirty;                      // [S,V] x_memo: the vehicle's QP changed since its last solve in this step
   int slots_dirty;                         // the slot arrays may hold anything (first step after piadmm_bind): zero all of them

@@ -117,6 +117,21 @@ def test_x_memo_is_exact_on_the_gpu(monkeypatch, coop):
     assert_same(b, ctwin.step(p0, xt, spd, refwin, D=8), what="memo off")
 
 
+@pytest.mark.parametrize("coop", ["1", "0"])
+def test_dense_scene_candidate_list_overflow(monkeypatch, coop):
+    """96 vehicles packed around the intersection: most vehicles have more than PIADMM_CAND_CAP = 64 candidates (their
+    slot phase walks the candidate bit row), the outer ones fewer (candidate list) -- both in one scene; neighbour
+    tables overflow too (D = 8), as in the oracle."""
+    monkeypatch.setenv("PIADMM_COOP", coop)
+    xt, spd, refwin = c3_intersection(V=96, N=30, r0=10.0, gap=1.5)
+    p = bench.coupled_params(30).update(iter_num=3)
+    ref = ctwin.step(p, xt, spd, refwin, D=8, nthreads=_threads())
+    assert ref["n_edge_solves"][0] > 50
+    got = _run(p, xt, spd, refwin, 8)
+    _assert_edges(got, ref)
+    assert_same(got, ref, what=f"dense96 coop={coop}")
+
+
 def test_cooperative_kernel_ragged_batch(monkeypatch):
     """S = 3 scenes of 5 vehicles (odd V, N=15: a warp holds groups of two scenarios), the middle one collision free."""
     from test_gpu_parity import _ragged_scene, _generic_params
