@@ -220,18 +220,20 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
   const bool test = !c.p.always_edge;
   const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
   const int k = lane <= N ? lane : 0;                        // padded lanes repeat point 0
-  const double* pi = c.b.pos + a * 2 * np1;
-  const double xi = pi[k], yi = pi[np1 + k];
   const bool moved_i = c.veh_stamp[a] == it || i < c.own_lo || i >= c.own_hi;
-  bool overflow = false;
+  int nbv = lane < c.D ? nb[lane] : -2;                      // the slot table in registers, lane = slot (D <= 32)
+  double xi = 0.0, yi = 0.0;
+  bool have_pos = false, overflow = false;
   for (int base = 0; base < cnt; base += 32) {
     const int q = base + lane;
     const int j = q < cnt ? c.cand_list[a * PIADMM_CAND_CAP + q] : -1;
     bool need = false;
     if (j >= 0) need = moved_i || c.veh_stamp[sv + j] == it || j < c.own_lo || j >= c.own_hi;
     const unsigned mask = __ballot_sync(PIADMM_FULL, need);
+    if (!mask) continue;
     unsigned hits = test ? 0u : mask;
     if (test) {                         // exact tests, eight pairs in flight (16 independent loads per lane)
+      if (!have_pos) { const double* pi = c.b.pos + a * 2 * np1; xi = pi[k]; yi = pi[np1 + k]; have_pos = true; }
       unsigned rem = mask;
       while (rem) {
         int src[8], jq[8];
@@ -256,19 +258,20 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
         }
       }
     }
-    unsigned rem = mask;                // slot tables, ascending j (= the order of the list)
-    while (rem) {
-      const int b = __ffs(rem) - 1;
-      rem &= rem - 1;
+    // slot of every tested candidate: all lanes search the register copy of the table at once
+    int slot = -1;
+    for (int d = 0; d < c.D; d++) { const int v = __shfl_sync(PIADMM_FULL, nbv, d); if (need && v == j) slot = d; }
+    const bool hit = (hits >> lane) & 1u;
+    if (need && slot >= 0) sh[slot] = hit ? 1 : 0;
+    unsigned fresh = __ballot_sync(PIADMM_FULL, need && hit && slot < 0);   // new partners: slots in ascending j
+    while (fresh) {
+      const int b = __ffs(fresh) - 1;
+      fresh &= fresh - 1;
       const int jb = __shfl_sync(PIADMM_FULL, j, b);
-      if (lane == 0) {
-        int slot = -1;
-        for (int d = 0; d < c.D; d++) if (nb[d] == jb) { slot = d; break; }
-        if ((hits >> b) & 1u) {
-          if (slot < 0) for (int d = 0; d < c.D; d++) if (nb[d] < 0) { nb[d] = jb; slot = d; break; }
-          if (slot < 0) overflow = true; else sh[slot] = 1;
-        } else if (slot >= 0) sh[slot] = 0;
-      }
+      const unsigned fr = __ballot_sync(PIADMM_FULL, lane < c.D && nbv == -1);
+      if (!fr) { overflow = true; continue; }
+      const int f = __ffs(fr) - 1;
+      if (lane == f) { nbv = jb; nb[f] = jb; sh[f] = 1; }
     }
   }
   if (lane == 0 && overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
@@ -277,7 +280,7 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
 // slot phase of one vehicle: candidate list, bit row of `cand` when the list overflowed, or the `hits` matrix
 template <bool EXACT>
 __device__ __forceinline__ void dev_slots(const DevCtx& c, int s, int i, int lane, int it) {
-  if (EXACT && c.cand_cnt[(size_t)s * c.V + i] >= 0) dev_slots_vehicle_list(c, s, i, lane, it);
+  if (EXACT && c.D <= 32 && c.cand_cnt[(size_t)s * c.V + i] >= 0) dev_slots_vehicle_list(c, s, i, lane, it);
   else dev_slots_vehicle<EXACT>(c, s, i, lane);
 }
 

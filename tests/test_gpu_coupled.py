@@ -66,7 +66,7 @@ def test_c5_grid_4096_vehicles_matches_twin():
     _assert_edges(got, ref)
     assert_same(got, ref, what="c5")
     assert converged(ref, p) and converged(got, p)
-    assert got["_launches"] == 3                         # candidate build (k_disc, k_cand) + ONE cooperative launch for the whole outer loop
+    assert got["_launches"] == 4                         # candidate build (k_disc, k_cand, k_cand_list) + ONE cooperative launch for the whole outer loop
 
 
 @pytest.mark.parametrize("detect", ["cand", "matrix_warp", "matrix_thread"])
@@ -84,7 +84,7 @@ def test_midsize_grid_every_detection_path(monkeypatch, detect, coop):
     _assert_edges(got, ref)
     assert_same(got, ref, what=f"grid640 {detect} coop={coop}")
     if detect == "cand" and coop == "1":
-        assert got["_launches"] == 3
+        assert got["_launches"] == 4
 
 
 @pytest.mark.parametrize("V,N,D,r0,gap", [(64, 30, 8, 12.0, 6.0), (32, 15, 8, 8.0, 4.0), (12, 20, 4, 12.0, 6.0)])
@@ -94,7 +94,7 @@ def test_cooperative_kernel_equals_phase_kernels_bit_for_bit(monkeypatch, V, N, 
     a = _run(p, xt, spd, refwin, D)
     monkeypatch.setenv("PIADMM_COOP", "0")
     b = _run(p, xt, spd, refwin, D)
-    assert a["_launches"] == 3 and b["_launches"] > 5
+    assert a["_launches"] == 4 and b["_launches"] > 5
     for k in ("u", "pos", "hat", "dual", "integ", "diff", "err_rk", "err_sk", "n_outer", "curr_iter", "nbr", "edge_n",
               "veh_inner", "edge_inner", "status", "xt_next", "edge_ij", "edge_slot"):
         assert np.array_equal(a[k], b[k]), k
@@ -139,7 +139,7 @@ def test_cooperative_kernel_ragged_batch(monkeypatch):
     xt, spd, refwin = _ragged_scene(5, 15, seeds=(3, 4, 5), far=1)
     ref = ctwin.step(p, xt, spd, refwin, D=4)
     got = _run(p, xt, spd, refwin, 4)
-    assert got["_launches"] == 3
+    assert got["_launches"] == 4
     _assert_edges(got, ref)
     assert_same(got, ref, what="coop ragged")
 
