@@ -250,6 +250,19 @@ def main():
     if args.impl == "reference":
         return run_reference(args, rank, world)
 
+    # one slice of the host cores per rank (eight ranks sharing all cores of one NUMA node lost 15 % end to
+    # end to each other's graph launches and zero-copy drains); set before torch / CUDA create their threads
+    pinned_cores = None
+    if world > 1 and os.environ.get("PIADMM_PIN", "1") != "0":
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            n = len(cores) // world
+            if n >= 1:
+                pinned_cores = cores[local_rank * n:(local_rank + 1) * n]
+                os.sched_setaffinity(0, pinned_cores)
+        except (AttributeError, OSError):
+            pinned_cores = None
+
     import torch
     import torch.distributed as dist
     from pi_admm_b200.scenarios import c4_scenarios
@@ -412,6 +425,7 @@ def main():
                                     "h2d_bytes_per_step": h2d_full, "d2h_bytes_per_step": d2h,
                                     "api": "piadmm_step_host (xt, spd and the reference window uploaded every step)"}},
             "gpu_launches": int(launches),
+            "host_cores_per_rank": len(pinned_cores) if pinned_cores else host_cores(),
             "clocks": clocks,
             "roofline": roofline,
             "work_per_step": {"agent_qp_solves": g_veh, "edge_solves": g_edge, "veh_inner_iters": g_vi,

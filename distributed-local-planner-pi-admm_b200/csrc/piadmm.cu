@@ -744,13 +744,14 @@ struct piadmm_handle {
 };
 
 // layout of an exchange block (S == 1): doubles first, then the barrier words
-struct XblkLayout { size_t pos, u, er, flags, epoch, aborted, bytes; };
+struct XblkLayout { size_t pos, u, er, stamp, flags, epoch, aborted, bytes; };
 static XblkLayout xblk_layout(int V, int N, int E) {
   XblkLayout L;
   L.pos = 0;
   L.u = L.pos + sizeof(double) * (size_t)V * 2 * (N + 1);
   L.er = L.u + sizeof(double) * (size_t)V * N;
-  L.flags = L.er + sizeof(double) * (size_t)E * 4;
+  L.stamp = L.er + sizeof(double) * (size_t)E * 4;
+  L.flags = L.stamp + ((sizeof(int32_t) * (size_t)V + 15) / 16) * 16;
   L.epoch = L.flags + sizeof(unsigned long long) * PIADMM_MAX_PEERS;
   L.aborted = L.epoch + sizeof(unsigned long long);
   L.bytes = L.aborted + 16;
@@ -996,7 +997,8 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     h->coop_grid_max = prop.multiProcessorCount * (pc < 1 ? 0 : pc);
     const char* ce_ = getenv("PIADMM_COOP");
     h->use_coop = coop_ok && h->coop_grid_max > 0 && !(ce_ && strcmp(ce_, "0") == 0);
-    if ((ce = cudaMalloc(&h->d_nactive, 2 * sizeof(int))) != cudaSuccess) return fail(ce, "nactive");
+    if ((ce = cudaMalloc(&h->d_nactive, 4 * sizeof(int))) != cudaSuccess) return fail(ce, "nactive");
+    if ((ce = cudaMemset(h->d_nactive, 0, 4 * sizeof(int))) != cudaSuccess) return fail(ce, "nactive");
   }
   *out = h;
   return PIADMM_OK;
@@ -1310,6 +1312,7 @@ int piadmm_peer_connect(piadmm_handle* h, int rank, int world, const void* handl
     }
     pc.pos[r] = (double*)(base + L.pos); pc.u[r] = (double*)(base + L.u); pc.edge_res[r] = (double*)(base + L.er);
     pc.flags[r] = (unsigned long long*)(base + L.flags);
+    pc.stamp[r] = (int32_t*)(base + L.stamp);
   }
   pc.epoch = (unsigned long long*)(h->xblk + L.epoch);
   pc.aborted = (int*)(h->xblk + L.aborted);
@@ -1340,6 +1343,7 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
   CoopArgs a;
   memset(&a, 0, sizeof a);
   a.n_active = h->d_nactive;
+  c.any_overflow = h->d_nactive + 2;
   a.trace = h->d_trace;
   if (h->d_trace) CK(cudaMemsetAsync(h->d_trace, 0, sizeof(long long), st));
   if (h->peer_on) {
@@ -1347,6 +1351,8 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
     a.peer = h->peer;
     a.peer.user_pos = h->c.b.pos; a.peer.user_u = h->c.b.u;
     c.b.pos = (double*)(h->xblk + L.pos); c.b.u = (double*)(h->xblk + L.u); c.edge_res = (double*)(h->xblk + L.er);
+    c.veh_stamp = (int32_t*)(h->xblk + L.stamp);
+    c.stamps_global = 1;
   }
   const long agents = (long)c.S * c.V, pairs = (long)c.S * c.E;
   long want;

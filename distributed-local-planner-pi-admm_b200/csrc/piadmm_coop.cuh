@@ -30,6 +30,7 @@ struct PeerCtx {
   double* pos[PIADMM_MAX_PEERS];                 // [V,2,N+1] exchange copy of pos_old on rank r (as mapped in this process)
   double* u[PIADMM_MAX_PEERS];                   // [V,N]
   double* edge_res[PIADMM_MAX_PEERS];            // [E,4]
+  int32_t* stamp[PIADMM_MAX_PEERS];              // [V] veh_stamp
   unsigned long long* flags[PIADMM_MAX_PEERS];   // [PIADMM_MAX_PEERS] barrier epochs signalled TO rank r, indexed by sender
   unsigned long long* epoch;                     // local: barrier epoch reached by the previous launch
   int* aborted;                                  // local: a barrier timed out (later barriers do not spin)
@@ -50,20 +51,23 @@ __device__ __forceinline__ unsigned long long coop_now_ns() {
   return t;
 }
 
-// Grid barrier extended to all ranks: every thread fences its peer stores system-wide, the grid meets, one thread per
-// peer publishes the new epoch in that peer's flag row and waits for the peer's epoch in its own row, the grid meets
-// again.  A peer that does not arrive within timeout_ns sets PIADMM_ST_PEER_TIMEOUT and stops all further waiting (the
-// kernel then runs to its end with meaningless results instead of hanging the GPU).
+// Grid barrier extended to all ranks.  Every thread that stored into peer memory fences system-wide, the grid meets,
+// CTA 0 publishes the new epoch in every peer's flag row, and then EVERY CTA waits on the local flag row for the peers'
+// epochs (one thread per peer, local L2 polling) -- no second grid barrier.  A peer that does not arrive within
+// timeout_ns sets PIADMM_ST_PEER_TIMEOUT and stops all further waiting (the kernel then runs to its end with
+// meaningless results instead of hanging the GPU).
 __device__ __forceinline__ void coop_cross_barrier(cg::grid_group& grid, const DevCtx& c, const PeerCtx& pc,
-                                                   unsigned long long& epoch) {
+                                                   unsigned long long& epoch, bool stored) {
   if (pc.world <= 1) { grid.sync(); return; }
-  __threadfence_system();
+  if (stored) __threadfence_system();
   grid.sync();
   epoch++;
-  if (blockIdx.x == 0 && (int)threadIdx.x < pc.world && (int)threadIdx.x != pc.rank) {
+  if ((int)threadIdx.x < pc.world && (int)threadIdx.x != pc.rank) {
     const int r = threadIdx.x;
-    unsigned long long* dst = pc.flags[r] + pc.rank;
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(epoch) : "memory");
+    if (blockIdx.x == 0) {
+      unsigned long long* dst = pc.flags[r] + pc.rank;
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(epoch) : "memory");
+    }
     const unsigned long long* src = pc.flags[pc.rank] + r;
     const unsigned long long t0 = coop_now_ns();
     unsigned long long seen = 0;
@@ -81,7 +85,7 @@ __device__ __forceinline__ void coop_cross_barrier(cg::grid_group& grid, const D
       }
     }
   }
-  grid.sync();
+  __syncthreads();
 }
 
 // ---- decide phase of scenario s by one CTA (any blockDim >= 64): residual sums (casadi/main.py:165-173), MATLAB :202
@@ -213,7 +217,12 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
       c.rho_new[t] = c.b.rho_s[t];
       c.dist_bad[t] = 0;
     }
-    for (size_t t = tid; t < (size_t)agents; t += nth) { c.veh_dirty[t] = 1; c.veh_stamp[t] = -1; }
+    for (size_t t = tid; t < (size_t)agents; t += nth) {
+      c.veh_dirty[t] = 1;
+      const int i = (int)(t % c.V);         // stamps of other ranks' vehicles are theirs to write (iteration 0 solves everybody)
+      if (i >= c.own_lo && i < c.own_hi) c.veh_stamp[t] = -1;
+    }
+    if (tid == 0) *c.any_overflow = 0;
   }
   // (the candidate matrix of this MPC step was built by k_disc + k_cand right before this launch: an O(V^2/32) pass that
   //  wants the whole machine at full occupancy, not the 8 warps per SM of this kernel)
@@ -241,6 +250,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
       }
     }
     // ---- x-update of the owned vehicles, casadi/main.py:81-106
+    bool stored = false;
     {
       const long items = (agents + groups_per_cta<LPQ>() - 1) / groups_per_cta<LPQ>();
       for (long item = blockIdx.x; item < items; item += gridDim.x) {
@@ -261,25 +271,32 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
             if (r == pc.rank) continue;
             if (k <= N) { pc.pos[r][po + k] = px; pc.pos[r][po + np1 + k] = py; }
             if (k < N) pc.u[r][uo + k] = uk;
+            if (k == 0) pc.stamp[r][a] = it;
           }
+          stored = true;
         }
       }
     }
-    coop_cross_barrier(grid, c, pc, epoch);
+    coop_cross_barrier(grid, c, pc, epoch, stored);
     COOP_TRACE();
     // ---- collision edges, casadi/main.py:110-118
     for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {
       const int s = (int)(a / c.V), i = (int)(a % c.V);
       if (!c.b.done[s]) dev_slots<true>(c, s, i, w.lane, it);
+      else if (w.lane == 0) c.up_cnt[a] = 0;
     }
     grid.sync();
     COOP_TRACE();
-    for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {           // a warp per vehicle, lane = slot
-      const int s = (int)(a / c.V), i = (int)(a % c.V);
-      if (c.b.done[s]) { if (w.lane == 0) c.up_cnt[a] = 0; continue; }
-      dev_count_vehicle_warp(c, s, i, w.lane);                                    // + MATLAB :202 distance flag
+    // (the slots phase left the per-vehicle edge counts; only a neighbour-table overflow somewhere in this step makes
+    //  them depend on the far side's table: then, and only then, a count phase redoes them -- grid uniform)
+    if (*reinterpret_cast<volatile int*>(c.any_overflow)) {
+      for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {         // a warp per vehicle, lane = slot
+        const int s = (int)(a / c.V), i = (int)(a % c.V);
+        if (c.b.done[s]) { if (w.lane == 0) c.up_cnt[a] = 0; continue; }
+        dev_count_vehicle_warp(c, s, i, w.lane);
+      }
+      grid.sync();
     }
-    grid.sync();
     COOP_TRACE();
     {
       const int chunks = (c.V + CTA_THREADS - 1) / CTA_THREADS;
@@ -301,6 +318,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
     grid.sync();
     COOP_TRACE();
     // ---- edge problems + dual / PI update, casadi/main.py:121-162 (every edge with an owned endpoint)
+    stored = false;
     {
       const long pairs = (long)c.S * c.E, items = (pairs + pairs_per_cta<LPQ>() - 1) / pairs_per_cta<LPQ>();
       for (long item = blockIdx.x; item < items; item += gridDim.x) {
@@ -328,11 +346,12 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
             if (r == pc.rank) continue;
             pc.edge_res[r][eo + w.half] = ss; pc.edge_res[r][eo + 2 + w.half] = rr;
           }
+          stored = true;
         }
       }
     }
     COOP_TRACE();                                        // z phase done on this rank (before the barrier)
-    coop_cross_barrier(grid, c, pc, epoch);
+    coop_cross_barrier(grid, c, pc, epoch, stored);
     COOP_TRACE();
     // ---- residuals + stop test, casadi/main.py:165-181
     for (int s = blockIdx.x; s < c.S; s += gridDim.x) {
@@ -349,7 +368,7 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
     const size_t n_pos = (size_t)agents * 2 * np1, n_u = (size_t)agents * N;
     if (pc.user_pos) for (size_t t = tid; t < n_pos; t += nth) pc.user_pos[t] = c.b.pos[t];
     if (pc.user_u) for (size_t t = tid; t < n_u; t += nth) pc.user_u[t] = c.b.u[t];
-    coop_cross_barrier(grid, c, pc, epoch);
+    coop_cross_barrier(grid, c, pc, epoch, false);
     if (tid == 0) *pc.epoch = epoch;
   }
 }

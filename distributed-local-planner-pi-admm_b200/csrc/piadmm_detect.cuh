@@ -175,7 +175,7 @@ __device__ __forceinline__ void dev_slots_vehicle(const DevCtx& c, int s, int i,
       }
     }
   }
-  if (lane == 0 && overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
+  if (lane == 0 && overflow) { atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW); if (c.any_overflow) *c.any_overflow = 1; }
 }
 
 __device__ __forceinline__ int dev_far_slot(const DevCtx& c, int s, int j, int i);
@@ -220,7 +220,8 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
   const bool test = !c.p.always_edge;
   const double thr = c.p.thr_squared ? c.p.dis_thres * c.p.dis_thres : c.p.dis_thres;
   const int k = lane <= N ? lane : 0;                        // padded lanes repeat point 0
-  const bool moved_i = c.veh_stamp[a] == it || i < c.own_lo || i >= c.own_hi;
+  const bool sg = c.stamps_global != 0;
+  const bool moved_i = c.veh_stamp[a] == it || (!sg && (i < c.own_lo || i >= c.own_hi));
   int nbv = lane < c.D ? nb[lane] : -2;                      // the slot table in registers, lane = slot (D <= 32)
   double xi = 0.0, yi = 0.0;
   bool have_pos = false, overflow = false;
@@ -228,7 +229,7 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
     const int q = base + lane;
     const int j = q < cnt ? c.cand_list[a * PIADMM_CAND_CAP + q] : -1;
     bool need = false;
-    if (j >= 0) need = moved_i || c.veh_stamp[sv + j] == it || j < c.own_lo || j >= c.own_hi;
+    if (j >= 0) need = moved_i || c.veh_stamp[sv + j] == it || (!sg && (j < c.own_lo || j >= c.own_hi));
     const unsigned mask = __ballot_sync(PIADMM_FULL, need);
     if (!mask) continue;
     unsigned hits = test ? 0u : mask;
@@ -274,14 +275,48 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
       if (lane == f) { nbv = jb; nb[f] = jb; sh[f] = 1; }
     }
   }
-  if (lane == 0 && overflow) atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW);
+  if (lane == 0 && overflow) { atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW); if (c.any_overflow) *c.any_overflow = 1; }
 }
 
 // slot phase of one vehicle: candidate list, bit row of `cand` when the list overflowed, or the `hits` matrix
+// ... and, from the vehicle's OWN table only: the number of its up-edges (i, j > i) of this outer iteration and its MATLAB
+// :202 distance flag.  Without a table overflow anywhere in the step this IS the number of valid edges (a partner
+// that collides holds the mirror slot); with one, the count phase (dev_count_vehicle_warp) redoes it with the far side.
 template <bool EXACT>
 __device__ __forceinline__ void dev_slots(const DevCtx& c, int s, int i, int lane, int it) {
   if (EXACT && c.D <= 32 && c.cand_cnt[(size_t)s * c.V + i] >= 0) dev_slots_vehicle_list(c, s, i, lane, it);
   else dev_slots_vehicle<EXACT>(c, s, i, lane);
+  __syncwarp();
+  const size_t a = (size_t)s * c.V + i;
+  const int32_t* nb = c.b.nbr + a * c.D;
+  const uint8_t* sh = c.slot_hit + a * c.D;
+  const piadmm_params& p = c.p;
+  int cnt = 0;
+  bool bad = false;
+  for (int d0 = 0; d0 < c.D; d0 += 32) {
+    const int d = d0 + lane;
+    bool up = false;
+    if (d < c.D) {
+      const int j = nb[d];
+      if (j > i) {
+        up = sh[d] != 0;
+        if (p.stop_dist_test) {
+          const double* xi = c.b.xt + a * 3;
+          const double* xj = c.b.xt + ((size_t)s * c.V + j) * 3;
+          const double vi = c.b.spd[a], vj = c.b.spd[(size_t)s * c.V + j];
+          const double dx = (xi[0] + p.dt * vi * cos(xi[2])) - (xj[0] + p.dt * vj * cos(xj[2]));
+          const double dy = (xi[1] + p.dt * vi * sin(xi[2])) - (xj[1] + p.dt * vj * sin(xj[2]));
+          if (!(sqrt(dx * dx + dy * dy) > p.dis_thres)) bad = true;
+        }
+      }
+    }
+    cnt += __popc(__ballot_sync(PIADMM_FULL, up));
+  }
+  bad = __any_sync(PIADMM_FULL, bad);
+  if (lane == 0) {
+    c.up_cnt[a] = cnt;
+    if (bad) c.dist_bad[s] = 1;
+  }
 }
 
 // valid up-edges of vehicle i (dev_count_vehicle) and its MATLAB :202 distance flag, one WARP per vehicle: lane = slot
