@@ -40,6 +40,26 @@ __device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool
       tx = p.Pnorm * rw[k];
       ty = p.Pnorm * rw[NP1 + k];
     }
+  }
+  // AL term over the allocated neighbour slots, ascending d.  The slot table is read by the lanes in parallel (lane d =
+  // slot d) and turned into a bit mask per group: D serial dependent loads (2.4 us at D = 8) become one, and a vehicle
+  // without neighbours -- almost every vehicle of a large scene -- skips the loop altogether.
+  if (c.D <= LPQ) {
+    const int nbv = (valid && k < c.D) ? c.b.nbr[((size_t)s * c.V + i) * c.D + k] : -1;
+    unsigned m = __ballot_sync(PIADMM_FULL, nbv >= 0);
+    if (LPQ == 16) m = (m >> (lane & 16)) & 0xffffu;
+    deg = __popc(m);
+    while (m) {
+      const int d = __ffs(m) - 1;
+      m &= m - 1;
+      if (k <= N) {
+        const double* hat = c.b.hat + SLOT_OFF(s, i, d);
+        const double* du = c.b.dual + SLOT_OFF(s, i, d);
+        tx += 0.5 * rho * (hat[k] - du[k]);
+        ty += 0.5 * rho * (hat[NP1 + k] - du[NP1 + k]);
+      }
+    }
+  } else if (valid) {
     for (int d = 0; d < c.D; d++) {
       if (c.b.nbr[((size_t)s * c.V + i) * c.D + d] < 0) continue;
       deg++;

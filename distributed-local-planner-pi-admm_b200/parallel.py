@@ -111,6 +111,9 @@ class VehicleShardedSolver:
         self.exchange = "none"
         self.exchange_note = ""
         self.perm = np.arange(V)
+        self._have_perm = False
+        self._perm_dev = None
+        self._stage = None
         if self.world > 1:
             want = exchange or os.environ.get("PIADMM_EXCHANGE", "peer")
             if want not in ("peer", "nccl"):
@@ -151,13 +154,40 @@ class VehicleShardedSolver:
         return True, ""
 
     # ------------------------------------------------------------------ per-step API (original vehicle numbering outside)
-    def setup(self, xt, spd, refwin):
-        xt = np.asarray(xt, dtype=np.float64).reshape(1, self.V, 3)
-        spd = np.broadcast_to(np.asarray(spd, dtype=np.float64), (1, self.V))
-        refwin = np.asarray(refwin, dtype=np.float64).reshape(1, self.V, 2, -1)
-        self.perm = spatial_order(xt)
+    def setup(self, xt, spd, refwin, reorder=None):
+        """Inputs of one MPC step in the caller's vehicle numbering (host arrays).  The spatial order is computed at the
+        first call and kept afterwards (reorder=True recomputes it): any fixed numbering is valid, vehicles move a few
+        metres per step, and a stable numbering keeps the per-vehicle K^-1 cache warm.  The rows are permuted into pinned
+        staging buffers and go to the device as three asynchronous copies."""
+        V = self.V
+        if torch.is_tensor(xt) and torch.is_tensor(spd) and torch.is_tensor(refwin) and self._have_perm and not reorder:
+            # (pinned) host tensors in the caller's numbering: three asynchronous H2D copies, the permutation is a gather on
+            # the device (no host pass over the rows at all)
+            if self._perm_dev is None:
+                self._perm_dev = torch.from_numpy(self.perm.copy()).to(self.sol.device)
+                self._tmp = {k: torch.empty_like(v) for k, v in ((n, self.sol.buf[n]) for n in ("xt", "spd", "refwin"))}
+            for name, src in (("xt", xt), ("spd", spd), ("refwin", refwin)):
+                self._tmp[name].copy_(src.view_as(self._tmp[name]), non_blocking=True)
+                torch.index_select(self._tmp[name], 1, self._perm_dev, out=self.sol.buf[name])
+            return
+        xt, spd, refwin = (x.numpy() if torch.is_tensor(x) else x for x in (xt, spd, refwin))
+        xt = np.asarray(xt, dtype=np.float64).reshape(V, 3)
+        spd = np.broadcast_to(np.asarray(spd, dtype=np.float64).reshape(-1), (V,))
+        refwin = np.asarray(refwin, dtype=np.float64).reshape(V, 2, -1)
+        if reorder or (reorder is None and not self._have_perm):
+            self.perm = spatial_order(xt)
+            self._have_perm = True
+            self._perm_dev = None
+        if self._stage is None:
+            mk = lambda *sh: torch.zeros(sh, dtype=torch.float64).pin_memory()
+            self._stage = dict(xt=mk(1, V, 3), spd=mk(1, V), refwin=mk(1, V, 2, self.sol.N + 1))
+            self._stage_np = {k: v.numpy() for k, v in self._stage.items()}
         p = self.perm
-        self.sol.setup(np.ascontiguousarray(xt[:, p]), np.ascontiguousarray(spd[:, p]), np.ascontiguousarray(refwin[:, p]))
+        np.take(xt, p, axis=0, out=self._stage_np["xt"][0], mode="clip")          # (mode="clip": no bounds-check buffering, 2.6x faster)
+        np.take(spd, p, axis=0, out=self._stage_np["spd"][0], mode="clip")
+        np.take(refwin.reshape(V, -1), p, axis=0, out=self._stage_np["refwin"][0].reshape(V, -1), mode="clip")
+        for k, v in self._stage.items():
+            self.sol.buf[k].copy_(v, non_blocking=True)
 
     def iterate(self):
         s = self.sol
