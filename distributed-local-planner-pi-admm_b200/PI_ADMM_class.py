@@ -3,9 +3,10 @@
 Same class name, constructor, ``param`` attribute bag, reference trajectories and method names /
 argument meaning as ``PI_ADMM_CASADI``.  What differs is what the symbolic methods return: the
 reference builds CasADi SX expressions that ``ca.qpsol("osqp")`` turns into a QP at every call;
-here ``cost_function_primal`` / ``cost_function_edge`` / ``nonlcon_function`` return light
-descriptors (the numeric data the QP depends on) and the solve itself runs in the CUDA kernels of
-libpiadmm.so (``solve_vehicles`` / ``solve_edges`` / ``step``).  The numeric (``if_SX=0``) roll-outs
+here ``cost_function_primal`` / ``cost_function_edge`` / ``nonlcon_function`` return
+descriptors (the numeric data the QP depends on) whose ``solve()`` runs the problem in the CUDA kernels of
+libpiadmm.so -- one at a time through ``solve`` / ``ca_shim.qpsol`` (a script in casadi/main.py's shape keeps its
+statements, see main_qpsol_shape.py), or the whole MPC step at once through ``step``.  The numeric (``if_SX=0``) roll-outs
 are the reference's own few lines of numpy index arithmetic and stay on the host, they are interface
 glue for scripts that call them directly; the batched solver never uses them.
 """
@@ -31,21 +32,80 @@ class Bunch(dict):
 
 
 class VehicleQP:
-    """Descriptor returned by cost_function_primal: everything the vehicle QP depends on."""
+    """What cost_function_primal returns: the numeric data the vehicle QP of casadi/PI_ADMM_class.py:114-135 depends on.
+    ``solve()`` runs it through piadmm_x_update (one owned vehicle of a V-vehicle handle, AL term over every j != i as the
+    reference states it, :126-129) and returns the UNROUNDED steering sequence, shape (1, N) -- the script rounds
+    (casadi/main.py:103)."""
 
-    def __init__(self, num_step, xt, hat_pos, dual_var, veh_index):
-        self.num_step, self.xt, self.hat_pos, self.dual_var, self.veh_index = num_step, xt, hat_pos, dual_var, veh_index
+    def __init__(self, owner, num_step, xt, hat_pos, dual_var, veh_index):
+        self.owner, self.num_step, self.veh_index = owner, int(num_step), int(veh_index)
+        self.xt, self.hat_pos, self.dual_var = np.asarray(xt, dtype=np.float64), hat_pos, dual_var
+
+    def solve(self, error_on_fail=True):
+        import torch
+        P, i = self.owner, self.veh_index
+        V, N = int(P.param.num_veh), int(P.param.num_ho)
+        sol = P._descriptor_solver("vehicle", V, max(1, V - 1))
+        xt = self.xt if self.xt.ndim == 2 else np.tile(self.xt, (V, 1))
+        sol.setup(xt[None], np.asarray(P.param.spd, dtype=np.float64)[None], P.ref_window(self.num_step)[None],
+                  rho=float(P.param.rho))
+        sol.begin_step()                                   # zero state, slot d of vehicle i <-> the d-th j != i
+        for d, j in enumerate([j for j in range(V) if j != i]):
+            sol.buf["hat"][0, i, d].copy_(torch.from_numpy(np.ascontiguousarray(self.hat_pos[i, j], dtype=np.float64)))
+            sol.buf["dual"][0, i, d].copy_(torch.from_numpy(np.ascontiguousarray(self.dual_var[i, j], dtype=np.float64)))
+        sol.set_ownership(i, i + 1)
+        sol.x_update()
+        status = int(sol.buf["status"][0].item())
+        if error_on_fail and status & _abi.ST_VEH_MAXITER:
+            raise RuntimeError("vehicle QP did not converge within in_max_iter inner iterations (qpsol error_on_fail)")
+        return sol.buf["u"][0, i].cpu().numpy().reshape(1, N).copy()
 
 
 class EdgeQP:
-    """Descriptor returned by cost_function_edge."""
+    """What cost_function_edge returns (casadi/PI_ADMM_class.py:145-169; convex statement).  ``solve()`` runs
+    the edge problem ALONE through piadmm_solve_edges and returns the unrounded controls of both vehicles, shape
+    (1, 2N) = [veh1 | veh2]; the script reshapes / rounds (casadi/main.py:153) and does the roll-out of z-hat and the dual
+    update itself.  Speeds are taken by LOCAL row index (spd[0], spd[1]) as dynamic_update_edge does (:93)."""
 
-    def __init__(self, xt, pos_old, dual_var_old, prev_pred_pos):
-        self.xt, self.pos_old, self.dual_var_old, self.prev_pred_pos = xt, pos_old, dual_var_old, prev_pred_pos
+    def __init__(self, owner, xt, pos_old, dual_var_old, prev_pred_pos):
+        self.owner = owner
+        self.xt = np.asarray(xt, dtype=np.float64).reshape(2, 3)
+        self.pos_old = np.asarray(pos_old, dtype=np.float64)
+        self.dual_var_old = np.asarray(dual_var_old, dtype=np.float64)
+        self.prev_pred_pos = np.asarray(prev_pred_pos, dtype=np.float64)
+
+    def solve(self, error_on_fail=False):
+        import ctypes as C
+        import torch
+        P = self.owner
+        N = int(P.param.num_ho)
+        sol = P._descriptor_solver("edge", 2, 1)
+        spd = np.asarray(P.param.spd, dtype=np.float64)[:2]
+        # the kernel forms the seed point itself (casadi/main.py:48-49); the script's value must be that very point
+        seed = np.around(self.xt[:, :2] + float(P.param.dt) * spd[:, None] * np.stack((np.cos(self.xt[:, 2]), np.sin(self.xt[:, 2])), 1), 4)
+        if not np.allclose(seed, self.prev_pred_pos.reshape(2, 2), atol=1e-9):
+            raise ValueError("prev_pred_pos is not the one-step-ahead point of xt_edge (casadi/main.py:48-49)")
+        put = lambda name, val: sol.buf[name].copy_(torch.from_numpy(np.ascontiguousarray(val)).reshape(sol.buf[name].shape))
+        put("xt", self.xt); put("spd", spd)
+        put("pos", self.pos_old.reshape(2, 2, N + 1))
+        put("dual", self.dual_var_old.reshape(2, 1, 2, N + 1))
+        sol.buf["rho_s"].fill_(float(P.param.rho))
+        put("nbr", np.array([1, 0], dtype=np.int32)); put("edge_n", np.array([1], dtype=np.int32))
+        put("edge_ij", np.array([0, 1], dtype=np.int32)); put("edge_slot", np.array([0, 0], dtype=np.int32))
+        sol.buf["done"].zero_(); sol.buf["status"].zero_()
+        sol._check(sol.lib.piadmm_solve_edges(sol._h, sol._stream()), "piadmm_solve_edges")
+        out = np.zeros((1, sol.E, 2, N))
+        sol._check(sol.lib.piadmm_get_edge_u(sol._h, out.ctypes.data_as(C.c_void_p), sol._stream()), "piadmm_get_edge_u")
+        if error_on_fail and int(sol.buf["status"][0].item()) & _abi.ST_EDGE_MAXITER:
+            raise RuntimeError("edge problem did not converge within in_max_iter inner iterations (qpsol error_on_fail)")
+        return out[0, 0].reshape(1, 2 * N).copy()
 
 
 class Constraints:
-    """Descriptor returned by nonlcon_function: g(u) = [u+pi/6; -u+pi/6; -D1u+pi/9; D1u+pi/9] >= 0."""
+    """What nonlcon_function returns: g(u) = [u+pi/6; -u+pi/6; -D1u+pi/9; D1u+pi/9] >= 0 (casadi/PI_ADMM_class.py:172-192).
+    The kernels carry exactly these rows (csrc/piadmm_dev.cuh); the descriptor lets qpsol check that the problem it is
+    given has them."""
+    is_steering_box = True
 
     def __init__(self, rows, N):
         self.rows, self.N = rows, N
@@ -83,6 +143,7 @@ class PI_ADMM_CASADI(object):
         self.error_on_fail = True
         self._solver = None
         self._solver_key = None
+        self._desc_solvers = {}
 
     # ------------------------------------------------------------------ numeric roll-outs (if_SX=0)
     def dynamic_update_local(self, xt, u, veh_index, if_SX=0):
@@ -120,17 +181,48 @@ class PI_ADMM_CASADI(object):
     # ------------------------------------------------------------------ problem descriptors
     def cost_function_primal(self, num_step, u, xt, hat_pos, dual_var, veh_index):
         """casadi/PI_ADMM_class.py:114-135 -> VehicleQP descriptor (u is ignored: the decision variable)."""
-        return VehicleQP(num_step, np.asarray(xt, dtype=np.float64), hat_pos, dual_var, veh_index)
+        return VehicleQP(self, num_step, xt, hat_pos, dual_var, veh_index)
 
     def cost_function_edge(self, hat_u, xt, pos_old, dual_var_old, prev_pred_pos):
         """casadi/PI_ADMM_class.py:145-169 -> EdgeQP descriptor (convex statement)."""
-        return EdgeQP(np.asarray(xt, dtype=np.float64), pos_old, dual_var_old, prev_pred_pos)
+        return EdgeQP(self, xt, pos_old, dual_var_old, prev_pred_pos)
 
     def nonlcon_function(self, u):
         """casadi/PI_ADMM_class.py:172-192: returns (ceq, cieq) with cieq a Constraints descriptor."""
         shape = getattr(u, "shape", (1, self.param.num_ho))
         rows = shape[0] if len(shape) == 2 else 1
         return [], Constraints(rows, self.param.num_ho)
+
+    # ------------------------------------------------------------------ descriptor solves (what ca_shim.qpsol calls)
+    def _descriptor_solver(self, kind, V, D) -> PIADMMSolver:
+        """Handle for single-problem solves in casadi/main.py's own statement order: the script rounds (:103,153), rolls
+        out and updates the duals itself, so rounding is off and the AL term runs over every j != i (:126-129)."""
+        p = self.abi_params()
+        p.update(round_u=-1, round_edge=-1, al_all=1)
+        key = (kind, V, D, p.num_ho, p.iter_num)
+        hit = self._desc_solvers.get(kind)
+        if hit is None or hit[0] != key:
+            if hit is not None:
+                hit[1].close()
+            hit = (key, PIADMMSolver(p, S=1, V=V, D=D))
+            self._desc_solvers[kind] = hit
+        else:
+            hit[1].set_params(**p.as_dict())
+        return hit[1]
+
+    def solve(self, desc, cieq=None, error_on_fail=None):
+        """Solve ONE described problem on the GPU (a VehicleQP or an EdgeQP); returns the unrounded solution."""
+        if cieq is not None and not getattr(cieq, "is_steering_box", False):
+            raise TypeError("cieq must come from nonlcon_function")
+        if error_on_fail is None:
+            error_on_fail = isinstance(desc, VehicleQP)
+        return desc.solve(error_on_fail=error_on_fail)
+
+    def solve_vehicles(self, descs):
+        return [self.solve(d) for d in descs]
+
+    def solve_edges(self, descs):
+        return [self.solve(d) for d in descs]
 
     # ------------------------------------------------------------------ solver plumbing
     def abi_params(self) -> _abi.Params:

@@ -1007,7 +1007,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.cand_list); cudaFree(h->c.cand_cnt); cudaFree(h->c.veh_stamp); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.edge_u); cudaFree(h->c.cand_list); cudaFree(h->c.cand_cnt); cudaFree(h->c.veh_stamp); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
   cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
   for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
   piadmm_peer_disconnect(h);
@@ -1137,6 +1137,29 @@ int piadmm_z_update(piadmm_handle* h, void* stream) {
     k_z_update<32><<<(unsigned)(pairs < h->z_grid ? pairs : h->z_grid), CTA_THREADS, 0, st>>>(h->c);
   }
   LAUNCHED();
+  return PIADMM_OK;
+}
+
+// casadi/main.py:133-153 for a caller-provided edge list: the edge problems alone (no roll-out of z-hat, no dual update)
+int piadmm_solve_edges(piadmm_handle* h, void* stream) {
+  REQUIRE_BOUND();
+  if (!h->c.edge_u) {
+    CK(cudaMalloc(&h->c.edge_u, sizeof(double) * (size_t)h->c.S * h->c.E * 2 * h->c.N));
+    CK(cudaMemset(h->c.edge_u, 0, sizeof(double) * (size_t)h->c.S * h->c.E * 2 * h->c.N));
+  }
+  h->c.z_solve_only = 1;
+  const int rc = piadmm_z_update(h, stream);
+  h->c.z_solve_only = 0;
+  return rc;
+}
+
+int piadmm_get_edge_u(piadmm_handle* h, double* host_out, void* stream) {
+  REQUIRE_BOUND();
+  if (!host_out) return PIADMM_E_ARG;
+  if (!h->c.edge_u) { h->err = "piadmm_get_edge_u: no edge solve yet (piadmm_solve_edges)"; return PIADMM_E_UNBOUND; }
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(cudaMemcpyAsync(host_out, h->c.edge_u, sizeof(double) * (size_t)h->c.S * h->c.E * 2 * h->c.N, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
   return PIADMM_OK;
 }
 

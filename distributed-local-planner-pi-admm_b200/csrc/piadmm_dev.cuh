@@ -47,6 +47,8 @@ struct DevCtx {
   double* bbox;                            // [S,V,4] trajectory bounding boxes (xmin,xmax,ymin,ymax) / reach discs (x0,y0,R,0)
   int32_t* cand_list;                      // [S,V,PIADMM_CAND_CAP] candidate partners of every vehicle, ascending
   int32_t* cand_cnt;                       // [S,V] their number, or -1: more than the cap, walk the bit row instead
+  double* edge_u;                          // [S,E,2,N] solution of every edge problem of the last z phase (piadmm_solve_edges), or NULL
+  int z_solve_only;                        // edge problems only: no z-hat roll-out, no dual / PI update (the caller's script does both)
   int stamps_global;                       // veh_stamp is exchanged between the ranks (peer mode): no rank-local guessing
   int* any_overflow;                       // cooperative kernel: a neighbour table overflowed in this step (or NULL)
   int32_t* veh_stamp;                      // [S,V] outer iteration in which the vehicle's trajectory was last recomputed

@@ -172,6 +172,15 @@ __device__ __forceinline__ void dev_z_update(const DevCtx& c, int s, int e, int 
   InnerOut o = inner_solve<LPQ, KS, LATENCY>(p, c.ik, N, k, half, true, pI, 0.0, pW, q, a0, a1, cvec, Wsm, gbuf, xch, krow, kc);
   // z-hat: non-linear roll-out of the rounded edge controls (casadi/main.py:153-158)
   const double uh = (k < N) ? round_scale(o.x, c.round_edge_scale) : 0.0;
+  if (c.edge_u && valid && k < N) c.edge_u[(((size_t)s * c.E + e) * 2 + half) * N + k] = uh;
+  if (c.z_solve_only) {            // casadi/main.py:133-153 alone; uniform over the pair (kernel parameter)
+    if (valid && k == 0 && half == 0) {
+      atomicAdd(reinterpret_cast<unsigned long long*>(c.b.edge_inner + s), (unsigned long long)o.iters);
+      atomicAdd(c.b.n_edge_solves + s, 1);
+      if (o.status) atomicOr(c.b.status + s, PIADMM_ST_EDGE_MAXITER);
+    }
+    return;
+  }
   double hx, hy, hth;
   rollout_nonlinear<LPQ>(p, xs[me][0], xs[me][1], xs[me][2], vme, uh, k, &hx, &hy, &hth);
   // gains

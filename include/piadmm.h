@@ -152,6 +152,13 @@ int piadmm_x_update(piadmm_handle* h, void* stream);
 int piadmm_detect_edges(piadmm_handle* h, void* stream);
 int piadmm_z_update(piadmm_handle* h, void* stream);     /* edge problems + dual / PI update */
 int piadmm_residuals(piadmm_handle* h, void* stream);    /* histories, stop flags, alias latch (= partials + decide) */
+/* The edge problems ALONE, for scripts that keep casadi/main.py's own statements around the solve (:133-153: build the
+ * problem, F = ca.qpsol("osqp"), result = F(lbg=0)) and do the z-hat roll-out (:156-158) and the dual update (:161-162)
+ * themselves: solves the edges listed in the bound edge_n / edge_ij / edge_slot from the bound xt, spd, pos, dual, rho_s;
+ * writes nothing but the library-owned solution buffer, read back with piadmm_get_edge_u (host_out [S,E,2,N], edge
+ * controls rounded to round_edge decimals; synchronises). */
+int piadmm_solve_edges(piadmm_handle* h, void* stream);
+int piadmm_get_edge_u(piadmm_handle* h, double* host_out, void* stream);
 /* vehicle-sharded (multi-GPU) form: this rank x-updates vehicles [lo,hi), solves every edge with an owned
  * endpoint, and sums the residual terms of the edges whose veh1 it owns into res_part; the caller
  * all-gathers pos/u rows after x_update and all-reduces (sum) res_part between the two residual calls. */

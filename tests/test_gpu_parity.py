@@ -624,3 +624,53 @@ def test_reference_error_behaviour_vehicle_failure_raises_edge_failure_is_record
         assert np.array_equal(h["status_his"][t], ref["status"]), t
         x = ref["xt_next"].copy()
     assert h["status_his"].any()
+
+
+def test_qpsol_shaped_script_equals_fused_step():
+    """VERDICT r1 #8 / SURVEY 8(b): a script in casadi/main.py's own shape -- ca.SX.sym, cost_function_primal / _edge,
+    nonlcon_function, ca.qpsol("solver", "osqp", ...), F(lbg=0) per vehicle and per edge, numpy for everything around --
+    runs over the descriptors (pi_admm_b200.ca_shim) and gives the same closed loop as the fused persistent kernel."""
+    from pi_admm_b200 import main_qpsol_shape, main_intersection
+    n = 22                                              # through the steps with an active edge
+    a = main_qpsol_shape.run(n_steps=n)
+    b = main_intersection.run(semantics="python_current", fast=True, n_steps=n)
+    assert [int(v) for v in a["iter_his"][:n]] == [int(v) for v in b["iter_his"][:n]]
+    assert a["n_outer"] == b["n_outer"] and max(a["n_outer"]) >= 2
+    assert np.allclose(np.array(a["x_vec"]), np.array(b["x_vec"]), rtol=1e-6, atol=1e-9)
+    assert np.allclose(np.array(a["u_vec"]), np.array(b["u_vec"]), rtol=1e-6, atol=1e-9)
+    for ra, rb in zip(a["err_rk"], b["err_rk"]):
+        if len(ra):
+            assert np.allclose(ra, rb[:len(ra)], rtol=1e-6, atol=1e-6)
+
+
+def test_descriptor_solves_match_the_oracle_problems():
+    """One vehicle QP and one edge problem through PI_ADMM_CASADI.solve(descriptor) against the numpy oracle's solver on
+    the same data (tight inner tolerance: the minimiser is solver independent)."""
+    from pi_admm_b200.PI_ADMM_class import PI_ADMM_CASADI
+    from oracle import problem as op, solver as osol
+    P = PI_ADMM_CASADI(semantics="python_current", inner="tight")
+    N, V = 15, 2
+    rng = np.random.default_rng(5)
+    xt = np.array([[-5.2, 0.1, 0.05], [0.2, 10.4, -np.pi / 2 + 0.03]])
+    hat = np.empty((V, V), dtype=object); dual = np.empty((V, V), dtype=object)
+    for i in range(V):
+        for j in range(V):
+            hat[i, j] = rng.normal(size=(2, N + 1)); dual[i, j] = 0.1 * rng.normal(size=(2, N + 1))
+    st = osol.InnerSettings.tight()
+    par = op.Params()
+    rw = P.ref_window(12)
+    for i in range(V):
+        desc = P.cost_function_primal(12, None, xt, hat, dual, i)
+        u = P.solve(desc, P.nonlcon_function(np.zeros((1, N)))[1])
+        H, q = op.vehicle_qp(par, xt[i], float(P.param.spd[i]), rw[i, 0], rw[i, 1], [hat[i, 1 - i]], [dual[i, 1 - i]], float(P.param.rho))
+        x_ref, info = osol.solve_box_qp(H, q, st)
+        assert info["status"] == 0 and np.abs(u[0] - x_ref).max() <= 1e-6
+    # edge problem of the pair, data as casadi/main.py:127-131 builds it
+    spd = np.asarray(P.param.spd, dtype=np.float64)
+    seed = np.around(xt[:, :2] + 0.1 * spd[:, None] * np.stack((np.cos(xt[:, 2]), np.sin(xt[:, 2])), 1), 4)
+    pos_edge = rng.normal(size=(4, N + 1)) + np.repeat(xt[:, :2].reshape(4, 1), N + 1, axis=1)
+    dual_edge = 0.1 * rng.normal(size=(4, N + 1))
+    ue = P.solve(P.cost_function_edge(None, xt, pos_edge, dual_edge, seed)).reshape(2, N)
+    blk = op.edge_qp_blocks(par, xt, spd, pos_edge, dual_edge, seed, float(P.param.rho))
+    xs, info = osol.solve_edge_pair(blk["H"], blk["q"], blk["a"], blk["c"], par.beta, st)
+    assert info["status"] == 0 and np.abs(ue - np.asarray(xs)).max() <= 1e-6
