@@ -363,11 +363,16 @@ def main():
 
     # ---- the coupled scenes (BASELINE configs 5 and 3): config 5 on ALL ranks of this run (vehicle-sharded, strong
     # scaling), config 3 at N=1.  Reported beside the config-4 headline as `coupled`.
-    coupled = None
+    coupled, config1, variants = None, None, None
     if not args.no_coupled:
         coupled = {"c5": measure_coupled("c5", args, rank, local_rank, world)}
         if world == 1:
             coupled["c3"] = measure_coupled("c3", args, rank, local_rank, world)
+            few = max(3, min(args.steps, 5))
+            coupled["c5_inner_tight"] = measure_coupled("c5", args, rank, local_rank, world, with_cpu=False, inner="tight", steps=few)
+            coupled["c3_inner_tight"] = measure_coupled("c3", args, rank, local_rank, world, with_cpu=False, inner="tight", steps=few)
+            config1 = measure_config1(args, local_rank)
+            variants = measure_c4_variants(args, local_rank, S, N)
 
     # ---- max over ranks, sums of work ------------------------------------------------------
     stats = torch.tensor([total_ms, e2e_s * 1e3, e2e_full_s * 1e3], dtype=torch.float64, device=sol.device)
@@ -428,11 +433,14 @@ def main():
             "host_cores_per_rank": len(pinned_cores) if pinned_cores else host_cores(),
             "clocks": clocks,
             "roofline": roofline,
+            "edge_qp_solves_per_s": g_edge / (ms_per_step * 1e-3),
             "work_per_step": {"agent_qp_solves": g_veh, "edge_solves": g_edge, "veh_inner_iters": g_vi,
                               "edge_inner_iters": g_ei, "outer_iters_mean": float(n_outer.mean()),
                               "outer_iters_max": int(n_outer.max()),
                               "ms_per_mpc_step": ms_per_step, "rank0": exit_summary(out, p)},
             "coupled": coupled,
+            "config1": config1,
+            "c4_variants": variants,
         }
         if not args.no_cpu_baseline and world == 1:       # reported at N=1 only (rank 0)
             line["cpu_baseline"] = cpu_baseline(p, xt, spd, refwin, S, N)
@@ -465,7 +473,7 @@ def exit_summary(out, p):
             "outer_cap": int(p.iter_num)}
 
 
-def measure_coupled(name, args, rank, local_rank, world, with_cpu=True):
+def measure_coupled(name, args, rank, local_rank, world, with_cpu=True, inner="osqp_default", steps=None):
     """One coupled scene (c3 / c5) on `world` ranks: vehicles in the spatial order, sharded by strips
     (parallel.VehicleShardedSolver; world == 1: the same numbering on one GPU).  Device-timed steps (L2 flushed, barrier
     on both sides, max over ranks), end-to-end steps from host arrays, exit / convergence summary, a checksum of the
@@ -477,12 +485,15 @@ def measure_coupled(name, args, rank, local_rank, world, with_cpu=True):
     from pi_admm_b200.parallel import VehicleShardedSolver
     (xt, spd, refwin), V, N, D = coupled_scene(name)
     p = coupled_params(N)
+    if inner == "tight":
+        import pi_admm_b200 as pa
+        pa.inner_tight(p)
     vs = VehicleShardedSolver(p, V, D, device=local_rank)
     sol = vs.sol
     vs.setup(xt, spd, refwin)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=sol.device)
     stream = torch.cuda.current_stream()
-    steps, warmup = max(1, args.steps), max(3, args.warmup)
+    steps, warmup = max(1, steps or args.steps), max(3, args.warmup)
 
     def barrier():
         if world > 1:
@@ -558,7 +569,7 @@ def measure_coupled(name, args, rank, local_rank, world, with_cpu=True):
         rec = {"workload": f"{what}, horizon N={N}, one coupled MPC step to PI-ADMM convergence (outer cap {p.iter_num})",
                "vehicles": V, "horizon": N, "neighbour_slots": D, "n_gpus": world, "scaling": "strong",
                "semantics": "dual=pi (per-edge integrators, clamp +-30 + back-calculation; kI=1.5, kP=0: profiles/r2_convergence.md), "
-                            "AL over activated edges, edge=convex, eps_pri=eps_dual=0.5, inner=osqp_default",
+                            "AL over activated edges, edge=convex, eps_pri=eps_dual=0.5, inner=" + inner,
                "parallelism": "single GPU, persistent cooperative kernel" if world == 1 else
                               f"vehicles sharded x{world} by spatial strips; exchange={vs.exchange}" +
                               (f" [{vs.exchange_note}]" if vs.exchange_note else ""),
@@ -605,6 +616,107 @@ def measure_coupled(name, args, rank, local_rank, world, with_cpu=True):
     barrier()
     vs.close()
     return rec
+
+
+def measure_config1(args, local_rank):
+    """BASELINE config 1, the reference's own case: ONE two-vehicle scenario, all 50 - num_ho = 35 receding-horizon steps
+    of casadi/main.py:43-201, in the script's semantics (python_current) and in dual=pi, both inner modes.  Per MPC step
+    the latency of the host-buffer call (piadmm_step_host_at: plant state in, u / pos / xt_next / counts out, synchronous)
+    -- mean and max over the steps with an active edge, as SURVEY 8(d) asks -- and the whole loop on the device."""
+    import torch
+    from pi_admm_b200 import main_intersection
+    from pi_admm_b200.PI_ADMM_class import PI_ADMM_CASADI
+    out = {}
+    for sem in ("python_current", "matlab_pi"):
+        for inner in ("osqp_default", "tight"):
+            P = PI_ADMM_CASADI(semantics=sem, inner=inner)
+            N, V = int(P.param.num_ho), int(P.param.num_veh)
+            sol = P.solver(1)
+            spd = np.asarray(P.param.spd, dtype=np.float64)[None]
+            sol.setup(np.zeros((1, V, 3)), spd, np.zeros((1, V, 2, N + 1)), rho=float(P.param.rho))
+            sol.set_reference(np.ascontiguousarray(P.ref_traj).reshape(1, V, 2, -1))
+            io = sol.alloc_host_io()
+            n_steps = P.ref_traj.shape[1] - N
+            best = None
+            for rep in range(3):                     # the third repetition is reported (clocks, caches, graph warm)
+                io["xt"].copy_(torch.tensor([[[-10.0, 0.0, 0.0], [0.0, 20.0, -np.pi / 2]]], dtype=torch.float64))
+                ms, active, outer = [], [], []
+                for step in range(n_steps):
+                    t0 = time.perf_counter()
+                    sol.step_host_at(step, io)
+                    ms.append((time.perf_counter() - t0) * 1e3)
+                    outer.append(int(io["n_outer"][0]))
+                    active.append(outer[-1] > 1)
+                    io["xt"].copy_(io["xt_next"])
+                best = (ms, active, outer)
+            ms, active, outer = best
+            act = [m for m, a in zip(ms, active) if a] or [0.0]
+            # the same loop without leaving the device
+            t_dev = None
+            for rep in range(3):
+                sol.setup(np.array([[[-10.0, 0.0, 0.0], [0.0, 20.0, -np.pi / 2]]]), spd, np.zeros((1, V, 2, N + 1)), rho=float(P.param.rho))
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); sol.run_closed_loop(0, n_steps); e1.record(); torch.cuda.synchronize()
+                t_dev = e0.elapsed_time(e1)
+            out[f"{sem}/{inner}"] = {"steps": n_steps, "steps_with_active_edge": int(sum(active)),
+                                     "ms_per_step_mean_active": float(np.mean(act)), "ms_per_step_max_active": float(np.max(act)),
+                                     "ms_per_step_mean_all": float(np.mean(ms)), "ms_total": float(np.sum(ms)),
+                                     "outer_iters_total": int(sum(outer)), "outer_iters_max": int(max(outer)),
+                                     "device_loop_ms_total": float(t_dev), "device_loop_ms_per_step": float(t_dev / n_steps)}
+            P._solver.close()
+    return {"workload": "c1: casadi/main.py two-vehicle intersection, 35 MPC steps, ONE scenario (BASELINE config 1); latency of the "
+                        "synchronous host-buffer call per step (wall clock) and of the on-device loop (CUDA events)",
+            "runs": out}
+
+
+def measure_c4_variants(args, local_rank, S, N):
+    """The headline workload in inner="tight" (parity mode: results are solver independent) and as a CLOSED LOOP (20
+    consecutive MPC steps on the device: inputs, active sets and the scheduling order change from step to step, the
+    K^-1 cache stays valid because the speeds do not change) -- ADVICE r1: the replayed step is the best case."""
+    import torch
+    import pi_admm_b200 as pa
+    from pi_admm_b200.scenarios import c4_scenarios, c4_reference
+    from pi_admm_b200.solver import PIADMMSolver
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local_rank}")
+    steps = max(3, min(args.steps, 10))
+    out = {}
+    p = pa.inner_tight(bench_params(N))
+    xt, spd, refwin = c4_scenarios(S=S, N=N)
+    sol = PIADMMSolver(p, S=S, V=2, device=local_rank)
+    sol.setup(xt, spd, refwin)
+    for _ in range(3):
+        sol.iterate()
+    ms = []
+    for _ in range(steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); sol.iterate(); b.record(); torch.cuda.synchronize()
+        ms.append(a.elapsed_time(b))
+    o = sol.to_numpy()
+    out["inner_tight"] = {"ms_per_step": float(np.mean(ms)), "agent_qp_solves_per_s": float(o["n_veh_solves"].sum() / (np.mean(ms) * 1e-3)),
+                          "edge_qp_solves_per_s": float(o["n_edge_solves"].sum() / (np.mean(ms) * 1e-3)),
+                          "veh_inner_iters": int(o["veh_inner"].sum()), "edge_inner_iters": int(o["edge_inner"].sum()),
+                          "inner": "eps 1e-9, max_iter 20000", "steps": steps}
+    sol.close()
+    p = bench_params(N)
+    first, n = 5, 20
+    xt, spd, _ = c4_scenarios(S=S, N=N, step=first)
+    sol = PIADMMSolver(p, S=S, V=2, device=local_rank)
+    sol.set_reference(c4_reference(S=S))
+    t = None
+    for rep in range(3):
+        sol.setup(xt, spd, np.zeros((S, 2, 2, N + 1)))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); h = sol.run_closed_loop(first, n); e1.record(); torch.cuda.synchronize()
+        t = e0.elapsed_time(e1)
+    no = h["n_outer_his"].cpu().numpy()
+    out["closed_loop"] = {"mpc_steps": n, "first_step": first, "ms_per_mpc_step": float(t / n), "ms_total": float(t),
+                          "outer_iters_mean": float(no.mean()), "outer_iters_max": int(no.max()),
+                          "outer_iters_hist": {int(k): int(v) for k, v in zip(*np.unique(no, return_counts=True))},
+                          "note": "piadmm_run_closed_loop: window gather, outer loop, plant step and histories on the device, "
+                                  "no host round trip per MPC step; no L2 flush between steps (one asynchronous call)"}
+    sol.close()
+    return out
 
 
 def run_coupled(args, rank, local_rank, world):
