@@ -435,6 +435,28 @@ template <int LPQ, bool KS>
 __device__ __forceinline__ void run_scenario_v2(const DevCtx& c, int s, const Who<LPQ>& w, const double* Wsm,
                                                 double* gbuf, double* xch, double* krow, int step);
 
+// end of MPC step t of scenario s inside the fused kernel (what k_advance does for the whole batch between launches)
+template <int LPQ>
+__device__ __forceinline__ void advance_scenario_v2(const DevCtx& c, int s, const Who<LPQ>& w, int t) {
+  const piadmm_histories& o = c.hist;
+  const size_t SV = (size_t)c.S * 2, a = (size_t)s * 2 + w.half;
+  if (w.k == 0) {
+    const double* xn = c.b.xt_next + a * 3;
+    double* xt = const_cast<double*>(c.b.xt) + a * 3;
+    const double x = xn[0], y = xn[1], th = xn[2];
+    if (o.x_vec) { o.x_vec[((size_t)t * SV + a) * 2] = x; o.x_vec[((size_t)t * SV + a) * 2 + 1] = y; }
+    if (o.theta_vec) o.theta_vec[(size_t)t * SV + a] = th;
+    if (o.u_vec) o.u_vec[(size_t)t * SV + a] = c.b.u[a * c.N];
+    xt[0] = x; xt[1] = y; xt[2] = th;
+    if (w.half == 0) {
+      if (o.iter_his) o.iter_his[(size_t)t * c.S + s] = c.b.curr_iter[s];
+      if (o.n_outer_his) o.n_outer_his[(size_t)t * c.S + s] = c.b.n_outer[s];
+      if (o.status_his) o.status_his[(size_t)t * c.S + s] = c.b.status[s];
+      if (o.err_rk_his) { const int n = c.b.n_outer[s]; o.err_rk_his[(size_t)t * c.S + s] = n > 0 ? c.b.err_rk[(size_t)s * c.I + n - 1] : 0.0; }
+    }
+  }
+}
+
 // scenario queue: LPQ==16 one scenario per warp, LPQ==32 one per 64-thread CTA
 template <int LPQ>
 __device__ __forceinline__ int next_scenario(const DevCtx& c, const Who<LPQ>& w, int* s_next) {
@@ -527,13 +549,22 @@ __global__ void __launch_bounds__(CTA_THREADS, FEW ? 4 : (LPQ == 16 ? FUSED16_MI
   const int step = c.ref ? step_sh : 0;
   Who<LPQ> w;
   // persistent: every pair pulls scenarios from a global counter until the batch is exhausted
+  const int nloop = c.loop_steps > 0 ? c.loop_steps : 1;
   for (;;) {
     const int s = next_scenario<LPQ>(c, w, &s_next);
     if (s >= c.s_hi) break;
 #ifdef PIADMM_TRACE
     const long long t0 = gtime();
 #endif
-    run_scenario_v2<LPQ, false>(c, s, w, Wsm, gbuf[w.group_in_cta], xch, nullptr, step);
+#pragma unroll 1
+    for (int t = 0; t < nloop; t++) {
+      run_scenario_v2<LPQ, false>(c, s, w, Wsm, gbuf[w.group_in_cta], xch, nullptr, step + t);
+      if (c.loop_steps > 0) {           // histories of casadi/main.py:186,199-201 and xt <- xt_next, by the scenario itself
+        pair_sync<LPQ>();
+        advance_scenario_v2<LPQ>(c, s, w, t);
+        pair_sync<LPQ>();
+      }
+    }
 #ifdef PIADMM_TRACE
     if (w.lane == 0 && s < 8192) {
       unsigned sm; asm("mov.u32 %0, %%smid;" : "=r"(sm));
@@ -1243,9 +1274,12 @@ struct HostStepArgs {
 };
 
 static int launch_fused(piadmm_handle* h, cudaStream_t st, int s_lo, int s_hi, int* queue, int range_id,
-                        const HostStepArgs* zc = nullptr, const int* gather_step = nullptr) {
+                        const HostStepArgs* zc = nullptr, const int* gather_step = nullptr, int loop_steps = 0,
+                        const piadmm_histories* hist = nullptr) {
   DevCtx c = h->c;
   c.s_lo = s_lo; c.s_hi = s_hi; c.queue = queue;
+  c.loop_steps = loop_steps;
+  if (hist) c.hist = *hist;
   if (gather_step) { c.ref = h->d_ref; c.ref_T = h->ref_T; c.step = gather_step; }   // window gather inside the kernel
   if (zc) {      // zero-copy epilogue into mapped host memory (device-visible addresses)
     c.host_out = 1;
@@ -1629,6 +1663,12 @@ int piadmm_run_closed_loop(piadmm_handle* h, int first_step, int n_steps, const 
   CK(cudaMemcpyAsync(h->d_step, h->h_step, sizeof(int), cudaMemcpyHostToDevice, st));
   HostStepArgs none;
   memset(&none, 0, sizeof none);
+  if (fused && !h->fused_ks) {
+    // V == 2: ONE launch.  Scenarios are independent, so each one runs its n_steps MPC steps back to back inside the
+    // persistent kernel (window gather at first_step + t, outer loop, plant step, histories, xt <- xt_next): no launch
+    // and no batch-wide tail per MPC step -- a step of the batch no longer lasts as long as its slowest scenario.
+    return launch_fused(h, st, 0, h->c.S, h->d_queue, 0, &none, h->d_step, n_steps, &o);
+  }
   for (int t = 0; t < n_steps; t++) {
     int rc;
     if (fused) {     // host_out with NULL targets: inline plant step; the kernel gathers the windows at *d_step itself

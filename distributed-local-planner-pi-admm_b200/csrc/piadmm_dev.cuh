@@ -74,6 +74,10 @@ struct DevCtx {
   int host_out;
   double *ho_u, *ho_pos, *ho_xt_next;
   int32_t *ho_curr_iter, *ho_n_outer;
+  // fused kernel, on-device closed loop (piadmm_run_closed_loop, V == 2): every scenario runs ALL loop_steps MPC steps
+  // back to back -- its step t+1 needs nothing but its own step t -- and appends the script's histories itself
+  int loop_steps;
+  piadmm_histories hist;
 };
 
 // ------------------------------------------------------------------ group primitives
