@@ -158,13 +158,26 @@ static int have_device() {
   } while (0)
 #define OBCA_LEAVE() return cudaGetLastError() == cudaSuccess ? PIADMM_OK : PIADMM_E_CUDA
 
+// run on the device that owns the caller's buffers (the entry points carry no handle) and size grids by ITS SM count
+static int use_device_of(const void* p) {
+  cudaPointerAttributes at;
+  int dev = 0;
+  if (p && cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeDevice) dev = at.device;
+  else { cudaGetLastError(); cudaGetDevice(&dev); }
+  cudaSetDevice(dev);
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 1;
+  return sms;
+}
+
 extern "C" {
 
 int obca_lambda_update(const obca_dims* d, obca_state* st, double rho, void* stream) {
   OBCA_ENTER(dims_ok(d) && state_ok(st));
   const size_t n = (size_t)d->S * d->V * d->H * (d->ns + d->nl);
+  const size_t cap = (size_t)use_device_of(st->lamb_bar) * 16;
   size_t grid = (n + 255) / 256;
-  if (grid > 148 * 16) grid = 148 * 16;
+  if (grid > cap) grid = cap;
   k_obca_lambda<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(*d, *st, rho);
   OBCA_LEAVE();
 }
@@ -172,6 +185,7 @@ int obca_lambda_update(const obca_dims* d, obca_state* st, double rho, void* str
 int obca_residuals(const obca_dims* d, const double* ctrl, const double* ctrl_prev, const double* lamb_bar,
                    const double* lamb_bar_prev, double* primal, double* dual, void* stream) {
   OBCA_ENTER(dims_ok(d) && ctrl && ctrl_prev && lamb_bar && lamb_bar_prev && primal && dual);
+  use_device_of(ctrl);
   k_obca_res<<<d->S, OBCA_THREADS, 0, (cudaStream_t)stream>>>(*d, ctrl, ctrl_prev, lamb_bar, lamb_bar_prev, primal, dual);
   OBCA_LEAVE();
 }
@@ -179,12 +193,14 @@ int obca_residuals(const obca_dims* d, const double* ctrl, const double* ctrl_pr
 int obca_check_converge(const obca_dims* d, const obca_state* st, double thres, double min_dis, int32_t* ok,
                         void* stream) {
   OBCA_ENTER(dims_ok(d) && state_ok(st) && ok);
+  use_device_of(ok);
   k_obca_check<<<d->S, 32, 0, (cudaStream_t)stream>>>(*d, *st, thres, min_dis, ok);
   OBCA_LEAVE();
 }
 
 int obca_iterate_next_state(const obca_dims* d, obca_state* st, void* stream) {
   OBCA_ENTER(dims_ok(d) && state_ok(st));
+  use_device_of(st->lamb_bar);
   k_obca_shift<<<d->S, OBCA_THREADS, 0, (cudaStream_t)stream>>>(*d, *st);
   OBCA_LEAVE();
 }
@@ -193,6 +209,7 @@ int obca_consensus_tail(const obca_dims* d, obca_state* cur, obca_state* prev, c
                         double* ctrl_prev, double rho, double primal_thres, double dual_thres, int32_t max_iter,
                         double* primal, double* dual, int32_t* n_iter, int32_t* stop, void* stream) {
   OBCA_ENTER(dims_ok(d) && state_ok(cur) && state_ok(prev) && ctrl && ctrl_prev && primal && dual && n_iter && stop);
+  use_device_of(ctrl);
   ObcaCtx c;
   c.d = *d; c.cur = *cur; c.prev = *prev; c.ctrl = ctrl; c.ctrl_prev = ctrl_prev; c.rho = rho;
   c.primal_thres = primal_thres; c.dual_thres = dual_thres; c.max_iter = max_iter;
