@@ -702,7 +702,7 @@ def measure_c4_variants(args, local_rank, S, N):
     first, n = 5, 20
     xt, spd, _ = c4_scenarios(S=S, N=N, step=first)
     sol = PIADMMSolver(p, S=S, V=2, device=local_rank)
-    sol.set_reference(c4_reference(S=S))
+    sol.set_reference(c4_reference(S=S, T=max(50, first + n + N + 1)))   # every window [step, step + N] of the run inside it
     t = None
     for rep in range(3):
         sol.setup(xt, spd, np.zeros((S, 2, 2, N + 1)))

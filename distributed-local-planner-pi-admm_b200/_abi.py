@@ -162,6 +162,10 @@ _PROTOS = {
     "piadmm_launch_count": (C.c_int64, [C.c_void_p]),
     "piadmm_debug_coop_trace": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "piadmm_fp64_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    # allocation-free collision-edge test (csrc/piadmm_static.cu; no reference counterpart, operators' request)
+    "piadmm_edge_list_static": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "piadmm_static_last_error": (C.c_char_p, []),
     # include/obca_consensus.h (struct pointers passed as void*: obca_consensus.py owns the ctypes mirrors)
     "obca_lambda_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p]),
     "obca_residuals": (C.c_int, [C.c_void_p] * 7 + [C.c_void_p]),

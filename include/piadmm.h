@@ -220,6 +220,30 @@ int piadmm_run_closed_loop(piadmm_handle* h, int first_step, int n_steps, const 
  * barrier, decide.  n <= 1024. */
 int piadmm_debug_coop_trace(piadmm_handle* h, int64_t* host_out, int n);
 
+/* Allocation-free collision-edge test.  NO COUNTERPART IN THE REFERENCE as an entry point: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  What it computes is casadi/main.py:110-113 (edge_mat[i,j] = 1 when any of the N+1
+ * trajectory points of vehicles i < j are closer than the threshold) and the row-major pair list of :121
+ * (np.where(edge_mat == 1)) -- the matrix form of piadmm_detect_edges (k_bbox + k_hits + emit) without a handle and
+ * without slot tables: its scratch (trajectory bounding boxes + the hit bit matrix) lives in ONE file-scope __device__
+ * array of fixed size (csrc/piadmm_static.cu, 2.25 MiB, held by every GPU that loads the library until exit).
+ *   pos [S,V,2,N+1] device, fp64 (pos_old of piadmm_buffers); N = 1..31;
+ *   threshold: d^2 < dis_thres (thr_squared = 0, casadi/main.py:113) or d^2 < dis_thres^2 (thr_squared = 1, MATLAB :109);
+ *   edge_n [S] device: number of colliding pairs of the scenario (may exceed e_cap);
+ *   edge_ij [S,e_cap,2] device: the first e_cap pairs (veh1 < veh2), sorted by (veh1, veh2); rows >= edge_n untouched.
+ * Limits: S*V <= PIADMM_STATIC_MAX_VEH and S*V*ceil(V/32) <= PIADMM_STATIC_MAX_WORDS (one 4096-vehicle scene, or 4096
+ * two-vehicle scenarios); anything larger returns PIADMM_E_UNSUPPORTED (text: piadmm_static_last_error).
+ * Calls no cudaMalloc / cudaFree / allocating routine; asynchronous on `stream`; runs on the device that owns `pos` and
+ * leaves the caller's current device as it was.  The first call on a device looks up the array's device address
+ * (cudaGetSymbolAddress) -- make it before starting a graph capture.  All calls on a device share the array: calls
+ * ordered on the GPU are fine, calls that OVERLAP on the GPU (different unordered streams) race on it.  Nothing has to
+ * be cleared between calls: every scratch word a call reads was written by the same call. */
+#define PIADMM_STATIC_MAX_VEH 8192
+#define PIADMM_STATIC_MAX_WORDS 524288
+int piadmm_edge_list_static(const double* pos, int S, int V, int N, double dis_thres, int thr_squared, int e_cap,
+                            int32_t* edge_n, int32_t* edge_ij, void* stream);
+const char* piadmm_static_last_error(void);
+
 /* statistics for the roofline: kernels launched by this handle since creation */
 int64_t piadmm_launch_count(const piadmm_handle* h);
 
