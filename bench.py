@@ -401,16 +401,18 @@ def main():
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         abytes = algorithmic_bytes(N, n_veh, n_edge, S)
-        traffic = None
+        traffic, traffic_source = None, None
         try:   # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+            tpath = [f for f in ("r2_traffic.json", "r1_traffic.json") if os.path.exists(os.path.join(ROOT, "profiles", f))][0]
+            tj = json.load(open(os.path.join(ROOT, "profiles", tpath)))
             if args.workload == "c4":
                 traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+                traffic_source = f"profiles/{tpath} (one ncu --set full capture of this kernel), NOT measured in this run"
         except Exception:
             pass
         roofline = {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
                     "frac": (achieved / fp64_peak) if fp64_peak else None, "traffic": traffic,
-                    "kernel": "k_fused_v2", "peak_source": "DFMA micro-benchmark of this repo (piadmm_fp64_peak), "
+                    "traffic_source": traffic_source, "kernel": "k_fused_v2", "peak_source": "DFMA micro-benchmark of this repo (piadmm_fp64_peak), "
                     "MEASURED_PEAKS.json has no fp64 figure",
                     "flops_per_launch": flops, "inner_iters_per_launch": veh_inner + edge_inner,
                     "hbm": {"achieved": abytes / kern_s / 1e9, "peak": hbm_peak, "unit": "GB/s",

@@ -1,5 +1,9 @@
-"""Regenerates profiles/ from the files a gpurun profiling call left in gpurun_out/ (tag = e.g. r1f):
-bench_<tag>.json, bench_<tag>_ref.json, launches_<tag>.csv, prof_<tag>.ncu-rep.   python tools/make_profiles.py r1f"""
+"""Regenerates the round's files under profiles/ from what a profiling gpurun call (tools/gpu_call_profile.sh <tag>) left in
+gpurun_out/:  bench_<tag>.json, bench_<tag>_ref.json, bench_<tag>_{c3,c5,n30}.json, launches_<tag>.csv, launches_<tag>_c5.csv,
+prof_<tag>.ncu-rep (k_fused_v2), prof_<tag>_coop.ncu-rep (k_coop).
+
+    python tools/make_profiles.py r2a [r2]        # tag of the call, prefix of the files written (default r2)
+"""
 import csv
 import json
 import os
@@ -10,37 +14,32 @@ from collections import defaultdict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G, P, S = (os.path.join(ROOT, d) for d in ("gpurun_out", "profiles", "scratch"))
+SCALE = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+KEYS = ("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "smsp__warps_active.avg.per_cycle_active", "smsp__warps_eligible.avg.per_cycle_active", "gpu__time_duration.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "launch__registers_per_thread", "launch__grid_size",
+        "smsp__sass_inst_executed_op_local_ld.sum", "smsp__sass_inst_executed_op_local_st.sum")
 
 
-def main(tag):
-    os.makedirs(S, exist_ok=True)
-    rep = os.path.join(G, f"prof_{tag}.ncu-rep")
+def ncu_summary(rep, out_txt, tag):
     raw, src = os.path.join(S, f"{tag}_raw.csv"), os.path.join(S, f"{tag}_src.csv")
     for page, out in (("raw", raw), ("source", src)):
         with open(out, "w") as f:
             subprocess.run(["ncu", "-i", rep, "--page", page, "--csv"], stdout=f, stderr=subprocess.DEVNULL, check=True)
-    subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_summary.py"), raw, src,
-                    os.path.join(P, "r1_k_fused_v2_ncu_full.txt")], check=True, stdout=subprocess.DEVNULL)
-    shutil.copy(os.path.join(G, f"launches_{tag}.csv"), os.path.join(P, "r1_launches_bench.csv"))
-    shutil.copy(os.path.join(G, f"bench_{tag}.json"), os.path.join(P, "r1_bench_1gpu.json"))
-    shutil.copy(os.path.join(G, f"bench_{tag}_ref.json"), os.path.join(P, "r1_bench_reference_arm.json"))
-    if os.path.exists(os.path.join(G, f"bench_{tag}_n30.json")):
-        shutil.copy(os.path.join(G, f"bench_{tag}_n30.json"), os.path.join(P, "r1_bench_1gpu_n30.json"))
+    subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_summary.py"), raw, src, out_txt], check=True,
+                   stdout=subprocess.DEVNULL)
     rows = list(csv.reader(open(raw)))
-    hdr, data = rows[0], rows[2:]
+    hdr, units, data = rows[0], rows[1], rows[2:]
     val = lambda k: float(data[0][hdr.index(k)].replace(",", ""))
-    unit = lambda k: rows[1][hdr.index(k)]
-    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    rd = val("dram__bytes_read.sum") * scale[unit("dram__bytes_read.sum")]
-    wr = val("dram__bytes_write.sum") * scale[unit("dram__bytes_write.sum")]
-    json.dump({"kernel": "k_fused_v2<16>", "dram_bytes_read": int(rd), "dram_bytes_write": int(wr),
-               "source": "profiles/r1_k_fused_v2_ncu_full.txt (ncu --set full, 1 launch; the writes are mostly the "
-                         "write-back of the 256 MiB L2-flush buffer)"}, open(os.path.join(P, "r1_traffic.json"), "w"))
-    m = {k: val(k) for k in ("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
-                             "smsp__issue_active.avg.pct_of_peak_sustained_active",
-                             "smsp__warps_active.avg.per_cycle_active", "smsp__warps_eligible.avg.per_cycle_active",
-                             "gpu__time_duration.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed")}
-    lr = [r for r in csv.reader(open(os.path.join(P, "r1_launches_bench.csv"))) if len(r) > 5]
+    m = {k: val(k) for k in KEYS if k in hdr}
+    m["dram_read"] = val("dram__bytes_read.sum") * SCALE[units[hdr.index("dram__bytes_read.sum")]]
+    m["dram_write"] = val("dram__bytes_write.sum") * SCALE[units[hdr.index("dram__bytes_write.sum")]]
+    tail = "\n".join(l for l in open(out_txt).read().splitlines() if l.startswith(("opcode mix", "warp stall", "hot straight", "  [")))
+    return m, tail
+
+
+def launch_table(path, step_kernels):
+    lr = [r for r in csv.reader(open(path)) if len(r) > 5]
     ki, vi = lr[0].index("Kernel Name"), lr[0].index("Metric Value")
     d = defaultdict(list)
     for r in lr[1:]:
@@ -48,99 +47,147 @@ def main(tag):
             d[r[ki][:70]].append(float(r[vi].replace(",", "")))
         except ValueError:
             pass
-    step = [k for k in d if "k_fused" in k or "k_order" in k or "k_refwin" in k or "k_plant" in k]
+    step = [k for k in d if any(s in k for s in step_kernels)]
+    per_launch = max(len(d[k]) for k in step) if step else 1
     tot = sum(sum(d[k]) for k in step)
-    lines = [f"| `{k}` | {len(v)} | {sum(v) / len(v) / 1e3:.1f} | {'%.3f' % (sum(v) / tot) if k in step else '(not part of a step)'} |"
-             for k, v in sorted(d.items(), key=lambda kv: -sum(kv[1]))]
-    b = json.load(open(os.path.join(P, "r1_bench_1gpu.json")))
-    r = json.load(open(os.path.join(P, "r1_bench_reference_arm.json")))
-    full = open(os.path.join(P, "r1_k_fused_v2_ncu_full.txt")).read().splitlines()
-    tail = "\n".join(l for l in full if l.startswith(("opcode mix", "warp stall", "hot straight", "  [")))
+    rows = [f"| `{k}` | {len(v)} | {sum(v) / len(v) / 1e3:.1f} | {'%.3f' % (sum(v) / tot) if k in step else '(not part of a step)'} |"
+            for k, v in sorted(d.items(), key=lambda kv: -sum(kv[1]))]
+    return "\n".join(rows), tot / per_launch / 1e3
+
+
+def coupled_row(name, c):
+    ex = [k for k, v in c["exit"].items() if v][0]
+    return (f"| {name} | {c['vehicles']} | {c['ms_per_step']:.3f} | {c['e2e']['ms_per_step']:.3f} | {c['work_per_step']['outer_iters']} | "
+            f"{ex} | {c['converged']} | {c['residual_at_exit']['err_rk_max']:.3g} / {c['residual_at_exit']['err_sk_max']:.3g} "
+            f"(eps {c['residual_at_exit']['eps_pri']}) | {int(c['work_per_step']['agent_qp_solves'])} / "
+            f"{int(c['work_per_step']['edge_solves_incl_redundant_cut_edges'])} | {c['gpu_launches_per_step']:.0f} | "
+            f"{c.get('cpu_baseline', {}).get('ms_per_step', float('nan')):.1f} |")
+
+
+def main(tag, R="r2"):
+    os.makedirs(S, exist_ok=True)
+    cp = lambda a, b: shutil.copy(os.path.join(G, a), os.path.join(P, b)) if os.path.exists(os.path.join(G, a)) and os.path.getsize(os.path.join(G, a)) else None
+    cp(f"launches_{tag}.csv", f"{R}_launches_bench.csv")
+    cp(f"launches_{tag}_c5.csv", f"{R}_launches_c5.csv")
+    cp(f"bench_{tag}.json", f"{R}_bench_1gpu.json")
+    cp(f"bench_{tag}_ref.json", f"{R}_bench_reference_arm.json")
+    cp(f"bench_{tag}_n30.json", f"{R}_bench_1gpu_n30.json")
+    cp(f"bench_{tag}_c3.json", f"{R}_bench_c3.json")
+    cp(f"bench_{tag}_c5.json", f"{R}_bench_c5.json")
+    m, tail = ncu_summary(os.path.join(G, f"prof_{tag}.ncu-rep"), os.path.join(P, f"{R}_k_fused_v2_ncu_full.txt"), tag)
+    mc, tailc = ncu_summary(os.path.join(G, f"prof_{tag}_coop.ncu-rep"), os.path.join(P, f"{R}_k_coop_ncu_full.txt"), tag + "_coop")
+    json.dump({"kernel": "k_fused_v2<16>", "dram_bytes_read": int(m["dram_read"]), "dram_bytes_write": int(m["dram_write"]),
+               "source": f"profiles/{R}_k_fused_v2_ncu_full.txt (ncu --set full, 1 launch; the writes are mostly the "
+                         "write-back of the 256 MiB L2-flush buffer)"}, open(os.path.join(P, f"{R}_traffic.json"), "w"))
+    b = json.load(open(os.path.join(P, f"{R}_bench_1gpu.json")))
+    r = json.load(open(os.path.join(P, f"{R}_bench_reference_arm.json")))
+    lines, step_us = launch_table(os.path.join(P, f"{R}_launches_bench.csv"), ("k_fused", "k_order", "k_refwin", "k_plant"))
+    lines5, step5_us = launch_table(os.path.join(P, f"{R}_launches_c5.csv"), ("k_coop", "k_cand", "k_disc", "k_plant"))
     w = b["work_per_step"]
-    open(os.path.join(P, "README.md"), "w").write(f"""# profiles/ — round 1 evidence (B200, sm_100a, driver 580.159, CUDA 12.9)
+    cpl = b.get("coupled", {})
+    c1 = b.get("config1", {}).get("runs", {})
+    n30 = json.load(open(os.path.join(P, f"{R}_bench_1gpu_n30.json"))) if os.path.exists(os.path.join(P, f"{R}_bench_1gpu_n30.json")) else None
+    c1rows = "\n".join(f"| {k} | {v['steps_with_active_edge']} / {v['steps']} | {v['ms_per_step_mean_active']:.3f} | {v['ms_per_step_max_active']:.3f} | "
+                       f"{v['ms_total']:.2f} | {v['device_loop_ms_per_step']:.3f} | {v['outer_iters_total']} |" for k, v in c1.items())
+    cv = b.get("c4_variants", {})
+    open(os.path.join(P, "README.md"), "w").write(f"""# profiles/ — round 2 evidence (B200, sm_100a, driver 580.159, CUDA 12.9)
 
-Regenerate with `python tools/make_profiles.py <tag>` after a profiling `gpurun` call (commands below).
+Regenerate with `python tools/make_profiles.py <tag>` after `gpurun -- 'bash tools/gpu_call_profile.sh <tag>'`.
+Round-1 files (`r1_*`) are kept as history; `r1_history.md` / `r2_history.md` say what each optimisation step bought.
 
-Files
-* `r1_bench_1gpu.json` — `python bench.py --steps 100 --warmup 5` (N=1, config 4: 4096 two-vehicle scenarios, N=15);
-  `r1_bench_1gpu_n30.json` — the N=30 variant (`--workload c4n30`).
-* `r1_bench_c3.json`, `r1_bench_c5.json`, `r1_bench_c5_2gpu.json` — `python bench.py --workload c3|c5` (ONE coupled scene through
-  the generic-V phase kernels: 64-vehicle intersection 1.21 ms, 4096-vehicle grid 5.76 ms per coupled MPC step; c5 under
-  torchrun on 2 GPUs, vehicles sharded over NCCL: 6.04 ms).
-* `r1_bench_reference_arm.json` — `python bench.py --impl reference --steps 20 --warmup 2` (oracle C twin, all host cores).
-* `r1_launches_bench.csv` — `ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv` of
-  `python bench.py --steps 3 --warmup 3 --no-cpu-baseline` (every launch with its device time).
-* `r1_k_fused_v2_ncu_full.txt` — summary (tools/ncu_summary.py) of one
-  `ncu --set full --clock-control none --import-source on -k regex:k_fused -s 3 -c 1` capture; `r1_traffic.json` = its DRAM bytes.
-* `r1_c5_phases.txt` — per-phase CUDA-event times of the generic-V phase kernels (configs 3 and 5 shapes) and the 2-GPU NCCL run.
-* `r1_history.md` — what each optimisation step bought (bench numbers per commit).
-* `r1_scaling.md` — 1 / 2 / 4 / 8 GPU runs (config 4 weak scaling, config 5 vehicle sharding over NCCL).
-* Tools behind the analysis in `r1_history.md`: `tools/single_scenario_latency.py` (one scenario alone on the GPU),
-  `tools/contention.py` (1-4 warps per SM sub-partition), `tools/trace_step.py` (start / end time of every scenario,
-  needs a `-DPIADMM_TRACE` build), `tools/sass_loops.py` (hot loops of the SASS), `tools/c5_phases.py`,
-  `tools/closed_loop_bench.py`.
+Files of this round
+* `{R}_bench_1gpu.json` — `python bench.py --steps 100 --warmup 5`: the default line (config 4, `value` / `e2e` / `roofline` /
+  `cpu_baseline`) with the `coupled` records (configs 5 and 3, osqp_default and tight), `config1` (the 35-step run of
+  `casadi/main.py`, 4 semantics x inner modes) and `c4_variants` (tight mode, 20-step closed loop on the device).
+  `{R}_bench_1gpu_n30.json` — `--workload c4n30`; `{R}_bench_c3.json`, `{R}_bench_c5.json` — `--workload c3|c5` as own lines.
+* `{R}_bench_reference_arm.json` — `python bench.py --impl reference --steps 20 --warmup 2` (oracle C twin, all host cores).
+* `{R}_launches_bench.csv`, `{R}_launches_c5.csv` — `ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv` of
+  `python bench.py --steps 3 --warmup 3 --no-cpu-baseline [--no-coupled | --workload c5]` (every launch with its device time).
+* `{R}_k_fused_v2_ncu_full.txt`, `{R}_k_coop_ncu_full.txt` — summaries (tools/ncu_summary.py) of one
+  `ncu --set full --clock-control none --import-source on -k regex:<kernel> -s 3 -c 1` capture each; `{R}_traffic.json` = DRAM bytes
+  of the fused kernel.
+* `{R}_scaling.md` — 1 / 2 / 8 GPU runs (config 4 weak scaling; config 5 vehicle-sharded, peer exchange vs NCCL) and what bounds them;
+  `{R}_mgpu_*.jsonl`, `{R}_bench_*gpu*.json` — the lines behind it.  `{R}_coop_phases_*.txt` — phase timelines of the cooperative
+  kernel (`piadmm_debug_coop_trace`, tools/coop_phases.py).
+* `{R}_convergence.md`, `{R}_coupled_gain_scan.txt` — convergence of the coupled configurations (VERDICT r1 #2);
+  `{R}_ruiz_experiment.txt` — OSQP's Ruiz equilibration restated on the numpy oracle (more inner iterations, not fewer).
 
-## Headline (1 x B200)
+## Headline (1 x B200): config 4, 4096 independent two-vehicle scenarios, N = 15
 
 | quantity | value |
 |---|---|
-| agent-QP solves/s, inputs resident in HBM (`value`) | **{b['value']:.3e}** ({b['ms_per_step']:.3f} ms per 4096-scenario MPC step: {int(w['agent_qp_solves'])} vehicle QPs + {int(w['edge_solves'])} edge problems, {int(w['veh_inner_iters'] + w['edge_inner_iters'])} inner ADMM iterations, outer iterations mean {w['outer_iters_mean']:.2f}) |
+| agent-QP solves/s, inputs resident in HBM (`value`) | **{b['value']:.3e}** ({b['ms_per_step']:.3f} ms per 4096-scenario MPC step: {int(w['agent_qp_solves'])} vehicle QPs + {int(w['edge_solves'])} edge problems, {int(w['veh_inner_iters'] + w['edge_inner_iters'])} inner ADMM iterations, outer iterations mean {w['outer_iters_mean']:.2f}; exits: {w['rank0']['exit']}) |
+| edge-QP solves/s | {b.get('edge_qp_solves_per_s', float('nan')):.3e} |
 | end to end through `piadmm_step_host_at`, pinned host buffers, reference trajectories resident (`e2e`) | **{b['e2e']['value']:.3e}** ({b['e2e']['ms_per_step']:.3f} ms; H2D {b['e2e']['h2d_bytes_per_step']} B (plant state + step index) + D2H {b['e2e']['d2h_bytes_per_step']} B per step, stored by the kernel into the mapped pinned buffers) |
 | end to end through `piadmm_step_host` (xt, spd and the reference window uploaded every step) | {b['e2e']['full_upload']['value']:.3e} ({b['e2e']['full_upload']['ms_per_step']:.3f} ms; H2D {b['e2e']['full_upload']['h2d_bytes_per_step']} B) |
 | CPU arm (`--impl reference`: oracle C twin = "port", {r['cpu_baseline']['cores']} OpenMP threads of the GPU box) | {r['value']:.3e} solves/s |
 | e2e / CPU arm | {b['e2e']['value'] / r['value']:.1f}x |
 | kernel launches per step | {b['gpu_launches'] // b['steps']} (`k_fused_v2<16>` + `k_order`, the longest-first schedule for the next step) |
 | FP64 roofline: algorithmic flops / launch time / repo-measured DFMA peak ({b['roofline']['peak']:.1f} TFLOP/s) | {b['roofline']['achieved']:.2f} TFLOP/s = **{b['roofline']['frac']:.3f}** |
-| ncu (one launch, {m['gpu__time_duration.sum']:.0f} us) | FP64 pipe active {m['sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active']:.1f} % of active cycles; issue slots busy {m['smsp__issue_active.avg.pct_of_peak_sustained_active']:.1f} %; {m['smsp__warps_active.avg.per_cycle_active']:.2f} warps / SM sub-partition active, {m['smsp__warps_eligible.avg.per_cycle_active']:.2f} eligible |
-| ncu DRAM | {rd / 1e6:.2f} MB read + {wr / 1e6:.1f} MB written per launch (the writes are the write-back of the L2-flush buffer); DRAM throughput {m['gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed']:.2f} % of peak: not HBM-bound |
+| ncu (one launch, {m['gpu__time_duration.sum']:.0f} us, {m['launch__registers_per_thread']:.0f} registers) | FP64 pipe active {m['sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active']:.1f} % of active cycles; issue slots busy {m['smsp__issue_active.avg.pct_of_peak_sustained_active']:.1f} %; {m['smsp__warps_active.avg.per_cycle_active']:.2f} warps / SM sub-partition active, {m['smsp__warps_eligible.avg.per_cycle_active']:.2f} eligible; local loads / stores {m.get('smsp__sass_inst_executed_op_local_ld.sum', 0):.0f} / {m.get('smsp__sass_inst_executed_op_local_st.sum', 0):.0f} |
+| ncu DRAM | {m['dram_read'] / 1e6:.2f} MB read + {m['dram_write'] / 1e6:.1f} MB written per launch (the writes are the write-back of the L2-flush buffer); DRAM throughput {m['gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed']:.2f} % of peak: not HBM-bound |
+| tight inner mode (eps 1e-9; results solver independent) | {cv.get('inner_tight', {}).get('ms_per_step', float('nan')):.3f} ms per step, {cv.get('inner_tight', {}).get('agent_qp_solves_per_s', float('nan')):.3e} solves/s |
+| closed loop on the device, 20 consecutive MPC steps of all 4096 scenarios | {cv.get('closed_loop', {}).get('ms_per_mpc_step', float('nan')):.3f} ms per MPC step (outer iterations up to {cv.get('closed_loop', {}).get('outer_iters_max', '?')}) |
+| N = 30 variant (`--workload c4n30`) | {('%.3f ms per step, %.3e solves/s, frac %.3f' % (n30['ms_per_step'], n30['value'], n30['roofline']['frac'])) if n30 else 'n/a'} |
 | clocks during the timed region | {b['clocks']} |
 
-## Launch list (shares of the MPC step = k_fused_v2 + k_order)
+## Coupled scenes (one scene per GPU, persistent cooperative kernel `k_coop`)
+
+| record | V | ms per coupled MPC step (device) | e2e ms (host buffers) | outer iterations | exit | converged | residual at exit | vehicle QPs / edge problems solved | launches per step | CPU twin ms (16 threads) |
+|---|---|---|---|---|---|---|---|---|---|---|
+{chr(10).join(coupled_row(k, v) for k, v in cpl.items())}
+
+Parity of every record against the CPU twin is checked inside the bench (`parity_vs_cpu_port`: identical outer iteration
+counts, edge lists and solve counts; u within {max(v.get('parity_vs_cpu_port', {}).get('u_rel_err', 0) for v in cpl.values()):.1e} relative).
+
+## Config 1 (`casadi/main.py`, ONE scenario, 35 MPC steps): latency
+
+| semantics / inner | steps with an active edge | mean ms per step (active) | max ms | total ms (35 steps, synchronous host calls) | on-device loop ms per step | outer iterations |
+|---|---|---|---|---|---|---|
+{c1rows}
+
+## Launch lists (cold cache, serialised under ncu: shares, not absolutes)
+
+Config-4 step = `k_fused_v2` + `k_order` ({step_us:.1f} us per step under ncu vs {b['ms_per_step'] * 1e3:.1f} us by CUDA events in the bench):
 
 | kernel | launches | avg us | share of step |
 |---|---|---|---|
-""" + "\n".join(lines) + f"""
+{lines}
 
-`k_fp64_peak` is the one-off peak micro-benchmark after the timed region; torch fill kernels are buffer initialisation
-and the L2 flush (outside the event pairs); with a resident reference the fused kernel gathers the reference windows
-itself (`k_refwin` only remains for the generic-V and non-zero-copy paths, `k_plant` for the non-zero-copy host path).  The ncu duration of `k_fused_v2<16>` plus `k_order`
-agrees with the CUDA-event time of the bench: the fused kernel IS the step.
+Config-5 step = `k_disc` + `k_cand` + `k_cand_list` (candidate build, once per MPC step) + `k_coop` (all outer iterations) (+ `k_plant`): {step5_us:.1f} us per step under ncu:
 
-## Reading of the full capture (what limits the kernel)
+| kernel | launches | avg us | share of step |
+|---|---|---|---|
+{lines5}
+
+`k_fp64_peak` is the one-off peak micro-benchmark after the timed region; torch fill / gather kernels are buffer
+initialisation, the spatial permutation of the inputs and the L2 flush (outside the event pairs).
+
+## Reading of the full capture: `k_fused_v2<16>` (what limits the config-4 step)
 
 {tail}
 
-* 4096 scenario-warps for 2368 resident warp slots (8 CTAs x 2 warps per SM, 128 registers).  Issue slots are about
-  half busy and the FP64 pipe 40 %: the kernel is **dependency-latency bound, not FP64-throughput bound**
-  (stalls: `wait` = fixed-latency dependent FP64 chains, `short_scoreboard` = LDS / SHFL results; in the mat-vec
-  only two of the eight LDS.128 of the right-hand side are in flight at a time because the 32 registers of the
-  K^-1 row leave no room for more).
-* More resident warps do not help: 96 / 80 registers (10 / 12 CTAs per SM) spill in the hot loop (0.348 / 0.407 ms
-  vs 0.319 ms at that commit); K^-1 rows in shared memory (`PIADMM_FUSED=ks`, 72 registers, all 4096 scenarios
-  resident) makes the mat-vec LDS-bound (shared-memory pipe 58 % busy) and is no faster.
-* What did help this round (profiles/r1_history.md): loop-invariant parameter loads hoisted out of the inner loop
-  (they were generic loads from the kernel parameter block on the dependency chain), branch-free hinge prox without
-  a division, 2x2-block Gauss-Jordan builds (half the latency rounds; the builds were ~20 % of the time), nested
-  block counters instead of a spilled loop counter, and a longest-first scenario order learnt from the previous step
-  (scenario work varies 2.7x; elapsed / active SM cycles went from 1.32 to 1.14).
-* Algorithmic flops are ~20 % of the DFMA peak while the pipe is ~40 % busy: the difference is Gauss-Jordan rebuilds
-  of K^-1 at an adapted rho (about 0.7 per solve), termination checks, the padded 16th lane and the lock-step wait of the faster
-  vehicle of a warp (16 %).
-* K^-1(rho0) is cached in global memory across outer iterations and MPC steps (key = the coefficients that define K),
-  so only the rebuilds at an adapted rho remain (~0.7 per solve, ~10 % of the samples).  The 35 MB of cache entries
-  are what the DRAM read figure above consists of (the bench flushes L2 before every step).
-* Sample shares of the current kernel (source page): inner-iteration loops 50 % (vehicle loop 70, edge loop 126 SASS
-  instructions per iteration), per-call prologue / epilogue of the x-update and the edge step 18 % (reference tracking
-  terms, roll-outs, dual / PI update), termination checks 13 %, Gauss-Jordan rebuilds 10 %, scenario initialisation
-  and queue 5 %.
-* What bounds the step is analysed in r1_history.md ("Where the time of a step goes now"): a scenario is a serial
-  chain (~680 cycles per edge iteration alone), the sub-partition saturates at 3-4 such warps (4.1 / 7.4 / 9.5 / 10.7
-  scenarios per us at 1 / 2 / 3 / 4 warps), and the step is two scenario latencies per warp slot.
-* Next candidates: pair like vehicles of two scenarios in a warp, rebuild K^-1(rho) from a cached eigen-decomposition
-  of the pencil (K0, A'A) instead of Gauss-Jordan, slimmer termination checks.
+* 4096 scenario-warps for 2368 resident warp slots (8 CTAs x 2 warps per SM, 128 registers).  Issue slots are about half busy and
+  the FP64 pipe ~40 %: the kernel is **dependency-latency bound, not FP64-throughput bound** (stalls: `wait` = fixed-latency
+  dependent FP64 chains, `short_scoreboard` = LDS / SHFL results).
+* Algorithmic flops are ~21 % of the DFMA peak while the pipe is ~39 % busy: the difference is Gauss-Jordan rebuilds of K^-1 at an
+  adapted rho, termination checks, prologue / epilogue of the x-update and edge step, the padded 16th lane and the lock-step wait of
+  the faster vehicle of a warp.  `{R}_history.md` has the per-region sample shares and what was tried against each.
+
+## Reading of the full capture: `k_coop<32>` (config 5, one 4096-vehicle scene)
+
+{tailc}
+
+* ncu: {mc['gpu__time_duration.sum']:.0f} us, grid {mc['launch__grid_size']:.0f} CTAs x 64 threads ({mc['launch__registers_per_thread']:.0f} registers, no spills in the loops), FP64 pipe
+  {mc['sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active']:.1f} %, issue slots {mc['smsp__issue_active.avg.pct_of_peak_sustained_active']:.1f} %, DRAM {mc['dram_read'] / 1e6:.1f} MB read (the K^-1 cache entries and the scene after the L2 flush).
+* The two hottest "regions" are the six-instruction polling loops of the grid barrier (`LD / CCTL / YIELD`): most CTAs WAIT most of
+  the time.  A coupled step is a chain of dependent phases (x phase -> slots -> edges -> z phase -> decide, 4 outer iterations
+  here), each as long as its slowest problem; after the first iteration x_memo leaves a few hundred vehicle QPs and ~10-360 edge
+  problems per phase, i.e. a small fraction of the 592 CTAs has work.  The fraction of the FP64 peak (0.026) says how little of a
+  B200 one coupled scene can fill; the batched config-4 line is the throughput figure.
 """)
-    print("profiles/ regenerated from tag", tag)
+    print("profiles/ regenerated from tag", tag, "as", R)
 
 
 if __name__ == "__main__":
-    main(sys.argv[1])
+    main(*sys.argv[1:3])
