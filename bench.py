@@ -377,7 +377,11 @@ def main():
     # ---- max over ranks, sums of work ------------------------------------------------------
     stats = torch.tensor([total_ms, e2e_s * 1e3, e2e_full_s * 1e3], dtype=torch.float64, device=sol.device)
     work = torch.tensor([n_veh, n_edge, veh_inner, edge_inner], dtype=torch.float64, device=sol.device)
+    per_rank = None
     if world > 1:
+        gathered = [torch.zeros_like(stats) for _ in range(world)]
+        dist.all_gather(gathered, stats)                  # per-rank times: how much of the max-over-ranks is spread
+        per_rank = [[float(x) / args.steps for x in g.tolist()] for g in gathered]
         dist.all_reduce(stats, op=dist.ReduceOp.MAX)
         dist.all_reduce(work, op=dist.ReduceOp.SUM)
     total_ms, e2e_ms, e2e_full_ms = [float(x) for x in stats.tolist()]
@@ -425,6 +429,7 @@ def main():
             "config": workload_config(args.workload, S, N, world),
             "e2e": {"value": e2e_value, "unit": "solves/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps,
+                    "ms_per_step_by_rank": [round(r[1], 5) for r in per_rank] if per_rank else None,
                     "api": "piadmm_step_host_at (C ABI, pinned host buffers, copies inside; reference trajectories "
                            "resident on the device as in the reference's PI_ADMM_CASADI.ref_traj, per step H2D = plant "
                            "state xt + step index, D2H = u, pos, xt_next, curr_iter, n_outer)",
