@@ -146,6 +146,8 @@ _PROTOS = {
     "piadmm_residuals": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_solve_edges": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_get_edge_u": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "piadmm_solve_joint": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]),
     "piadmm_set_ownership": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "piadmm_residual_partials": (C.c_int, [C.c_void_p, C.c_void_p]),
     "piadmm_residual_decide": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -70,6 +70,7 @@ template <int LPQ>
 __device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) { load_tabs<LPQ>(c, Wsm, 0, PIADMM_NTAB); }
 
 #include "piadmm_coop.cuh"
+#include "piadmm_joint.cuh"
 
 // ------------------------------------------------------------------ phase kernels (generic V)
 __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
@@ -1191,6 +1192,27 @@ int piadmm_get_edge_u(piadmm_handle* h, double* host_out, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   CK(cudaMemcpyAsync(host_out, h->c.edge_u, sizeof(double) * (size_t)h->c.S * h->c.E * 2 * h->c.N, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  return PIADMM_OK;
+}
+
+int piadmm_solve_joint(piadmm_handle* h, const int32_t* pair_n, const int32_t* pair_ij, int P, double hinge_weight,
+                       double* u_out, int32_t* iters_out, int32_t* status_out, void* stream) {
+  REQUIRE_BOUND();
+  if (!pair_n || !pair_ij || P < 1 || !u_out || !iters_out || !status_out || !(hinge_weight >= 0.0)) {
+    h->err = "piadmm_solve_joint: NULL argument, P < 1 or a negative hinge weight";
+    return PIADMM_E_ARG;
+  }
+  const int G = JT_THREADS / h->lpq, CL = (h->c.V + G - 1) / G;
+  if (CL > JT_MAX_CLUSTER) {
+    h->err = "piadmm_solve_joint: the scene does not fit one thread-block cluster (V <= 64 for N > 15, V <= 128 for N <= 15)";
+    return PIADMM_E_UNSUPPORTED;
+  }
+  JointArgs ja;
+  ja.pair_n = pair_n; ja.pair_ij = pair_ij; ja.P = P; ja.hinge = hinge_weight;
+  ja.u_out = u_out; ja.iters_out = iters_out; ja.status_out = status_out;
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(h->lpq == 16 ? launch_joint<16>(h->c, ja, CL, st) : launch_joint<32>(h->c, ja, CL, st));
+  LAUNCHED();
   return PIADMM_OK;
 }
 

@@ -103,6 +103,30 @@ class PIADMMSolver:
     def update_residuals(self):
         self._check(self.lib.piadmm_residuals(self._h, self._stream()), "piadmm_residuals")
 
+    def solve_joint(self, pair_n, pair_ij, hinge_weight=None):
+        """ONE joint RSU edge problem per scenario over all V vehicles (piadmm_solve_joint; cost_function_edge of
+        matlab_old_files/ADMM_fmincon_multi_veh_intesection_static.m:250-291 in its convex statement).  Uses the bound xt,
+        spd, pos_old, rho_s and neighbour slot 0 of dual as the vehicles' ONE multiplier.  pair_n (S,), pair_ij (S,P,2) with
+        veh_lo < veh_hi, at most 8 pairs per vehicle; hinge_weight defaults to 2*beta (the reference's ordered-pair sum).
+        Returns device tensors u (S,V,N), iters (S,), status (S,)."""
+        dev = self.device
+        pn = torch.as_tensor(pair_n, dtype=torch.int32).to(dev).contiguous().reshape(self.S)
+        pij = torch.as_tensor(pair_ij, dtype=torch.int32).to(dev).contiguous()
+        if pij.dim() != 3 or pij.shape[0] != self.S or pij.shape[2] != 2 or pij.shape[1] < 1:
+            raise _abi.PIADMMError(f"pair_ij must have shape ({self.S},P,2) with P >= 1, got {tuple(pij.shape)}")
+        if int(pn.max()) > pij.shape[1]:
+            raise _abi.PIADMMError("pair_n exceeds the pair list")
+        u = torch.zeros((self.S, self.V, self.N), dtype=torch.float64, device=dev)
+        iters = torch.zeros(self.S, dtype=torch.int32, device=dev)
+        status = torch.zeros(self.S, dtype=torch.int32, device=dev)
+        w = 2.0 * float(self.params.beta) if hinge_weight is None else float(hinge_weight)
+        self._check(self.lib.piadmm_solve_joint(self._h, C.c_void_p(pn.data_ptr()), C.c_void_p(pij.data_ptr()),
+                                                int(pij.shape[1]), w, C.c_void_p(u.data_ptr()),
+                                                C.c_void_p(iters.data_ptr()), C.c_void_p(status.data_ptr()),
+                                                self._stream()), "piadmm_solve_joint")
+        self._joint_keep = (pn, pij)      # the launch is asynchronous: keep the inputs alive
+        return u, iters, status
+
     def set_ownership(self, lo: int, hi: int):
         """Vehicle sharding: this instance x-updates vehicles [lo, hi) only (see parallel.py)."""
         self._check(self.lib.piadmm_set_ownership(self._h, int(lo), int(hi)), "piadmm_set_ownership")

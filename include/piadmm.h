@@ -159,6 +159,19 @@ int piadmm_residuals(piadmm_handle* h, void* stream);    /* histories, stop flag
  * controls rounded to round_edge decimals; synchronises). */
 int piadmm_solve_edges(piadmm_handle* h, void* stream);
 int piadmm_get_edge_u(piadmm_handle* h, double* host_out, void* stream);
+/* The joint N-vehicle RSU edge problem: cost_function_edge of
+ * matlab_old_files/ADMM_fmincon_multi_veh_intesection_static.m:250-291 (= casadi_old_PI_ADMM/PI_ADMM_class.py:141-178) in its
+ * convex statement -- ONE edge problem over all V vehicles of every scenario, with ONE consensus copy / multiplier per
+ * vehicle (neighbour slot 0 of the bound pos_old / dual buffers), the hinge summed over the pairs of the given list
+ * (pair_n [S], pair_ij [S,P,2] with veh_lo < veh_hi; DEVICE pointers; at most 8 pairs per vehicle, else the scenario's
+ * status is PIADMM_ST_SLOT_OVERFLOW and nothing is solved), bounds / rate rows of nonlcon_function on every vehicle.
+ * hinge_weight = the weight of ONE pair's hinge: the reference sums over ordered pairs (:265-276), i.e. 2 * beta.
+ * The reference forms last_dis from linear indices (:268), the pair's own offset only for V = 2; here every pair is
+ * linearised about its own seed offset l_ij (as every two-vehicle statement does).  Outputs (device): u_out [S,V,N]
+ * (rounded to round_edge decimals), iters_out [S], status_out [S] (0 / PIADMM_ST_EDGE_MAXITER / PIADMM_ST_SLOT_OVERFLOW).
+ * One thread-block cluster per scenario (V <= 64 for N > 15, V <= 128 for N <= 15; PIADMM_E_UNSUPPORTED beyond). */
+int piadmm_solve_joint(piadmm_handle* h, const int32_t* pair_n, const int32_t* pair_ij, int P, double hinge_weight,
+                       double* u_out, int32_t* iters_out, int32_t* status_out, void* stream);
 /* vehicle-sharded (multi-GPU) form: this rank x-updates vehicles [lo,hi), solves every edge with an owned
  * endpoint, and sums the residual terms of the edges whose veh1 it owns into res_part; the caller
  * all-gathers pos/u rows after x_update and all-reduces (sum) res_part between the two residual calls. */
