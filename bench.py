@@ -371,6 +371,7 @@ def main():
             few = max(3, min(args.steps, 5))
             coupled["c5_inner_tight"] = measure_coupled("c5", args, rank, local_rank, world, with_cpu=False, inner="tight", steps=few)
             coupled["c3_inner_tight"] = measure_coupled("c3", args, rank, local_rank, world, with_cpu=False, inner="tight", steps=few)
+            coupled["c3_joint_edge"] = measure_joint(args, local_rank)
             config1 = measure_config1(args, local_rank)
             variants = measure_c4_variants(args, local_rank, S, N)
 
@@ -723,6 +724,56 @@ def measure_c4_variants(args, local_rank, S, N):
                           "note": "piadmm_run_closed_loop: window gather, outer loop, plant step and histories on the device, "
                                   "no host round trip per MPC step; no L2 flush between steps (one asynchronous call)"}
     sol.close()
+    return out
+
+
+def measure_joint(args, local_rank):
+    """The joint N-vehicle RSU edge problem (piadmm_solve_joint: one thread-block cluster per scene) on the
+    config-3 scene: the pairs that collide after the first vehicle QPs (at most 8 per vehicle), one joint solve per timed
+    step; also a batch of 16 copies of the scene in one launch (one cluster each).  Device-timed, L2 flushed."""
+    import ctypes as C
+    import torch
+    from pi_admm_b200.solver import PIADMMSolver
+    from pi_admm_b200.scenarios import c3_intersection
+    V, N = 64, 30
+    p = coupled_params(N).update(x_memo=0)
+    xt, spd, refwin = c3_intersection(V=V, N=N)
+    out = {"workload": "ONE joint edge problem over the 64 vehicles of the config-3 intersection (N = 30): hinge over the pairs that "
+                       "collide after the first vehicle QPs, <= 8 per vehicle; matlab_old_files/ADMM_fmincon_multi_veh_intesection_"
+                       "static.m:250-291 in its convex statement",
+           "kernel": "k_joint<32>: 8 CTAs x 256 threads per scene (one cluster), t~ exchanged through distributed shared memory, "
+                     "one cluster barrier per inner iteration"}
+    for S in (1, 16):
+        sol = PIADMMSolver(p, S=S, V=V, D=1, device=local_rank)
+        sol.setup(np.broadcast_to(xt, (S, V, 3)).copy(), np.broadcast_to(spd, (S, V)).copy(), np.broadcast_to(refwin, (S, V, 2, N + 1)).copy())
+        sol.begin_step(); sol.x_update()
+        e_cap = V * (V - 1) // 2
+        en = torch.zeros(S, dtype=torch.int32, device=sol.device); eij = torch.zeros((S, e_cap, 2), dtype=torch.int32, device=sol.device)
+        rc = sol.lib.piadmm_edge_list_static(C.c_void_p(sol.buf["pos"].data_ptr()), S, V, N, float(p.dis_thres), int(p.thr_squared), e_cap,
+                                             C.c_void_p(en.data_ptr()), C.c_void_p(eij.data_ptr()), sol._stream())
+        assert rc == 0
+        n0 = int(en[0]); lst = sorted(map(tuple, eij[0, :n0].cpu().numpy().tolist()))
+        deg = [0] * V; pairs = []
+        for (i, j) in lst:
+            if deg[i] < 8 and deg[j] < 8:
+                pairs.append((i, j)); deg[i] += 1; deg[j] += 1
+        pij = np.broadcast_to(np.array(pairs, np.int32), (S, len(pairs), 2)).copy(); pn = np.full(S, len(pairs), np.int32)
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=sol.device)
+        for _ in range(3):
+            u, it, st = sol.solve_joint(pn, pij)
+        reps = max(5, min(args.steps, 20)); ms = []
+        for _ in range(reps):
+            flush.fill_(1)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); u, it, st = sol.solve_joint(pn, pij); b.record(); torch.cuda.synchronize()
+            ms.append(a.elapsed_time(b))
+        iters = int(it[0]); t = float(np.mean(ms))
+        # per inner iteration and vehicle: the N x N mat-vec, the 4N-2 bound rows and one position-row copy per incident pair
+        flops = iters * S * (V * (2 * N * N + 12 * (4 * N - 2) + 6 * N) + 2 * len(pairs) * 12 * N)
+        out[f"S{S}"] = {"scenes_per_launch": S, "pairs": len(pairs), "colliding_pairs_found": n0, "inner_iters": iters, "status": int(st[0]),
+                        "ms_per_joint_solve": t, "us_per_inner_iter": t * 1e3 / max(iters, 1), "joint_solves_per_s": S / (t * 1e-3),
+                        "algorithmic_tflops": flops / (t * 1e-3) / 1e12, "reps": reps}
+        sol.close()
     return out
 
 

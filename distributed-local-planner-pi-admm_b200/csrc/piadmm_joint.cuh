@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(JT_THREADS, 1) k_joint(const __grid_constant__
         }
       }
     }
+    for (int d = deg; d < JT_D; d++) pnb[g * JT_D + d] = valid ? i : 0;   // unused slots point at a readable row
     pdeg[g] = over ? -1 : deg;
   }
   __syncwarp();
@@ -215,6 +216,11 @@ __global__ void __launch_bounds__(JT_THREADS, 1) k_joint(const __grid_constant__
       }
       __syncwarp();
       const double tt = (acc[0] + acc[2]) + (acc[1] + acc[3]);
+      // ---- the pairs: publish t~ (position rows only) and ARRIVE at the cluster barrier; the bound rows of this vehicle
+      // are updated while the other CTAs arrive, the partners' rows are read after the WAIT
+      const double tme = srow ? tt : 0.0;
+      tbuf[(par * G + g) * LPQ + k] = tme;
+      cl.barrier_arrive();
       double xt = tt;
       {
         const double u1 = __shfl_up_sync(PIADMM_FULL, tt, 1, LPQ), u2 = __shfl_up_sync(PIADMM_FULL, tt, 2, LPQ);
@@ -231,17 +237,20 @@ __global__ void __launch_bounds__(JT_THREADS, 1) k_joint(const __grid_constant__
       ch0 = fma(b1, a0r, fma(-ha, m0, -alu)); ch1 = fma(b1, a1r, fma(-ha, m1, -alu));
       ch2 = fma(b1, a2r, fma(-ha, m2, -ald)); ch3 = fma(b1, a3r, fma(-ha, m3, -ald));
       t = fma(al, tt, oma * t);
-      // ---- the pairs: publish t~ (position rows only), ONE cluster barrier, read the partners' rows
-      const double tme = srow ? tt : 0.0;
-      tbuf[(par * G + g) * LPQ + k] = tme;
-      cl.sync();
+      cl.barrier_wait();
       gsum = 0.0;
+      // all partner rows first (independent distributed-shared-memory loads in flight together), then the proxes
+      double tjv[JT_D];
+#pragma unroll
+      for (int d = 0; d < JT_D; d++) {
+        const int j = pnb[g * JT_D + d];
+        tjv[d] = cl.map_shared_rank(tbuf, j / G)[(par * G + (j % G)) * LPQ + k];
+      }
 #pragma unroll
       for (int d = 0; d < JT_D; d++) {
         if (d < deg) {                               // group uniform
-          const int j = pnb[g * JT_D + d];
           const double* sc = psc + (g * JT_D + d) * 4;
-          const double tj = cl.map_shared_rank(tbuf, j / G)[(par * G + (j % G)) * LPQ + k];
+          const double tj = tjv[d];
           const double a_me = sc[0], a_pt = sc[1];
           const double vs_me = fma(al, tme, cs_me[d]), vs_pt = fma(al, tj, cs_pt[d]);
           const bool me_lo = sc[3] != 0.0;

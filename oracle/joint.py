@@ -171,3 +171,81 @@ def solve_joint(H, q, pairs, hinge, s: InnerSettings):
                     K = factor(rho)
                     nref += 1
     return np.stack(x), dict(iters=it, status=status, refactors=nref, rho=rho)
+
+
+# ------------------------------------------------------------------ the joint flow: one MPC step
+def capped_pairs(ever, V, cap=8):
+    """Sorted pair list with at most `cap` pairs per vehicle (the kernel's per-vehicle row state); returns (pairs, dropped)."""
+    deg = [0] * V
+    out, dropped = [], 0
+    for (i, j) in sorted(ever):
+        if deg[i] < cap and deg[j] < cap:
+            out.append((i, j)); deg[i] += 1; deg[j] += 1
+        else:
+            dropped += 1
+    return out, dropped
+
+
+def run_joint_step(p: Params, inner: InnerSettings, xt, spd, refwin, thr_squared=1, round_u=-1, round_edge=-1, cap=8, kI=None, pos_nonlinear=1):
+    """One MPC step of the JOINT flow -- the loop of casadi_old_PI_ADMM/main.py:60-164 / ...static.m:57-164 with the
+    edge side solved as ONE problem over all vehicles (cost_function_edge, ...static.m:250-291):
+
+      x-update per vehicle against its ONE consensus copy (AL term only once the vehicle is in a pair),
+      collision test (casadi/main.py:110-113), pairs = every pair that collided so far in this step (with the pairs that
+      collide NOW only, the pair set oscillates and the loop does not settle: measured),
+      joint edge problem -> hat_u, z-hat_i = non-linear roll-out of hat_u_i (casadi/main.py:156-158),
+      lambda_i += kI (pos_i - z-hat_i)  (plain law, ...static.m:131-132; kI = rho unless given),
+      global Frobenius residuals (old main.py:154-155) over the vehicles that are in a pair.
+    """
+    from .problem import vehicle_qp, affine_rollout, literal_dynamic_update_edge
+    from .solver import solve_box_qp
+    V, N = xt.shape[0], refwin.shape[2] - 1
+    rho = float(p.rho)
+    kI = rho if kI is None else float(kI)
+    pos = np.zeros((V, 2, N + 1)); hat = np.zeros((V, 2, N + 1)); dual = np.zeros((V, 2, N + 1)); last_hat = np.zeros((V, 2, N + 1))
+    u = np.zeros((V, N))
+    ever, in_pair = set(), np.zeros(V, bool)
+    err_rk, err_sk, joint_iters, n_outer, converged, dropped = [], [], [], 0, False, 0
+    pairs = []
+    thr = p.dis_thres ** 2 if thr_squared else p.dis_thres
+    for it in range(p.iter_num):
+        n_outer += 1
+        for i in range(V):
+            hl, dl = ([hat[i]], [dual[i]]) if in_pair[i] else ([], [])
+            H, q = vehicle_qp(p, xt[i], spd[i], refwin[i, 0], refwin[i, 1], hl, dl, rho=rho)
+            ui, _ = solve_box_qp(H, q, inner)
+            u[i] = np.around(ui, round_u) if round_u >= 0 else ui
+            if pos_nonlinear:                     # MATLAB ...PI_antiwindup.m:312-330: numeric pos_old is the non-linear roll-out
+                x_, y_, _ = literal_dynamic_update_edge(p, xt[i:i + 1], u[i][None, :], spd[i:i + 1])
+                pos[i, 0], pos[i, 1] = x_[0], y_[0]
+            else:
+                pos[i, 0], pos[i, 1] = affine_rollout(p, xt[i], spd[i], u[i])
+        for i in range(V):
+            for j in range(i + 1, V):
+                d2 = (pos[i, 0] - pos[j, 0]) ** 2 + (pos[i, 1] - pos[j, 1]) ** 2
+                if np.any(d2 < thr):
+                    ever.add((i, j))
+        if not ever:
+            converged = True
+            break
+        pairs, dropped = capped_pairs(ever, V, cap)
+        for (i, j) in pairs:
+            in_pair[i] = in_pair[j] = True
+        B = joint_blocks(p, xt, spd, pos, dual, pairs, rho=rho)
+        uh, info = solve_joint(B["H"], B["q"], B["pairs"], 2.0 * p.beta, inner)
+        joint_iters.append(info["iters"])
+        uh = np.around(uh, round_edge) if round_edge >= 0 else uh
+        hx, hy, _ = literal_dynamic_update_edge(p, xt, uh, spd)
+        new = np.stack((hx, hy), 1)
+        act = in_pair[:, None, None]
+        hat = np.where(act, new, hat)
+        dual = np.where(act, dual + kI * (pos - hat), dual)
+        rk = np.sqrt(np.sum(np.where(act, (pos - hat) ** 2, 0.0)))
+        sk = np.sqrt(np.sum(np.where(act, (rho * (last_hat - hat)) ** 2, 0.0)))
+        err_rk.append(rk); err_sk.append(sk)
+        if rk <= p.eps_pri and sk <= p.eps_dual:
+            converged = True
+            break
+        last_hat = hat.copy()
+    return dict(u=u, pos=pos, hat=hat, dual=dual, n_outer=n_outer, err_rk=np.array(err_rk), err_sk=np.array(err_sk),
+                joint_iters=joint_iters, pairs=pairs, dropped=dropped, converged=converged)

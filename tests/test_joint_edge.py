@@ -207,3 +207,33 @@ def test_gpu_joint_rejects_what_it_cannot_hold():
     with pytest.raises(_abi.PIADMMError, match="cluster"):
         sol.solve_joint(np.array([1], np.int32), np.array([[[0, 1]]], np.int32))
     sol.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("V,N,r0,gap,cap_it,conv", [(6, 10, 5.0, 4.0, 40, True), (8, 15, 7.0, 5.0, 5, False), (12, 10, 6.0, 4.0, 6, False)])
+def test_gpu_joint_flow_equals_oracle(V, N, r0, gap, cap_it, conv):
+    """The whole JOINT outer loop (JointRSUSolver: vehicle QPs, collision test, one joint edge problem per iteration,
+    multiplier update, global residuals) on small intersections against oracle.joint.run_joint_step: same outer and inner
+    iteration counts, same pair lists, trajectories / multipliers / residual histories within 1e-6.  The 6-vehicle scene
+    converges (stop test passed after 8 iterations); the other two are cut at a few iterations -- there the joint
+    consensus stalls at a residual the steering bounds do not let it close, in the oracle alike."""
+    from pi_admm_b200.joint import JointRSUSolver
+    from pi_admm_b200.scenarios import c3_intersection
+    from util import make_params
+    xt, spd, rw = c3_intersection(V=V, N=N, r0=r0, gap=gap)
+    ap = make_params("matlab_pi", "default", num_ho=N, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5, kI=1.5, iter_num=cap_it)
+    js = JointRSUSolver(ap, S=1, V=V)
+    js.setup(xt, spd, rw)
+    got = js.iterate()
+    js.close()
+    p = Params(num_ho=N, beta=10.0, rho=2.0, Pnorm=1.0, eps_pri=0.5, eps_dual=0.5, iter_num=cap_it)
+    ref = oj.run_joint_step(p, InnerSettings.osqp_default(), xt[0], spd[0], rw[0], kI=1.5)
+    assert ref["converged"] == conv and len(ref["pairs"]) >= V
+    assert got["n_outer"][0] == ref["n_outer"] and bool(got["converged"][0]) == conv
+    assert got["pairs"][0] == ref["pairs"] and got["joint_iters"][0] == ref["joint_iters"]
+    for k in ("u", "pos", "hat", "dual"):
+        e = np.abs(got[k][0] - ref[k]).max() / max(1.0, np.abs(ref[k]).max())
+        assert e <= 1e-6, (k, e)
+    assert np.allclose(got["err_rk"][0], ref["err_rk"], rtol=1e-6, atol=1e-9) and np.allclose(got["err_sk"][0], ref["err_sk"], rtol=1e-6, atol=1e-9)
+    if conv:
+        assert ref["n_outer"] < cap_it and ref["err_rk"][-1] <= 0.5 and ref["err_sk"][-1] <= 0.5

@@ -29,4 +29,7 @@ echo "ncu fused rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_coop -s 3 -c 1 -f -o $O/prof_${TAG}_coop \
     python bench.py --workload c5 --steps 3 --warmup 3 --no-cpu-baseline > $O/ncu_f5_$TAG.log 2>&1
 echo "ncu coop rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_joint -s 3 -c 1 -f -o $O/prof_${TAG}_joint \
+    python bench.py --steps 5 --warmup 3 --no-cpu-baseline > $O/ncu_fj_$TAG.log 2>&1
+echo "ncu joint rc=$?"
 ls -la $O | tail -30

@@ -76,6 +76,9 @@ def main(tag, R="r2"):
     cp(f"bench_{tag}_c5.json", f"{R}_bench_c5.json")
     m, tail = ncu_summary(os.path.join(G, f"prof_{tag}.ncu-rep"), os.path.join(P, f"{R}_k_fused_v2_ncu_full.txt"), tag)
     mc, tailc = ncu_summary(os.path.join(G, f"prof_{tag}_coop.ncu-rep"), os.path.join(P, f"{R}_k_coop_ncu_full.txt"), tag + "_coop")
+    mj, tailj = (None, "")
+    if os.path.exists(os.path.join(G, f"prof_{tag}_joint.ncu-rep")):
+        mj, tailj = ncu_summary(os.path.join(G, f"prof_{tag}_joint.ncu-rep"), os.path.join(P, f"{R}_k_joint_ncu_full.txt"), tag + "_joint")
     json.dump({"kernel": "k_fused_v2<16>", "dram_bytes_read": int(m["dram_read"]), "dram_bytes_write": int(m["dram_write"]),
                "source": f"profiles/{R}_k_fused_v2_ncu_full.txt (ncu --set full, 1 launch; the writes are mostly the "
                          "write-back of the 256 MiB L2-flush buffer)"}, open(os.path.join(P, f"{R}_traffic.json"), "w"))
@@ -90,6 +93,15 @@ def main(tag, R="r2"):
     c1rows = "\n".join(f"| {k} | {v['steps_with_active_edge']} / {v['steps']} | {v['ms_per_step_mean_active']:.3f} | {v['ms_per_step_max_active']:.3f} | "
                        f"{v['ms_total']:.2f} | {v['device_loop_ms_per_step']:.3f} | {v['outer_iters_total']} |" for k, v in c1.items())
     cv = b.get("c4_variants", {})
+    jt = cpl.get("c3_joint_edge")
+    joint_txt = ""
+    if jt:
+        joint_txt = ("\n### Joint N-vehicle RSU edge problem (SURVEY 8(f)-4, `piadmm_solve_joint`, cluster kernel `k_joint<32>`)\n\n"
+                     + jt["workload"] + ".\n\n| scenes per launch | pairs | inner iterations | ms per joint solve | us per inner iteration | joint solves/s | algorithmic TFLOP/s |\n|---|---|---|---|---|---|---|\n"
+                     + "\n".join(f"| {r['scenes_per_launch']} | {r['pairs']} | {r['inner_iters']} | {r['ms_per_joint_solve']:.3f} | {r['us_per_inner_iter']:.2f} | {r['joint_solves_per_s']:.0f} | {r['algorithmic_tflops']:.3f} |"
+                                 for k, r in jt.items() if k.startswith("S"))
+                     + (f"\n\nncu (`{R}_k_joint_ncu_full.txt`, one launch, {mj['gpu__time_duration.sum']:.0f} us, {mj['launch__registers_per_thread']:.0f} registers, grid {mj['launch__grid_size']:.0f} CTAs): FP64 pipe {mj['sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active']:.1f} %, issue slots {mj['smsp__issue_active.avg.pct_of_peak_sustained_active']:.1f} %.\n" + tailj if mj else "")
+                     + "\n\nOne inner iteration = one mat-vec per vehicle + one HARDWARE CLUSTER BARRIER + <= 8 distributed-shared-memory reads per lane: the iteration time is the barrier + DSMEM round trip, not arithmetic (the pairwise z phase of the same scene takes ~15 us per OUTER iteration; the joint problem is the alternative z-step of the reference's old flow, not the latency path).\n")
     open(os.path.join(P, "README.md"), "w").write(f"""# profiles/ — round 2 evidence (B200, sm_100a, driver 580.159, CUDA 12.9)
 
 Regenerate with `python tools/make_profiles.py <tag>` after `gpurun -- 'bash tools/gpu_call_profile.sh <tag>'`.
@@ -135,10 +147,11 @@ Files of this round
 
 | record | V | ms per coupled MPC step (device) | e2e ms (host buffers) | outer iterations | exit | converged | residual at exit | vehicle QPs / edge problems solved | launches per step | CPU twin ms (16 threads) |
 |---|---|---|---|---|---|---|---|---|---|---|
-{chr(10).join(coupled_row(k, v) for k, v in cpl.items())}
+{chr(10).join(coupled_row(k, v) for k, v in cpl.items() if 'exit' in v)}
 
 Parity of every record against the CPU twin is checked inside the bench (`parity_vs_cpu_port`: identical outer iteration
 counts, edge lists and solve counts; u within {max(v.get('parity_vs_cpu_port', {}).get('u_rel_err', 0) for v in cpl.values()):.1e} relative).
+{joint_txt}
 
 ## Config 1 (`casadi/main.py`, ONE scenario, 35 MPC steps): latency
 
