@@ -169,6 +169,7 @@ _PROTOS = {
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "piadmm_static_last_error": (C.c_char_p, []),
     # include/obca_consensus.h (struct pointers passed as void*: obca_consensus.py owns the ctypes mirrors)
+    "obca_bar_state_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "obca_lambda_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p]),
     "obca_residuals": (C.c_int, [C.c_void_p] * 7 + [C.c_void_p]),
     "obca_check_converge": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_void_p, C.c_void_p]),

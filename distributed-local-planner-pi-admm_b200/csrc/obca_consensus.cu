@@ -140,6 +140,45 @@ __global__ void k_obca_tail(const ObcaCtx c) {
   }
 }
 
+// bar_state_update (optimizer.py:205-222): half-spaces A x <= b of every vehicle rectangle at every predicted step from
+// the local solutions, and local_x <- the states.  prob != 0: compute_square_halfspaces_ca_prob (util.py:76-101, the
+// delay-tightened form: A = [R'; -R'], b = b0 + A (pos + avg_delay v (c,s) + sqrt(p/(1-p)) (var_delay v (c,s))^2));
+// prob == 0: generate_vehicle_vertices + compute_square_halfspaces_ca (util.py:12-74).  One thread per (s, v, h).
+__global__ void k_obca_halfspaces(const obca_dims d, obca_state st, const double* __restrict__ fullx, const obca_vehicle cfg, int prob) {
+  const size_t n = (size_t)d.S * d.V * d.H;
+  const int nz = d.ns + d.nl;
+  for (size_t row = (size_t)blockIdx.x * blockDim.x + threadIdx.x; row < n; row += (size_t)gridDim.x * blockDim.x) {
+    const double* fx = fullx + row * nz;
+    const double x = fx[0], y = fx[1], v = fx[2], th = fx[3];
+    for (int w = 0; w < d.ns; w++) st.local_x[row * d.ns + w] = fx[w];
+    double sn, cs;
+    sincos(th, &sn, &cs);
+    double* A = st.A + row * d.nl * 2;
+    double* b = st.b + row * d.nl;
+    const double hl = 0.5 * cfg.length, hw = 0.5 * cfg.width;
+    if (prob) {
+      const double a[4][2] = {{cs, sn}, {-sn, cs}, {-cs, -sn}, {sn, -cs}};
+      const double b0[4] = {hl, hw, hl, hw};
+      const double kq = sqrt(cfg.prob / (1.0 - cfg.prob));
+      const double vx = cfg.var_delay * v * cs, vy = cfg.var_delay * v * sn;
+      const double px = x + cfg.avg_delay * v * cs + kq * (vx * vx), py = y + cfg.avg_delay * v * sn + kq * (vy * vy);
+      for (int r = 0; r < 4; r++) {
+        A[2 * r] = a[r][0]; A[2 * r + 1] = a[r][1];
+        b[r] = __dadd_rn(b0[r], __dadd_rn(__dmul_rn(a[r][0], px), __dmul_rn(a[r][1], py)));
+      }
+    } else {
+      const double vxs[4] = {x + hl * cs - hw * sn, x + hl * cs + hw * sn, x - hl * cs + hw * sn, x - hl * cs - hw * sn};
+      const double vys[4] = {y + hl * sn + hw * cs, y + hl * sn - hw * cs, y - hl * sn - hw * cs, y - hl * sn + hw * cs};
+      for (int r = 0; r < 4; r++) {
+        const double p1x = vxs[r], p1y = vys[r], p2x = vxs[(r + 1) & 3], p2y = vys[(r + 1) & 3];
+        const double nx = p2y - p1y, ny = p1x - p2x, nrm = sqrt(__dadd_rn(__dmul_rn(nx, nx), __dmul_rn(ny, ny)));
+        A[2 * r] = (p1y - p2y) / nrm; A[2 * r + 1] = (p2x - p1x) / nrm;
+        b[r] = __dsub_rn(__dmul_rn(p2x, p1y), __dmul_rn(p2y, p1x)) / nrm;
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ C ABI
 static int dims_ok(const obca_dims* d) {
   return d && d->S >= 1 && d->V >= 1 && d->H >= 1 && d->ns >= 1 && d->nl >= 1 && d->C >= 0;
@@ -202,6 +241,17 @@ int obca_iterate_next_state(const obca_dims* d, obca_state* st, void* stream) {
   OBCA_ENTER(dims_ok(d) && state_ok(st));
   use_device_of(st->lamb_bar);
   k_obca_shift<<<d->S, OBCA_THREADS, 0, (cudaStream_t)stream>>>(*d, *st);
+  OBCA_LEAVE();
+}
+
+int obca_bar_state_update(const obca_dims* d, obca_state* st, const double* fullx, const obca_vehicle* cfg, int prob, void* stream) {
+  OBCA_ENTER(dims_ok(d) && state_ok(st) && fullx && cfg && d->nl == 4 && d->ns >= 4 && cfg->length > 0.0 && cfg->width > 0.0 &&
+             (!prob || (cfg->prob > 0.0 && cfg->prob < 1.0)));
+  const size_t n = (size_t)d->S * d->V * d->H;
+  const size_t cap = (size_t)use_device_of(fullx) * 16;
+  size_t grid = (n + 127) / 128;
+  if (grid > cap) grid = cap;
+  k_obca_halfspaces<<<(unsigned)grid, 128, 0, (cudaStream_t)stream>>>(*d, *st, fullx, *cfg, prob);
   OBCA_LEAVE();
 }
 

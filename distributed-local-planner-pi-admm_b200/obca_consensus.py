@@ -41,6 +41,11 @@ class State(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in FIELDS]
 
 
+class Vehicle(C.Structure):
+    """struct obca_vehicle: Distributed_planner/decentralized/veh_config.py:9-27"""
+    _fields_ = [(n, C.c_double) for n in ("length", "width", "avg_delay", "var_delay", "prob")]
+
+
 class mid_state:
     """optimizer.py:351-373 with a leading scenario axis."""
 
@@ -108,6 +113,18 @@ class OBCAConsensus:
     # -- reference surface
     def create_bar_state(self) -> mid_state:
         return mid_state(self)
+
+    def bar_state_update(self, bar_fullx_vehs, bar_lambda=None, prob=1, cfg: Vehicle | None = None):
+        """optimizer.py:205-222: half-spaces (A, b) of every vehicle rectangle and local_x from the local solutions
+        bar_fullx_vehs [S, V, N_horz-1, 9] (the reference passes a list over vehicles of (N_horz-1) x 9 arrays).
+        prob=1: the delay-tightened half-spaces the driver runs (util.py:76-101); lamb_ij is not touched (:219-220)."""
+        fx = bar_fullx_vehs if torch.is_tensor(bar_fullx_vehs) else torch.as_tensor(bar_fullx_vehs, dtype=torch.float64)
+        fx = fx.to(self.device, torch.float64).reshape(self.S, self.num_veh, self.N_horz - 1, self.n_states + self.n_loc_lambda).contiguous()
+        cfg = cfg or Vehicle(3.5, 2.0, 0.05, 0.025, 0.95)
+        st = self.bar_state._c()
+        self._ck(self.lib.obca_bar_state_update(C.byref(self.dims), C.byref(st), C.c_void_p(fx.data_ptr()), C.byref(cfg), int(prob),
+                                                self._stream()), "obca_bar_state_update")
+        self._fx_keep = fx
 
     def lambda_update(self, rho):
         st = self.bar_state._c()

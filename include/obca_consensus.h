@@ -4,6 +4,7 @@
  * The local / RSU problems of that driver are IPOPT NLPs (out of scope); what sits between
  * them on the per-iteration path is plain array arithmetic, batched here over S independent scenarios:
  *
+ *   obca_bar_state_update     Distributed_planner/decentralized/optimizer.py:205-222  (bar_state_update, util.py half-spaces)
  *   obca_lambda_update        Distributed_planner/decentralized/optimizer.py:330-335  (lambda_update)
  *   obca_residuals            Distributed_planner/decentralized_overtaking_ADMM.py:82-85 (L1 residuals)
  *   obca_check_converge       Distributed_planner/decentralized/optimizer.py:225-235  (check_converge)
@@ -41,6 +42,21 @@ typedef struct obca_state {
   double* lamb_ij;   /* [S,V,H,nl]    */
   double* local_x;   /* [S,V,H,ns]    */
 } obca_state;
+
+/* vehicle rectangle + communication-delay model: Distributed_planner/decentralized/veh_config.py:9-27 */
+typedef struct obca_vehicle {
+  double length, width;          /* 3.5, 2 */
+  double avg_delay, var_delay;   /* 0.05, 0.025 */
+  double prob;                   /* 0.95 */
+} obca_vehicle;
+
+/* bar_state_update (optimizer.py:205-222): for every vehicle and predicted step, A [4,2] and b [4] of the vehicle
+ * rectangle's half-spaces A x <= b from the local solutions fullx [S,V,H,ns+nl] (state = x, y, v, heading, steer), and
+ * local_x <- the states.  prob != 0: compute_square_halfspaces_ca_prob (util.py:76-101, delay-tightened, what the driver
+ * runs: if_comm_delay = 1, decentralized_overtaking_ADMM.py:21-23); prob == 0: generate_vehicle_vertices +
+ * compute_square_halfspaces_ca (util.py:12-74).  lamb_ij is NOT touched (the reference's update of it is commented out,
+ * optimizer.py:219-220). */
+int obca_bar_state_update(const obca_dims* d, obca_state* st, const double* fullx, const obca_vehicle* cfg, int prob, void* stream);
 
 /* lamb_bar += rho * ([local_x, lamb_ij] - Z_bar) */
 int obca_lambda_update(const obca_dims* d, obca_state* st, double rho, void* stream);

@@ -4,12 +4,17 @@ import this module; the product path never does.
 
 numpy restatement, loop for loop, of
   * ``mid_state``            Distributed_planner/decentralized/optimizer.py:351-373
+  * ``bar_state_update``     Distributed_planner/decentralized/optimizer.py:205-222 (+ util.py:12-101 half-spaces)
   * ``lambda_update``        Distributed_planner/decentralized/optimizer.py:330-335
   * ``check_converge``       Distributed_planner/decentralized/optimizer.py:225-235
   * ``iterate_next_state``   Distributed_planner/decentralized/optimizer.py:337-344
   * residuals / stop / carry Distributed_planner/decentralized_overtaking_ADMM.py:79-97
-Parity unpinned: the reference has no tests or stored outputs for these functions and its module cannot
-be imported here (it imports casadi at the top); the statements are short enough to be restated literally.
+PINNED against the reference's own methods: tests/golden/reference_vectors.json holds what
+OBCAOptimizer.bar_state_update / check_converge / lambda_update / iterate_next_state / mid_state returned when the
+reference package was imported unmodified from /root/reference (numpy stand-ins for the casadi containers it imports,
+tests/golden/make_reference_vectors.py); tests/test_reference_vectors.py compares this module and the CUDA kernels with
+them (multipliers and shifts bit-exact).  The driver-inline statements (residuals / stop / carry) have no function in
+the reference to call and stay literal restatements.
 """
 from __future__ import annotations
 
@@ -106,3 +111,46 @@ def lambda_update_batched(local_x, lamb_ij, Z_bar, lamb_bar, rho):
 
 def shift_batched(a):
     return np.concatenate((a[:, :, 1:], a[:, :, -1:]), axis=2)
+
+
+# ---- half-spaces of the vehicle rectangle (Distributed_planner/decentralized/util.py, veh_config.py:9-27) ----
+VEH_LENGTH, VEH_WIDTH, AVG_DELAY, VAR_DELAY, DELAY_PROB = 3.5, 2.0, 0.05, 0.025, 0.95
+
+
+def halfspaces_prob(state):
+    """compute_square_halfspaces_ca_prob (util.py:76-101), numeric: A [4,2], b [4] of the delay-tightened rectangle."""
+    x, y, v, th = state[0], state[1], state[2], state[3]
+    c, s = np.cos(th), np.sin(th)
+    R = np.array([[c, -s], [s, c]])
+    A = np.vstack((R.T, -R.T))
+    b0 = np.array([VEH_LENGTH / 2, VEH_WIDTH / 2, VEH_LENGTH / 2, VEH_WIDTH / 2])          # `if(~base_link)` is always true (:94)
+    d_avg = np.array([AVG_DELAY * v * c, AVG_DELAY * v * s])
+    d_var = np.array([(VAR_DELAY * v * c) ** 2, (VAR_DELAY * v * s) ** 2])
+    return A, b0 + A @ (np.array([x, y]) + d_avg + np.sqrt(DELAY_PROB / (1 - DELAY_PROB)) * d_var)
+
+
+def halfspaces_vertices(state):
+    """generate_vehicle_vertices (util.py:12-47, base_link=False) + compute_square_halfspaces_ca (:49-74), numeric."""
+    x, y, th = state[0], state[1], state[3]
+    c, s, L, W = np.cos(th), np.sin(th), VEH_LENGTH, VEH_WIDTH
+    P = np.array([[x + L / 2 * c - W / 2 * s, y + L / 2 * s + W / 2 * c], [x + L / 2 * c + W / 2 * s, y + L / 2 * s - W / 2 * c],
+                  [x - L / 2 * c + W / 2 * s, y - L / 2 * s - W / 2 * c], [x - L / 2 * c - W / 2 * s, y - L / 2 * s + W / 2 * c]])
+    A = np.zeros((4, 2)); b = np.zeros(4)
+    for i in range(4):
+        p1, p2 = P[i], P[(i + 1) % 4]
+        nrm = np.sqrt((p2[1] - p1[1]) ** 2 + (p1[0] - p2[0]) ** 2)
+        A[i] = np.array([p1[1] - p2[1], p2[0] - p1[0]]) / nrm
+        b[i] = (p2[0] * p1[1] - p2[1] * p1[0]) / nrm
+    return A, b
+
+
+def bar_state_update(st: MidState, bar_fullx_vehs, prob=1):
+    """optimizer.py:205-222 (lamb_ij is not updated: the reference's line is commented out, :219-220)."""
+    V, H = st.local_x.shape[:2]
+    for i_tstep in range(H):
+        for i_veh in range(V):
+            bar_x = np.asarray(bar_fullx_vehs[i_veh])[:, :5]
+            A, b = (halfspaces_prob if prob else halfspaces_vertices)(bar_x[i_tstep])
+            st.A[i_veh, i_tstep] = A
+            st.b[i_veh, i_tstep] = b
+            st.local_x[i_veh, i_tstep] = bar_x[i_tstep]

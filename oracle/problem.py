@@ -12,10 +12,18 @@ Two layers live here:
 * closed forms (``roll_matrix``, ``vehicle_qp``, ``edge_qp_blocks``): what the
   C twin (oracle/piadmm_ref.c) and the CUDA kernels implement.
 
-PARITY UNPINNED: the reference ships no tests / golden vectors and its solver
-stack (CasADi 3.5.6.pre2 + vendored OSQP) is not installable here, so nothing
-under oracle/ could be checked against outputs of the reference itself.  What
-pins it instead is listed in DESIGN.md section "Oracle".
+PINNED, for everything in THIS file, against outputs of the reference's own code:
+tests/golden/reference_vectors.json is produced by importing casadi/PI_ADMM_class.py
+unmodified from /root/reference (numpy stand-ins for the `casadi` / `bunch` containers,
+tests/golden/make_reference_vectors.py) and calling its methods on numeric arrays --
+param, ref_traj, both roll-outs, cost_function_primal (its exact (H, q)),
+nonlcon_function, cost_function_edge, and the convex edge statement composed from the
+reference's two functions; tests/test_reference_vectors.py compares the closed forms
+below, the C twin's inputs and the CUDA path with them.
+PARITY UNPINNED for solver OUTPUTS: the reference ships no tests / golden vectors and
+its solver stack (CasADi 3.5.6.pre2 + vendored OSQP) is not installable here, so no
+iterate or iteration count of the inner solver could be checked against the reference
+(oracle/solver.py, oracle/driver.py).  DESIGN.md section "Oracle" has the full list.
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline/reference arm
 may import this package.

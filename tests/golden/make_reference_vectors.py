@@ -1,0 +1,175 @@
+"""Golden vectors produced by the REFERENCE'S OWN CODE, run in the build container (where /root/reference exists):
+
+    python tests/golden/make_reference_vectors.py        # writes tests/golden/reference_vectors.json
+
+The reference's classes import `casadi` and `bunch`, which are not installed here; tests/golden/_ref_import_stubs.py puts
+numpy-backed stand-ins for exactly the container functions the class bodies call into sys.modules, the reference modules are
+then imported UNMODIFIED from /root/reference and their methods are called on numeric arrays.  What is recorded:
+
+  casadi/PI_ADMM_class.py      param, ref_traj (:13-37); dynamic_update_local numeric branch (:45-70); dynamic_update_edge numeric
+                               branch (:77-105); cost_function_primal (:114-135) evaluated at 0, +-e_i and e_i+e_j -> the exact
+                               (H, q) of the quadratic it is, and at random u; nonlcon_function (:172-192) at random u;
+                               cost_function_edge (:145-169, the Python non-convex statement) at random hat_u.
+  Distributed_planner/decentralized/optimizer.py, util.py
+                               mid_state (:351-373), lambda_update (:330-335), check_converge (:225-235),
+                               iterate_next_state (:337-344), bar_state_update (:205-222) with
+                               compute_square_halfspaces_ca_prob (util.py:76-101).
+
+The solvers (OSQP / IPOPT inside the CasADi wheel) are NOT available, so no solver output is recorded: these vectors pin the
+problem construction, the roll-outs, the constraints and the consensus arithmetic of the oracle and of the CUDA path to the
+reference's own statements; iterates of the inner solver stay unpinned."""
+import importlib
+import importlib.util
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+import _ref_import_stubs as stubs  # noqa: E402
+
+REF = "/root/reference"
+
+
+def load_class():
+    stubs.install()
+    spec = importlib.util.spec_from_file_location("ref_PI_ADMM_class", os.path.join(REF, "casadi", "PI_ADMM_class.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m.PI_ADMM_CASADI
+
+
+def scal(x):
+    return float(np.asarray(x).reshape(-1)[0])
+
+
+def vehicle_case(PI, rng, num_step, veh, xt, N, spd):
+    PI.param.num_ho = N
+    PI.param.spd = np.array(spd, dtype=float)
+    V = PI.param.num_veh
+    hat = np.empty((V, V), dtype=object); dual = np.empty((V, V), dtype=object)
+    for i in range(V):
+        for j in range(V):
+            hat[i, j] = rng.normal(0, 3, (2, N + 1)); dual[i, j] = rng.normal(0, 1, (2, N + 1))
+    f = lambda u: scal(PI.cost_function_primal(num_step, stubs.Mat(np.asarray(u).reshape(1, N)), xt, hat, dual, veh))
+    E = np.eye(N)
+    f0 = f(np.zeros(N))
+    fp = np.array([f(E[i]) for i in range(N)]); fm = np.array([f(-E[i]) for i in range(N)])
+    q = (fp - fm) / 2.0
+    H = np.zeros((N, N))
+    for i in range(N):
+        H[i, i] = fp[i] + fm[i] - 2.0 * f0
+        for j in range(i + 1, N):
+            H[i, j] = H[j, i] = f(E[i] + E[j]) - fp[i] - fp[j] + f0
+    us = rng.normal(0, 0.3, (4, N))
+    vals = [f(u) for u in us]
+    cons = [np.asarray(PI.nonlcon_function(stubs.Mat(u.reshape(1, N)))[1]).ravel().tolist() for u in us]
+    roll = []
+    for u in us:
+        x, y, th = PI.dynamic_update_local(xt[veh], np.around(u.reshape(1, N), 4), veh, if_SX=0)
+        roll.append([np.asarray(x).tolist(), np.asarray(y).tolist(), np.asarray(th).tolist()])
+    other = 1 - veh
+    return dict(num_step=num_step, veh=veh, N=N, spd=list(map(float, spd)), xt=xt.tolist(),
+                hat=hat[veh, other].tolist(), dual=dual[veh, other].tolist(), f0=f0, H=H.tolist(), q=q.tolist(),
+                u=us.tolist(), cost=vals, cieq=cons, rollout_local_of_rounded_u=roll)
+
+
+def edge_case(PI, rng, xt, N, spd):
+    PI.param.num_ho = N
+    PI.param.spd = np.array(spd, dtype=float)
+    pos_old = rng.normal(0, 5, (4, N + 1)); dual = rng.normal(0, 1, (4, N + 1))
+    seed = np.stack((np.around(xt[:, 0] + PI.param.dt * PI.param.spd * np.cos(xt[:, 2]), 4),
+                     np.around(xt[:, 1] + PI.param.dt * PI.param.spd * np.sin(xt[:, 2]), 4)), 1)      # casadi/main.py:48-49
+    us = rng.normal(0, 0.25, (4, 2, N))
+    cost = [scal(PI.cost_function_edge(stubs.Mat(u), xt, pos_old, dual, seed)) for u in us]
+    roll = []
+    for u in us:
+        x, y, th = PI.dynamic_update_edge(xt, np.around(u, 4), if_SX=0)
+        roll.append([np.asarray(x).tolist(), np.asarray(y).tolist(), np.asarray(th).tolist()])
+    # the CONVEX statement (MATLAB ...PI_antiwindup.m:276-304 with the edge roll-out linearised about xt(:,3), :383-396) composed
+    # from the reference's OWN two Python functions: cost_function_edge (:145-169) with its roll-out replaced by the reference's
+    # linearised dynamic_update_local (:45-70) of each vehicle.  Both bodies are the reference's; only the composition is ours.
+    def lin_edge(xt_, u_, if_SX):
+        rows = [PI.dynamic_update_local(xt_[i], stubs.Mat(np.asarray(u_)[i].reshape(1, N)), i, if_SX=1) for i in range(2)]
+        st = lambda c: stubs.Mat(np.vstack([np.asarray(r[c]).reshape(1, -1) for r in rows]))
+        return st(0), st(1), st(2)
+    nonlin = PI.dynamic_update_edge
+    PI.dynamic_update_edge = lin_edge
+    # seeds that put the pair at the collision threshold, so that the hinge is active for some steps and some hat_u
+    pos_c = np.vstack((xt[0, 0] + np.arange(N + 1) * 0.1 * spd[0] * np.cos(xt[0, 2]), xt[0, 1] + np.arange(N + 1) * 0.1 * spd[0] * np.sin(xt[0, 2]),
+                       xt[1, 0] + np.arange(N + 1) * 0.1 * spd[1] * np.cos(xt[1, 2]), xt[1, 1] + np.arange(N + 1) * 0.1 * spd[1] * np.sin(xt[1, 2])))
+    us_c = np.vstack((np.zeros((1, 2, N)), rng.normal(0, 0.3, (7, 2, N))))
+    cost_c = [scal(PI.cost_function_edge(stubs.Mat(u), xt, pos_c, dual, seed)) for u in us_c]
+    PI.dynamic_update_edge = nonlin
+    return dict(N=N, spd=list(map(float, spd)), xt=xt.tolist(), pos_old=pos_old.tolist(), dual=dual.tolist(), seed=seed.tolist(),
+                hat_u=us.tolist(), cost_python_nonconvex=cost, rollout_edge_of_rounded_u=roll,
+                convex=dict(pos_old=pos_c.tolist(), hat_u=us_c.tolist(), cost=cost_c))
+
+
+def obca_cases(rng):
+    stubs.install()
+    sys.path.insert(0, os.path.join(REF, "Distributed_planner"))
+    dec = importlib.import_module("decentralized")
+    out = []
+    for case in range(4):
+        opt = dec.OBCAOptimizer(min_dis=0.1, prob=1)
+        bar = opt.create_bar_state()
+        opt.bar_state = bar
+        V, H = opt.num_veh, opt.N_horz - 1
+        init = dict(lamb_ij0=bar.lamb_ij.tolist(), lamb_bar0=bar.lamb_bar.tolist())
+        # local solutions of a fictitious iteration: states near the reference trajectories, multipliers near the warm start
+        fullx = []
+        for v in range(V):
+            st = opt.ref_traj[v][3 * case + 1: 3 * case + 1 + H].copy()
+            st += rng.normal(0, 1, st.shape) * np.array([0.5, 0.3, 0.5, 0.05, 0.02])
+            lam = np.abs(bar.lamb_ij[v] + rng.normal(0, 0.05, (H, 4)))
+            fullx.append(np.hstack((st, lam)))
+        opt.bar_state_update(fullx, None)
+        A, b, local_x = bar.A.copy(), bar.b.copy(), bar.local_x.copy()
+        bar.Z_bar = np.round(np.stack([fx + rng.normal(0, 0.05 * (case + 1), fx.shape) for fx in fullx]), 4)
+        if case == 3:          # a state in which check_converge is true: opposite half-spaces, equal multipliers
+            bar.A[1] = -bar.A[0]; bar.lamb_ij[1] = bar.lamb_ij[0]; bar.b[1] = -bar.b[0] - 0.2 / np.maximum(bar.lamb_ij[0].sum(-1, keepdims=True), 1e-9)
+        conv = bool(opt.check_converge(0.1))
+        A_cc, b_cc, lij_cc = bar.A.copy(), bar.b.copy(), bar.lamb_ij.copy()
+        rho = [1.0, 0.5, 2.0, 1.0][case]
+        lb0 = bar.lamb_bar.copy()
+        opt.lambda_update(rho)
+        lb1 = bar.lamb_bar.copy()
+        before = {f: getattr(bar, f).copy() for f in ("Z_bar", "A", "b", "lamb_bar", "lamb_ij", "local_x")}
+        nxt = opt.iterate_next_state(bar)
+        out.append(dict(fullx=[fx.tolist() for fx in fullx], A=A.tolist(), b=b.tolist(), local_x=local_x.tolist(),
+                        Z_bar=before["Z_bar"].tolist(), check_A=A_cc.tolist(), check_b=b_cc.tolist(), check_lamb_ij=lij_cc.tolist(),
+                        check_converge=conv, thres=0.1, min_dis=0.1, rho=rho, lamb_bar_before=lb0.tolist(), lamb_bar_after=lb1.tolist(),
+                        shift_before={k: v.tolist() for k, v in before.items()},
+                        shift_after={f: getattr(nxt, f).tolist() for f in before}, **init))
+    return out
+
+
+def main():
+    rng = np.random.default_rng(20261105)
+    PI_cls = load_class()
+    PI = PI_cls()
+    out = {"generator": "tests/golden/make_reference_vectors.py (reference code imported unmodified from /root/reference; numpy stand-ins "
+                        "for the casadi / bunch containers, no solver)",
+           "param": {k: (v.tolist() if isinstance(v, np.ndarray) else v) for k, v in PI.param.items()},
+           "ref_traj": PI.ref_traj.tolist()}
+    xt0 = np.array([[-10.0, 0.0, 0.0], [0.0, 20.0, -np.pi / 2]])
+    veh = []
+    for (step, v, N, spd, xt) in [(0, 0, 15, (4, 8), xt0), (3, 1, 15, (4, 8), xt0 + rng.normal(0, 0.3, (2, 3))),
+                                  (12, 0, 15, (4.3, 7.4), np.array([[-5.2, 0.1, 0.05], [0.2, 10.4, -1.5]])),
+                                  (5, 1, 30, (6.5, 5.0), np.array([[-7.0, 0.3, 0.7], [0.4, 12.0, -1.2]])),
+                                  (20, 0, 8, (8, 4), np.array([[-1.0, 0.0, 2.1], [0.0, 3.0, -0.4]]))]:
+        veh.append(vehicle_case(PI_cls(), rng, step, v, np.asarray(xt, dtype=float), N, spd))
+    out["vehicle"] = veh
+    near = np.array([[-4.0, 0.0, 0.0], [0.0, 7.0, -np.pi / 2]])        # close enough for the hinge of the edge cost to be active
+    out["edge"] = [edge_case(PI_cls(), rng, near + rng.normal(0, 0.3, (2, 3)), N, spd) for N, spd in ((15, (4, 8)), (30, (6, 7)), (5, (8, 4)))]
+    out["obca"] = obca_cases(rng)
+    path = os.path.join(HERE, "reference_vectors.json")
+    json.dump(out, open(path, "w"))
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,233 @@
+"""Parity against vectors produced by the REFERENCE'S OWN CODE (tests/golden/reference_vectors.json, generated in the build
+container by tests/golden/make_reference_vectors.py: casadi/PI_ADMM_class.py and Distributed_planner/decentralized/* imported
+unmodified, numpy stand-ins for the casadi / bunch containers, no solver).  They pin the problem construction -- constants,
+reference trajectories, (H, q) of the vehicle QP, the constraint rows, both roll-outs, the Python edge cost, the config-2
+consensus arithmetic and half-spaces -- of the oracle, of the product's host mirror and of the CUDA path to the reference's
+statements.  Solver iterates (OSQP / IPOPT) are not in the vectors: see DESIGN.md section 3."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle.problem import (Params, reference_trajectories, vehicle_qp, constraint_matrix, constraint_lower, affine_rollout,
+                            literal_dynamic_update_local, literal_dynamic_update_edge)
+from oracle.solver import InnerSettings, solve_box_qp
+from oracle import obca_consensus as oc
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+VEC = json.load(open(os.path.join(HERE, "golden", "reference_vectors.json")))
+A_ = lambda x: np.asarray(x, dtype=np.float64)
+
+
+def _params(case):
+    return Params(num_ho=case["N"], spd=A_(case["spd"]))
+
+
+def test_constants_and_reference_trajectories():
+    rp = VEC["param"]
+    p = Params()
+    for k in ("dt", "Nt", "L", "num_ho", "num_veh", "dis_thres", "beta", "Pnorm", "Pcost", "iter_num", "rho", "eps_pri", "eps_dual"):
+        assert float(getattr(p, k)) == float(rp[k]), k
+    assert np.array_equal(A_(p.spd), A_(rp["spd"]))
+    assert np.array_equal(reference_trajectories(p), A_(VEC["ref_traj"]))
+    import pi_admm_b200 as pa
+    from pi_admm_b200.PI_ADMM_class import PI_ADMM_CASADI
+    P = PI_ADMM_CASADI()
+    assert np.array_equal(P.ref_traj, A_(VEC["ref_traj"]))
+    for k, v in rp.items():
+        assert np.array_equal(np.asarray(P.param[k], dtype=np.float64), np.asarray(v, dtype=np.float64)), k
+    d = pa.default_params()
+    for k in ("dt", "L", "dis_thres", "beta", "Pnorm", "Pcost", "rho", "eps_pri", "eps_dual"):
+        assert float(getattr(d, k)) == float(rp[k]), k
+    assert d.num_ho == rp["num_ho"] and d.iter_num == rp["iter_num"]
+
+
+@pytest.mark.parametrize("ci", range(len(VEC["vehicle"])))
+def test_vehicle_qp_equals_the_reference_cost_function(ci):
+    """(H, q) extracted EXACTLY from cost_function_primal (casadi/PI_ADMM_class.py:114-135; it is a quadratic: values at 0,
+    +-e_i, e_i+e_j) equal the oracle's closed form; the cost at random u and the constraint rows of nonlcon_function
+    (:172-192) agree too."""
+    c = VEC["vehicle"][ci]
+    p, N, v = _params(c), c["N"], c["veh"]
+    xt = A_(c["xt"])
+    ref = A_(VEC["ref_traj"])[2 * v:2 * v + 2, c["num_step"]:c["num_step"] + N + 1]
+    H, q = vehicle_qp(p, xt[v], p.spd[v], ref[0], ref[1], [A_(c["hat"])], [A_(c["dual"])])
+    Hr, qr = A_(c["H"]), A_(c["q"])
+    assert np.abs(H - Hr).max() <= 1e-8 * np.abs(Hr).max() and np.abs(q - qr).max() <= 1e-8 * max(1.0, np.abs(qr).max())
+    A, l = constraint_matrix(N), constraint_lower(N)
+    for u, f, g in zip(A_(c["u"]), c["cost"], c["cieq"]):
+        quad = 0.5 * u @ H @ u + q @ u
+        assert abs((f - c["f0"]) - quad) <= 1e-9 * max(1.0, abs(f))
+        assert np.abs(A_(g) - (A @ u - l)).max() <= 1e-14
+    for u, (x, y, th) in zip(A_(c["u"]), c["rollout_local_of_rounded_u"]):
+        ur = np.around(u, 4)
+        xa, ya = affine_rollout(p, xt[v], p.spd[v], ur)
+        xl, yl, tl = literal_dynamic_update_local(p, xt[v], ur, p.spd[v])
+        for got, want in ((xa, x), (ya, y), (xl, x), (yl, y), (tl, th)):
+            assert np.abs(got - A_(want)).max() <= 1e-11 * max(1.0, np.abs(A_(want)).max())
+        from pi_admm_b200.PI_ADMM_class import PI_ADMM_CASADI
+        P = PI_ADMM_CASADI(); P.param.num_ho = N; P.param.spd = p.spd
+        xh, yh, thh = P.dynamic_update_local(xt[v], ur.reshape(1, N), v, if_SX=0)
+        assert np.array_equal(xh, A_(x)) and np.array_equal(yh, A_(y)) and np.array_equal(thh, A_(th))
+
+
+@pytest.mark.parametrize("ci", range(len(VEC["edge"])))
+def test_edge_rollout_and_python_edge_cost(ci):
+    """dynamic_update_edge numeric branch (casadi/PI_ADMM_class.py:77-105) and the value of the Python cost_function_edge
+    (:145-169, the non-convex statement: same hinge / effort / AL terms as the convex one, non-linear roll-out inside)."""
+    c = VEC["edge"][ci]
+    p, N = _params(c), c["N"]
+    xt, pos_old, dual, seed = A_(c["xt"]), A_(c["pos_old"]), A_(c["dual"]), A_(c["seed"])
+    from pi_admm_b200.PI_ADMM_class import PI_ADMM_CASADI
+    from pi_admm_b200.joint import nonlinear_rollout
+    import torch
+    P = PI_ADMM_CASADI(); P.param.num_ho = N; P.param.spd = p.spd
+    for u, (x, y, th) in zip(A_(c["hat_u"]), c["rollout_edge_of_rounded_u"]):
+        ur = np.around(u, 4)
+        xo, yo, to = literal_dynamic_update_edge(p, xt, ur, p.spd)
+        assert np.abs(xo - A_(x)).max() <= 1e-11 and np.abs(yo - A_(y)).max() <= 1e-11 and np.abs(to - A_(th)).max() <= 1e-12
+        xh, yh, thh = P.dynamic_update_edge(xt, ur, if_SX=0)
+        assert np.array_equal(xh, A_(x)) and np.array_equal(yh, A_(y))
+        r = nonlinear_rollout(torch.from_numpy(xt)[None], torch.from_numpy(p.spd)[None], torch.from_numpy(ur)[None], p.dt, p.L)[0].numpy()
+        assert np.abs(r[:, 0] - A_(x)).max() <= 1e-11 and np.abs(r[:, 1] - A_(y)).max() <= 1e-11
+    ell = seed[1] - seed[0]
+    for u, f in zip(A_(c["hat_u"]), c["cost_python_nonconvex"]):
+        x, y, _ = literal_dynamic_update_edge(p, xt, u, p.spd)
+        dis = 2.0 * (ell[0] * (x[1, 1:] - x[0, 1:]) + ell[1] * (y[1, 1:] - y[0, 1:])) - np.sum(ell ** 2)
+        edge_pos = np.vstack((x[0], y[0], x[1], y[1]))
+        mine = p.beta * np.sum(np.maximum(0.0, p.dis_thres ** 2 - dis)) + p.Pcost * np.sum(u ** 2) + p.rho / 2 * np.sum((pos_old - edge_pos + dual) ** 2)
+        assert abs(mine - f) <= 1e-10 * max(1.0, abs(f))
+
+
+@pytest.mark.parametrize("ci", range(len(VEC["obca"])))
+def test_obca_consensus_oracle_equals_the_reference_methods(ci):
+    """mid_state, bar_state_update (+ util half-spaces), check_converge, lambda_update, iterate_next_state of
+    Distributed_planner/decentralized/optimizer.py, run by the reference itself."""
+    c = VEC["obca"][ci]
+    st = oc.MidState()
+    assert np.array_equal(st.lamb_ij, A_(c["lamb_ij0"])) and np.array_equal(st.lamb_bar, A_(c["lamb_bar0"]))
+    oc.bar_state_update(st, [A_(f) for f in c["fullx"]], prob=1)
+    assert np.abs(st.A - A_(c["A"])).max() <= 1e-15 and np.abs(st.b - A_(c["b"])).max() <= 1e-12 * np.abs(A_(c["b"])).max()
+    assert np.array_equal(st.local_x, A_(c["local_x"]))
+    st.A, st.b, st.lamb_ij = A_(c["check_A"]), A_(c["check_b"]), A_(c["check_lamb_ij"])
+    assert oc.check_converge(st, c["thres"], c["min_dis"]) == c["check_converge"]
+    st.Z_bar, st.lamb_bar = A_(c["Z_bar"]), A_(c["lamb_bar_before"])
+    oc.lambda_update(st, c["rho"])
+    assert np.array_equal(st.lamb_bar, A_(c["lamb_bar_after"]))
+    for f in oc.MidState.FIELDS:
+        setattr(st, f, A_(c["shift_before"][f]))
+    oc.iterate_next_state(st)
+    for f in oc.MidState.FIELDS:
+        assert np.array_equal(getattr(st, f), A_(c["shift_after"][f])), f
+    assert any(v["check_converge"] for v in VEC["obca"]) and not all(v["check_converge"] for v in VEC["obca"])
+
+
+# ------------------------------------------------------------------ GPU: the CUDA path against the reference's vectors
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", range(len(VEC["vehicle"])))
+def test_gpu_vehicle_qp_minimises_the_reference_cost(ci):
+    """cost_function_primal -> VehicleQP descriptor -> piadmm_x_update (tight inner tolerance): the returned steering
+    sequence is the minimiser of the reference's OWN quadratic (H, q from its cost function) under its own constraint rows
+    (oracle ADMM on that (H, q), and the KKT conditions checked directly)."""
+    from pi_admm_b200.PI_ADMM_class import PI_ADMM_CASADI
+    c = VEC["vehicle"][ci]
+    N, v = c["N"], c["veh"]
+    P = PI_ADMM_CASADI(inner="tight")
+    P.param.num_ho = N; P.param.spd = A_(c["spd"])
+    xt = A_(c["xt"])
+    hat = np.empty((2, 2), dtype=object); dual = np.empty((2, 2), dtype=object)
+    for i in range(2):
+        for j in range(2):
+            hat[i, j] = A_(c["hat"]); dual[i, j] = A_(c["dual"])
+    desc = P.cost_function_primal(c["num_step"], None, xt, hat, dual, v)
+    u = P.solve(desc)[0]
+    Hr, qr = A_(c["H"]), A_(c["q"])
+    ur, info = solve_box_qp(Hr, qr, InnerSettings.tight())
+    assert info["status"] == 0
+    assert np.abs(u - ur).max() <= 1e-6 * max(1.0, np.abs(ur).max())
+    A, l = constraint_matrix(N), constraint_lower(N)
+    assert (A @ u - l).min() >= -1e-7                                    # feasible for nonlcon_function's rows
+    f = lambda w: 0.5 * w @ Hr @ w + qr @ w
+    assert f(u) <= f(ur) + 1e-7 * max(1.0, abs(f(ur)))                   # and as good as the oracle's minimiser of the reference cost
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", range(len(VEC["edge"])))
+def test_gpu_plant_step_equals_the_reference_edge_rollout(ci):
+    """k_plant (casadi/main.py:185-192: xt <- column 1 of dynamic_update_edge(xt, primal_u)) against the reference's own
+    dynamic_update_edge output."""
+    import torch
+    from pi_admm_b200.solver import PIADMMSolver
+    from util import make_params
+    c = VEC["edge"][ci]
+    N = c["N"]
+    xt, spd = A_(c["xt"]), A_(c["spd"])
+    sol = PIADMMSolver(make_params("python_current", num_ho=N), S=1, V=2)
+    for u, (x, y, th) in zip(A_(c["hat_u"]), c["rollout_edge_of_rounded_u"]):
+        sol.setup(xt[None], spd[None], np.zeros((1, 2, 2, N + 1)))
+        sol.buf["u"].copy_(torch.from_numpy(np.around(u, 4))[None])
+        sol.plant_step()
+        nxt = sol.buf["xt_next"].cpu().numpy()[0]
+        want = np.stack((A_(x)[:, 1], A_(y)[:, 1], A_(th)[:, 1]), 1)
+        assert np.abs(nxt - want).max() <= 1e-12 * max(1.0, np.abs(want).max())
+    sol.close()
+
+
+@pytest.mark.gpu
+def test_gpu_obca_kernels_equal_the_reference_methods():
+    """obca_bar_state_update / obca_check_converge / obca_lambda_update / obca_iterate_next_state, all four recorded cases as
+    one batch of scenarios, against what the reference's own methods returned."""
+    import torch
+    from pi_admm_b200.obca_consensus import OBCAConsensus, FIELDS
+    cs = VEC["obca"]
+    S = len(cs)
+    o = OBCAConsensus(S=S)
+    dev = o.device
+    T = lambda key, sub=None: torch.from_numpy(np.stack([A_(c[key] if sub is None else c[key][sub]) for c in cs])).to(dev).contiguous()
+    assert np.array_equal(o.bar_state.lamb_ij[0].cpu().numpy(), A_(cs[0]["lamb_ij0"]))
+    o.bar_state_update(T("fullx"), prob=1)
+    torch.cuda.synchronize()
+    assert np.abs(o.bar_state.A.cpu().numpy() - T("A").cpu().numpy()).max() <= 1e-15
+    bw = T("b").cpu().numpy()
+    assert np.abs(o.bar_state.b.cpu().numpy() - bw).max() <= 1e-12 * np.abs(bw).max()
+    assert np.array_equal(o.bar_state.local_x.cpu().numpy(), T("local_x").cpu().numpy())
+    o.bar_state.A.copy_(T("check_A")); o.bar_state.b.copy_(T("check_b")); o.bar_state.lamb_ij.copy_(T("check_lamb_ij"))
+    ok = o.check_converge(cs[0]["thres"], cs[0]["min_dis"]).cpu().numpy()
+    assert ok.tolist() == [c["check_converge"] for c in cs]
+    for s, c in enumerate(cs):                                           # lambda_update takes one rho: scenario by scenario
+        o1 = OBCAConsensus(S=1)
+        for f, key in (("Z_bar", "Z_bar"), ("lamb_bar", "lamb_bar_before"), ("local_x", "local_x"), ("lamb_ij", "check_lamb_ij")):
+            getattr(o1.bar_state, f).copy_(torch.from_numpy(A_(c[key]))[None].to(dev))
+        o1.lambda_update(c["rho"])
+        assert np.array_equal(o1.bar_state.lamb_bar[0].cpu().numpy(), A_(c["lamb_bar_after"])), s      # bit exact
+    for f in FIELDS:
+        getattr(o.bar_state, f).copy_(T("shift_before", f))
+    o.iterate_next_state(o.bar_state)
+    for f in FIELDS:
+        assert np.array_equal(getattr(o.bar_state, f).cpu().numpy(), T("shift_after", f).cpu().numpy()), f
+
+
+@pytest.mark.parametrize("ci", range(len(VEC["edge"])))
+def test_convex_edge_blocks_equal_the_reference_statements_composed(ci):
+    """The convex edge statement (MATLAB ...PI_antiwindup.m:276-304,383-396) evaluated by the reference's OWN Python
+    functions -- cost_function_edge (casadi/PI_ADMM_class.py:145-169) with its roll-out replaced by the reference's
+    linearised dynamic_update_local (:45-70) -- against the oracle's literal transcription AND the split blocks
+    (H, q, a, c) the kernels iterate on; the hinge is active in part of the recorded points."""
+    from oracle.problem import literal_cost_edge_convex, edge_qp_blocks, roll_matrix
+    c = VEC["edge"][ci]
+    p, N = _params(c), c["N"]
+    xt, dual, seed = A_(c["xt"]), A_(c["dual"]), A_(c["seed"])
+    pos_old, us, cost = A_(c["convex"]["pos_old"]), A_(c["convex"]["hat_u"]), c["convex"]["cost"]
+    B = edge_qp_blocks(p, xt, p.spd, pos_old, dual, seed)
+    M = roll_matrix(N)[1:]
+    model = lambda u: (sum(0.5 * u[r] @ B["H"][r] @ u[r] + B["q"][r] @ u[r] for r in range(2))
+                       + p.beta * np.sum(np.maximum(0.0, B["c"] - B["a"][0] * (M @ u[0]) - B["a"][1] * (M @ u[1]))))
+    assert np.abs(us[0]).max() == 0.0
+    active = 0
+    for u, f in zip(us, cost):
+        lit = literal_cost_edge_convex(p, u, xt, p.spd, pos_old, dual, seed)
+        assert abs(lit - f) <= 1e-10 * max(1.0, abs(f))
+        assert abs((f - cost[0]) - (model(u) - model(us[0]))) <= 1e-9 * max(1.0, abs(f))
+        active += int(np.sum(B["c"] - B["a"][0] * (M @ u[0]) - B["a"][1] * (M @ u[1]) > 0))
+    assert active > 0

@@ -101,9 +101,41 @@ def obca(S=5):
     torch.cuda.synchronize()
 
 
+def joint():
+    """k_joint<16|32> (cluster + distributed shared memory; 1 and 2 CTAs per cluster, a rho change) and the joint flow."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_joint_edge as T
+    for V, N, cap in ((5, 8, 4), (10, 30, 3), (20, 15, 3)):
+        sc = T.scene(V, N, seed=V + N, spread=4.0 + 0.35 * V)
+        pairs = T.near_pairs(sc[0], sc[1], sc[2], cap)
+        u, it, st = T._gpu_joint([sc, sc], [pairs, pairs[:1]], N, "default")
+        assert np.isfinite(u).all()
+    from pi_admm_b200.joint import JointRSUSolver
+    ap = make_params("matlab_pi", "default", num_ho=10, beta=10.0, Pnorm=1.0, rho=2.0, eps_pri=0.5, eps_dual=0.5, kI=1.5, iter_num=2)
+    xt, spd, rw = c3_intersection(V=6, N=10, r0=5.0, gap=4.0)
+    js = JointRSUSolver(ap, S=1, V=6)
+    js.setup(xt, spd, rw)
+    assert np.isfinite(js.iterate()["u"]).all()
+    js.close()
+
+
+def static():
+    """piadmm_edge_list_static (k_static_bbox / k_static_hits / k_static_emit) on two shapes back to back."""
+    import ctypes as C
+    from pi_admm_b200 import _abi
+    lib = _abi.load_library()
+    for S, V, N in ((1, 70, 30), (9, 2, 15), (1, 70, 30)):
+        pos = torch.randn(S, V, 2, N + 1, dtype=torch.float64, device="cuda") * 5.0
+        en = torch.zeros(S, dtype=torch.int32, device="cuda"); eij = torch.zeros(S, 64, 2, dtype=torch.int32, device="cuda")
+        rc = lib.piadmm_edge_list_static(C.c_void_p(pos.data_ptr()), S, V, N, 2.0, 1, 64, C.c_void_p(en.data_ptr()),
+                                         C.c_void_p(eij.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 0
+    torch.cuda.synchronize()
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["fused15", "fused30", "phases15", "phases30", "ragged", "obca"]
+    which = sys.argv[1:] or ["fused15", "fused30", "phases15", "phases30", "ragged", "obca", "joint", "static"]
     for w in which:
         {"fused15": lambda: fused(15), "fused30": lambda: fused(30), "phases15": lambda: phases(15),
-         "phases30": lambda: phases(30), "ragged": ragged, "obca": obca}[w]()
+         "phases30": lambda: phases(30), "ragged": ragged, "obca": obca, "joint": joint, "static": static}[w]()
         print("ok", w, flush=True)
