@@ -10,7 +10,10 @@ selectable through ``Modes``.  The edge step is the convex statement
 (MATLAB :276-304 with :383-396); the CasADi Taylor-at-0 model of the non-convex
 Python edge cost is NOT reproduced (ill-posed).
 
-PARITY UNPINNED (see oracle/problem.py header).
+OUTER LOOP PINNED to the reference's own script: tests/golden/reference_main_run.json is /root/reference/casadi/main.py run
+unmodified (QP solves stood in by oracle/solver.py, tests/golden/run_reference_main.py); run_closed_loop in python_current
+semantics reproduces its histories exactly (tests/test_reference_vectors.py).  The PI variants (MATLAB / old Python scripts) and
+the inner solver's iterates stay unpinned (oracle/problem.py header).
 """
 from __future__ import annotations
 

@@ -1,8 +1,10 @@
 """Generates tests/golden/*.json from the numpy oracle (oracle/driver.py).
 
-The reference ships no golden vectors and cannot run here (CasADi/OSQP absent), so these files
-freeze the ORACLE's outputs ("parity unpinned" against the reference itself); they guard the
-oracle, its C twin and the CUDA path against regressions.   python tests/golden/make_golden.py
+These files freeze the ORACLE's outputs; they guard the oracle, its C twin and the CUDA path against regressions.
+c1_python_current_default.json is additionally equal (difference 0.0) to what the reference's own casadi/main.py computed
+when run unmodified here with the oracle's solver standing in for OSQP (tests/golden/run_reference_main.py ->
+reference_main_run.json); the PI variants have no runnable reference script (MATLAB / IPOPT).
+   python tests/golden/make_golden.py
 """
 import json
 import os

@@ -231,3 +231,55 @@ def test_convex_edge_blocks_equal_the_reference_statements_composed(ci):
         assert abs((f - cost[0]) - (model(u) - model(us[0]))) <= 1e-9 * max(1.0, abs(f))
         active += int(np.sum(B["c"] - B["a"][0] * (M @ u[0]) - B["a"][1] * (M @ u[1]) > 0))
     assert active > 0
+
+
+# ------------------------------------------------------------------ the reference's own SCRIPT, run in the build container
+RUN = json.load(open(os.path.join(HERE, "golden", "reference_main_run.json")))
+
+
+def test_reference_script_run_equals_the_oracle_closed_loop():
+    """tests/golden/reference_main_run.json = /root/reference/casadi/main.py executed unmodified (35 MPC steps; QP solves by the
+    oracle's OSQP restatement, see tests/golden/run_reference_main.py).  The oracle's driver (python_current semantics) must
+    reproduce the script's histories: this pins the OUTER LOOP -- edge_mat rule, early exit, dual update, residual sums,
+    aliasing quirk, stop test, plant step, histories -- to the reference's own statements."""
+    from oracle.driver import Modes, run_closed_loop
+    p = Params()
+    out = run_closed_loop(p, Modes.python_current(), InnerSettings.osqp_default(),
+                          np.array([[-10, 0, 0], [0, 20, -np.pi / 2]], dtype=float), p.spd.astype(float), reference_trajectories(p))
+    assert [int(v) for v in out["iter_his"]] == RUN["iter_his"] and len(RUN["iter_his"]) == 35
+    assert int(np.sum(out["n_outer"])) == RUN["total_iter"]
+    for k in ("x_vec", "theta_vec", "u_vec"):
+        assert np.abs(np.array(out[k]) - A_(RUN[k])).max() <= 1e-9, k
+    assert sum(sum(s["veh_iters"]) for s in out["steps"]) == sum(RUN["veh_inner"])
+    assert sum(sum(s["edge_iters"]) for s in out["steps"]) == sum(RUN["edge_inner"])
+    assert sum(len(s["veh_iters"]) for s in out["steps"]) == RUN["veh_solves"] and sum(len(s["edge_iters"]) for s in out["steps"]) == RUN["edge_solves"]
+    assert max(RUN["iter_his"]) == 2 and RUN["edge_solves"] > 0       # the collision edge is active in part of the run
+    g = json.load(open(os.path.join(HERE, "golden", "c1_python_current_default.json")))   # the frozen oracle loop the GPU tests use
+    assert g["iter_his"] == RUN["iter_his"] and np.abs(A_(g["x_vec"]) - A_(RUN["x_vec"])).max() <= 1e-12
+
+
+def test_c_twin_closed_loop_equals_the_reference_script_run():
+    from oracle import ctwin
+    import pi_admm_b200 as pa
+    from pi_admm_b200.scenarios import ref_window
+    p = pa.preset("python_current")
+    ref = reference_trajectories(Params())
+    xt = np.array([[[-10, 0, 0], [0, 20, -np.pi / 2]]], dtype=np.float64)
+    for step in range(35):
+        r = ctwin.step(p, xt, np.array([[4.0, 8.0]]), ref_window(ref, step, p.num_ho)[None])
+        xt = r["xt_next"].copy()
+        assert int(r["curr_iter"][0]) == RUN["iter_his"][step]
+        assert np.abs(xt[0, :, :2].T - A_(RUN["x_vec"][step])).max() <= 1e-9 and np.abs(r["u"][0, :, 0] - A_(RUN["u_vec"][step])).max() <= 1e-9
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("how", ["device_loop", "host_steps"])
+def test_gpu_closed_loop_equals_the_reference_script_run(how):
+    """The CUDA closed loop of config 1 (piadmm_run_closed_loop, and the drop-in driver stepping the class mirror) against the
+    histories the reference's own casadi/main.py produced in the build container."""
+    from pi_admm_b200.main_intersection import run
+    out = run(semantics="python_current", inner="osqp_default", fast=True, device_loop=(how == "device_loop"))
+    assert [int(v) for v in out["iter_his"]] == RUN["iter_his"]
+    assert np.abs(np.array(out["x_vec"]) - A_(RUN["x_vec"])).max() <= 1e-6
+    assert np.abs(np.array(out["u_vec"]) - A_(RUN["u_vec"])).max() <= 1e-6
+    assert np.abs(np.array(out["theta_vec"]) - A_(RUN["theta_vec"])).max() <= 1e-6
