@@ -81,6 +81,25 @@ def _round(a, dec):
     return np.around(a, dec) if dec >= 0 else np.asarray(a, dtype=np.float64)
 
 
+def pi_old_gains(md: Modes, dmin):
+    """casadi_old_PI_ADMM/main.py:135-137: K_P = min(5/d_min, 2.5), rho = max(1, min(5, 4/d_min)) (K_I = 3 is md.K_I)."""
+    return min(md.KP_num / dmin, md.KP_max), max(md.rho_min, min(md.rho_max, md.rho_num / dmin))
+
+
+def pi_old_output_and_integrate(md: Modes, dmin, e, dual, integ, diffv):
+    """casadi_old_PI_ADMM/main.py:138-142 for one block of rows: output THEN integrate (trad: plain update + diff)."""
+    K_P, rho = pi_old_gains(md, dmin)
+    if md.trad:
+        return dual + rho * e + diffv, integ
+    return integ + K_P * e, integ + md.K_I * e + md.backcalc * diffv
+
+
+def clamp_with_backcalc(md: Modes, raw):
+    """Saturation + back-calculation term (old main.py:144-151, MATLAB :173-188): diff = clamped - raw, 0 where unclipped."""
+    cl = np.minimum(md.windup_sat, np.maximum(raw, -md.windup_sat))
+    return cl, cl - raw
+
+
 def run_step(p: Params, md: Modes, inner: InnerSettings, xt, spd, refwin, rho_state=None):
     """One MPC step (all outer iterations).
 
@@ -173,24 +192,14 @@ def run_step(p: Params, md: Modes, inner: InnerSettings, xt, spd, refwin, rho_st
             elif md.dual == "pi_old":
                 px, py, _ = literal_dynamic_update_edge(p, xt_e, np.vstack((primal_u[v1], primal_u[v2])), spd_e)
                 dmin = np.sqrt((px[0] - px[1]) ** 2 + (py[0] - py[1]) ** 2).min()
-                K_P = min(md.KP_num / dmin, md.KP_max)
-                rho = max(md.rho_min, min(md.rho_max, md.rho_num / dmin))
-                if md.trad:
-                    dual[v1, v2] = dual[v1, v2] + rho * e1 + diffv[v1, v2]
-                    dual[v2, v1] = dual[v2, v1] + rho * e2 + diffv[v2, v1]
-                else:
-                    dual[v1, v2] = integ[v1, v2] + K_P * e1
-                    dual[v2, v1] = integ[v2, v1] + K_P * e2
-                    integ[v1, v2] = integ[v1, v2] + md.K_I * e1 + md.backcalc * diffv[v1, v2]
-                    integ[v2, v1] = integ[v2, v1] + md.K_I * e2 + md.backcalc * diffv[v2, v1]
+                rho = pi_old_gains(md, dmin)[1]
+                for key, e in (((v1, v2), e1), ((v2, v1), e2)):
+                    dual[key], integ[key] = pi_old_output_and_integrate(md, dmin, e, dual[key], integ[key], diffv[key])
             else:
                 raise ValueError(md.dual)
             if md.dual != "plain" and md.windup:
                 for key in ((v1, v2), (v2, v1)):
-                    raw = dual[key]
-                    cl = np.minimum(md.windup_sat, np.maximum(raw, -md.windup_sat))
-                    dual[key] = cl
-                    diffv[key] = cl - raw       # == 0 when nothing clipped (MATLAB :181-185)
+                    dual[key], diffv[key] = clamp_with_backcalc(md, dual[key])
         # ---- residuals (main.py:165-178) ----
         sk = 0.0; rk = 0.0
         for (v1, v2) in edges:

@@ -10,6 +10,7 @@ then imported UNMODIFIED from /root/reference and their methods are called on nu
                                branch (:77-105); cost_function_primal (:114-135) evaluated at 0, +-e_i and e_i+e_j -> the exact
                                (H, q) of the quadratic it is, and at random u; nonlcon_function (:172-192) at random u;
                                cost_function_edge (:145-169, the Python non-convex statement) at random hat_u.
+  casadi_old_PI_ADMM/main.py   the dual / PI update block :127-164 exec'd verbatim over several outer iterations (the PI_OLD law).
   Distributed_planner/decentralized/optimizer.py, util.py
                                mid_state (:351-373), lambda_update (:330-335), check_converge (:225-235),
                                iterate_next_state (:337-344), bar_state_update (:205-222) with
@@ -147,6 +148,49 @@ def obca_cases(rng):
     return out
 
 
+def old_pi_block_cases(rng):
+    """The dual / PI update block of the OLD Python script, casadi_old_PI_ADMM/main.py:127-164 (gains from the minimum
+    distance, output-then-integrate, saturation +-20, back-calculation 2*diff, global Frobenius residuals, stop test with
+    the distance condition, the last_iter_hat_pos alias): those source lines are EXEC'd verbatim, several outer iterations in
+    a row, in a namespace that holds what the script holds at that point (the old class instance imported unmodified)."""
+    stubs.install()
+    spec = importlib.util.spec_from_file_location("ref_old_PI_ADMM_class", os.path.join(REF, "casadi_old_PI_ADMM", "PI_ADMM_class.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    lines = open(os.path.join(REF, "casadi_old_PI_ADMM", "main.py")).read().split("\n")[126:164]
+    assert "dual variable update" in lines[0] and "sum_iter_num += 1" in lines[-1]
+    src = "for num_step in [num_step_]:\n    for i_iter in [i_iter_]:\n" + "\n".join(lines) + "\n"
+    code = compile(src, "casadi_old_PI_ADMM/main.py:127-164", "exec")
+    out = []
+    for case, (trad, scale) in enumerate(((0, 1.0), (0, 6.0), (1, 3.0))):
+        PI = m.PI_ADMM_CASADI()
+        N, V = PI.param.num_ho, PI.param.num_veh
+        xt = np.array([[-3.0, 0.2, 0.05], [0.3, 6.0, -1.5]]) + rng.normal(0, 0.2, (2, 3))
+        hat_pos_old = np.zeros((2 * V, N + 1))
+        ns = dict(PI_ADMM=PI, np=np, xt=xt, trad=trad, windup_sat=20, sum_err=0, diff_val=0, err_rk_vec=[], sum_iter_num=0,
+                  dual_var_old=np.zeros((2 * V, N + 1)), hat_pos_old=hat_pos_old, last_iter_hat_pos=hat_pos_old.copy(),
+                  curr_iter=-1, num_step_=3)
+        its = []
+        for it in range(6):
+            primal_u = rng.normal(0, 0.2, (V, N))
+            pos_old = rng.normal(0, 1.0, (2 * V, N + 1)) * scale
+            new_hat = pos_old + rng.normal(0, 0.5, pos_old.shape) * scale * (0.02 if (case == 0 and it >= 4) else 1.0)
+            for r in range(2 * V):
+                hat_pos_old[r] = new_hat[r]             # the script writes hat_pos_old row by row, in place (:121-125)
+            ns.update(primal_u=primal_u, pos_old=pos_old, i_iter_=it, curr_iter=-1)
+            exec(code, ns)
+            dv = ns["diff_val"]
+            its.append(dict(primal_u=primal_u.tolist(), pos_old=pos_old.tolist(), hat_pos_old=new_hat.tolist(),
+                            dual_var_old=np.asarray(ns["dual_var_old"]).tolist(), sum_err=np.broadcast_to(np.asarray(ns["sum_err"], dtype=float), pos_old.shape).tolist(),
+                            diff_val=np.broadcast_to(np.asarray(dv, dtype=float), pos_old.shape).tolist(), rho=float(PI.param.rho),
+                            error_sk=float(ns["error_sk"]), error_rk=float(ns["error_rk"]), dis_vec=np.asarray(ns["dis_vec"]).tolist(),
+                            stopped=bool(ns["curr_iter"] == it + 1)))
+        out.append(dict(trad=trad, xt=xt.tolist(), spd=np.asarray(PI.param.spd, dtype=float).tolist(), N=int(N), windup_sat=20,
+                        eps_pri=float(PI.param.eps_pri), eps_dual=float(PI.param.eps_dual), dis_thres=float(PI.param.dis_thres),
+                        dt=float(PI.param.dt), L=float(PI.param.L), iterations=its))
+    return out
+
+
 def main():
     rng = np.random.default_rng(20261105)
     PI_cls = load_class()
@@ -166,6 +210,7 @@ def main():
     near = np.array([[-4.0, 0.0, 0.0], [0.0, 7.0, -np.pi / 2]])        # close enough for the hinge of the edge cost to be active
     out["edge"] = [edge_case(PI_cls(), rng, near + rng.normal(0, 0.3, (2, 3)), N, spd) for N, spd in ((15, (4, 8)), (30, (6, 7)), (5, (8, 4)))]
     out["obca"] = obca_cases(rng)
+    out["old_pi_block"] = old_pi_block_cases(np.random.default_rng(77))
     path = os.path.join(HERE, "reference_vectors.json")
     json.dump(out, open(path, "w"))
     print("wrote", path, os.path.getsize(path), "bytes")

@@ -283,3 +283,45 @@ def test_gpu_closed_loop_equals_the_reference_script_run(how):
     assert np.abs(np.array(out["x_vec"]) - A_(RUN["x_vec"])).max() <= 1e-6
     assert np.abs(np.array(out["u_vec"]) - A_(RUN["u_vec"])).max() <= 1e-6
     assert np.abs(np.array(out["theta_vec"]) - A_(RUN["theta_vec"])).max() <= 1e-6
+
+
+@pytest.mark.parametrize("ci", range(len(VEC["old_pi_block"])))
+def test_pi_old_law_equals_the_old_scripts_own_lines(ci):
+    """casadi_old_PI_ADMM/main.py:127-164, exec'd verbatim for six outer iterations in a row (gains from the minimum distance of
+    the non-linear roll-outs, output-then-integrate, saturation +-20, back-calculation 2*diff, global residuals, the
+    last_iter_hat_pos alias, the stop test with the distance condition), against the functions oracle/driver.py's pi_old
+    branch is made of -- the law the kernels implement as PIADMM_DUAL_PI_OLD."""
+    from oracle.driver import Modes, pi_old_gains, pi_old_output_and_integrate, clamp_with_backcalc
+    c = VEC["old_pi_block"][ci]
+    md = Modes.python_old_pi(trad=c["trad"], windup_sat=float(c["windup_sat"]))
+    p = Params(num_ho=c["N"], spd=A_(c["spd"]), dt=c["dt"], L=c["L"])
+    xt = A_(c["xt"])
+    shape = A_(c["iterations"][0]["pos_old"]).shape
+    dual, integ, diffv = np.zeros(shape), np.zeros(shape), np.zeros(shape)
+    last_hat = np.zeros(shape)
+    aliased = False
+    clipped = stopped = 0
+    for it in c["iterations"]:
+        pos, hat = A_(it["pos_old"]), A_(it["hat_pos_old"])
+        px, py, _ = literal_dynamic_update_edge(p, xt, A_(it["primal_u"]), p.spd)
+        dis = np.sqrt((px[0] - px[1]) ** 2 + (py[0] - py[1]) ** 2)
+        assert np.abs(dis - A_(it["dis_vec"])).max() <= 1e-12
+        dmin = dis.min()
+        rho = pi_old_gains(md, dmin)[1]
+        assert abs(rho - it["rho"]) <= 1e-13 * rho          # dis_vec comes out of a matrix product in the script: last-bit differences
+        dual, integ = pi_old_output_and_integrate(md, dmin, pos - hat, dual, integ, diffv)
+        dual, diffv = clamp_with_backcalc(md, dual)
+        assert np.abs(dual - A_(it["dual_var_old"])).max() <= 1e-12 and np.abs(diffv - A_(it["diff_val"])).max() <= 1e-12
+        if not c["trad"]:
+            assert np.abs(integ - A_(it["sum_err"])).max() <= 1e-12
+        lh = hat if aliased else last_hat                           # the script's last_iter_hat_pos IS hat_pos_old from iteration 2 on
+        sk = np.sqrt(np.sum((rho * (lh - hat)) ** 2)); rk = np.sqrt(np.sum((pos - hat) ** 2))
+        assert abs(sk - it["error_sk"]) <= 1e-10 * max(1.0, sk) and abs(rk - it["error_rk"]) <= 1e-10 * max(1.0, rk)
+        stop = bool(rk <= c["eps_pri"] and sk <= c["eps_dual"] and dis[1] > c["dis_thres"])
+        assert stop == it["stopped"]
+        aliased = True
+        clipped += int(np.any(np.abs(dual) == c["windup_sat"])); stopped += int(stop)
+    if ci == 0:
+        assert stopped > 0
+    if ci == 1:
+        assert clipped > 0
