@@ -184,10 +184,12 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "agent-QP solves/s", "value": val, "unit": "solves/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args.workload, S, N, 1),
+        # the GPU arm's config at this N (the metric is a throughput: the CPU arm times a bounded SAMPLE of that workload,
+        # one rank's 4096 scenarios per step, whatever N is -- said in cpu_baseline.sample)
+        "config": workload_config(args.workload, S, N, max(1, args.gpus)),
         "cpu_baseline": {"value": val, "unit": "solves/s", "cores": cores, "kind": "port",
-                         "sample": f"the full {S}-scenario MPC step x {args.steps} steps on {cores} OpenMP threads "
-                                   "(oracle/piadmm_ref.c; CasADi+OSQP not installable)"},
+                         "sample": f"one rank's share of the workload ({S} scenarios = one full MPC step) x {args.steps} steps on "
+                                   f"{cores} OpenMP threads (oracle/piadmm_ref.c; CasADi+OSQP not installable)"},
         "e2e": {"value": val, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
