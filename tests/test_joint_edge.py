@@ -137,7 +137,8 @@ def _oracle_joint(sc, pairs, inner):
 @pytest.mark.gpu
 @pytest.mark.parametrize("V,N,cap,inner", [(2, 15, 1, "default"), (3, 8, 2, "default"), (6, 15, 5, "default"), (6, 15, 5, "tight"),
                                            (9, 30, 8, "default"), (20, 15, 4, "default"), (40, 30, 3, "default"),
-                                           (64, 30, 4, "default"), (20, 15, 4, "tight"), (100, 15, 3, "default")])
+                                           (64, 30, 4, "default"), (20, 15, 4, "tight"), (100, 15, 3, "default"),
+                                           (3, 2, 2, "default"), (4, 16, 3, "default"), (5, 31, 4, "default"), (17, 7, 2, "default")])
 def test_gpu_joint_equals_oracle(V, N, cap, inner):
     """One scene per launch: same inner iteration count as the oracle (same iteration, same termination rule), controls
     within 1e-6 (north_star tolerance)."""

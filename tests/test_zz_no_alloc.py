@@ -106,3 +106,29 @@ def test_static_edge_list_rejects_scenes_beyond_its_scratch():
     assert rc == -4
     rc = lib.piadmm_edge_list_static(None, 1, 2, 15, 2.0, 1, 1, C.c_void_p(n.data_ptr()), C.c_void_p(ij.data_ptr()), st)
     assert rc == -1
+
+
+@pytest.mark.parametrize("S,V,N", [(3, 1, 15), (2, 5, 1), (1, 33, 31), (7, 40, 8)])
+def test_static_edge_list_small_and_odd_shapes_against_numpy(S, V, N):
+    """Shapes the solver-based comparison does not reach (a single vehicle, N = 1, N = 31, V just over a word), against the
+    statement itself in numpy: edge_mat[i, j] = any_k(d^2 < thr) for i < j, pairs in np.where order (casadi/main.py:110-113,121)."""
+    lib = _abi.load_library()
+    rng = np.random.default_rng(S * 100 + V)
+    pos = rng.normal(0, 2.5, (S, V, 2, N + 1))
+    thr = 1.7
+    t = torch.from_numpy(pos).cuda()
+    cap = max(1, V * (V - 1) // 2)
+    en = torch.full((S,), -1, dtype=torch.int32, device="cuda"); eij = torch.full((S, cap, 2), -1, dtype=torch.int32, device="cuda")
+    rc = lib.piadmm_edge_list_static(C.c_void_p(t.data_ptr()), S, V, N, thr, 0, cap, C.c_void_p(en.data_ptr()), C.c_void_p(eij.data_ptr()),
+                                     C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    en, eij = en.cpu().numpy(), eij.cpu().numpy()
+    for s in range(S):
+        mat = np.zeros((V, V), int)
+        for i in range(V):
+            for j in range(i + 1, V):
+                d2 = (pos[s, i, 0] - pos[s, j, 0]) ** 2 + (pos[s, i, 1] - pos[s, j, 1]) ** 2
+                mat[i, j] = int(np.any(d2 < thr))
+        r, c = np.where(mat == 1)
+        assert en[s] == len(r) and np.array_equal(eij[s, :len(r)], np.stack((r, c), 1))
