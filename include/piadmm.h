@@ -71,7 +71,7 @@ typedef struct piadmm_params {
   double K_I, KP_num, KP_max, rho_num, rho_min, rho_max; /* old main.py:135-137 */
   /* --- inner OSQP-style ADMM (OSQP defaults: 0.1, 1e-6, 1.6, 1e-3, 1e-3, 5) --- */
   double in_rho0, in_sigma, in_alpha, in_eps_abs, in_eps_rel, in_adapt_tol;
-  int32_t num_ho;          /* horizon N (2..32) */
+  int32_t num_ho;          /* horizon N (3..31) */
   int32_t iter_num;        /* outer iteration cap */
   int32_t dual_mode;       /* PIADMM_DUAL_* */
   int32_t thr_squared;     /* 0: d^2 < dis_thres (casadi/main.py:113) ; 1: d^2 < dis_thres^2 (MATLAB :109) */
