@@ -539,7 +539,11 @@ extern "C" int piadmm_debug_read_trace(long long* host, int n) {
 // when the batch has at most two CTAs per SM -- config 1 is ONE scenario, i.e. one dependent chain whose spills are
 // pure latency.  Same PTX arithmetic, so results are bit-identical to the throughput build.
 template <int LPQ, bool FEW = false>
+#ifdef FUSED16_MAXNREG   // A/B build: cap the registers of the LPQ == 16 throughput build directly (NVCC_EXTRA=-DFUSED16_MAXNREG=112)
+__global__ void __launch_bounds__(CTA_THREADS) __maxnreg__(FEW ? 248 : (LPQ == 16 ? FUSED16_MAXNREG : 168)) k_fused_v2(const __grid_constant__ DevCtx c) {
+#else
 __global__ void __launch_bounds__(CTA_THREADS, FEW ? 4 : (LPQ == 16 ? FUSED16_MIN_CTAS : FUSED32_MIN_CTAS)) k_fused_v2(const __grid_constant__ DevCtx c) {
+#endif
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];
   __shared__ __align__(16) double xch[128];
