@@ -12,8 +12,9 @@ Python edge cost is NOT reproduced (ill-posed).
 
 OUTER LOOP PINNED to the reference's own script: tests/golden/reference_main_run.json is /root/reference/casadi/main.py run
 unmodified (QP solves stood in by oracle/solver.py, tests/golden/run_reference_main.py); run_closed_loop in python_current
-semantics reproduces its histories exactly (tests/test_reference_vectors.py).  The PI variants (MATLAB / old Python scripts) and
-the inner solver's iterates stay unpinned (oracle/problem.py header).
+semantics reproduces its histories exactly (tests/test_reference_vectors.py).  The two PI laws are pinned statement by statement:
+pi_old against lines 127-164 of casadi_old_PI_ADMM/main.py exec'd verbatim, pi against the MATLAB script's own text executed by
+tests/golden/_matlab_subset.py (:6-25,105-124,152-209).  The inner solver's iterates stay unpinned (oracle/problem.py header).
 """
 from __future__ import annotations
 
@@ -79,6 +80,18 @@ class Modes:
 
 def _round(a, dec):
     return np.around(a, dec) if dec >= 0 else np.asarray(a, dtype=np.float64)
+
+
+def pi_gain(md: Modes, dmin):
+    """MATLAB ...PI_antiwindup.m:160: kP = theta1 - theta2 / (1 + exp(-min(dis_vec)))."""
+    return md.theta1 - md.theta2 / (1.0 + np.exp(-dmin))
+
+
+def pi_integrate_and_output(md: Modes, rho, dmin, e, integ, diffv):
+    """MATLAB ...PI_antiwindup.m:160-166 for one directed edge: integrate (kI = rho unless given, :21) THEN output."""
+    kI = rho if md.kI is None else md.kI
+    integ = integ + kI * e + md.backcalc * diffv
+    return integ + pi_gain(md, dmin) * e, integ
 
 
 def pi_old_gains(md: Modes, dmin):
@@ -183,12 +196,8 @@ def run_step(p: Params, md: Modes, inner: InnerSettings, xt, spd, refwin, rho_st
                 dual[v2, v1] = dual[v2, v1] + rho_it * e2
             elif md.dual == "pi":
                 dmin = np.sqrt(((pos[v1] - pos[v2]) ** 2).sum(axis=0)).min()
-                kP = md.theta1 - md.theta2 / (1.0 + np.exp(-dmin))
-                kI = rho_it if md.kI is None else md.kI
-                integ[v1, v2] = integ[v1, v2] + kI * e1 + md.backcalc * diffv[v1, v2]
-                integ[v2, v1] = integ[v2, v1] + kI * e2 + md.backcalc * diffv[v2, v1]
-                dual[v1, v2] = integ[v1, v2] + kP * e1
-                dual[v2, v1] = integ[v2, v1] + kP * e2
+                for key, e in (((v1, v2), e1), ((v2, v1), e2)):
+                    dual[key], integ[key] = pi_integrate_and_output(md, rho_it, dmin, e, integ[key], diffv[key])
             elif md.dual == "pi_old":
                 px, py, _ = literal_dynamic_update_edge(p, xt_e, np.vstack((primal_u[v1], primal_u[v2])), spd_e)
                 dmin = np.sqrt((px[0] - px[1]) ** 2 + (py[0] - py[1]) ** 2).min()

@@ -11,6 +11,9 @@ then imported UNMODIFIED from /root/reference and their methods are called on nu
                                (H, q) of the quadratic it is, and at random u; nonlcon_function (:172-192) at random u;
                                cost_function_edge (:145-169, the Python non-convex statement) at random hat_u.
   casadi_old_PI_ADMM/main.py   the dual / PI update block :127-164 exec'd verbatim over several outer iterations (the PI_OLD law).
+  matlab_old_files/ADMM_CVX_two_veh_intesection_PI_antiwindup.m
+                               param :6-25, collision test :105-121, dual / PI update + saturation + back-calculation :152-189,
+                               residual sums and stop test :191-209 -- the .m text executed by tests/golden/_matlab_subset.py.
   Distributed_planner/decentralized/optimizer.py, util.py
                                mid_state (:351-373), lambda_update (:330-335), check_converge (:225-235),
                                iterate_next_state (:337-344), bar_state_update (:205-222) with
@@ -191,6 +194,70 @@ def old_pi_block_cases(rng):
     return out
 
 
+def matlab_pi_block_cases(rng):
+    """The default dual law (dual="pi") comes from MATLAB source, which cannot run here.  Its statements are therefore
+    EXECUTED FROM THE .m TEXT by the small interpreter of tests/golden/_matlab_subset.py:
+    matlab_old_files/ADMM_CVX_two_veh_intesection_PI_antiwindup.m  :6-25 (param), :43 (windup_sat), :105-121 (collision test,
+    early exit, find), :122-124 + :152-189 (per-edge dual / PI update, saturation, back-calculation), :190-209 (residual
+    sums, stop test with the distance condition, last_iter_hat_pos, curr_iter).  The CVX solve and the roll-out between
+    :126 and :151 are replaced by the harness writing pos_old / hat_pos_old for the iteration."""
+    import _matlab_subset as ms
+    path = os.path.join(REF, "matlab_old_files", "ADMM_CVX_two_veh_intesection_PI_antiwindup.m")
+    L = open(path).read().split("\n")
+    seg = lambda a, b: "\n".join(L[a - 1:b])
+    assert L[5].startswith("param.dt") and L[24].startswith("param.windup") and "windup_sat" in L[42] and "edge_mat(i, j)" in L[108]
+    assert L[121].strip().startswith("for i_edge") and "veh2 = edge_col" in L[123] and "dual variable update" in L[151]
+    assert L[188].strip() == "end" and "%% summary" in L[190] and "curr_iter = i_iter;" in L[208]
+    body = ("for i_iter = i_iter_: i_iter_\n" + seg(105, 121) + "\n" + seg(122, 124) + "\n" + seg(152, 189) + "\n" + seg(191, 209) + "\nend\n")
+    out = []
+    for case, (PI, windup, scale, close) in enumerate(((1, 1, 1.0, 1), (1, 1, 8.0, 1), (0, 1, 2.0, 1), (1, 0, 3.0, 1), (1, 1, 1.0, 0))):
+        it = ms.Interp()
+        it.run(seg(6, 25) + "\n" + seg(43, 43))
+        P = it.ns["param"]
+        P["PI"], P["windup"] = float(PI), float(windup)
+        N, V = int(P["num_ho"]), int(P["num_veh"])
+        z = lambda: np.zeros((2, N + 1))
+        cell = lambda: ms.Cell({(i, j): z() for i in (1, 2) for j in (1, 2)})
+        it.ns.update(hat_pos_old=cell(), dual_var_old=cell(), diff_val_veh=cell(), edge_mat=np.zeros((V, V)),
+                     kP_mat=P["kP"] * np.ones((V, V)), sum_err_veh1=0.0, sum_err_veh2=0.0, err_rk_vec=np.zeros((0, 0)), flag=0.0,
+                     curr_iter=1.0, sum_iter_num=0.0)
+        it.ns["last_iter_hat_pos"] = ms.Interp.value_copy(it.ns["hat_pos_old"])
+        its = []
+        for k in range(6):
+            base = rng.normal(0, 1.0, (2, N + 1)) * scale
+            sep = (0.3 if close else 40.0) if k < 5 else 40.0            # last iteration: far apart (the edge drops out)
+            pos_old = np.vstack((base, base + sep + rng.normal(0, 0.3, (2, N + 1))))
+            shrink = 0.002 if (case == 0 and k >= 3) else 1.0
+            hat = {(1, 2): pos_old[:2] + rng.normal(0, 0.5, (2, N + 1)) * scale * shrink,
+                   (2, 1): pos_old[2:] + rng.normal(0, 0.5, (2, N + 1)) * scale * shrink}
+            if case == 0 and k >= 3:
+                pos_old[2:, 1] = pos_old[:2, 1] + 3.0              # dis_vec(2) > dis_thres, so that the stop test can pass
+            it.ns["pos_old"] = pos_old.copy()
+            for key, v in hat.items():
+                it.ns["hat_pos_old"][key] = v.copy()               # what :149-150 would have written for the colliding pair
+            it.ns["i_iter_"] = float(k + 1)
+            before = it.ns["sum_iter_num"]
+            it.run(body)
+            ns = it.ns
+            edges = int(np.sum(mat_(ns["edge_mat"]) == 1))
+            its.append(dict(pos_old=pos_old.tolist(), hat12=hat[(1, 2)].tolist(), hat21=hat[(2, 1)].tolist(), edges=edges,
+                            flag=float(ns["flag"]), went_on=bool(ns["sum_iter_num"] > before),
+                            dual12=mat_(ns["dual_var_old"][(1, 2)]).tolist(), dual21=mat_(ns["dual_var_old"][(2, 1)]).tolist(),
+                            diff12=mat_(ns["diff_val_veh"][(1, 2)]).tolist(), diff21=mat_(ns["diff_val_veh"][(2, 1)]).tolist(),
+                            sum_err1=np.broadcast_to(mat_(ns["sum_err_veh1"]), (2, N + 1)).tolist(),
+                            sum_err2=np.broadcast_to(mat_(ns["sum_err_veh2"]), (2, N + 1)).tolist(),
+                            kP=float(mat_(ns["kP_mat"])[0, 1]), error_rk=float(ns.get("error_rk", 0.0)), error_sk=float(ns.get("error_sk", 0.0)),
+                            curr_iter=float(ns["curr_iter"])))
+        out.append(dict(param={k: (np.asarray(v).tolist() if isinstance(v, np.ndarray) else v) for k, v in P.items()},
+                        windup_sat=float(it.ns["windup_sat"]), iterations=its))
+    return out
+
+
+def mat_(x):
+    x = np.asarray(x, dtype=np.float64)
+    return x.reshape(1, 1) if x.ndim == 0 else x
+
+
 def main():
     rng = np.random.default_rng(20261105)
     PI_cls = load_class()
@@ -211,6 +278,7 @@ def main():
     out["edge"] = [edge_case(PI_cls(), rng, near + rng.normal(0, 0.3, (2, 3)), N, spd) for N, spd in ((15, (4, 8)), (30, (6, 7)), (5, (8, 4)))]
     out["obca"] = obca_cases(rng)
     out["old_pi_block"] = old_pi_block_cases(np.random.default_rng(77))
+    out["matlab_pi_block"] = matlab_pi_block_cases(np.random.default_rng(78))
     path = os.path.join(HERE, "reference_vectors.json")
     json.dump(out, open(path, "w"))
     print("wrote", path, os.path.getsize(path), "bytes")

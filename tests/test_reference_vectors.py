@@ -325,3 +325,60 @@ def test_pi_old_law_equals_the_old_scripts_own_lines(ci):
         assert stopped > 0
     if ci == 1:
         assert clipped > 0
+
+
+@pytest.mark.parametrize("ci", range(len(VEC["matlab_pi_block"])))
+def test_matlab_pi_law_equals_the_m_file_statements(ci):
+    """The default dual law (dual="pi": every bench configuration) is MATLAB source.  Its statements -- parameter block,
+    collision test with the squared threshold and the early exit, per-edge PI update (sigmoid kP from the minimum distance,
+    kI = rho, integrate THEN output), saturation +-30 with back-calculation, residual sums, stop test with dis_vec(2), the
+    COPY of last_iter_hat_pos, curr_iter every iteration -- were executed from the .m text
+    (matlab_old_files/ADMM_CVX_two_veh_intesection_PI_antiwindup.m:6-25,43,105-124,152-209) by tests/golden/_matlab_subset.py
+    for six outer iterations per case (PI on / off, back-calculation on / off, clipping, no collision at all, an edge that
+    drops out).  The functions oracle/driver.py's "pi" branch is made of must reproduce every iteration."""
+    from oracle.driver import Modes, pi_gain, pi_integrate_and_output, clamp_with_backcalc
+    c = VEC["matlab_pi_block"][ci]
+    P = c["param"]
+    md = Modes.matlab_pi(PI=int(P["PI"]), windup=int(P["windup"]), windup_sat=float(c["windup_sat"]), theta1=P["theta1"], theta2=P["theta2"])
+    assert P["kI"] == P["rho"] and md.kI is None and md.thr_squared == 1 and md.dual_res_alias == 0 and md.stop_dist_test == 1
+    rho, thr = float(P["rho"]), float(P["dis_thres"]) ** 2
+    shape = A_(c["iterations"][0]["pos_old"])[:2].shape
+    z = lambda: np.zeros(shape)
+    dual, integ, diffv, hat, last_hat = [z(), z()], [z(), z()], [z(), z()], [z(), z()], [z(), z()]
+    flag, curr_iter, dis2 = 0, 1, None
+    for k, it in enumerate(c["iterations"]):
+        pos = A_(it["pos_old"]); p = [pos[:2], pos[2:]]
+        d2 = (p[0][0] - p[1][0]) ** 2 + (p[0][1] - p[1][1]) ** 2
+        edge = bool(np.any(d2 < thr))
+        assert int(edge) == it["edges"]
+        if not edge and flag == 0:                                   # :113-114 no collision so far: leave the loop
+            assert it["flag"] == 0 and not it["went_on"]
+            continue
+        flag = 1
+        assert it["flag"] == 1
+        rk = sk = 0.0
+        if edge:
+            hat = [A_(it["hat12"]), A_(it["hat21"])]
+            dis = np.sqrt(((p[0] - p[1]) ** 2).sum(axis=0)); dis2 = dis[1]
+            e = [p[0] - hat[0], p[1] - hat[1]]
+            for r in range(2):
+                if md.PI:
+                    dual[r], integ[r] = pi_integrate_and_output(md, rho, dis.min(), e[r], integ[r], diffv[r])
+                else:
+                    dual[r] = dual[r] + rho * e[r]
+                if md.windup:
+                    dual[r], diffv[r] = clamp_with_backcalc(md, dual[r])
+            if md.PI:
+                assert abs(pi_gain(md, dis.min()) - it["kP"]) <= 1e-13
+            sk = 2 * np.sqrt(np.sum((rho * (last_hat[0] - hat[0])) ** 2)); rk = 2 * np.sqrt(np.sum((p[0] - hat[0]) ** 2))
+        for got, key in ((dual[0], "dual12"), (dual[1], "dual21"), (diffv[0], "diff12"), (diffv[1], "diff21")):
+            assert np.abs(got - A_(it[key])).max() <= 1e-12, (k, key)
+        if md.PI:
+            assert np.abs(integ[0] - A_(it["sum_err1"])).max() <= 1e-12 and np.abs(integ[1] - A_(it["sum_err2"])).max() <= 1e-12
+        assert abs(rk - it["error_rk"]) <= 1e-11 * max(1.0, rk) and abs(sk - it["error_sk"]) <= 1e-11 * max(1.0, sk)
+        stop = bool(rk <= P["eps_pri"] and sk <= P["eps_dual"] and dis2 > P["dis_thres"])
+        assert stop == (not it["went_on"]), k
+        curr_iter = k + 1                                            # :203 and :209: either way
+        assert it["curr_iter"] == curr_iter
+        last_hat = [hat[0].copy(), hat[1].copy()]                    # :207 is a COPY in MATLAB (no alias quirk here)
+    assert (P["PI"], P["windup"]) in ((1.0, 1.0), (0.0, 1.0), (1.0, 0.0))
