@@ -17,8 +17,10 @@ tests/golden/reference_vectors.json is produced by importing casadi/PI_ADMM_clas
 unmodified from /root/reference (numpy stand-ins for the `casadi` / `bunch` containers,
 tests/golden/make_reference_vectors.py) and calling its methods on numeric arrays --
 param, ref_traj, both roll-outs, cost_function_primal (its exact (H, q)),
-nonlcon_function, cost_function_edge, and the convex edge statement composed from the
-reference's two functions; tests/test_reference_vectors.py compares the closed forms
+nonlcon_function, cost_function_edge, the convex edge statement composed from the
+reference's two functions -- and the MATLAB script's own function bodies (roll-outs,
+cost_function_primal, the convex cost_function_edge) executed from the .m text by
+tests/golden/_matlab_subset.py; tests/test_reference_vectors.py compares the closed forms
 below, the C twin's inputs and the CUDA path with them.
 PARITY UNPINNED for solver OUTPUTS: the reference ships no tests / golden vectors and
 its solver stack (CasADi 3.5.6.pre2 + vendored OSQP) is not installable here, so no

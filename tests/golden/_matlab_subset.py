@@ -41,7 +41,10 @@ def tokenize(src):
                 break
             if not ch.isspace():
                 prev = ch
-        line = line[:cut]
+        line = line[:cut].rstrip()
+        cont = line.endswith("...")
+        if cont:
+            line = line[:-3]
         pos = 0
         prev_tok = None
         while pos < len(line):
@@ -58,7 +61,8 @@ def tokenize(src):
                 continue
             prev_tok = (kind, m.group())
             out.append(prev_tok)
-        out.append(("nl", "\n"))
+        if not cont:
+            out.append(("nl", "\n"))
     return out
 
 
@@ -236,7 +240,8 @@ class Interp:
                 path.append(("field", self.next()[1]))
             elif self.peek() == ("op", "("):
                 self.i += 1
-                path.append(("paren", self.args(")", execute)))
+                base = self.ns.get(val) if (execute and len(path) == 1) else None
+                path.append(("paren", self.args(")", execute, base=base)))
             elif self.peek() == ("op", "{"):
                 self.i += 1
                 path.append(("brace", self.args("}", execute)))
@@ -373,11 +378,38 @@ class Interp:
             return simplify(np.negative(v)) if ex else 0.0
         return self.postfix(ex)
 
-    def args(self, close, ex):
+    def arity(self, close):
+        """Number of arguments of the index list that starts at the current token (look-ahead, for `end`)."""
+        depth, n, i = 0, 1, self.i
+        while True:
+            k, v = self.t[i]
+            if k == "op" and v in "([{":
+                depth += 1
+            elif k == "op" and v in ")]}":
+                if depth == 0:
+                    return n
+                depth -= 1
+            elif k == "op" and v == "," and depth == 0:
+                n += 1
+            i += 1
+
+    def args(self, close, ex, base=None):
         out = []
         if self.accept(close):
             return out
+        self.end_ctx = getattr(self, "end_ctx", [])
+        n_args = self.arity(close)
         while True:
+            self.end_ctx.append((base, len(out), n_args))
+            try:
+                done = self._one_arg(out, close, ex)
+            finally:
+                self.end_ctx.pop()
+            if done:
+                return out
+
+    def _one_arg(self, out, close, ex):
+        if True:
             if self.peek() == ("op", ":") and self.t[self.i + 1][1] in (",", close):
                 self.i += 1
                 out.append(":")
@@ -386,8 +418,9 @@ class Interp:
             else:
                 out.append(self.expr(ex))
             if self.accept(close):
-                return out
+                return True
             self.expect(",")
+            return False
 
     def index_tuple(self, base, arg):
         def one(a, n):
@@ -454,6 +487,10 @@ class Interp:
         elif kind == "id":
             if val == "pi":
                 v = float(np.pi)
+            elif val == "end" and getattr(self, "end_ctx", None):
+                base, pos, n_args = self.end_ctx[-1]
+                b = mat(base) if base is not None and ex else np.zeros((1, 1))
+                v = float(b.size if n_args == 1 else b.shape[pos])
             elif self.peek() == ("op", "(") and val not in self.ns:
                 self.i += 1
                 arg = self.args(")", ex)
@@ -465,7 +502,7 @@ class Interp:
         while True:
             if self.peek() == ("op", "(") and kind != "num":
                 self.i += 1
-                arg = self.args(")", ex)
+                arg = self.args(")", ex, base=v if ex else None)
                 v = self.index(v, arg) if ex else 0.0
             elif self.peek() == ("op", "{"):
                 self.i += 1

@@ -13,7 +13,9 @@ then imported UNMODIFIED from /root/reference and their methods are called on nu
   casadi_old_PI_ADMM/main.py   the dual / PI update block :127-164 exec'd verbatim over several outer iterations (the PI_OLD law).
   matlab_old_files/ADMM_CVX_two_veh_intesection_PI_antiwindup.m
                                param :6-25, collision test :105-121, dual / PI update + saturation + back-calculation :152-189,
-                               residual sums and stop test :191-209 -- the .m text executed by tests/golden/_matlab_subset.py.
+                               residual sums and stop test :191-209; the bodies of dynamic_update_local / _edge (:312-397),
+                               cost_function_primal (:254-273), cost_function_edge (:287-302, the CONVEX edge statement)
+                               -- the .m text executed by tests/golden/_matlab_subset.py.
   Distributed_planner/decentralized/optimizer.py, util.py
                                mid_state (:351-373), lambda_update (:330-335), check_converge (:225-235),
                                iterate_next_state (:337-344), bar_state_update (:205-222) with
@@ -253,6 +255,90 @@ def matlab_pi_block_cases(rng):
     return out
 
 
+def matlab_function_cases(rng):
+    """Function bodies of the same MATLAB script, executed from the .m text with the arguments preset in the namespace:
+    dynamic_update_local (:312-348, both branches: numeric non-linear roll-out / linearised about xt(3)),
+    dynamic_update_edge (:357-397, both branches), cost_function_primal (:254-273, with the linearised roll-out of :332-347
+    run first, as its line :258 does), cost_function_edge (:287-302 after the linearised edge roll-out :379-396 of its line
+    :286) -- the CONVEX edge statement this repository implements, evaluated by the reference's own MATLAB statements."""
+    import _matlab_subset as ms
+    path = os.path.join(REF, "matlab_old_files", "ADMM_CVX_two_veh_intesection_PI_antiwindup.m")
+    L = open(path).read().split("\n")
+    seg = lambda a, b: "\n".join(L[a - 1:b])
+    assert L[311].strip().startswith("if nargin  == 4") and L[347].strip() == "end" and L[356].strip().startswith("if nargin  == 3")
+    assert L[396].strip() == "end" and "ref_val_x = ref_traj" in L[253] and "cost = cost_norm" in L[272]
+    assert "last_dis = prev_pred_pos" in L[286] and "cost = cost_punish" in L[301]
+    out = []
+    for case, (N, spd, close) in enumerate(((8, (4.0, 8.0), 1), (15, (6.0, 5.0), 1), (5, (8.0, 4.0), 0))):
+        it0 = ms.Interp(); it0.run(seg(6, 25))
+        P = it0.ns["param"]; P["num_ho"] = float(N); P["spd"] = np.array(spd).reshape(2, 1)
+        xt = np.array([[-3.0, 0.2, 0.1], [0.4, 5.0, -1.45]]) + rng.normal(0, 0.2, (2, 3))
+        if not close:
+            xt[1, :2] += 40.0
+        T = 50
+        ref_traj = rng.normal(0, 3, (4, T))
+        rec = dict(N=N, spd=list(spd), xt=xt.tolist(), ref_traj=ref_traj.tolist(), param={k: (np.asarray(v).tolist() if isinstance(v, np.ndarray) else v) for k, v in P.items()})
+        zer = lambda r: np.zeros((r, N + 1))
+        # --- roll-outs of one vehicle (numeric: nargin == 4; symbolic branch: nargin == 7) and of the pair (3 / 6)
+        rolls = []
+        for v in (1, 2):
+            u = rng.normal(0, 0.25, (1, N))
+            r_ = dict(veh=v, u=u.tolist())
+            for nargin, key in ((4, "nonlinear"), (7, "linear")):
+                ns = dict(param=P, xt=xt[v - 1:v].copy(), u=u, veh_index=float(v), nargin=float(nargin), x_pred=zer(1), y_pred=zer(1), theta_pred=zer(1))
+                ms.Interp(ns).run(seg(312, 348))
+                r_[key] = [ns["x_pred"].tolist(), ns["y_pred"].tolist(), ns["theta_pred"].tolist()]
+            rolls.append(r_)
+        rec["local_rollouts"] = rolls
+        ue = rng.normal(0, 0.25, (2, N))
+        er = dict(u=ue.tolist())
+        for nargin, key in ((3, "nonlinear"), (6, "linear")):
+            ns = dict(param=P, xt=xt.copy(), u=ue, nargin=float(nargin), x_pred=zer(2), y_pred=zer(2), theta_pred=zer(2))
+            ms.Interp(ns).run(seg(357, 397))
+            er[key] = [ns["x_pred"].tolist(), ns["y_pred"].tolist(), ns["theta_pred"].tolist()]
+        rec["edge_rollouts"] = er
+        # --- cost_function_primal at 0, +-e_i, e_i+e_j (exact H, q) and at random u
+        veh, num_step = 1 + case % 2, 3 + case
+        hat = ms.Cell({(i, j): rng.normal(0, 3, (2, N + 1)) for i in (1, 2) for j in (1, 2)})
+        dual = ms.Cell({(i, j): rng.normal(0, 1, (2, N + 1)) for i in (1, 2) for j in (1, 2)})
+
+        def f_primal(u):
+            ns = dict(param=P, xt=xt[veh - 1:veh].copy(), u=np.asarray(u, dtype=float).reshape(1, N), veh_index=float(veh), nargin=7.0,
+                      x_pred=zer(1), y_pred=zer(1), theta_pred=zer(1), ref_traj=ref_traj, num_step=float(num_step), hat_pos=hat, dual_var=dual)
+            I = ms.Interp(ns)
+            I.run(seg(312, 348))                     # = the call at :258
+            I.run(seg(254, 257) + "\n" + seg(259, 273))
+            return float(ns["cost"])
+        E = np.eye(N)
+        f0 = f_primal(np.zeros(N)); fp = np.array([f_primal(E[i]) for i in range(N)]); fm = np.array([f_primal(-E[i]) for i in range(N)])
+        H = np.zeros((N, N))
+        for i in range(N):
+            H[i, i] = fp[i] + fm[i] - 2 * f0
+            for j in range(i + 1, N):
+                H[i, j] = H[j, i] = f_primal(E[i] + E[j]) - fp[i] - fp[j] + f0
+        us = rng.normal(0, 0.3, (3, N))
+        other = 3 - veh
+        rec["primal"] = dict(veh=veh, num_step=num_step, hat=hat[(veh, other)].tolist(), dual=dual[(veh, other)].tolist(), f0=f0,
+                             q=((fp - fm) / 2).tolist(), H=H.tolist(), u=us.tolist(), cost=[f_primal(u) for u in us])
+        # --- cost_function_edge: the convex statement
+        k = np.arange(N + 1)
+        pos_old = np.vstack([xt[v, c] + k * 0.1 * spd[v] * (np.cos, np.sin)[c](xt[v, 2]) for v in (0, 1) for c in (0, 1)]) + rng.normal(0, 0.1, (4, N + 1))
+        dual_e = rng.normal(0, 0.5, (4, N + 1))
+        prev = np.stack((xt[:, 0] + 0.1 * np.array(spd) * np.cos(xt[:, 2]), xt[:, 1] + 0.1 * np.array(spd) * np.sin(xt[:, 2])), 1)   # :54-55 (no rounding in MATLAB)
+
+        def f_edge(hu):
+            ns = dict(param=P, xt=xt.copy(), u=np.asarray(hu, dtype=float), hat_u=np.asarray(hu, dtype=float), nargin=6.0, x_pred=zer(2), y_pred=zer(2), theta_pred=zer(2),
+                      edge_pos=zer(4), pos_old=pos_old, dual_var_old=dual_e, prev_pred_pos=prev)
+            I = ms.Interp(ns)
+            I.run(seg(357, 397))                     # = the call at :286 (symbolic branch: linearised about xt(:,3))
+            I.run(seg(287, 302))
+            return float(ns["cost"])
+        hus = np.vstack((np.zeros((1, 2, N)), rng.normal(0, 0.3, (7, 2, N))))
+        rec["edge_cost"] = dict(pos_old=pos_old.tolist(), dual=dual_e.tolist(), prev_pred_pos=prev.tolist(), hat_u=hus.tolist(), cost=[f_edge(h) for h in hus])
+        out.append(rec)
+    return out
+
+
 def mat_(x):
     x = np.asarray(x, dtype=np.float64)
     return x.reshape(1, 1) if x.ndim == 0 else x
@@ -279,6 +365,7 @@ def main():
     out["obca"] = obca_cases(rng)
     out["old_pi_block"] = old_pi_block_cases(np.random.default_rng(77))
     out["matlab_pi_block"] = matlab_pi_block_cases(np.random.default_rng(78))
+    out["matlab_functions"] = matlab_function_cases(np.random.default_rng(79))
     path = os.path.join(HERE, "reference_vectors.json")
     json.dump(out, open(path, "w"))
     print("wrote", path, os.path.getsize(path), "bytes")

@@ -382,3 +382,54 @@ def test_matlab_pi_law_equals_the_m_file_statements(ci):
         assert it["curr_iter"] == curr_iter
         last_hat = [hat[0].copy(), hat[1].copy()]                    # :207 is a COPY in MATLAB (no alias quirk here)
     assert (P["PI"], P["windup"]) in ((1.0, 1.0), (0.0, 1.0), (1.0, 0.0))
+
+
+@pytest.mark.parametrize("ci", range(len(VEC["matlab_functions"])))
+def test_matlab_function_bodies_equal_the_oracle(ci):
+    """dynamic_update_local / dynamic_update_edge (both branches), cost_function_primal and cost_function_edge of
+    matlab_old_files/ADMM_CVX_two_veh_intesection_PI_antiwindup.m (:254-273, :287-302, :312-397), executed from the .m text:
+    the roll-outs, the exact (H, q) of the vehicle cost and the CONVEX edge statement -- literal transcription and the split
+    blocks (H, q, a, c) the kernels iterate on -- as the MATLAB statements evaluate them (hinge active in the close cases)."""
+    from oracle.problem import literal_cost_edge_convex, literal_edge_linear_rollout, edge_qp_blocks, roll_matrix
+    c = VEC["matlab_functions"][ci]
+    P, N = c["param"], c["N"]
+    spd = A_(c["spd"])
+    p = Params(num_ho=N, spd=spd, dt=P["dt"], L=P["L"], dis_thres=P["dis_thres"], beta=P["beta"], Pnorm=P["Pnorm"], Pcost=P["Pcost"], rho=P["rho"])
+    xt = A_(c["xt"])
+    for r in c["local_rollouts"]:
+        v, u = r["veh"] - 1, A_(r["u"])[0]
+        xl, yl, tl = literal_dynamic_update_local(p, xt[v], u, spd[v])
+        xa, ya = affine_rollout(p, xt[v], spd[v], u)
+        want = [A_(a)[0] for a in r["linear"]]
+        for got, w in ((xl, want[0]), (yl, want[1]), (tl, want[2]), (xa, want[0]), (ya, want[1])):
+            assert np.abs(got - w).max() <= 1e-11 * max(1.0, np.abs(w).max())
+        xn, yn, tn = literal_dynamic_update_edge(p, xt[v:v + 1], u[None], spd[v:v + 1])
+        wantn = [A_(a)[0] for a in r["nonlinear"]]
+        assert np.abs(xn[0] - wantn[0]).max() <= 1e-11 and np.abs(yn[0] - wantn[1]).max() <= 1e-11 and np.abs(tn[0] - wantn[2]).max() <= 1e-12
+    ue = A_(c["edge_rollouts"]["u"])
+    xn, yn, tn = literal_dynamic_update_edge(p, xt, ue, spd)
+    assert np.abs(xn - A_(c["edge_rollouts"]["nonlinear"][0])).max() <= 1e-11 and np.abs(yn - A_(c["edge_rollouts"]["nonlinear"][1])).max() <= 1e-11
+    xl, yl = literal_edge_linear_rollout(p, xt, ue, spd)
+    assert np.abs(xl - A_(c["edge_rollouts"]["linear"][0])).max() <= 1e-11 and np.abs(yl - A_(c["edge_rollouts"]["linear"][1])).max() <= 1e-11
+    # vehicle QP
+    q_ = c["primal"]
+    v, s0 = q_["veh"] - 1, q_["num_step"] - 1                         # MATLAB indices are 1-based
+    ref = A_(c["ref_traj"])[2 * v:2 * v + 2, s0:s0 + N + 1]
+    H, q = vehicle_qp(p, xt[v], spd[v], ref[0], ref[1], [A_(q_["hat"])], [A_(q_["dual"])])
+    assert np.abs(H - A_(q_["H"])).max() <= 1e-8 * np.abs(H).max() and np.abs(q - A_(q_["q"])).max() <= 1e-8 * max(1.0, np.abs(q).max())
+    for u, f in zip(A_(q_["u"]), q_["cost"]):
+        assert abs((f - q_["f0"]) - (0.5 * u @ H @ u + q @ u)) <= 1e-9 * max(1.0, abs(f))
+    # convex edge statement
+    e = c["edge_cost"]
+    pos_old, dual, prev, hus = A_(e["pos_old"]), A_(e["dual"]), A_(e["prev_pred_pos"]), A_(e["hat_u"])
+    B = edge_qp_blocks(p, xt, spd, pos_old, dual, prev)
+    M = roll_matrix(N)[1:]
+    model = lambda u: (sum(0.5 * u[r] @ B["H"][r] @ u[r] + B["q"][r] @ u[r] for r in range(2))
+                       + p.beta * np.sum(np.maximum(0.0, B["c"] - B["a"][0] * (M @ u[0]) - B["a"][1] * (M @ u[1]))))
+    active = 0
+    for u, f in zip(hus, e["cost"]):
+        lit = literal_cost_edge_convex(p, u, xt, spd, pos_old, dual, prev)
+        assert abs(lit - f) <= 1e-10 * max(1.0, abs(f))
+        assert abs((f - e["cost"][0]) - (model(u) - model(hus[0]))) <= 1e-9 * max(1.0, abs(f))
+        active += int(np.sum(B["c"] - B["a"][0] * (M @ u[0]) - B["a"][1] * (M @ u[1]) > 0))
+    assert (active > 0) == (ci < 2)                                      # the third case keeps the pair 40 m apart
