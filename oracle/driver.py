@@ -14,7 +14,8 @@ OUTER LOOP PINNED to the reference's own script: tests/golden/reference_main_run
 unmodified (QP solves stood in by oracle/solver.py, tests/golden/run_reference_main.py); run_closed_loop in python_current
 semantics reproduces its histories exactly (tests/test_reference_vectors.py).  The two PI laws are pinned statement by statement:
 pi_old against lines 127-164 of casadi_old_PI_ADMM/main.py exec'd verbatim, pi against the MATLAB script's own text executed by
-tests/golden/_matlab_subset.py (:6-25,105-124,152-209).  The inner solver's iterates stay unpinned (oracle/problem.py header).
+tests/golden/_matlab_subset.py (:6-25,105-124,152-209) -- and the WHOLE MATLAB script run from its text for its 42 MPC steps
+(tests/golden/run_reference_matlab.py): run_closed_loop in matlab_pi semantics (tight) reproduces its iter_his and trajectories.  The inner solver's iterates stay unpinned (oracle/problem.py header).
 """
 from __future__ import annotations
 

@@ -89,9 +89,46 @@ class Struct(dict):
     pass
 
 
+NOOP_COMMANDS = ("tic", "hold", "refreshdata", "drawnow", "clear", "rng", "fprintf", "plot", "figure", "disp")
+
+
+def parse_functions(src):
+    """`function [o1, o2] = name(a1, a2) ... end` definitions at the end of a script file -> {name: (outs, args, body)}."""
+    out = {}
+    lines = src.split("\n")
+    i = 0
+    while i < len(lines):
+        m = re.match(r"\s*function\s+(?:\[([^\]]*)\]|(\w+))\s*=\s*(\w+)\s*\(([^)]*)\)", lines[i])
+        if not m:
+            i += 1
+            continue
+        outs = [o.strip() for o in (m.group(1) or m.group(2)).split(",")]
+        args = [a.strip() for a in m.group(4).split(",")]
+        depth, j = 1, i + 1
+        while j < len(lines):
+            code = lines[j].split("%")[0]
+            depth += len(re.findall(r"\b(?:if|for|while|function)\b", code))
+            depth -= len(re.findall(r"(?<![\w:(,-])\bend\b(?!\s*[-+)\],])", code)) if not re.search(r"[({].*\bend\b", code) else 0
+            if depth == 0:
+                break
+            j += 1
+        out[m.group(3)] = (outs, args, "\n".join(lines[i + 1:j]))
+        i = j + 1
+    return out
+
+
 class Interp:
-    def __init__(self, ns=None):
+    def __init__(self, ns=None, functions=None, hooks=None):
         self.ns = ns if ns is not None else {}
+        self.functions = functions or {}
+        self.hooks = hooks or {}
+
+    def call_user(self, name, argv, nout):
+        outs, args, body = self.functions[name]
+        local = {a: self.value_copy(v) for a, v in zip(args, argv)}
+        local["nargin"] = float(len(argv))
+        Interp(local, self.functions, self.hooks).run(body)
+        return [local[o] for o in outs[:max(nout, 1)]]
 
     # ------------------------------------------------------------------ driver
     def run(self, src):
@@ -185,6 +222,21 @@ class Interp:
             if execute:
                 raise Break()
             return
+        if kind == "id" and val in self.hooks:     # harness hooks standing in for text that cannot run (cvx_begin ... cvx_end)
+            self.i += 1
+            if execute:
+                self.hooks[val](self.ns)
+            return
+        if kind == "id" and val in NOOP_COMMANDS and val not in self.ns:      # `tic`, `hold on`, `fprintf(...)`, `plot(...)`: to end of line
+            while self.peek()[0] not in ("nl", "eof"):
+                self.i += 1
+            return
+        if kind == "op" and val == "[":
+            save = self.i
+            got = self.try_general_multi(execute)
+            if got:
+                return
+            self.i = save
         if kind == "op" and val == "[":          # [a, b] = find(...)  or an expression statement
             save = self.i
             names = self.try_multi_lhs()
@@ -213,6 +265,64 @@ class Interp:
             return
         self.i = save
         self.expr(execute)
+
+    def try_general_multi(self, execute):
+        """`[lhs1, lhs2, ~] = f(args)` with indexed targets, a user function or find; `[c{:}] = deal(v)`."""
+        start = self.i
+        depth, j = 0, self.i
+        while True:                                  # find the matching ']' and require '=' after it (not '==')
+            k, v = self.t[j]
+            if k in ("nl", "eof"):
+                return False
+            if k == "op" and v in "[({":
+                depth += 1
+            elif k == "op" and v in "])}":
+                depth -= 1
+                if depth == 0:
+                    break
+            j += 1
+        if self.t[j + 1] != ("op", "="):
+            return False
+        self.i += 1
+        targets = []
+        while True:
+            if self.accept("~"):
+                targets.append(None)
+            else:
+                kind, val = self.peek()
+                if kind == "id" and self.t[self.i + 1] == ("op", "{") and self.t[self.i + 2] == ("op", ":"):
+                    self.i += 4                        # name { : }
+                    targets.append(("dealall", val))
+                else:
+                    targets.append(self.try_lhs(execute))
+            if self.accept("]"):
+                break
+            self.expect(",")
+        self.expect("=")
+        fn = self.next()[1]
+        self.expect("(")
+        argv = self.args(")", execute)
+        if not execute:
+            return True
+        if fn == "deal":
+            for t in targets:
+                cell = self.ns[t[1]]
+                n = max(k[0] for k in cell), max(k[1] for k in cell)
+                for a in range(1, n[0] + 1):
+                    for b in range(1, n[1] + 1):
+                        cell[(a, b)] = self.value_copy(argv[0])
+            return True
+        if fn == "find":
+            r, c = np.nonzero(mat(argv[0]).T)
+            vals = [simplify(mat((c + 1).astype(float)).T), simplify(mat((r + 1).astype(float)).T)]
+        elif fn in self.functions:
+            vals = self.call_user(fn, argv, len(targets))
+        else:
+            raise NotImplementedError(f"multi-output call of {fn}")
+        for t, v in zip(targets, vals):
+            if t is not None:
+                self.assign(t, v)
+        return True
 
     def try_multi_lhs(self):
         self.expect("[")
@@ -273,6 +383,15 @@ class Interp:
             self.ns.setdefault(name, Cell())[tuple(int(a) for a in arg)] = value
         else:
             base = mat(self.ns[name]).copy() if name in self.ns else np.zeros((0, 0))
+            if len(arg) == 1:                                  # linear index into a vector: v(k) = scalar
+                k = int(round(arg[0])) - 1
+                flat = base.reshape(-1)
+                if k >= flat.size:
+                    flat = np.concatenate((flat, np.zeros(k + 1 - flat.size)))
+                    base = flat.reshape(1, -1) if base.shape[0] <= 1 else flat.reshape(-1, 1)
+                base.reshape(-1)[k] = float(value)
+                self.ns[name] = base
+                return
             idx = self.index_tuple(base, arg)
             base[idx] = value if is_scalar(value) else mat(value).reshape(base[idx].shape)
             self.ns[name] = base
@@ -313,8 +432,12 @@ class Interp:
         if self.peek() == ("op", ":") and self.range_ok():
             self.i += 1
             b = self.add(ex)
+            step = 1.0
+            if self.peek() == ("op", ":") and self.range_ok():
+                self.i += 1
+                step, b = b, self.add(ex)
             if ex:
-                return mat(np.arange(int(round(a)), int(round(b)) + 1, dtype=float))
+                return mat(np.arange(int(round(a)), int(round(b)) + (1 if step > 0 else -1), int(round(step)), dtype=float))
             return 0.0
         return a
 
@@ -471,6 +594,12 @@ class Interp:
             return (np.zeros if name == "zeros" else np.ones)(shape)
         if name == "length":
             return float(max(mat(arg[0]).shape)) if np.size(arg[0]) else 0.0
+        if name == "linspace":
+            return mat(np.linspace(arg[0], arg[1], int(round(arg[2]))))
+        if name == "size":
+            return mat(np.array(mat(arg[0]).shape, dtype=float))
+        if name in self.functions:
+            return self.call_user(name, arg, 1)[0]
         raise NotImplementedError(f"function {name}")
 
     def postfix(self, ex):
@@ -487,6 +616,8 @@ class Interp:
         elif kind == "id":
             if val == "pi":
                 v = float(np.pi)
+            elif val == "toc" and "toc" not in self.ns:
+                v = 0.0
             elif val == "end" and getattr(self, "end_ctx", None):
                 base, pos, n_args = self.end_ctx[-1]
                 b = mat(base) if base is not None and ex else np.zeros((1, 1))

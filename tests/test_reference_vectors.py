@@ -433,3 +433,69 @@ def test_matlab_function_bodies_equal_the_oracle(ci):
         assert abs((f - e["cost"][0]) - (model(u) - model(hus[0]))) <= 1e-9 * max(1.0, abs(f))
         active += int(np.sum(B["c"] - B["a"][0] * (M @ u[0]) - B["a"][1] * (M @ u[1]) > 0))
     assert (active > 0) == (ci < 2)                                      # the third case keeps the pair 40 m apart
+
+
+# ------------------------------------------------------------------ the reference's MATLAB script, run from its own text
+MRUN = json.load(open(os.path.join(HERE, "golden", "reference_matlab_run.json")))
+MATLAB_PARAMS = dict(beta=1000.0, Pnorm=5.0, rho=3.5, eps_pri=0.1, eps_dual=0.1, num_ho=8)      # ...PI_antiwindup.m:6-25
+MTOL = 2e-4      # the matlab_pi preset keeps the Python script's 4-decimal rounding of the seed points (casadi/main.py:48-49); MATLAB (:56-57) has none
+
+
+def test_matlab_script_run_equals_the_oracle_matlab_pi_closed_loop():
+    """tests/golden/reference_matlab_run.json = matlab_old_files/ADMM_CVX_two_veh_intesection_PI_antiwindup.m executed from its
+    own text for all 42 MPC steps (tests/golden/run_reference_matlab.py; the two CVX blocks solved to optimality by the
+    oracle's solver, two-sided steering rows).  The oracle's driver in matlab_pi semantics with the tight inner tolerance
+    (solver independent) must reproduce it: identical iter_his (incl. the 4-iteration steps), the same number of vehicle and
+    edge solves, trajectories within the seed-rounding tolerance.  This pins the whole OUTER LOOP of the semantics every bench
+    configuration uses to the MATLAB source."""
+    from oracle.driver import Modes, run_closed_loop
+    r = MRUN["two_sided"]
+    p = Params(**MATLAB_PARAMS)
+    out = run_closed_loop(p, Modes.matlab_pi(), InnerSettings.tight(), np.array([[-10, 0, 0], [0, 20, -np.pi / 2]], dtype=float),
+                          p.spd.astype(float), reference_trajectories(p))
+    assert [int(v) for v in out["iter_his"]] == r["iter_his"] and len(r["iter_his"]) == 42 and max(r["iter_his"]) == 4
+    assert sum(len(s["veh_iters"]) for s in out["steps"]) == r["vehicle_solves"] and sum(len(s["edge_iters"]) for s in out["steps"]) == r["edge_solves"]
+    for k in ("x_vec", "theta_vec", "u_vec"):
+        assert np.abs(np.array(out[k]) - A_(r[k])).max() <= MTOL, k
+    assert r["max_cost_mismatch"] < 1e-10                    # the quadratic / hinge model IS the MATLAB cost functions (checked in every solve)
+    g = json.load(open(os.path.join(HERE, "golden", "c1_matlab_pi_default.json")))        # the osqp_default golden the GPU tests use
+    assert g["iter_his"] == r["iter_his"]
+    # the script's own steering rows are one-sided (veh_u <= pi/6, :95): on this scenario that changes the run -- recorded
+    assert MRUN["as_written_differs"]["max_abs_u"] > 0.1 and MRUN["as_written"]["min_u"] < -np.pi / 6 - 1e-3
+
+
+def test_c_twin_equals_the_matlab_script_run():
+    from oracle import ctwin
+    import pi_admm_b200 as pa
+    from pi_admm_b200.scenarios import ref_window
+    r = MRUN["two_sided"]
+    p = pa.inner_tight(pa.preset("matlab_pi").update(**{k: (int(v) if k == "num_ho" else v) for k, v in MATLAB_PARAMS.items()}))
+    ref = reference_trajectories(Params())
+    xt = np.array([[[-10, 0, 0], [0, 20, -np.pi / 2]]], dtype=np.float64)
+    for step in range(42):
+        o = ctwin.step(p, xt, np.array([[4.0, 8.0]]), ref_window(ref, step, p.num_ho)[None])
+        xt = o["xt_next"].copy()
+        assert int(o["curr_iter"][0]) == r["iter_his"][step], step
+        assert np.abs(xt[0, :, :2].T - A_(r["x_vec"][step])).max() <= MTOL and np.abs(o["u"][0, :, 0] - A_(r["u_vec"][step])).max() <= MTOL
+
+
+@pytest.mark.gpu
+def test_gpu_closed_loop_equals_the_matlab_script_run():
+    """The CUDA closed loop in matlab_pi semantics (tight inner tolerance): piadmm_run_closed_loop, all 42 MPC steps on the
+    device, against the histories of the MATLAB script itself."""
+    from pi_admm_b200.solver import PIADMMSolver
+    from pi_admm_b200.scenarios import c1_initial_state
+    from util import make_params
+    r = MRUN["two_sided"]
+    p = make_params("matlab_pi", "tight")
+    assert p.num_ho == 8 and p.beta == 1000.0 and p.rho == 3.5 and p.Pnorm == 5.0 and p.eps_pri == 0.1
+    ref_traj = reference_trajectories(Params())
+    sol = PIADMMSolver(p, S=1, V=2)
+    sol.setup(c1_initial_state()[None], np.array([[4.0, 8.0]]), np.zeros((1, 2, 2, p.num_ho + 1)))
+    sol.set_reference(ref_traj.reshape(1, 2, 2, -1))
+    h = {k: v.cpu().numpy() for k, v in sol.run_closed_loop(0, 42).items()}
+    sol.close()
+    assert h["iter_his"][:, 0].tolist() == r["iter_his"]
+    assert np.abs(h["x_vec"][:, 0].transpose(0, 2, 1) - A_(r["x_vec"])).max() <= MTOL
+    assert np.abs(h["theta_vec"][:, 0] - A_(r["theta_vec"])).max() <= MTOL
+    assert np.abs(h["u_vec"][:, 0] - A_(r["u_vec"])).max() <= MTOL
