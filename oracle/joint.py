@@ -21,8 +21,10 @@ Deviations, stated:
 Solver: the OSQP-style ADMM of oracle/solver.py on the split  z_i = [A u_i ; one copy of (M u_i)_{1..N} per incident pair],
 so the linear system stays block diagonal (one N x N matrix per vehicle, K_i = H_i + sigma I + rho (A'A + deg_i M'M)) and
 the pairs couple only through the closed-form 2-D prox of their hinge.  One rho for the whole problem, termination and
-adaptive rho on the residuals of the whole problem.  PARITY UNPINNED (oracle/problem.py header); pinned against scipy
-SLSQP on the slack form and, for V = 2, against solve_edge_pair with beta doubled (tests/test_joint_edge.py).
+adaptive rho on the residuals of the whole problem.  Pinning: the COST (literal_cost_joint, and through it joint_blocks) equals
+the MATLAB function body executed from its text, V = 2 exactly and V = 3, 4 in its as-written form
+(tests/golden/reference_vectors.json key matlab_joint_cost); the MINIMISER is pinned against scipy SLSQP on the slack form
+and, for V = 2, against solve_edge_pair with beta doubled (tests/test_joint_edge.py); fmincon's own iterates stay unpinned.
 """
 from __future__ import annotations
 
@@ -43,14 +45,15 @@ def seeds(p: Params, xt, spd):
                      np.round(xt[:, 1] + p.dt * spd * np.sin(xt[:, 2]), 4)), 1)
 
 
-def joint_blocks(p: Params, xt, spd, pos_old, dual, pairs, rho=None):
+def joint_blocks(p: Params, xt, spd, pos_old, dual, pairs, rho=None, prev_pred_pos=None):
     """Per vehicle (H_i, q_i) and per pair (a_i, a_j, c[N]) of the joint problem.
-    pos_old, dual: (V, 2, N+1).  Returns dict(H, q, pairs=[(i, j, ai, aj, c)])."""
+    pos_old, dual: (V, 2, N+1).  ``prev_pred_pos`` (V, 2) replaces the rounded seed points when given.
+    Returns dict(H, q, pairs=[(i, j, ai, aj, c)])."""
     rho = p.rho if rho is None else rho
     V, N = len(spd), pos_old.shape[2] - 1
     M = roll_matrix(N)
     kk = np.arange(N + 1)
-    sd = seeds(p, xt, spd)
+    sd = seeds(p, xt, spd) if prev_pred_pos is None else np.asarray(prev_pred_pos, dtype=np.float64)
     H, q, sn, cs, g, xb, yb = [], [], [], [], [], [], []
     for i in range(V):
         s, c = np.sin(xt[i, 2]), np.cos(xt[i, 2])
@@ -72,20 +75,35 @@ def joint_blocks(p: Params, xt, spd, pos_old, dual, pairs, rho=None):
     return dict(H=H, q=q, pairs=out)
 
 
-def literal_cost_joint(p: Params, hat_u, xt, spd, pos_old, dual, pairs, rho=None):
-    """The cost of ...static.m:250-291 evaluated literally (ordered pairs, linearised roll-out): pins joint_blocks."""
+def literal_cost_joint(p: Params, hat_u, xt, spd, pos_old, dual, pairs, rho=None, prev_pred_pos=None, as_written=False):
+    """The cost of ...static.m:250-291 evaluated literally (ordered pairs, linearised roll-out): pins joint_blocks.
+    ``prev_pred_pos`` (V, 2) replaces the rounded seed points when given.  ``as_written=True`` keeps the script's
+    linear indices ``last_dis(1)``, ``last_dis(2)`` (:270) -- column-major over the (V-1) x 2 difference matrix, so for
+    V > 2 every other vehicle of row i gets the direction (dx to the first other, dx to the second other); ``pairs`` is
+    then ignored (the script sums over every ordered pair).  Both forms are checked against the MATLAB text executed by
+    tests/golden/_matlab_subset.py (tests/test_reference_vectors.py)."""
     from .problem import affine_rollout
     rho = p.rho if rho is None else rho
     V = len(spd)
-    sd = seeds(p, xt, spd)
+    sd = seeds(p, xt, spd) if prev_pred_pos is None else np.asarray(prev_pred_pos, dtype=np.float64)
     P = [np.stack(affine_rollout(p, xt[i], spd[i], hat_u[i])) for i in range(V)]
     cost = 0.0
-    for (a, b) in pairs:
-        for (i, j) in ((a, b), (b, a)):
-            ell = sd[j] - sd[i]
-            cur = P[j][:, 1:] - P[i][:, 1:]
-            dis = 2.0 * (ell[0] * cur[0] + ell[1] * cur[1]) - np.sum(ell ** 2)
-            cost += p.beta * np.sum(np.maximum(0.0, p.dis_thres ** 2 - dis))
+    if as_written:
+        for i in range(V):
+            others = [j for j in range(V) if j != i]
+            flat = (sd[others] - sd[i]).ravel(order="F")
+            ell = flat[:2]
+            for j in others:
+                cur = P[j][:, 1:] - P[i][:, 1:]
+                dis = 2.0 * (ell[0] * cur[0] + ell[1] * cur[1]) - np.sum(ell ** 2)
+                cost += p.beta * np.sum(np.maximum(0.0, p.dis_thres ** 2 - dis))
+    else:
+        for (a, b) in pairs:
+            for (i, j) in ((a, b), (b, a)):
+                ell = sd[j] - sd[i]
+                cur = P[j][:, 1:] - P[i][:, 1:]
+                dis = 2.0 * (ell[0] * cur[0] + ell[1] * cur[1]) - np.sum(ell ** 2)
+                cost += p.beta * np.sum(np.maximum(0.0, p.dis_thres ** 2 - dis))
     cost += p.Pcost * np.sum(np.asarray(hat_u) ** 2)
     for i in range(V):
         cost += rho / 2.0 * np.sum((pos_old[i] - P[i] + dual[i]) ** 2)

@@ -392,6 +392,12 @@ class Interp:
                 base.reshape(-1)[k] = float(value)
                 self.ns[name] = base
                 return
+            if isinstance(value, np.ndarray) and value.size == 0:          # x(i, :) = []  /  x(:, j) = []: deletion
+                if isinstance(arg[1], str):
+                    self.ns[name] = np.delete(base, int(round(arg[0])) - 1, axis=0)
+                else:
+                    self.ns[name] = np.delete(base, int(round(arg[1])) - 1, axis=1)
+                return
             idx = self.index_tuple(base, arg)
             base[idx] = value if is_scalar(value) else mat(value).reshape(base[idx].shape)
             self.ns[name] = base
@@ -594,6 +600,8 @@ class Interp:
             return (np.zeros if name == "zeros" else np.ones)(shape)
         if name == "length":
             return float(max(mat(arg[0]).shape)) if np.size(arg[0]) else 0.0
+        if name == "repmat":
+            return np.tile(mat(arg[0]), (int(arg[1]), int(arg[2])))
         if name == "linspace":
             return mat(np.linspace(arg[0], arg[1], int(round(arg[2]))))
         if name == "size":

@@ -339,6 +339,46 @@ def matlab_function_cases(rng):
     return out
 
 
+def matlab_joint_cost_cases(rng):
+    """the body of cost_function_edge of matlab_old_files/ADMM_fmincon_multi_veh_intesection_static.m
+    (:262-289 -- ONE edge problem over all num_veh vehicles), executed from the .m text on the LINEARISED roll-out of
+    ...PI_antiwindup.m:357-397 (nargin == 6 branch, which loops over param.num_veh) -- i.e. the convex statement of the joint
+    problem that oracle/joint.py and k_joint solve.  V = 2, 3, 4.  For V > 2 the script's `last_dis(1)`, `last_dis(2)` (:270)
+    are LINEAR indices into a (V-1) x 2 matrix; the value recorded is what the text computes (oracle: as_written=True)."""
+    import _matlab_subset as ms
+    L = open(os.path.join(REF, "matlab_old_files", "ADMM_fmincon_multi_veh_intesection_static.m")).read().split("\n")
+    Lp = open(os.path.join(REF, "matlab_old_files", "ADMM_CVX_two_veh_intesection_PI_antiwindup.m")).read().split("\n")
+    assert L[249].startswith("function cost = cost_function_edge") and L[261].strip() == "num_veh = param.num_veh;"
+    assert L[288].strip().startswith("cost = cost_punish + cost_u + cost_AL") and "last_dis(1)" in L[269]
+    assert Lp[356].strip().startswith("if nargin  == 3") and Lp[396].strip() == "end"
+    body, roll = "\n".join(L[261:289]), "\n".join(Lp[356:397])
+    base = np.array([[-3.0, 0.2, 0.1], [0.4, 5.0, -1.45], [3.0, 1.0, 2.9], [-0.5, -4.0, 1.5]])
+    speeds = np.array([4.0, 8.0, 6.0, 5.0])
+    out = []
+    for V, N in ((2, 5), (2, 15), (3, 8), (4, 6)):
+        P = ms.Struct(dt=0.1, L=1.0, num_ho=float(N), num_veh=float(V), dis_thres=2.0, spd=speeds[:V].reshape(V, 1), beta=1000.0,
+                      Pnorm=5.0, Pcost=1.0, rho=2.0)
+        xt = base[:V] + rng.normal(0, 0.2, (V, 3))
+        spd = speeds[:V]
+        prev = np.stack((xt[:, 0] + 0.1 * spd * np.cos(xt[:, 2]), xt[:, 1] + 0.1 * spd * np.sin(xt[:, 2])), 1)
+        k = np.arange(N + 1)
+        pos_old = np.vstack([xt[v, c] + k * 0.1 * spd[v] * (np.cos, np.sin)[c](xt[v, 2]) for v in range(V) for c in (0, 1)]) + rng.normal(0, 0.1, (2 * V, N + 1))
+        dual = rng.normal(0, 0.5, (2 * V, N + 1))
+        hus = np.vstack((np.zeros((1, V, N)), rng.normal(0, 0.3, (5, V, N))))
+        costs = []
+        for hu in hus:
+            z = lambda: np.zeros((V, N + 1))
+            ns = dict(param=P, xt=xt.copy(), u=hu, hat_u=hu, nargin=6.0, x_pred=z(), y_pred=z(), theta_pred=z(),
+                      pos_old=pos_old, dual_var_old=dual, prev_pred_pos=prev)
+            I = ms.Interp(ns)
+            I.run(roll)
+            I.run(body)
+            costs.append(float(ns["cost"]))
+        out.append(dict(V=V, N=N, spd=spd.tolist(), xt=xt.tolist(), prev_pred_pos=prev.tolist(), pos_old=pos_old.tolist(), dual=dual.tolist(),
+                        hat_u=hus.tolist(), cost=costs))
+    return out
+
+
 def mat_(x):
     x = np.asarray(x, dtype=np.float64)
     return x.reshape(1, 1) if x.ndim == 0 else x
@@ -366,6 +406,7 @@ def main():
     out["old_pi_block"] = old_pi_block_cases(np.random.default_rng(77))
     out["matlab_pi_block"] = matlab_pi_block_cases(np.random.default_rng(78))
     out["matlab_functions"] = matlab_function_cases(np.random.default_rng(79))
+    out["matlab_joint_cost"] = matlab_joint_cost_cases(np.random.default_rng(80))
     path = os.path.join(HERE, "reference_vectors.json")
     json.dump(out, open(path, "w"))
     print("wrote", path, os.path.getsize(path), "bytes")

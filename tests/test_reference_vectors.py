@@ -435,6 +435,40 @@ def test_matlab_function_bodies_equal_the_oracle(ci):
     assert (active > 0) == (ci < 2)                                      # the third case keeps the pair 40 m apart
 
 
+@pytest.mark.parametrize("ci", range(len(VEC["matlab_joint_cost"])))
+def test_matlab_joint_edge_cost_equals_the_joint_oracle(ci):
+    """cost_function_edge of matlab_old_files/ADMM_fmincon_multi_veh_intesection_static.m (:262-289),
+    executed from its text on the linearised roll-out of ...PI_antiwindup.m:357-397 -- the convex joint statement.
+    V = 2: the oracle's literal cost AND the split blocks (H_i, q_i, a, c; hinge 2 beta per pair) k_joint iterates on equal
+    the MATLAB values.  V > 2: the MATLAB value equals the oracle's `as_written` form (linear indices `last_dis(1)`,
+    `last_dis(2)`, :270), and differs from the per-pair form the product implements whenever the hinge is active."""
+    from oracle import joint as oj
+    from oracle.problem import roll_matrix
+    c = VEC["matlab_joint_cost"][ci]
+    V, N = c["V"], c["N"]
+    spd, xt, prev = A_(c["spd"]), A_(c["xt"]), A_(c["prev_pred_pos"])
+    p = Params(num_ho=N, beta=1000.0, rho=2.0, Pcost=1.0, dis_thres=2.0, dt=0.1, L=1.0)
+    pos, dual = A_(c["pos_old"]).reshape(V, 2, N + 1), A_(c["dual"]).reshape(V, 2, N + 1)
+    pairs = oj.all_pairs(V)
+    hus, want = A_(c["hat_u"]), c["cost"]
+    per_pair = []
+    for u, f in zip(hus, want):
+        assert abs(oj.literal_cost_joint(p, u, xt, spd, pos, dual, pairs, prev_pred_pos=prev, as_written=True) - f) <= 1e-10 * max(1.0, abs(f))
+        per_pair.append(oj.literal_cost_joint(p, u, xt, spd, pos, dual, pairs, prev_pred_pos=prev))
+    if V > 2:
+        assert max(abs(a - b) for a, b in zip(per_pair, want)) > 1.0          # the linear-index defect is visible
+        return
+    assert max(abs(a - b) / max(1.0, abs(b)) for a, b in zip(per_pair, want)) <= 1e-10
+    # the blocks the kernel iterates on, on the MATLAB seed points: the same quadratic + hinge
+    B = oj.joint_blocks(p, xt, spd, pos, dual, pairs, prev_pred_pos=prev)
+    M = roll_matrix(N)[1:]
+    (i, j, ai, aj, cc), = B["pairs"]
+    model = lambda u: (sum(0.5 * u[r] @ B["H"][r] @ u[r] + B["q"][r] @ u[r] for r in range(2))
+                       + 2.0 * p.beta * np.sum(np.maximum(0.0, cc - ai * (M @ u[i]) - aj * (M @ u[j]))))
+    for u, f in zip(hus, want):
+        assert abs((f - want[0]) - (model(u) - model(hus[0]))) <= 1e-9 * max(1.0, abs(f))
+
+
 # ------------------------------------------------------------------ the reference's MATLAB script, run from its own text
 MRUN = json.load(open(os.path.join(HERE, "golden", "reference_matlab_run.json")))
 MATLAB_PARAMS = dict(beta=1000.0, Pnorm=5.0, rho=3.5, eps_pri=0.1, eps_dual=0.1, num_ho=8)      # ...PI_antiwindup.m:6-25
