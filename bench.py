@@ -43,6 +43,20 @@ COUPLED = {
     # name: (vehicles, horizon N, neighbour slots D)   -- BASELINE configs 3 and 5, SURVEY.md 8(d)
     "c3": (64, 30, 8),
     "c5": (4096, 30, 8),
+    # capacity scenes (not BASELINE configs): the config-5 generator with 4x / 8x the vehicles, for the multi-GPU strong-scaling
+    # measurement of a scene whose first x phase is many waves of one GPU (profiles/r2_scaling.md)
+    "c5x4": (16384, 30, 8),
+    "c5x8": (32768, 30, 8),
+}
+C5_GRID = {"c5": (64, 32), "c5x4": (128, 64), "c5x8": (128, 128)}      # (lanes per direction, vehicles per lane)
+COUPLED_WHAT = {
+    "c3": "c3: ONE 64-vehicle 4-arm intersection (BASELINE config 3)",
+    "c5": "c5: ONE 4096-vehicle coupled grid scene, 64+64 lanes x 32 vehicles (BASELINE config 5; generator with the "
+          "rejection rule clear=3 m: no pair starts inside dis_thres)",
+    "c5x4": "c5x4: ONE 16384-vehicle coupled grid scene, 128+128 lanes x 64 vehicles (the config-5 generator at 4x the vehicles; "
+            "a capacity scene, not a BASELINE config)",
+    "c5x8": "c5x8: ONE 32768-vehicle coupled grid scene, 128+128 lanes x 128 vehicles (the config-5 generator at 8x the vehicles; "
+            "a capacity scene, not a BASELINE config)",
 }
 
 
@@ -62,12 +76,14 @@ def coupled_params(N):
 def coupled_scene(name):
     from pi_admm_b200.scenarios import c3_intersection, c5_grid
     V, N, D = COUPLED[name]
-    return (c3_intersection(V=V, N=N) if name == "c3" else c5_grid(N=N)), V, N, D
+    if name == "c3":
+        return c3_intersection(V=V, N=N), V, N, D
+    lanes, per_lane = C5_GRID[name]
+    return c5_grid(lanes=lanes, per_lane=per_lane, N=N), V, N, D
 
 
 def coupled_config(name, V, N, D, world):
-    what = {"c3": "c3: ONE 64-vehicle 4-arm intersection (BASELINE config 3)",
-            "c5": "c5: ONE 4096-vehicle coupled grid scene, 64+64 lanes x 32 vehicles (BASELINE config 5)"}[name]
+    what = COUPLED_WHAT[name]
     return {"workload": f"{what}, horizon N={N}, one coupled MPC step to PI-ADMM convergence (outer cap 100)",
             "vehicles": V, "horizon": N, "neighbour_slots": D,
             "semantics": "dual=pi (per-edge integrators, clamp +-30 + back-calculation; kI=1.5, kP=0), AL over activated edges, "
@@ -573,9 +589,7 @@ def measure_coupled(name, args, rank, local_rank, world, with_cpu=True, inner="o
             stored = json.load(open(os.path.join(ROOT, "profiles", "r2_coupled_checksums.json"))).get(name)
         except Exception:
             pass
-        what = {"c3": "c3: ONE 64-vehicle 4-arm intersection (BASELINE config 3)",
-                "c5": "c5: ONE 4096-vehicle coupled grid scene, 64+64 lanes x 32 vehicles (BASELINE config 5; generator with the "
-                      "rejection rule clear=3 m: no pair starts inside dis_thres)"}[name]
+        what = COUPLED_WHAT[name]
         rec = {"workload": f"{what}, horizon N={N}, one coupled MPC step to PI-ADMM convergence (outer cap {p.iter_num})",
                "vehicles": V, "horizon": N, "neighbour_slots": D, "n_gpus": world, "scaling": "strong",
                "semantics": "dual=pi (per-edge integrators, clamp +-30 + back-calculation; kI=1.5, kP=0: profiles/r2_convergence.md), "

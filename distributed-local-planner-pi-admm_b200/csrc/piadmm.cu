@@ -71,6 +71,7 @@ __device__ __forceinline__ void load_W(const DevCtx& c, double* Wsm) { load_tabs
 
 #include "piadmm_coop.cuh"
 #include "piadmm_joint.cuh"
+static_assert(PIADMM_CHUNK == CTA_THREADS, "chunk totals are per CTA_THREADS vehicles");
 
 // ------------------------------------------------------------------ phase kernels (generic V)
 __global__ void k_begin_step(const __grid_constant__ DevCtx c) {
@@ -212,6 +213,7 @@ __global__ void k_hits_warp(const __grid_constant__ DevCtx c) {
 // ---- candidate pairs of the MPC step (piadmm_detect.cuh): reach discs, then the symmetric candidate bit matrix
 __global__ void k_disc(const __grid_constant__ DevCtx c) {
   const long a = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a == 0 && c.cand_over) *c.cand_over = 0;              // set by the list kernel that follows
   if (a < (long)c.S * c.V) dev_disc_vehicle(c, a);
   const int words = (c.V + 31) / 32;
   const long wb = a >> 5;                                  // warp -> (scenario, block of 32 vehicles)
@@ -228,6 +230,10 @@ __global__ void k_cand(const __grid_constant__ DevCtx c) {
 __global__ void k_cand_list(const __grid_constant__ DevCtx c) {
   const long a = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (a < (long)c.S * c.V) dev_cand_list_vehicle(c, (int)(a / c.V), (int)(a % c.V), threadIdx.x & 31);
+}
+__global__ void k_cand_direct(const __grid_constant__ DevCtx c) {
+  const long a = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (a < (long)c.S * c.V) dev_cand_direct_vehicle(c, (int)(a / c.V), (int)(a % c.V), threadIdx.x & 31);
 }
 
 // per vehicle (one warp): exact test of the candidates (EXACT) / walk of the hit matrix, neighbour slots in ascending j
@@ -768,11 +774,12 @@ struct piadmm_handle {
   int64_t launches;
   // persistent cooperative kernel for generic V (piadmm_coop.cuh); PIADMM_COOP=0 selects the phase kernels
   bool use_coop;
+  bool cand_matrix;           // PIADMM_CAND=matrix: candidate bit matrix + list kernel instead of k_cand_direct (A/B)
   int coop_grid_max;          // co-resident CTAs of k_coop<lpq>
   int* d_nactive;             // [2]
   long long* d_trace;         // piadmm_debug_coop_trace
   // vehicle-sharded multi-GPU exchange (piadmm_peer_export / piadmm_peer_connect)
-  char* xblk;                 // library-owned exchange block of THIS rank: pos | u | edge_res | flags | epoch | aborted
+  char* xblk;                 // library-owned exchange block of THIS rank: pos | u | edge_res | stamp | need | flags | epoch | aborted
   bool peer_on;
   void* peer_base[PIADMM_MAX_PEERS];   // the peers' exchange blocks as mapped into this process (cudaIpcOpenMemHandle)
   PeerCtx peer;
@@ -780,14 +787,15 @@ struct piadmm_handle {
 };
 
 // layout of an exchange block (S == 1): doubles first, then the barrier words
-struct XblkLayout { size_t pos, u, er, stamp, flags, epoch, aborted, bytes; };
+struct XblkLayout { size_t pos, u, er, stamp, need, flags, epoch, aborted, bytes; };
 static XblkLayout xblk_layout(int V, int N, int E) {
   XblkLayout L;
   L.pos = 0;
   L.u = L.pos + sizeof(double) * (size_t)V * 2 * (N + 1);
   L.er = L.u + sizeof(double) * (size_t)V * N;
   L.stamp = L.er + sizeof(double) * (size_t)E * 4;
-  L.flags = L.stamp + ((sizeof(int32_t) * (size_t)V + 15) / 16) * 16;
+  L.need = L.stamp + ((sizeof(int32_t) * (size_t)V + 15) / 16) * 16;
+  L.flags = L.need + ((sizeof(int32_t) * (size_t)V + 15) / 16) * 16;
   L.epoch = L.flags + sizeof(unsigned long long) * PIADMM_MAX_PEERS;
   L.aborted = L.epoch + sizeof(unsigned long long);
   L.bytes = L.aborted + 16;
@@ -868,6 +876,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   piadmm_handle* h = new piadmm_handle();
   memset(&h->c, 0, sizeof h->c);
   h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_count2 = nullptr; h->h_count2 = nullptr; h->ev_count[0] = h->ev_count[1] = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false; h->gexec = nullptr; h->d_ref = nullptr; h->ref_T = 0; h->h_step = nullptr; h->d_step = nullptr;
+  { const char* e_ = getenv("PIADMM_CAND"); h->cand_matrix = e_ && strcmp(e_, "matrix") == 0; }
   h->use_coop = true; h->coop_grid_max = 0; h->d_nactive = nullptr; h->d_trace = nullptr; h->xblk = nullptr; h->peer_on = false;
   memset(&h->peer, 0, sizeof h->peer);
   for (int i = 0; i < PIADMM_MAX_PEERS; i++) h->peer_base[i] = nullptr;
@@ -949,6 +958,13 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMalloc(&h->c.cand_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "cand_cnt");
   if ((ce = cudaMemset(h->c.cand_cnt, 0xff, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "cand_cnt");
   if ((ce = cudaMalloc(&h->c.veh_stamp, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_stamp");
+  if ((ce = cudaMalloc(&h->c.veh_need, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_need");
+  if ((ce = cudaMemset(h->c.veh_need, 0, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_need");
+  {
+    const size_t nct = (size_t)S * ((V + CTA_THREADS - 1) / CTA_THREADS);
+    if ((ce = cudaMalloc(&h->c.chunk_tot, sizeof(int32_t) * nct)) != cudaSuccess) return fail(ce, "chunk_tot");
+    if ((ce = cudaMemset(h->c.chunk_tot, 0, sizeof(int32_t) * nct)) != cudaSuccess) return fail(ce, "chunk_tot");
+  }
   if ((ce = cudaMalloc(&h->c.blockbox, sizeof(double) * 4 * (size_t)S * words)) != cudaSuccess) return fail(ce, "blockbox");
   if ((ce = cudaMalloc(&h->c.veh_dirty, (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_dirty");
   if ((ce = cudaMemset(h->c.veh_dirty, 1, (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_dirty");
@@ -1035,6 +1051,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     h->use_coop = coop_ok && h->coop_grid_max > 0 && !(ce_ && strcmp(ce_, "0") == 0);
     if ((ce = cudaMalloc(&h->d_nactive, 4 * sizeof(int))) != cudaSuccess) return fail(ce, "nactive");
     if ((ce = cudaMemset(h->d_nactive, 0, 4 * sizeof(int))) != cudaSuccess) return fail(ce, "nactive");
+    h->c.cand_over = h->d_nactive + 3;
   }
   *out = h;
   return PIADMM_OK;
@@ -1043,7 +1060,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.edge_u); cudaFree(h->c.cand_list); cudaFree(h->c.cand_cnt); cudaFree(h->c.veh_stamp); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.edge_u); cudaFree(h->c.cand_list); cudaFree(h->c.cand_cnt); cudaFree(h->c.veh_stamp); cudaFree(h->c.veh_need); cudaFree(h->c.chunk_tot); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
   cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
   for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
   piadmm_peer_disconnect(h);
@@ -1103,6 +1120,11 @@ static int build_candidates(piadmm_handle* h, cudaStream_t st) {
   const long nt_disc = std::max(agents, (long)h->c.S * ((h->c.V + 31) / 32) * 32);
   k_disc<<<(unsigned)((nt_disc + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
+  if (h->c.D <= 32 && !h->cand_matrix) {       // lists straight from the discs (PIADMM_CAND=matrix: the two-kernel form, A/B)
+    k_cand_direct<<<(unsigned)((agents * 32 + 127) / 128), 128, 0, st>>>(h->c);
+    LAUNCHED();
+    return PIADMM_OK;
+  }
   k_cand<<<(unsigned)((wtot + 255) / 256), 256, 0, st>>>(h->c);
   LAUNCHED();
   k_cand_list<<<(unsigned)((agents * 32 + 255) / 256), 256, 0, st>>>(h->c);
@@ -1396,6 +1418,7 @@ int piadmm_peer_connect(piadmm_handle* h, int rank, int world, const void* handl
     pc.pos[r] = (double*)(base + L.pos); pc.u[r] = (double*)(base + L.u); pc.edge_res[r] = (double*)(base + L.er);
     pc.flags[r] = (unsigned long long*)(base + L.flags);
     pc.stamp[r] = (int32_t*)(base + L.stamp);
+    pc.need[r] = (int32_t*)(base + L.need);
   }
   pc.epoch = (unsigned long long*)(h->xblk + L.epoch);
   pc.aborted = (int*)(h->xblk + L.aborted);
@@ -1426,7 +1449,9 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
   CoopArgs a;
   memset(&a, 0, sizeof a);
   a.n_active = h->d_nactive;
+  { const char* e_ = getenv("PIADMM_SLOT_GATE"); a.slot_gate = !(e_ && strcmp(e_, "0") == 0); }
   c.any_overflow = h->d_nactive + 2;
+  c.use_chunk_tot = 1;
   a.trace = h->d_trace;
   if (h->d_trace) CK(cudaMemsetAsync(h->d_trace, 0, sizeof(long long), st));
   if (h->peer_on) {
@@ -1435,6 +1460,7 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
     a.peer.user_pos = h->c.b.pos; a.peer.user_u = h->c.b.u;
     c.b.pos = (double*)(h->xblk + L.pos); c.b.u = (double*)(h->xblk + L.u); c.edge_res = (double*)(h->xblk + L.er);
     c.veh_stamp = (int32_t*)(h->xblk + L.stamp);
+    c.veh_need = (int32_t*)(h->xblk + L.need);
     c.stamps_global = 1;
   }
   const long agents = (long)c.S * c.V, pairs = (long)c.S * c.E;

@@ -31,6 +31,7 @@ struct PeerCtx {
   double* u[PIADMM_MAX_PEERS];                   // [V,N]
   double* edge_res[PIADMM_MAX_PEERS];            // [E,4]
   int32_t* stamp[PIADMM_MAX_PEERS];              // [V] veh_stamp
+  int32_t* need[PIADMM_MAX_PEERS];               // [V] veh_need
   unsigned long long* flags[PIADMM_MAX_PEERS];   // [PIADMM_MAX_PEERS] barrier epochs signalled TO rank r, indexed by sender
   unsigned long long* epoch;                     // local: barrier epoch reached by the previous launch
   int* aborted;                                  // local: a barrier timed out (later barriers do not spin)
@@ -42,6 +43,7 @@ struct PeerCtx {
 struct CoopArgs {
   long long* trace;                              // debug (piadmm_debug_coop_trace): globaltimer at every phase boundary, or NULL
   int* n_active;                                 // [2] scenarios still active after the decide phase (double buffered)
+  int slot_gate;                                 // skip the slot phase of vehicles without a recomputed pair (default 1)
   PeerCtx peer;
 };
 
@@ -193,6 +195,9 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
   const long agents = (long)c.S * c.V;
   unsigned long long epoch = sharded ? *pc.epoch : 0ull;
   const bool memo = dev_memo_on(c);
+  // slot phase only for the vehicles with something to re-test (veh_need): needs every vehicle's candidates as a LIST
+  // (the candidate kernels ran before this launch; PIADMM_SLOT_GATE=0 switches it off, A/B)
+  const bool gate = ca.slot_gate && c.D <= 32 && *reinterpret_cast<volatile int*>(c.cand_over) == 0;
   load_tabs<LPQ>(c, Wsm, 0, PIADMM_NTAB);                // (ends with a CTA barrier)
   COOP_TRACE();                                          // [0] start
 
@@ -219,9 +224,11 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
     }
     for (size_t t = tid; t < (size_t)agents; t += nth) {
       c.veh_dirty[t] = 1;
+      c.up_cnt[t] = 0;
       const int i = (int)(t % c.V);         // stamps of other ranks' vehicles are theirs to write (iteration 0 solves everybody)
       if (i >= c.own_lo && i < c.own_hi) c.veh_stamp[t] = -1;
     }
+    for (size_t t = tid; t < (size_t)c.S * ((c.V + CTA_THREADS - 1) / CTA_THREADS); t += nth) c.chunk_tot[t] = 0;
     if (tid == 0) *c.any_overflow = 0;
   }
   // (the candidate matrix of this MPC step was built by k_disc + k_cand right before this launch: an O(V^2/32) pass that
@@ -233,7 +240,9 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
 #pragma unroll 1
   for (int it = 0; it < c.I; it++) {
     if (tid == 0) ca.n_active[it & 1] = 0;
-    for (size_t t = tid; t < (size_t)c.S; t += nth) c.dist_bad[t] = 0;      // set again in the count phase
+    // (dist_bad[s] is NOT cleared here: the MATLAB :202 flag of a vehicle is over its ALLOCATED slots, which only grow
+    //  during a step, so the flag of the scenario is monotone within the step -- and a vehicle whose slot phase is
+    //  skipped below would not set it again)
     if (it > 0) {
       // last_iter_hat_pos = hat_pos_old (casadi/main.py:180) for the scenarios that go on, spread over the grid; the
       // edge list of the previous iteration is intact until the edges phase, last_hat is next read in the z phase
@@ -262,6 +271,16 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
         if (!__any_sync(PIADMM_FULL, valid)) continue;
         dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr);
         if (valid && w.k == 0) { c.veh_dirty[a] = 0; c.veh_stamp[a] = it; }
+        if (gate && valid && it > 0) {      // this vehicle and its candidates have a pair to re-test (iteration 0 tests all)
+          const int cnt = c.cand_cnt[a];
+          const size_t sv = (size_t)s * c.V;
+          for (int q = w.k; q <= cnt; q += LPQ) {
+            const int j = q < cnt ? c.cand_list[a * PIADMM_CAND_CAP + q] : i;
+            c.veh_need[sv + j] = it;
+            if (sharded)
+              for (int r = 0; r < pc.world; r++) if (r != pc.rank) pc.need[r][sv + j] = it;
+          }
+        }
         if (sharded && valid) {       // fused exchange: this lane's point / control of the row, to every peer
           const size_t po = ((size_t)s * c.V + i) * 2 * np1, uo = ((size_t)s * c.V + i) * N;
           const int k = w.k;
@@ -280,10 +299,33 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
     coop_cross_barrier(grid, c, pc, epoch, stored);
     COOP_TRACE();
     // ---- collision edges, casadi/main.py:110-118
-    for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {
-      const int s = (int)(a / c.V), i = (int)(a % c.V);
-      if (!c.b.done[s]) dev_slots<true>(c, s, i, w.lane, it);
-      else if (w.lane == 0) c.up_cnt[a] = 0;
+    if (!gate || it == 0) {
+      for (long a = (long)(tid >> 5); a < agents; a += (long)(nth >> 5)) {
+        const int s = (int)(a / c.V), i = (int)(a % c.V);
+        if (!c.b.done[s]) dev_slots<true>(c, s, i, w.lane, it);
+        else if (w.lane == 0) dev_set_up_cnt(c, s, i, 0);
+      }
+    } else {
+      // only the vehicles marked by this iteration's x phase (here or on a peer) have a pair with a recomputed
+      // trajectory; the slot tables, hit flags and edge counts of all the others are those of the previous iteration.
+      // Lane l looks at vehicle  warp + l * n_warps  (neighbours in the spatial order go to different warps), then the
+      // warp serves the marked ones one after the other.
+      const long n_warps = (long)(nth >> 5), wid = (long)(tid >> 5);
+      for (long a0 = wid; a0 < agents; a0 += n_warps * 32) {
+        const long al = a0 + (long)w.lane * n_warps;
+        bool todo = false;
+        if (al < agents) {
+          const int s = (int)(al / c.V);
+          if (c.b.done[s]) dev_set_up_cnt(c, s, (int)(al % c.V), 0);
+          else todo = c.veh_need[al] == it;
+        }
+        unsigned m = __ballot_sync(PIADMM_FULL, todo);
+        while (m) {
+          const long a = a0 + (long)(__ffs(m) - 1) * n_warps;
+          m &= m - 1;
+          dev_slots<true>(c, (int)(a / c.V), (int)(a % c.V), w.lane, it);
+        }
+      }
     }
     grid.sync();
     COOP_TRACE();
@@ -304,8 +346,9 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
         const int s = (int)(item / chunks), ch = (int)(item % chunks);
         if (c.b.done[s]) continue;                                    // CTA uniform
         const int32_t* uc = c.up_cnt + (size_t)s * c.V;
+        const int32_t* ct = c.chunk_tot + (size_t)s * chunks;
         int part = 0;
-        for (int v = threadIdx.x; v < ch * CTA_THREADS; v += CTA_THREADS) part += uc[v];
+        for (int q = threadIdx.x; q < ch; q += CTA_THREADS) part += ct[q];          // chunk totals kept by dev_set_up_cnt
         int base, total;
         cta_excl_scan(part, ish, &base);                              // base = edges of all lower vehicles
         const int i = ch * CTA_THREADS + threadIdx.x;

@@ -35,21 +35,28 @@ __host__ __device__ inline double reach_radius(const piadmm_params& p, int N, do
 __device__ __forceinline__ void dev_begin_slots(const DevCtx& c, size_t warp_id, size_t n_warps, int lane) {
   const int per = 2 * (c.N + 1);
   const size_t n_slots = (size_t)c.S * c.V * c.D;
-  for (size_t t = warp_id; t < n_slots; t += n_warps) {
-    const bool used = c.slots_dirty || c.b.nbr[t] >= 0;
-    __syncwarp();
-    if (used) {
-      for (int el = lane; el < per; el += 32) {
-        const size_t o = t * per + el;
-        c.b.hat[o] = 0.0; c.b.dual[o] = 0.0; c.b.integ[o] = 0.0; c.b.diff[o] = 0.0; c.b.last_hat[o] = 0.0;
-      }
-    }
-    if (lane == 0) {
+  // a LANE per slot for the table entries and the "was it in use" test (one coalesced read of nbr per 32 slots: with a
+  // warp per slot the 32768 slots of config 5 were 28 dependent rounds per warp, ~25 us of the step), then the warp
+  // zeroes the slots that were in use one after the other
+  for (size_t base = warp_id * 32; base < n_slots; base += n_warps * 32) {
+    const size_t t = base + lane;
+    bool used = false;
+    if (t < n_slots) {
+      used = c.slots_dirty || c.b.nbr[t] >= 0;
       const int d = (int)(t % c.D), i = (int)((t / c.D) % c.V);
       int j = -1;
       if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;      // AL over every j != i: slots pre-assigned, ascending
       c.b.nbr[t] = j;
       c.slot_hit[t] = 0;
+    }
+    unsigned m = __ballot_sync(PIADMM_FULL, used);
+    while (m) {
+      const size_t tt = base + (__ffs(m) - 1);
+      m &= m - 1;
+      for (int el = lane; el < per; el += 32) {
+        const size_t o = tt * per + el;
+        c.b.hat[o] = 0.0; c.b.dual[o] = 0.0; c.b.integ[o] = 0.0; c.b.diff[o] = 0.0; c.b.last_hat[o] = 0.0;
+      }
     }
   }
 }
@@ -203,7 +210,78 @@ __device__ __forceinline__ void dev_cand_list_vehicle(const DevCtx& c, int s, in
     }
     n += __shfl_sync(PIADMM_FULL, inc, 31);
   }
-  if (lane == 0) c.cand_cnt[a] = n <= PIADMM_CAND_CAP ? n : -1;
+  if (lane == 0) {
+    c.cand_cnt[a] = n <= PIADMM_CAND_CAP ? n : -1;
+    if (n > PIADMM_CAND_CAP && c.cand_over) *c.cand_over = 1;
+  }
+}
+
+// Candidate list of vehicle (s,i) STRAIGHT from the reach discs, one warp, ascending j -- the same tests as dev_cand_word
+// (block box first, then the 32 discs of a block that passes, one per lane), so the list is the one dev_cand_list_vehicle
+// reads off the bit matrix, without writing and re-reading the V x V/32 words of it (2 MB at config 5, 134 MB at 32768
+// vehicles) and one launch less per MPC step.  A vehicle with more than PIADMM_CAND_CAP candidates gets cand_cnt = -1 AND
+// its bit row (second pass), which is what the slot phase walks for it; the rows of the other vehicles are not written.
+// Only for D <= 32 (with more slots the slot phase walks the bit rows of every vehicle: k_cand + k_cand_list).
+__device__ __forceinline__ void dev_cand_direct_vehicle(const DevCtx& c, int s, int i, int lane) {
+  const int words = (c.V + 31) / 32;
+  const size_t a = (size_t)s * c.V + i;
+  const double4* disc = reinterpret_cast<const double4*>(c.bbox) + (size_t)s * c.V;
+  const double4* box = reinterpret_cast<const double4*>(c.blockbox) + (size_t)s * words;
+  const double4 di = disc[i];
+  const double thr_d = c.p.thr_squared ? c.p.dis_thres : sqrt(c.p.dis_thres);
+  const double rb = (di.z + thr_d) * (1.0 + 1e-9);
+  const bool all = c.p.always_edge != 0;
+  int32_t* lst = c.cand_list + a * PIADMM_CAND_CAP;
+  uint32_t* row = c.cand + a * words;
+  for (int pass = 0; pass < 2; pass++) {            // 0: the list; 1 (only after an overflow): the bit row
+    int n = 0;
+    if (pass == 1) {
+      for (int w = lane; w < words; w += 32) row[w] = 0u;
+      __syncwarp();
+    }
+    for (int w0 = 0; w0 < words; w0 += 32) {
+      const int jb = w0 + lane;
+      bool pass_box = false;
+      if (jb < words) {
+        pass_box = all;
+        if (!all) {
+          const double4 bb = box[jb];
+          const double gx = fmax(0.0, fmax(bb.x - di.x, di.x - bb.y)), gy = fmax(0.0, fmax(bb.z - di.y, di.y - bb.w));
+          pass_box = !(gx * gx + gy * gy >= rb * rb);
+        }
+      }
+      unsigned pm = __ballot_sync(PIADMM_FULL, pass_box);
+      while (pm) {
+        const int jbb = w0 + __ffs(pm) - 1;
+        pm &= pm - 1;
+        const int j = jbb * 32 + lane;
+        bool near = false;
+        if (j < c.V && j != i) {
+          near = all;
+          if (!all) {
+            const double4 dj = disc[j];
+            const double dx = di.x - dj.x, dy = di.y - dj.y, rr = (di.z + dj.z + thr_d) * (1.0 + 1e-9);
+            near = dx * dx + dy * dy < rr * rr;
+          }
+        }
+        const unsigned m = __ballot_sync(PIADMM_FULL, near);
+        if (pass == 0) {
+          const int at = n + __popc(m & ((1u << lane) - 1u));
+          if (near && at < PIADMM_CAND_CAP) lst[at] = j;
+          n += __popc(m);
+        } else if (lane == 0) {
+          row[jbb] = m;
+        }
+      }
+    }
+    if (pass == 0) {
+      if (lane == 0) {
+        c.cand_cnt[a] = n <= PIADMM_CAND_CAP ? n : -1;
+        if (n > PIADMM_CAND_CAP && c.cand_over) *c.cand_over = 1;
+      }
+      if (n <= PIADMM_CAND_CAP) break;
+    }
+  }
 }
 
 // Slot phase over the candidate LIST (the default): lane q holds candidate q.  Only pairs with a recomputed trajectory
@@ -278,6 +356,20 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
   if (lane == 0 && overflow) { atomicOr(c.b.status + s, PIADMM_ST_SLOT_OVERFLOW); if (c.any_overflow) *c.any_overflow = 1; }
 }
 
+// up_cnt[a] = cnt (one thread).  In the cooperative kernel the per-chunk sums follow by the difference, so its edge phase
+// adds up V / CTA_THREADS chunk totals instead of up to V counts per chunk (and a vehicle whose slot phase is skipped keeps
+// both its count and its share of the total)
+#define PIADMM_CHUNK 64                    // == CTA_THREADS (piadmm.cu; static_assert there)
+__device__ __forceinline__ void dev_set_up_cnt(const DevCtx& c, int s, int i, int cnt) {
+  const size_t a = (size_t)s * c.V + i;
+  if (!c.use_chunk_tot) { c.up_cnt[a] = cnt; return; }
+  const int old = c.up_cnt[a];
+  if (old != cnt) {
+    c.up_cnt[a] = cnt;
+    atomicAdd(c.chunk_tot + (size_t)s * ((c.V + PIADMM_CHUNK - 1) / PIADMM_CHUNK) + i / PIADMM_CHUNK, cnt - old);
+  }
+}
+
 // slot phase of one vehicle: candidate list, bit row of `cand` when the list overflowed, or the `hits` matrix
 // ... and, from the vehicle's OWN table only: the number of its up-edges (i, j > i) of this outer iteration and its MATLAB
 // :202 distance flag.  Without a table overflow anywhere in the step this IS the number of valid edges (a partner
@@ -314,7 +406,7 @@ __device__ __forceinline__ void dev_slots(const DevCtx& c, int s, int i, int lan
   }
   bad = __any_sync(PIADMM_FULL, bad);
   if (lane == 0) {
-    c.up_cnt[a] = cnt;
+    dev_set_up_cnt(c, s, i, cnt);
     if (bad) c.dist_bad[s] = 1;
   }
 }
@@ -348,7 +440,7 @@ __device__ __forceinline__ void dev_count_vehicle_warp(const DevCtx& c, int s, i
   }
   bad = __any_sync(PIADMM_FULL, bad);
   if (lane == 0) {
-    c.up_cnt[a] = cnt;
+    dev_set_up_cnt(c, s, i, cnt);
     if (bad) c.dist_bad[s] = 1;
   }
 }

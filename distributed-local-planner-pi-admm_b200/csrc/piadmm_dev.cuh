@@ -51,6 +51,11 @@ struct DevCtx {
   int z_solve_only;                        // edge problems only: no z-hat roll-out, no dual / PI update (the caller's script does both)
   int stamps_global;                       // veh_stamp is exchanged between the ranks (peer mode): no rank-local guessing
   int* any_overflow;                       // cooperative kernel: a neighbour table overflowed in this step (or NULL)
+  int* cand_over;                          // some vehicle has more than PIADMM_CAND_CAP candidates in this MPC step (set by the list kernels)
+  int32_t* veh_need;                       // [S,V] cooperative kernel: outer iteration (>= 1) in which the vehicle or one of its candidates
+                                           // was re-solved, i.e. its slot phase has something to re-test (stale values only cost work)
+  int32_t* chunk_tot;                      // [S,ceil(V/CTA_THREADS)] cooperative kernel: sum of up_cnt over each chunk of vehicles
+  int use_chunk_tot;                       // up_cnt is kept together with chunk_tot (set in the cooperative launch only)
   int32_t* veh_stamp;                      // [S,V] outer iteration in which the vehicle's trajectory was last recomputed
   double* blockbox;                        // [S,ceil(V/32),4] bounding box of the reach discs of 32 consecutive vehicles
   uint8_t* veh_dirty;                      // [S,V] x_memo: the vehicle's QP changed since its last solve in this step

@@ -66,7 +66,7 @@ def test_c5_grid_4096_vehicles_matches_twin():
     _assert_edges(got, ref)
     assert_same(got, ref, what="c5")
     assert converged(ref, p) and converged(got, p)
-    assert got["_launches"] == 4                         # candidate build (k_disc, k_cand, k_cand_list) + ONE cooperative launch for the whole outer loop
+    assert got["_launches"] == 3                         # candidate build (k_disc, k_cand_direct) + ONE cooperative launch for the whole outer loop
 
 
 @pytest.mark.parametrize("detect", ["cand", "matrix_warp", "matrix_thread"])
@@ -84,7 +84,7 @@ def test_midsize_grid_every_detection_path(monkeypatch, detect, coop):
     _assert_edges(got, ref)
     assert_same(got, ref, what=f"grid640 {detect} coop={coop}")
     if detect == "cand" and coop == "1":
-        assert got["_launches"] == 4
+        assert got["_launches"] == 3
 
 
 @pytest.mark.parametrize("V,N,D,r0,gap", [(64, 30, 8, 12.0, 6.0), (32, 15, 8, 8.0, 4.0), (12, 20, 4, 12.0, 6.0)])
@@ -94,7 +94,7 @@ def test_cooperative_kernel_equals_phase_kernels_bit_for_bit(monkeypatch, V, N, 
     a = _run(p, xt, spd, refwin, D)
     monkeypatch.setenv("PIADMM_COOP", "0")
     b = _run(p, xt, spd, refwin, D)
-    assert a["_launches"] == 4 and b["_launches"] > 5
+    assert a["_launches"] == 3 and b["_launches"] > 5
     for k in ("u", "pos", "hat", "dual", "integ", "diff", "err_rk", "err_sk", "n_outer", "curr_iter", "nbr", "edge_n",
               "veh_inner", "edge_inner", "status", "xt_next", "edge_ij", "edge_slot"):
         assert np.array_equal(a[k], b[k]), k
@@ -139,9 +139,46 @@ def test_cooperative_kernel_ragged_batch(monkeypatch):
     xt, spd, refwin = _ragged_scene(5, 15, seeds=(3, 4, 5), far=1)
     ref = ctwin.step(p, xt, spd, refwin, D=4)
     got = _run(p, xt, spd, refwin, 4)
-    assert got["_launches"] == 4
+    assert got["_launches"] == 3
     _assert_edges(got, ref)
     assert_same(got, ref, what="coop ragged")
+
+
+ALL_KEYS = ("u", "pos", "hat", "dual", "integ", "diff", "err_rk", "err_sk", "n_outer", "curr_iter", "nbr", "edge_n", "veh_inner",
+            "edge_inner", "status", "xt_next", "edge_ij", "edge_slot", "n_veh_solves", "n_edge_solves")
+
+
+@pytest.mark.parametrize("scene", ["grid640", "dense96", "ragged", "c3"])
+def test_slot_gate_and_direct_candidate_lists_are_exact(monkeypatch, scene):
+    """The cooperative kernel's slot phase only serves the vehicles marked by the x phase (veh_need), its edge phase adds
+    chunk totals, and the candidate lists come straight from the reach discs (k_cand_direct): bit for bit what the
+    un-gated slot phase (PIADMM_SLOT_GATE=0) on lists read off the candidate bit matrix (PIADMM_CAND=matrix) gives -- on a
+    scene with several outer iterations, one with list overflow (gate off by itself), a ragged batch with a scenario that
+    finishes early, and BASELINE config 3 (stop test with active edges, MATLAB :202 distance flag in the decision)."""
+    if scene == "grid640":
+        xt, spd, refwin = c5_grid(lanes=10, per_lane=32, N=30, seed=11, clear=0.0)
+        p, D = bench.coupled_params(30).update(iter_num=8), 8
+    elif scene == "dense96":
+        xt, spd, refwin = c3_intersection(V=96, N=30, r0=10.0, gap=1.5)
+        p, D = bench.coupled_params(30).update(iter_num=3), 8
+    elif scene == "ragged":
+        from test_gpu_parity import _ragged_scene, _generic_params
+        p, D = _generic_params(15), 4
+        xt, spd, refwin = _ragged_scene(5, 15, seeds=(3, 4, 5), far=1)
+    else:
+        xt, spd, refwin = c3_intersection(V=64, N=30, r0=12.0, gap=6.0)          # BASELINE config 3: 7 outer iterations
+        p, D = bench.coupled_params(30), 8
+    a = _run(p, xt, spd, refwin, D)
+    monkeypatch.setenv("PIADMM_SLOT_GATE", "0")
+    b = _run(p, xt, spd, refwin, D)
+    monkeypatch.setenv("PIADMM_CAND", "matrix")
+    c = _run(p, xt, spd, refwin, D)
+    assert a["_launches"] == 3 and b["_launches"] == 3 and c["_launches"] == 4
+    assert int(a["n_outer"].max()) >= 2
+    for k in ALL_KEYS:
+        assert np.array_equal(a[k], b[k]), ("gate", k)
+        assert np.array_equal(a[k], c[k]), ("direct lists", k)
+    assert_same(a, ctwin.step(p, xt, spd, refwin, D=D, nthreads=_threads()), what=f"gate {scene}")
 
 
 @pytest.mark.parametrize("coop", ["1", "0"])
