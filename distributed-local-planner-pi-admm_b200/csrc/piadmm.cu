@@ -779,7 +779,7 @@ struct piadmm_handle {
   int* d_nactive;             // [2]
   long long* d_trace;         // piadmm_debug_coop_trace
   // vehicle-sharded multi-GPU exchange (piadmm_peer_export / piadmm_peer_connect)
-  char* xblk;                 // library-owned exchange block of THIS rank: pos | u | edge_res | stamp | need | flags | epoch | aborted
+  char* xblk;                 // library-owned exchange block of THIS rank: pos | u | edge_res | tbox | stamp | need | flags | epoch | aborted
   bool peer_on;
   void* peer_base[PIADMM_MAX_PEERS];   // the peers' exchange blocks as mapped into this process (cudaIpcOpenMemHandle)
   PeerCtx peer;
@@ -787,13 +787,14 @@ struct piadmm_handle {
 };
 
 // layout of an exchange block (S == 1): doubles first, then the barrier words
-struct XblkLayout { size_t pos, u, er, stamp, need, flags, epoch, aborted, bytes; };
+struct XblkLayout { size_t pos, u, er, tbox, stamp, need, flags, epoch, aborted, bytes; };
 static XblkLayout xblk_layout(int V, int N, int E) {
   XblkLayout L;
   L.pos = 0;
   L.u = L.pos + sizeof(double) * (size_t)V * 2 * (N + 1);
   L.er = L.u + sizeof(double) * (size_t)V * N;
-  L.stamp = L.er + sizeof(double) * (size_t)E * 4;
+  L.tbox = ((L.er + sizeof(double) * (size_t)E * 4 + 31) / 32) * 32;        // double4 accesses
+  L.stamp = L.tbox + sizeof(double) * (size_t)V * 4;
   L.need = L.stamp + ((sizeof(int32_t) * (size_t)V + 15) / 16) * 16;
   L.flags = L.need + ((sizeof(int32_t) * (size_t)V + 15) / 16) * 16;
   L.epoch = L.flags + sizeof(unsigned long long) * PIADMM_MAX_PEERS;
@@ -958,6 +959,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   if ((ce = cudaMalloc(&h->c.cand_cnt, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "cand_cnt");
   if ((ce = cudaMemset(h->c.cand_cnt, 0xff, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "cand_cnt");
   if ((ce = cudaMalloc(&h->c.veh_stamp, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_stamp");
+  if ((ce = cudaMalloc(&h->c.tbox, sizeof(double) * 4 * (size_t)S * V)) != cudaSuccess) return fail(ce, "tbox");
   if ((ce = cudaMalloc(&h->c.veh_need, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_need");
   if ((ce = cudaMemset(h->c.veh_need, 0, sizeof(int32_t) * (size_t)S * V)) != cudaSuccess) return fail(ce, "veh_need");
   {
@@ -1060,7 +1062,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
 void piadmm_destroy(piadmm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.edge_u); cudaFree(h->c.cand_list); cudaFree(h->c.cand_cnt); cudaFree(h->c.veh_stamp); cudaFree(h->c.veh_need); cudaFree(h->c.chunk_tot); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
+  cudaFree(h->d_W); cudaFree(h->c.edge_res); cudaFree(h->c.rho_new); cudaFree(h->c.hits); cudaFree(h->c.cand); cudaFree(h->c.slot_hit); cudaFree(h->c.veh_dirty); cudaFree(h->c.blockbox); cudaFree(h->c.edge_u); cudaFree(h->c.cand_list); cudaFree(h->c.cand_cnt); cudaFree(h->c.veh_stamp); cudaFree(h->c.veh_need); cudaFree(h->c.chunk_tot); cudaFree(h->c.tbox); cudaFree(h->c.up_cnt); cudaFree(h->c.bbox); cudaFree(h->c.dist_bad); cudaFree(h->c.kcache);
   cudaFree(h->d_count); cudaFree(h->d_count2); if (h->h_count2) cudaFreeHost(h->h_count2);
   for (int i = 0; i < 2; i++) if (h->ev_count[i]) cudaEventDestroy(h->ev_count[i]);
   piadmm_peer_disconnect(h);
@@ -1419,6 +1421,7 @@ int piadmm_peer_connect(piadmm_handle* h, int rank, int world, const void* handl
     pc.flags[r] = (unsigned long long*)(base + L.flags);
     pc.stamp[r] = (int32_t*)(base + L.stamp);
     pc.need[r] = (int32_t*)(base + L.need);
+    pc.tbox[r] = (double*)(base + L.tbox);
   }
   pc.epoch = (unsigned long long*)(h->xblk + L.epoch);
   pc.aborted = (int*)(h->xblk + L.aborted);
@@ -1452,6 +1455,7 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
   { const char* e_ = getenv("PIADMM_SLOT_GATE"); a.slot_gate = !(e_ && strcmp(e_, "0") == 0); }
   c.any_overflow = h->d_nactive + 2;
   c.use_chunk_tot = 1;
+  { const char* e_ = getenv("PIADMM_TBOX"); c.use_tbox = !(e_ && strcmp(e_, "0") == 0); }
   a.trace = h->d_trace;
   if (h->d_trace) CK(cudaMemsetAsync(h->d_trace, 0, sizeof(long long), st));
   if (h->peer_on) {
@@ -1461,6 +1465,7 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
     c.b.pos = (double*)(h->xblk + L.pos); c.b.u = (double*)(h->xblk + L.u); c.edge_res = (double*)(h->xblk + L.er);
     c.veh_stamp = (int32_t*)(h->xblk + L.stamp);
     c.veh_need = (int32_t*)(h->xblk + L.need);
+    c.tbox = (double*)(h->xblk + L.tbox);
     c.stamps_global = 1;
   }
   const long agents = (long)c.S * c.V, pairs = (long)c.S * c.E;

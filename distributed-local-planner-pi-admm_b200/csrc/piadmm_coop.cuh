@@ -32,6 +32,7 @@ struct PeerCtx {
   double* edge_res[PIADMM_MAX_PEERS];            // [E,4]
   int32_t* stamp[PIADMM_MAX_PEERS];              // [V] veh_stamp
   int32_t* need[PIADMM_MAX_PEERS];               // [V] veh_need
+  double* tbox[PIADMM_MAX_PEERS];                // [V,4] trajectory boxes
   unsigned long long* flags[PIADMM_MAX_PEERS];   // [PIADMM_MAX_PEERS] barrier epochs signalled TO rank r, indexed by sender
   unsigned long long* epoch;                     // local: barrier epoch reached by the previous launch
   int* aborted;                                  // local: a barrier timed out (later barriers do not spin)
@@ -269,8 +270,24 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
         if (valid && memo) valid = c.veh_dirty[a] != 0;             // unchanged QP: u / pos_old (here and on the peers) stay
         if (!__syncthreads_or(valid)) continue;
         if (!__any_sync(PIADMM_FULL, valid)) continue;
-        dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr);
+        double px, py, uk;
+        dev_x_update<LPQ, false>(c, s, i, valid, w.k, w.lane, w.half, Wsm, gbuf[w.group_in_cta], xch, nullptr, &px, &py, &uk);
         if (valid && w.k == 0) { c.veh_dirty[a] = 0; c.veh_stamp[a] = it; }
+        {   // bounding box of the new pos_old row (all lanes shuffle; only a solved vehicle stores)
+          const bool pt = valid && w.k <= N;
+          double x0 = pt ? px : 1e300, x1 = pt ? px : -1e300, y0 = pt ? py : 1e300, y1 = pt ? py : -1e300;
+#pragma unroll
+          for (int o = LPQ / 2; o >= 1; o >>= 1) {
+            x0 = fmin(x0, __shfl_xor_sync(PIADMM_FULL, x0, o)); x1 = fmax(x1, __shfl_xor_sync(PIADMM_FULL, x1, o));
+            y0 = fmin(y0, __shfl_xor_sync(PIADMM_FULL, y0, o)); y1 = fmax(y1, __shfl_xor_sync(PIADMM_FULL, y1, o));
+          }
+          if (valid && w.k == 0) {
+            const double4 bx = make_double4(x0, x1, y0, y1);
+            reinterpret_cast<double4*>(c.tbox)[a] = bx;
+            if (sharded)
+              for (int r = 0; r < pc.world; r++) if (r != pc.rank) reinterpret_cast<double4*>(pc.tbox[r])[a] = bx;
+          }
+        }
         if (gate && valid && it > 0) {      // this vehicle and its candidates have a pair to re-test (iteration 0 tests all)
           const int cnt = c.cand_cnt[a];
           const size_t sv = (size_t)s * c.V;
@@ -284,8 +301,6 @@ __global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __gri
         if (sharded && valid) {       // fused exchange: this lane's point / control of the row, to every peer
           const size_t po = ((size_t)s * c.V + i) * 2 * np1, uo = ((size_t)s * c.V + i) * N;
           const int k = w.k;
-          const double px = k <= N ? c.b.pos[po + k] : 0.0, py = k <= N ? c.b.pos[po + np1 + k] : 0.0;
-          const double uk = k < N ? c.b.u[uo + k] : 0.0;
           for (int r = 0; r < pc.world; r++) {
             if (r == pc.rank) continue;
             if (k <= N) { pc.pos[r][po + k] = px; pc.pos[r][po + np1 + k] = py; }

@@ -35,9 +35,30 @@ __host__ __device__ inline double reach_radius(const piadmm_params& p, int N, do
 __device__ __forceinline__ void dev_begin_slots(const DevCtx& c, size_t warp_id, size_t n_warps, int lane) {
   const int per = 2 * (c.N + 1);
   const size_t n_slots = (size_t)c.S * c.V * c.D;
-  // a LANE per slot for the table entries and the "was it in use" test (one coalesced read of nbr per 32 slots: with a
-  // warp per slot the 32768 slots of config 5 were 28 dependent rounds per warp, ~25 us of the step), then the warp
-  // zeroes the slots that were in use one after the other
+  if (n_slots <= 4 * n_warps) {
+    // few slots per warp (dense small scenes, config 3: most slots are in use): a WARP per slot
+    for (size_t t = warp_id; t < n_slots; t += n_warps) {
+      const bool used = c.slots_dirty || c.b.nbr[t] >= 0;
+      __syncwarp();
+      if (used) {
+        for (int el = lane; el < per; el += 32) {
+          const size_t o = t * per + el;
+          c.b.hat[o] = 0.0; c.b.dual[o] = 0.0; c.b.integ[o] = 0.0; c.b.diff[o] = 0.0; c.b.last_hat[o] = 0.0;
+        }
+      }
+      if (lane == 0) {
+        const int d = (int)(t % c.D), i = (int)((t / c.D) % c.V);
+        int j = -1;
+        if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;      // AL over every j != i: slots pre-assigned, ascending
+        c.b.nbr[t] = j;
+        c.slot_hit[t] = 0;
+      }
+    }
+    return;
+  }
+  // large scenes (config 5: 32768 slots, a few hundred in use): a LANE per slot for the table entries and the "was it in
+  // use" test -- one coalesced read of nbr per 32 slots instead of 28 dependent rounds per warp (~25 us of the step) --
+  // then the warp zeroes the slots that were in use one after the other
   for (size_t base = warp_id * 32; base < n_slots; base += n_warps * 32) {
     const size_t t = base + lane;
     bool used = false;
@@ -45,7 +66,7 @@ __device__ __forceinline__ void dev_begin_slots(const DevCtx& c, size_t warp_id,
       used = c.slots_dirty || c.b.nbr[t] >= 0;
       const int d = (int)(t % c.D), i = (int)((t / c.D) % c.V);
       int j = -1;
-      if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;      // AL over every j != i: slots pre-assigned, ascending
+      if (c.p.al_all && d < c.V - 1) j = d < i ? d : d + 1;
       c.b.nbr[t] = j;
       c.slot_hit[t] = 0;
     }
@@ -301,6 +322,10 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
   const bool sg = c.stamps_global != 0;
   const bool moved_i = c.veh_stamp[a] == it || (!sg && (i < c.own_lo || i >= c.own_hi));
   int nbv = lane < c.D ? nb[lane] : -2;                      // the slot table in registers, lane = slot (D <= 32)
+  // a point pair closer than sqrt(thr) needs both coordinate gaps of the boxes below it (margin: one rounding of the gap)
+  const double box_d = sqrt(thr) * (1.0 + 1e-9) + 1e-12;
+  double4 bi = make_double4(0.0, 0.0, 0.0, 0.0);
+  if (test && c.use_tbox) bi = reinterpret_cast<const double4*>(c.tbox)[a];
   double xi = 0.0, yi = 0.0;
   bool have_pos = false, overflow = false;
   for (int base = 0; base < cnt; base += 32) {
@@ -311,9 +336,19 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
     const unsigned mask = __ballot_sync(PIADMM_FULL, need);
     if (!mask) continue;
     unsigned hits = test ? 0u : mask;
-    if (test) {                         // exact tests, eight pairs in flight (16 independent loads per lane)
+    unsigned tmask = mask;                                    // pairs that get the exact test
+    if (test && c.use_tbox) {           // the two trajectory boxes first: a lane per candidate, 32 B instead of 2(N+1) points
+      bool close = false;
+      if (need) {
+        const double4 bj = reinterpret_cast<const double4*>(c.tbox)[sv + j];
+        const double gx = fmax(bj.x - bi.y, bi.x - bj.y), gy = fmax(bj.z - bi.w, bi.z - bj.w);   // gaps (negative: overlap)
+        close = gx < box_d && gy < box_d;
+      }
+      tmask = __ballot_sync(PIADMM_FULL, close);
+    }
+    if (test && tmask) {                // exact tests, eight pairs in flight (16 independent loads per lane)
       if (!have_pos) { const double* pi = c.b.pos + a * 2 * np1; xi = pi[k]; yi = pi[np1 + k]; have_pos = true; }
-      unsigned rem = mask;
+      unsigned rem = tmask;
       while (rem) {
         int src[8], jq[8];
         double xs[8], ys[8];
@@ -360,14 +395,16 @@ __device__ __forceinline__ void dev_slots_vehicle_list(const DevCtx& c, int s, i
 // adds up V / CTA_THREADS chunk totals instead of up to V counts per chunk (and a vehicle whose slot phase is skipped keeps
 // both its count and its share of the total)
 #define PIADMM_CHUNK 64                    // == CTA_THREADS (piadmm.cu; static_assert there)
-__device__ __forceinline__ void dev_set_up_cnt(const DevCtx& c, int s, int i, int cnt) {
+__device__ __forceinline__ void dev_set_up_cnt(const DevCtx& c, int s, int i, int cnt, int old) {     // old = up_cnt[a], read before
   const size_t a = (size_t)s * c.V + i;
   if (!c.use_chunk_tot) { c.up_cnt[a] = cnt; return; }
-  const int old = c.up_cnt[a];
   if (old != cnt) {
     c.up_cnt[a] = cnt;
     atomicAdd(c.chunk_tot + (size_t)s * ((c.V + PIADMM_CHUNK - 1) / PIADMM_CHUNK) + i / PIADMM_CHUNK, cnt - old);
   }
+}
+__device__ __forceinline__ void dev_set_up_cnt(const DevCtx& c, int s, int i, int cnt) {
+  dev_set_up_cnt(c, s, i, cnt, c.use_chunk_tot ? c.up_cnt[(size_t)s * c.V + i] : 0);
 }
 
 // slot phase of one vehicle: candidate list, bit row of `cand` when the list overflowed, or the `hits` matrix
@@ -376,6 +413,7 @@ __device__ __forceinline__ void dev_set_up_cnt(const DevCtx& c, int s, int i, in
 // that collides holds the mirror slot); with one, the count phase (dev_count_vehicle_warp) redoes it with the far side.
 template <bool EXACT>
 __device__ __forceinline__ void dev_slots(const DevCtx& c, int s, int i, int lane, int it) {
+  const int old_cnt = c.use_chunk_tot ? c.up_cnt[(size_t)s * c.V + i] : 0;      // (early: its latency hides behind the tests)
   if (EXACT && c.D <= 32 && c.cand_cnt[(size_t)s * c.V + i] >= 0) dev_slots_vehicle_list(c, s, i, lane, it);
   else dev_slots_vehicle<EXACT>(c, s, i, lane);
   __syncwarp();
@@ -406,7 +444,7 @@ __device__ __forceinline__ void dev_slots(const DevCtx& c, int s, int i, int lan
   }
   bad = __any_sync(PIADMM_FULL, bad);
   if (lane == 0) {
-    dev_set_up_cnt(c, s, i, cnt);
+    dev_set_up_cnt(c, s, i, cnt, old_cnt);
     if (bad) c.dist_bad[s] = 1;
   }
 }

@@ -56,6 +56,10 @@ struct DevCtx {
                                            // was re-solved, i.e. its slot phase has something to re-test (stale values only cost work)
   int32_t* chunk_tot;                      // [S,ceil(V/CTA_THREADS)] cooperative kernel: sum of up_cnt over each chunk of vehicles
   int use_chunk_tot;                       // up_cnt is kept together with chunk_tot (set in the cooperative launch only)
+  double* tbox;                            // [S,V,4] cooperative kernel: (xmin, xmax, ymin, ymax) of the vehicle's pos_old row, written by
+                                           // whoever solves its QP (x phase); the slot phase rejects a candidate on the two boxes
+                                           // (32 B per candidate) before it loads the 2(N+1) points of the exact test
+  int use_tbox;                            // tbox is maintained (set in the cooperative launch only)
   int32_t* veh_stamp;                      // [S,V] outer iteration in which the vehicle's trajectory was last recomputed
   double* blockbox;                        // [S,ceil(V/32),4] bounding box of the reach discs of 32 consecutive vehicles
   uint8_t* veh_dirty;                      // [S,V] x_memo: the vehicle's QP changed since its last solve in this step

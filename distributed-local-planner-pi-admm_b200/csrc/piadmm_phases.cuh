@@ -24,7 +24,8 @@ __device__ __forceinline__ void rollout_nonlinear(const piadmm_params& p, double
 // ---- x-update of agent (s,i): casadi/main.py:81-106 --------------------------------------------
 template <int LPQ, bool KS>
 __device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool valid, int k, int lane,
-                                             int half, const double* Wsm, double* gbuf, double* xch, double* krow) {
+                                             int half, const double* Wsm, double* gbuf, double* xch, double* krow,
+                                             double* px_out = nullptr, double* py_out = nullptr, double* u_out = nullptr) {
   const piadmm_params& p = c.p;
   const int N = c.N;
   double x0 = 0.0, y0 = 0.0, th0 = 0.0, v = 1.0, rho = 1.0;
@@ -92,6 +93,7 @@ __device__ __forceinline__ void dev_x_update(const DevCtx& c, int s, int i, bool
     px = x0 + k * p.dt * v * cs - g * sn * m;
     py = y0 + k * p.dt * v * sn + g * cs * m;
   }
+  if (px_out) { *px_out = px; *py_out = py; *u_out = u; }      // this lane's point k / control k of the new row (k <= N / k < N)
   if (valid) {
     if (k < N) c.b.u[((size_t)s * c.V + i) * N + k] = u;
     if (k <= N) {

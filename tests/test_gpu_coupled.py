@@ -151,8 +151,9 @@ ALL_KEYS = ("u", "pos", "hat", "dual", "integ", "diff", "err_rk", "err_sk", "n_o
 @pytest.mark.parametrize("scene", ["grid640", "dense96", "ragged", "c3"])
 def test_slot_gate_and_direct_candidate_lists_are_exact(monkeypatch, scene):
     """The cooperative kernel's slot phase only serves the vehicles marked by the x phase (veh_need), its edge phase adds
-    chunk totals, and the candidate lists come straight from the reach discs (k_cand_direct): bit for bit what the
-    un-gated slot phase (PIADMM_SLOT_GATE=0) on lists read off the candidate bit matrix (PIADMM_CAND=matrix) gives -- on a
+    chunk totals, rejects candidates on the two trajectory boxes before the exact point test, and the candidate lists
+    come straight from the reach discs (k_cand_direct): bit for bit what the un-gated slot phase (PIADMM_SLOT_GATE=0)
+    without the boxes (PIADMM_TBOX=0) on lists read off the candidate bit matrix (PIADMM_CAND=matrix) gives -- on a
     scene with several outer iterations, one with list overflow (gate off by itself), a ragged batch with a scenario that
     finishes early, and BASELINE config 3 (stop test with active edges, MATLAB :202 distance flag in the decision)."""
     if scene == "grid640":
@@ -172,12 +173,13 @@ def test_slot_gate_and_direct_candidate_lists_are_exact(monkeypatch, scene):
     monkeypatch.setenv("PIADMM_SLOT_GATE", "0")
     b = _run(p, xt, spd, refwin, D)
     monkeypatch.setenv("PIADMM_CAND", "matrix")
+    monkeypatch.setenv("PIADMM_TBOX", "0")
     c = _run(p, xt, spd, refwin, D)
     assert a["_launches"] == 3 and b["_launches"] == 3 and c["_launches"] == 4
     assert int(a["n_outer"].max()) >= 2
     for k in ALL_KEYS:
         assert np.array_equal(a[k], b[k]), ("gate", k)
-        assert np.array_equal(a[k], c[k]), ("direct lists", k)
+        assert np.array_equal(a[k], c[k]), ("direct lists / trajectory boxes", k)
     assert_same(a, ctwin.step(p, xt, spd, refwin, D=D, nthreads=_threads()), what=f"gate {scene}")
 
 
