@@ -16,6 +16,12 @@ echo "ref rc=$?"
 timeout 300 python bench.py --workload c3 --steps 50 --warmup 5 > $O/bench_${TAG}_c3.json 2> $O/bench_${TAG}_c3.err
 timeout 300 python bench.py --workload c5 --steps 50 --warmup 5 > $O/bench_${TAG}_c5.json 2> $O/bench_${TAG}_c5.err
 timeout 300 python bench.py --workload c4n30 --steps 50 --warmup 5 --no-cpu-baseline > $O/bench_${TAG}_n30.json 2> $O/bench_${TAG}_n30.err
+for w in c5x4 c5x8; do     # capacity scenes (16384 / 32768 vehicles), with the CPU-twin comparison
+  timeout 600 python bench.py --workload $w --steps 50 --warmup 5 > $O/bench_${TAG}_${w}.json 2> $O/bench_${TAG}_${w}.err
+  timeout 300 python tools/coop_phases.py $w > $O/coop_phases_${w}_${TAG}.txt 2>&1
+done
+timeout 300 python tools/coop_phases.py c5 > $O/coop_phases_c5_${TAG}.txt 2>&1
+timeout 300 python tools/coop_phases.py c3 > $O/coop_phases_c3_${TAG}.txt 2>&1
 echo "coupled benches done"
 # launch lists (cold-cache, serialised: shares only)
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/launches_$TAG.csv \

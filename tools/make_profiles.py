@@ -74,6 +74,10 @@ def main(tag, R="r2"):
     cp(f"bench_{tag}_n30.json", f"{R}_bench_1gpu_n30.json")
     cp(f"bench_{tag}_c3.json", f"{R}_bench_c3.json")
     cp(f"bench_{tag}_c5.json", f"{R}_bench_c5.json")
+    for w in ("c5x4", "c5x8"):
+        cp(f"bench_{tag}_{w}.json", f"{R}_bench_{w}.json")
+    for w in ("c3", "c5", "c5x4", "c5x8"):
+        cp(f"coop_phases_{w}_{tag}.txt", f"{R}_coop_phases_{w}_1gpu.txt")
     m, tail = ncu_summary(os.path.join(G, f"prof_{tag}.ncu-rep"), os.path.join(P, f"{R}_k_fused_v2_ncu_full.txt"), tag)
     mc, tailc = ncu_summary(os.path.join(G, f"prof_{tag}_coop.ncu-rep"), os.path.join(P, f"{R}_k_coop_ncu_full.txt"), tag + "_coop")
     mj, tailj = (None, "")
@@ -167,7 +171,7 @@ Config-4 step = `k_fused_v2` + `k_order` ({step_us:.1f} us per step under ncu vs
 |---|---|---|---|
 {lines}
 
-Config-5 step = `k_disc` + `k_cand` + `k_cand_list` (candidate build, once per MPC step) + `k_coop` (all outer iterations) (+ `k_plant`): {step5_us:.1f} us per step under ncu:
+Config-5 step = `k_disc` + `k_cand_direct` (candidate lists, once per MPC step) + `k_coop` (all outer iterations) (+ `k_plant`): {step5_us:.1f} us per step under ncu:
 
 | kernel | launches | avg us | share of step |
 |---|---|---|---|
