@@ -69,6 +69,30 @@ def test_c5_grid_4096_vehicles_matches_twin():
     assert got["_launches"] == 3                         # candidate build (k_disc, k_cand_direct) + ONE cooperative launch for the whole outer loop
 
 
+@pytest.mark.parametrize("name,iters,exit_edges", [("c5x4", 4, 0), ("c5x8", 14, None)])
+def test_capacity_scenes_match_twin(name, iters, exit_edges):
+    """The largest scenes the bench measures: the config-5 generator at 16384 and 32768 coupled vehicles (N=30, D=8) on ONE
+    GPU against the C twin on all host threads -- outer iterations, edge lists and slots, solve and inner-iteration counts
+    identical, floats to 1e-6.  (The twin needs ~1 s / ~15 s of 16 cores per step; the GPU ~1 ms / ~4 ms.)"""
+    from pi_admm_b200.parallel import spatial_order
+    (xt, spd, refwin), V, N, D = bench.coupled_scene(name)
+    # the bench's vehicle numbering (spatial strips): the residual sums take the veh1 side of every edge
+    # (casadi/main.py:165-173), so the stop iteration depends on the numbering -- 32768 vehicles pass the stop test after 14
+    # iterations in this order and run into the cap of 100 in the generator's lane-major order
+    pm = spatial_order(xt)
+    xt, spd, refwin = (np.ascontiguousarray(np.broadcast_to(a, (1, V) + np.shape(a)[2:])[:, pm]) for a in (xt, spd, refwin))
+    p = bench.coupled_params(N)
+    ref = ctwin.step(p, xt, spd, refwin, D=D, nthreads=_threads())
+    got = _run(p, xt, spd, refwin, D)
+    assert int(ref["n_outer"][0]) == iters and ref["status"][0] == 0
+    if exit_edges is not None:
+        assert int(ref["edge_n"][0]) == exit_edges
+    _assert_edges(got, ref)
+    assert_same(got, ref, what=name)
+    assert converged(ref, p) and converged(got, p)
+    assert got["_launches"] == 3
+
+
 @pytest.mark.parametrize("detect", ["cand", "matrix_warp", "matrix_thread"])
 @pytest.mark.parametrize("coop", ["1", "0"])
 def test_midsize_grid_every_detection_path(monkeypatch, detect, coop):
