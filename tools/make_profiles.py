@@ -122,7 +122,9 @@ Files of this round
 * `{R}_k_fused_v2_ncu_full.txt`, `{R}_k_coop_ncu_full.txt` — summaries (tools/ncu_summary.py) of one
   `ncu --set full --clock-control none --import-source on -k regex:<kernel> -s 3 -c 1` capture each; `{R}_traffic.json` = DRAM bytes
   of the fused kernel.
-* `{R}_scaling.md` — 1 / 2 / 8 GPU runs (config 4 weak scaling; config 5 vehicle-sharded, peer exchange vs NCCL) and what bounds them;
+* `{R}_bench_c5x4.json`, `{R}_bench_c5x8.json` (+ `_2gpu`, `_8gpu`) — the capacity scenes (16384 / 32768 coupled vehicles,
+  `--workload c5x4|c5x8`), `{R}_bench_c5_{{2,8}}gpu.json` — config 5 as its own line at 2 / 8 ranks (`tools/gpu_call_multi_cap.sh`).
+* `{R}_scaling.md` — 1 / 2 / 8 GPU runs (config 4 weak scaling; config 5 and the capacity scenes vehicle-sharded, peer exchange vs NCCL) and what bounds them;
   `{R}_mgpu_*.jsonl`, `{R}_bench_*gpu*.json` — the lines behind it.  `{R}_coop_phases_*.txt` — phase timelines of the cooperative
   kernel (`piadmm_debug_coop_trace`, tools/coop_phases.py).
 * `{R}_convergence.md`, `{R}_coupled_gain_scan.txt` — convergence of the coupled configurations (VERDICT r1 #2);
