@@ -258,6 +258,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS) + sorted(COUPLED))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-capacity", action="store_true", help="skip the 16384-vehicle capacity scene of the `coupled` records")
     ap.add_argument("--no-coupled", action="store_true", help="skip the coupled (config 5 / 3) records of the default line")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -384,6 +385,10 @@ def main():
     coupled, config1, variants = None, None, None
     if not args.no_coupled:
         coupled = {"c5": measure_coupled("c5", args, rank, local_rank, world)}
+        if not args.no_capacity:
+            # capacity scene (16384 coupled vehicles, not a BASELINE config): the strong-scaling curve of ONE coupled scene
+            # that is large enough to have waves to shard, on ALL ranks of this run (profiles/r2_scaling.md)
+            coupled["c5x4"] = measure_coupled("c5x4", args, rank, local_rank, world, with_cpu=False, steps=min(args.steps, 30))
         if world == 1:
             coupled["c3"] = measure_coupled("c3", args, rank, local_rank, world)
             few = max(3, min(args.steps, 5))
