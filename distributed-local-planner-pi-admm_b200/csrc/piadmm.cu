@@ -775,7 +775,9 @@ struct piadmm_handle {
   // persistent cooperative kernel for generic V (piadmm_coop.cuh); PIADMM_COOP=0 selects the phase kernels
   bool use_coop;
   bool cand_matrix;           // PIADMM_CAND=matrix: candidate bit matrix + list kernel instead of k_cand_direct (A/B)
-  int coop_grid_max;          // co-resident CTAs of k_coop<lpq>
+  int coop_grid_max;          // co-resident CTAs of k_coop<lpq, COOP_MIN_CTAS>
+  int coop_grid_max_hi;       // ... of k_coop<lpq, COOP_MANY_CTAS> (the occupancy build, large scenes)
+  int coop_occ;               // PIADMM_COOP_OCC: 0 choose by size, 1 lo, 2 hi
   int* d_nactive;             // [2]
   long long* d_trace;         // piadmm_debug_coop_trace
   // vehicle-sharded multi-GPU exchange (piadmm_peer_export / piadmm_peer_connect)
@@ -878,7 +880,7 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
   memset(&h->c, 0, sizeof h->c);
   h->device = device; h->bound = false; h->launches = 0; h->d_W = nullptr; h->d_count = nullptr; h->d_count2 = nullptr; h->h_count2 = nullptr; h->ev_count[0] = h->ev_count[1] = nullptr; h->d_queue = nullptr; h->d_order = nullptr; h->fused_grid = 0; h->have_streams = false; h->gexec = nullptr; h->d_ref = nullptr; h->ref_T = 0; h->h_step = nullptr; h->d_step = nullptr;
   { const char* e_ = getenv("PIADMM_CAND"); h->cand_matrix = e_ && strcmp(e_, "matrix") == 0; }
-  h->use_coop = true; h->coop_grid_max = 0; h->d_nactive = nullptr; h->d_trace = nullptr; h->xblk = nullptr; h->peer_on = false;
+  h->use_coop = true; h->coop_grid_max = 0; h->coop_grid_max_hi = 0; h->coop_occ = 0; h->d_nactive = nullptr; h->d_trace = nullptr; h->xblk = nullptr; h->peer_on = false;
   memset(&h->peer, 0, sizeof h->peer);
   for (int i = 0; i < PIADMM_MAX_PEERS; i++) h->peer_base[i] = nullptr;
   h->c.p = *p; set_inner_consts(h->c.ik, p->in_alpha); h->c.S = S; h->c.V = V; h->c.D = D; h->c.E = piadmm_max_edges(V, D);
@@ -1044,8 +1046,16 @@ int piadmm_create(const piadmm_params* p, int device, int S, int V, int D, piadm
     h->x_grid = prop.multiProcessorCount * (px < 1 ? 1 : px);
     h->z_grid = prop.multiProcessorCount * (pz < 1 ? 1 : pz);
     int pc = 0;
-    if (h->lpq == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pc, k_coop<16>, CTA_THREADS, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pc, k_coop<32>, CTA_THREADS, 0);
+    int pc_hi = 0;
+    if (h->lpq == 16) {
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pc, k_coop<16, COOP_MIN_CTAS>, CTA_THREADS, 0);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pc_hi, k_coop<16, COOP_MANY_CTAS>, CTA_THREADS, 0);
+    } else {
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pc, k_coop<32, COOP_MIN_CTAS>, CTA_THREADS, 0);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pc_hi, k_coop<32, COOP_MANY_CTAS>, CTA_THREADS, 0);
+    }
+    h->coop_grid_max_hi = prop.multiProcessorCount * (pc_hi < 1 ? 0 : pc_hi);
+    { const char* e_ = getenv("PIADMM_COOP_OCC"); h->coop_occ = e_ && strcmp(e_, "lo") == 0 ? 1 : (e_ && strcmp(e_, "hi") == 0 ? 2 : 0); }
     int coop_ok = 0;
     cudaDeviceGetAttribute(&coop_ok, cudaDevAttrCooperativeLaunch, device);
     h->coop_grid_max = prop.multiProcessorCount * (pc < 1 ? 0 : pc);
@@ -1472,12 +1482,20 @@ static int launch_coop(piadmm_handle* h, cudaStream_t st) {
   long want;
   if (h->lpq == 16) want = std::max((agents + 3) / 4, (pairs + 1) / 2);
   else want = std::max((agents + 1) / 2, pairs);
-  int grid = (int)std::min<long>(h->coop_grid_max, std::max<long>(want, 1));
+  // the occupancy build when this rank's vehicle QPs are more than two waves of the register build's group slots
+  const long own_agents = (long)c.S * (c.own_hi - c.own_lo);
+  const long slots_lo = (long)h->coop_grid_max * (h->lpq == 16 ? groups_per_cta<16>() : groups_per_cta<32>());
+  // (not at tight inner tolerances: every solve is then hundreds of inner iterations, the step is the slowest chains again
+  //  and the spills are on them -- config 5 with inner=tight: 2.71 ms with the register build, 3.33 ms with this one)
+  const bool hi = h->coop_grid_max_hi > h->coop_grid_max &&
+                  (h->coop_occ == 2 || (h->coop_occ == 0 && own_agents > 2 * slots_lo && c.p.in_eps_abs >= 1e-6));
+  int grid = (int)std::min<long>(hi ? h->coop_grid_max_hi : h->coop_grid_max, std::max<long>(want, 1));
   int rc = build_candidates(h, st);          // reads xt / spd only
   if (rc) return rc;
   void* args[2] = {&c, &a};
-  if (h->lpq == 16) CK(cudaLaunchCooperativeKernel((void*)k_coop<16>, dim3(grid), dim3(CTA_THREADS), args, 0, st));
-  else CK(cudaLaunchCooperativeKernel((void*)k_coop<32>, dim3(grid), dim3(CTA_THREADS), args, 0, st));
+  void* kern = h->lpq == 16 ? (hi ? (void*)k_coop<16, COOP_MANY_CTAS> : (void*)k_coop<16, COOP_MIN_CTAS>)
+                            : (hi ? (void*)k_coop<32, COOP_MANY_CTAS> : (void*)k_coop<32, COOP_MIN_CTAS>);
+  CK(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(CTA_THREADS), args, 0, st));
   LAUNCHED();
   h->c.slots_dirty = 0;
   return PIADMM_OK;

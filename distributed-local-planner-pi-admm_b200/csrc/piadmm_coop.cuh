@@ -167,8 +167,17 @@ __device__ __forceinline__ void dev_res_all(const DevCtx& c, int s, int i_iter, 
 
 // ------------------------------------------------------------------ the persistent cooperative kernel
 // (Who, load_tabs, groups_per_cta, pairs_per_cta, CTA_THREADS: piadmm.cu, defined before this file is included)
+// Two builds of the kernel.  COOP_MIN_CTAS (4 CTAs per SM, ~250 registers, no spills): registers over occupancy, as the
+// generic-V phase kernels -- a scene of a few hundred vehicles is ONE dependent chain per phase and every spilled value is
+// on it (config 3: 0.413 vs 0.465 ms).  COOP_MANY_CTAS (6 CTAs per SM, 168 registers, 300 B of spill stores): half as many
+// more resident QP groups -- a scene whose x phase is several waves of the machine gains more from the extra slots than the
+// spills cost (4096 / 16384 / 32768 vehicles: 0.497 / 1.094 / 4.120 -> 0.479 / 0.994 / 3.866 ms).  launch_coop picks by the
+// number of vehicle QPs of this rank (and the inner tolerance); PIADMM_COOP_OCC=lo|hi forces one (A/B).  Same arithmetic, identical results.
 #ifndef COOP_MIN_CTAS
-#define COOP_MIN_CTAS 4   // registers over occupancy, as the generic-V phase kernels (x and z bodies are both inlined here)
+#define COOP_MIN_CTAS 4
+#endif
+#ifndef COOP_MANY_CTAS
+#define COOP_MANY_CTAS 6
 #endif
 
 #define COOP_TRACE()                                                                  \
@@ -179,9 +188,9 @@ __device__ __forceinline__ void dev_res_all(const DevCtx& c, int s, int i_iter, 
     }                                                                                 \
   } while (0)
 
-template <int LPQ>
-__global__ void __launch_bounds__(CTA_THREADS, COOP_MIN_CTAS) k_coop(const __grid_constant__ DevCtx c,
-                                                                       const __grid_constant__ CoopArgs ca) {
+template <int LPQ, int MIN_CTAS>
+__global__ void __launch_bounds__(CTA_THREADS, MIN_CTAS) k_coop(const __grid_constant__ DevCtx c,
+                                                                  const __grid_constant__ CoopArgs ca) {
   cg::grid_group grid = cg::this_grid();
   __shared__ __align__(16) double Wsm[PIADMM_NTAB * LPQ * LPQ];
   __shared__ __align__(16) double gbuf[groups_per_cta<LPQ>()][2 * LPQ];

@@ -172,6 +172,24 @@ ALL_KEYS = ("u", "pos", "hat", "dual", "integ", "diff", "err_rk", "err_sk", "n_o
             "edge_inner", "status", "xt_next", "edge_ij", "edge_slot", "n_veh_solves", "n_edge_solves")
 
 
+@pytest.mark.parametrize("V,N", [(640, 30), (40, 15)])
+def test_cooperative_kernel_register_and_occupancy_builds_agree(monkeypatch, V, N):
+    """k_coop exists in two builds (4 CTAs per SM / ~250 registers for small scenes, 6 CTAs per SM / 168 registers for scenes
+    of several waves; launch_coop picks by size): the same arithmetic, bit-identical results, both horizons' kernels."""
+    if V == 640:
+        xt, spd, refwin = c5_grid(lanes=10, per_lane=32, N=N, seed=11, clear=0.0)
+    else:
+        xt, spd, refwin = c3_intersection(V=V, N=N, r0=9.0, gap=5.0)
+    p = bench.coupled_params(N).update(iter_num=8)
+    monkeypatch.setenv("PIADMM_COOP_OCC", "lo")
+    a = _run(p, xt, spd, refwin, 8)
+    monkeypatch.setenv("PIADMM_COOP_OCC", "hi")
+    b = _run(p, xt, spd, refwin, 8)
+    assert int(a["n_outer"].max()) >= 2 and int(a["n_edge_solves"][0]) > 0
+    for k in ALL_KEYS:
+        assert np.array_equal(a[k], b[k]), k
+
+
 @pytest.mark.parametrize("scene", ["grid640", "dense96", "ragged", "c3"])
 def test_slot_gate_and_direct_candidate_lists_are_exact(monkeypatch, scene):
     """The cooperative kernel's slot phase only serves the vehicles marked by the x phase (veh_need), its edge phase adds

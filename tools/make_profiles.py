@@ -116,6 +116,9 @@ Files of this round
   `cpu_baseline`) with the `coupled` records (configs 5 and 3, osqp_default and tight), `config1` (the 35-step run of
   `casadi/main.py`, 4 semantics x inner modes) and `c4_variants` (tight mode, 20-step closed loop on the device).
   `{R}_bench_1gpu_n30.json` — `--workload c4n30`; `{R}_bench_c3.json`, `{R}_bench_c5.json` — `--workload c3|c5` as own lines.
+* `{R}_bench_1gpu_final_20steps.json` — `python bench.py --steps 20 --warmup 3` on the LAST build: `launch_coop` keeps the register
+  build of `k_coop` at tight inner tolerances, so `coupled.c5_inner_tight` is 2.71 ms there (3.33 ms in `{R}_bench_1gpu.json`, which
+  ran that record on the occupancy build one commit earlier); every other record agrees between the two files.
 * `{R}_bench_reference_arm.json` — `python bench.py --impl reference --steps 20 --warmup 2` (oracle C twin, all host cores).
 * `{R}_launches_bench.csv`, `{R}_launches_c5.csv` — `ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv` of
   `python bench.py --steps 3 --warmup 3 --no-cpu-baseline [--no-coupled | --workload c5]` (every launch with its device time).
