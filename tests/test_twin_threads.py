@@ -48,6 +48,26 @@ def test_coupled_configs_converge_in_the_oracle():
         assert r["n_edge_solves"][0] > 0
 
 
+def test_capacity_scene_generator_and_convergence():
+    """bench.py's capacity scenes: shapes, no pair inside dis_thres at t = 0 (the generator's rejection rule), and the
+    16384-vehicle scene leaves the outer loop through the empty-edge rule after 4 iterations in the oracle."""
+    for name, V in (("c5x4", 16384), ("c5x8", 32768)):
+        (xt, spd, refwin), v, N, D = bench.coupled_scene(name)
+        assert v == V and xt.shape == (1, V, 3) and refwin.shape == (1, V, 2, N + 1) and (N, D) == (30, 8)
+        east, south = xt[0, :V // 2], xt[0, V // 2:]
+        # east-bound vehicles sit on y = 20 r, south-bound ones on x = 20 c: the closest pair of a crossing is found per lane pair
+        dmin = np.inf
+        for r in range(0, V // 2, V // 2 // 128 * 16):                    # a sample of the lanes (every 16th)
+            e = east[r:r + V // 2 // 128]
+            d = np.hypot(e[:, None, 0] - south[None, :, 0], e[:, None, 1] - south[None, :, 1])
+            dmin = min(dmin, d.min())
+        assert dmin > 2.0
+    (xt, spd, refwin), V, N, D = bench.coupled_scene("c5x4")
+    p = bench.coupled_params(N)
+    r = ctwin.step(p, xt, spd, refwin, D=D, nthreads=8)
+    assert int(r["n_outer"][0]) == 4 and int(r["edge_n"][0]) == 0 and int(r["status"][0]) == 0 and r["n_edge_solves"][0] > 1000
+
+
 def test_x_memo_is_exact():
     """x_memo skips vehicle QPs whose inputs did not change: identical results, fewer executed solves."""
     xt, spd, refwin = c5_grid(lanes=8, per_lane=16, N=30, seed=2, clear=0.0)
